@@ -1,0 +1,6 @@
+// ABI bookkeeping shared by every translation unit of libllmtrain_b200.so.
+#include "host.cuh"
+#include "../../include/llmtrain_b200.h"
+
+extern "C" const char* llmtrain_b200_last_error(void) { return b200::last_error_slot().c_str(); }
+extern "C" int llmtrain_b200_abi_version(void) { return 1000; }

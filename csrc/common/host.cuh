@@ -1,0 +1,107 @@
+// Host-side helpers: error plumbing for the C ABI, TMA tensor-map construction.
+#pragma once
+
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+
+namespace b200 {
+
+// ---- error reporting through the C ABI: functions return 0 on success, non-zero on failure,
+// ---- and the text is available from llmtrain_b200_last_error().
+inline std::string& last_error_slot() {
+  thread_local std::string slot;
+  return slot;
+}
+inline int fail(const std::string& what) {
+  last_error_slot() = what;
+  return 1;
+}
+#define B200_CHECK_CUDA(expr)                                                              \
+  do {                                                                                     \
+    cudaError_t _e = (expr);                                                               \
+    if (_e != cudaSuccess) {                                                               \
+      return ::b200::fail(std::string(#expr) + " failed: " + cudaGetErrorString(_e) +      \
+                          " (" __FILE__ ":" + std::to_string(__LINE__) + ")");             \
+    }                                                                                      \
+  } while (0)
+#define B200_REQUIRE(cond, msg)                                                            \
+  do {                                                                                     \
+    if (!(cond)) return ::b200::fail(std::string(msg) + " [" #cond "]");                   \
+  } while (0)
+
+// ---- cuTensorMapEncodeTiled, resolved at run time so the library never links libcuda
+// ---- (it must import on a CPU-only build box).
+using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                   const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+inline EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* sym = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) ==
+            cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess) {
+      fn = reinterpret_cast<EncodeTiledFn>(sym);
+    }
+  });
+  return fn;
+}
+
+enum class Swz { None, B128 };
+
+// 2-D row-major tensor [rows, cols] with `ld` elements between rows; box = [box_rows, box_cols].
+// Out-of-bounds elements are read as zero and never written.
+template <typename T>
+inline int make_tmap_2d(CUtensorMap* out, const T* base, uint64_t rows, uint64_t cols, uint64_t ld,
+                        uint32_t box_rows, uint32_t box_cols, Swz swz) {
+  EncodeTiledFn enc = encode_tiled_fn();
+  B200_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled is unavailable (no CUDA driver?)");
+  CUtensorMapDataType dt;
+  if (sizeof(T) == 2) {
+    dt = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  } else {
+    dt = CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+  }
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {ld * sizeof(T)};
+  cuuint32_t box[2] = {box_cols, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  B200_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "TMA base must be 16-byte aligned");
+  B200_REQUIRE((ld * sizeof(T)) % 16 == 0, "TMA row pitch must be a multiple of 16 bytes");
+  B200_REQUIRE(box_cols * sizeof(T) <= 128 || swz == Swz::None,
+               "swizzled TMA box inner extent must be <= 128 bytes");
+  CUresult r = enc(out, dt, 2, const_cast<T*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   swz == Swz::B128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    return fail("cuTensorMapEncodeTiled failed with CUresult " + std::to_string(int(r)));
+  }
+  return 0;
+}
+
+inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+
+inline int sm_count() {
+  static int cached = 0;
+  if (cached == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&cached, cudaDevAttrMultiProcessorCount, dev);
+    if (cached <= 0) cached = 148;
+  }
+  return cached;
+}
+
+}  // namespace b200

@@ -1,0 +1,411 @@
+// Persistent, warp-specialised bf16 GEMM for sm_100a:  TMA -> smem ring -> tcgen05.mma -> TMEM
+// (double-buffered accumulator) -> epilogue warps -> swizzled smem staging -> TMA store.
+//
+// Replaces every ATen GEMM the reference makes from `src/llmtrain/models/gpt.py` (qkv_proj :27,
+// out_proj :29, mlp_fc :94, mlp_proj :96, lm_head :143) and their autograd dgrad / wgrad
+// counterparts (SURVEY §2.5 K3,K5,K7,K8,K10,K12).  One kernel family, three operand layouts:
+//
+//   NT  C[M,N]  = A[M,K]   * B[N,K]^T      forward      (A, B both K-major)
+//   NN  C[M,N]  = A[M,K]   * B[K,N]        dgrad        (A K-major, B MN-major)
+//   TN  C[M,N] += A[K,M]^T * B[K,N]        wgrad        (A, B both MN-major; split-K; fp32
+//                                                        accumulate into the gradient arena via
+//                                                        TMA reduce-add)
+//
+// Fused epilogues: +bias, +bias & exact-erf GELU (writes pre- and post-activation), +bias &
+// residual add, x GELU'(pre) for the MLP dgrad, fp32 accumulate.
+//
+// Tile: 128 x 256 x 64, UMMA 128x256x16 (cta_group::1), 4-stage smem ring (48 KB / stage),
+// 2 x 256 TMEM columns.  6 warps: 0 = TMA producer, 1 = MMA issuer + TMEM owner, 2..5 = epilogue
+// (warp w reads TMEM lanes 32*(w%4)..+31).  Grid = #SMs, static round-robin tile schedule with M
+// fastest so concurrently running CTAs share the weight tile through L2.
+
+#include "../common/host.cuh"
+#include "../common/ptx.cuh"
+#include "../../include/llmtrain_b200.h"
+
+namespace b200 {
+namespace gemm {
+
+constexpr int BM = 128;
+constexpr int BN = 256;
+constexpr int BK = 64;  // 64 bf16 = 128 B = one swizzle row
+constexpr int UK = 16;
+constexpr int STAGES = 4;
+constexpr int A_BYTES = BM * BK * 2;  // 16 KB
+constexpr int B_BYTES = BN * BK * 2;  // 32 KB
+constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+constexpr int EPI_WARPS = 4;
+constexpr int EPI_BUF_BYTES = 32 * 128;  // 32 rows x 128 B per staging buffer
+constexpr int EPI_BYTES = EPI_WARPS * 2 * EPI_BUF_BYTES;
+constexpr int NUM_THREADS = 32 * (2 + EPI_WARPS);
+constexpr int TMEM_COLS = 512;
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + 256 /*barriers*/ + 1024 /*align*/;
+
+enum Epi : int {
+  kBias = 0,      // C = acc (+ bias)
+  kBiasGelu = 1,  // C2 = acc + bias ; C = gelu(C2)
+  kBiasResid = 2, // C = acc (+ bias) + R
+  kDGelu = 3,     // C = acc * gelu'(R)          (R holds the saved pre-activation)
+  kAccumF32 = 4,  // C(fp32) += acc              (TMA reduce-add)
+};
+
+struct Params {
+  int M, N, K;
+  int k_splits;          // >1 only with kAccumF32
+  const float* bias;     // [N] fp32 or nullptr
+  const __nv_bfloat16* R;  // residual / saved pre-activation, row pitch ldr
+  int ldr;
+};
+
+__device__ __forceinline__ float gelu_erf(float x) {
+  return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f));
+}
+__device__ __forceinline__ float gelu_erf_grad(float x) {
+  const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752f));
+  const float pdf = 0.3989422804014327f * __expf(-0.5f * x * x);
+  return cdf + x * pdf;
+}
+
+template <bool A_MN, bool B_MN, int EPI>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+            const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmC2,
+            const Params p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~uintptr_t(1023));
+  uint8_t* epi_smem = smem + STAGES * STAGE_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(epi_smem + EPI_BYTES);
+  uint64_t* full_bar = bars;                  // [STAGES]
+  uint64_t* empty_bar = bars + STAGES;        // [STAGES]
+  uint64_t* tfull_bar = bars + 2 * STAGES;    // [2]
+  uint64_t* tempty_bar = bars + 2 * STAGES + 2;  // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  const int num_m = (p.M + BM - 1) / BM;
+  const int num_n = (p.N + BN - 1) / BN;
+  const int tiles_mn = num_m * num_n;
+  const int num_tiles = tiles_mn * p.k_splits;
+  const int kb_total = (p.K + BK - 1) / BK;
+  const int kb_per_split = (kb_total + p.k_splits - 1) / p.k_splits;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    tma_prefetch_desc(&tmC);
+    if (EPI == kBiasGelu) tma_prefetch_desc(&tmC2);
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&tfull_bar[s], 1);
+      mbar_init(&tempty_bar[s], EPI_WARPS);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, TMEM_COLS);
+    tmem_relinquish();
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================================== TMA producer =====================================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int split = tile / tiles_mn;
+        const int mn = tile - split * tiles_mn;
+        const int m0 = (mn % num_m) * BM;
+        const int n0 = (mn / num_m) * BN;
+        const int kb_begin = split * kb_per_split;
+        const int kb_end = min(kb_total, kb_begin + kb_per_split);
+        for (int kb = kb_begin; kb < kb_end; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * STAGE_BYTES;
+          uint8_t* sb = sa + A_BYTES;
+          mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
+          const int k0 = kb * BK;
+          if (!A_MN) {
+            tma_load_2d(sa, &tmA, &full_bar[stage], k0, m0);
+          } else {
+#pragma unroll
+            for (int i = 0; i < BM / 64; ++i)
+              tma_load_2d(sa + i * (BK * 128), &tmA, &full_bar[stage], m0 + i * 64, k0);
+          }
+          if (!B_MN) {
+            tma_load_2d(sb, &tmB, &full_bar[stage], k0, n0);
+          } else {
+#pragma unroll
+            for (int i = 0; i < BN / 64; ++i)
+              tma_load_2d(sb + i * (BK * 128), &tmB, &full_bar[stage], n0 + i * 64, k0);
+          }
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================================== MMA issuer =======================================
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(BM, BN, A_MN, B_MN);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int split = tile / tiles_mn;
+        const int kb_begin = split * kb_per_split;
+        const int kb_end = min(kb_total, kb_begin + kb_per_split);
+        mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+        tc_fence_after_sync();
+        const uint32_t d_tmem = tmem_base + acc * BN;
+        for (int kb = kb_begin; kb < kb_end; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after_sync();
+          const uint32_t sa = smem_u32(smem + stage * STAGE_BYTES);
+          const uint32_t sb = sa + A_BYTES;
+#pragma unroll
+          for (int k = 0; k < BK / UK; ++k) {
+            // K-major: 32 B per UMMA_K inside the swizzled 128 B row; SBO = 8 rows * 128 B.
+            // MN-major: 16 K-rows * 128 B per UMMA_K; LBO = one 64-wide box (BK rows * 128 B).
+            const uint64_t da = A_MN ? umma_smem_desc(sa + k * (UK * 128), BK * 128, 1024)
+                                     : umma_smem_desc(sa + k * (UK * 2), 0, 1024);
+            const uint64_t db = B_MN ? umma_smem_desc(sb + k * (UK * 128), BK * 128, 1024)
+                                     : umma_smem_desc(sb + k * (UK * 2), 0, 1024);
+            umma_ss(d_tmem, da, db, idesc, (kb > kb_begin) || (k > 0));
+          }
+          umma_commit(&empty_bar[stage]);  // frees this smem stage once the MMAs have read it
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(&tfull_bar[acc]);  // accumulator complete -> epilogue
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+  } else {
+    // ===================================== epilogue =========================================
+    const int ew = warp - 2;        // 0..3 : staging-buffer owner
+    const int quarter = warp & 3;   // TMEM lane quarter this warp may access
+    uint8_t* stg0 = epi_smem + (ew * 2 + 0) * EPI_BUF_BYTES;
+    uint8_t* stg1 = epi_smem + (ew * 2 + 1) * EPI_BUF_BYTES;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    int buf = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int split = tile / tiles_mn;
+      const int mn = tile - split * tiles_mn;
+      const int m0 = (mn % num_m) * BM;
+      const int n0 = (mn / num_m) * BN;
+      const int row = m0 + quarter * 32 + lane;  // this thread's output row
+      const bool row_ok = row < p.M;
+      mbar_wait(&tfull_bar[acc], acc_phase);
+      tc_fence_after_sync();
+      const uint32_t t_row = tmem_base + (uint32_t(quarter * 32) << 16) + acc * BN;
+
+      if (EPI == kAccumF32) {
+        // 8 chunks of 32 fp32 columns (128 B rows), reduce-added into global fp32.
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+          if (n0 + c * 32 >= p.N) break;
+          uint32_t v[32];
+          tmem_ld_32x32b_x32(t_row + c * 32, v);
+          tmem_ld_wait();
+          uint8_t* stg = buf ? stg1 : stg0;
+          tma_store_wait_read<1>();  // the buffer used two chunks ago is free again
+          __syncwarp();
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const uint32_t off = swizzle128(lane * 128 + j * 16);
+            *reinterpret_cast<uint4*>(stg + off) =
+                make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_reduce_add_2d(&tmC, stg, n0 + c * 32, m0 + quarter * 32);
+            tma_store_commit();
+          }
+          buf ^= 1;
+        }
+      } else {
+        // 4 chunks of 64 bf16 columns (128 B rows).
+#pragma unroll 1
+        for (int c = 0; c < BN / 64; ++c) {
+          const int col0 = n0 + c * 64;
+          if (col0 >= p.N) break;
+          uint32_t v[2][32];
+          tmem_ld_32x32b_x32(t_row + c * 64, v[0]);
+          tmem_ld_32x32b_x32(t_row + c * 64 + 32, v[1]);
+          tmem_ld_wait();
+
+          uint32_t out[32];   // 64 bf16 packed
+          uint32_t out2[32];  // pre-activation (GELU variant only)
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 2) {
+              const int col = col0 + h * 32 + j;
+              float x0 = __uint_as_float(v[h][j]);
+              float x1 = __uint_as_float(v[h][j + 1]);
+              if (EPI == kBias || EPI == kBiasGelu || EPI == kBiasResid) {
+                if (p.bias != nullptr) {
+                  if (col < p.N) x0 += __ldg(p.bias + col);
+                  if (col + 1 < p.N) x1 += __ldg(p.bias + col + 1);
+                }
+              }
+              if (EPI == kBiasResid || EPI == kDGelu) {
+                float r0 = 0.f, r1 = 0.f;
+                if (row_ok && col + 1 < p.N) {
+                  const uint32_t rr = __ldg(reinterpret_cast<const uint32_t*>(
+                      p.R + size_t(row) * p.ldr + col));
+                  const float2 f = unpack_bf16x2(rr);
+                  r0 = f.x; r1 = f.y;
+                } else if (row_ok && col < p.N) {
+                  r0 = __bfloat162float(p.R[size_t(row) * p.ldr + col]);
+                }
+                if (EPI == kBiasResid) { x0 += r0; x1 += r1; }
+                else { x0 *= gelu_erf_grad(r0); x1 *= gelu_erf_grad(r1); }
+              }
+              if (EPI == kBiasGelu) {
+                out2[h * 16 + j / 2] = pack_bf16x2(x0, x1);
+                x0 = gelu_erf(x0); x1 = gelu_erf(x1);
+              }
+              out[h * 16 + j / 2] = pack_bf16x2(x0, x1);
+            }
+          }
+
+          if (EPI == kBiasGelu) {
+            tma_store_wait_read<0>();  // both staging buffers are reused every chunk
+          } else {
+            tma_store_wait_read<1>();
+          }
+          __syncwarp();
+          uint8_t* stg = (EPI == kBiasGelu) ? stg0 : (buf ? stg1 : stg0);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const uint32_t off = swizzle128(lane * 128 + j * 16);
+            *reinterpret_cast<uint4*>(stg + off) =
+                make_uint4(out[4 * j], out[4 * j + 1], out[4 * j + 2], out[4 * j + 3]);
+            if (EPI == kBiasGelu) {
+              *reinterpret_cast<uint4*>(stg1 + off) =
+                  make_uint4(out2[4 * j], out2[4 * j + 1], out2[4 * j + 2], out2[4 * j + 3]);
+            }
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(&tmC, stg, col0, m0 + quarter * 32);
+            if (EPI == kBiasGelu) tma_store_2d(&tmC2, stg1, col0, m0 + quarter * 32);
+            tma_store_commit();
+          }
+          buf ^= 1;
+        }
+      }
+      // TMEM reads for this accumulator are complete (wait::ld above): hand it back.
+      tc_fence_before_sync();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+    tma_store_wait<0>();  // global writes landed before the kernel exits
+  }
+
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Host launcher
+// ------------------------------------------------------------------------------------------------
+template <bool A_MN, bool B_MN, int EPI>
+int launch(const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tC,
+           const CUtensorMap& tC2, const Params& p, cudaStream_t stream) {
+  auto kern = gemm_kernel<A_MN, B_MN, EPI>;
+  static bool configured = false;
+  if (!configured) {
+    B200_CHECK_CUDA(
+        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    configured = true;
+  }
+  const int tiles = ceil_div(p.M, BM) * ceil_div(p.N, BN) * p.k_splits;
+  const int grid = tiles < sm_count() ? tiles : sm_count();
+  kern<<<grid, NUM_THREADS, SMEM_BYTES, stream>>>(tA, tB, tC, tC2, p);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int pick_splits(int M, int N, int K) {
+  const int tiles = ceil_div(M, BM) * ceil_div(N, BN);
+  const int kb = ceil_div(K, BK);
+  int s = sm_count() / (tiles > 0 ? tiles : 1);
+  if (s < 1) s = 1;
+  if (s > 16) s = 16;
+  while (s > 1 && kb / s < 8) --s;  // keep >= 8 k-blocks per split
+  // avoid empty trailing splits
+  while (s > 1 && (s - 1) * ceil_div(kb, s) >= kb) --s;
+  return s;
+}
+
+}  // namespace gemm
+}  // namespace b200
+
+using namespace b200;
+using namespace b200::gemm;
+
+// layout: 0 = NT, 1 = NN, 2 = TN (see header).  All pointers are device pointers.
+extern "C" int llmtrain_b200_gemm(int layout, int epilogue, int M, int N, int K, const void* A,
+                                  int lda, const void* B, int ldb, void* C, int ldc, void* C2,
+                                  int ldc2, const float* bias, const void* R, int ldr,
+                                  cudaStream_t stream) {
+  B200_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem");
+  Params p{};
+  p.M = M; p.N = N; p.K = K; p.k_splits = 1;
+  p.bias = bias;
+  p.R = static_cast<const __nv_bfloat16*>(R);
+  p.ldr = ldr;
+  const auto* a = static_cast<const __nv_bfloat16*>(A);
+  const auto* b = static_cast<const __nv_bfloat16*>(B);
+  CUtensorMap tA, tB, tC, tC2;
+  std::memset(&tC2, 0, sizeof(tC2));
+  const bool a_mn = (layout == 2);
+  const bool b_mn = (layout == 1 || layout == 2);
+  // K-major operand: memory [rows, K]; box = [tile rows, 64].  MN-major: memory [K, rows];
+  // box = [64 k-rows, 64 cols].
+  if (!a_mn) { if (make_tmap_2d(&tA, a, M, K, lda, BM, BK, Swz::B128)) return 1; }
+  else       { if (make_tmap_2d(&tA, a, K, M, lda, BK, 64, Swz::B128)) return 1; }
+  if (!b_mn) { if (make_tmap_2d(&tB, b, N, K, ldb, BN, BK, Swz::B128)) return 1; }
+  else       { if (make_tmap_2d(&tB, b, K, N, ldb, BK, 64, Swz::B128)) return 1; }
+
+  if (epilogue == kAccumF32) {
+    if (make_tmap_2d(&tC, static_cast<float*>(C), M, N, ldc, 32, 32, Swz::B128)) return 1;
+    p.k_splits = pick_splits(M, N, K);
+  } else {
+    if (make_tmap_2d(&tC, static_cast<__nv_bfloat16*>(C), M, N, ldc, 32, 64, Swz::B128)) return 1;
+    if (epilogue == kBiasGelu) {
+      B200_REQUIRE(C2 != nullptr, "gemm: GELU epilogue needs the pre-activation output C2");
+      if (make_tmap_2d(&tC2, static_cast<__nv_bfloat16*>(C2), M, N, ldc2, 32, 64, Swz::B128))
+        return 1;
+    }
+    if (epilogue == kBiasResid || epilogue == kDGelu)
+      B200_REQUIRE(R != nullptr, "gemm: this epilogue needs R");
+  }
+
+#define B200_GEMM_CASE(L, AMN, BMN, E) \
+  if (layout == L && epilogue == E) return launch<AMN, BMN, E>(tA, tB, tC, tC2, p, stream);
+  B200_GEMM_CASE(0, false, false, kBias)
+  B200_GEMM_CASE(0, false, false, kBiasGelu)
+  B200_GEMM_CASE(0, false, false, kBiasResid)
+  B200_GEMM_CASE(1, false, true, kBias)
+  B200_GEMM_CASE(1, false, true, kDGelu)
+  B200_GEMM_CASE(2, true, true, kAccumF32)
+#undef B200_GEMM_CASE
+  return fail("gemm: unsupported layout/epilogue combination");
+}

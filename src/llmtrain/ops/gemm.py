@@ -1,0 +1,49 @@
+"""tcgen05 GEMM family (``csrc/kernels/gemm.cu``) — see ``llmtrain_b200_gemm`` in the header."""
+
+from __future__ import annotations
+
+import ctypes
+
+import torch
+
+from llmtrain.ops import native
+
+NT, NN, TN = 0, 1, 2
+EPI_BIAS, EPI_BIAS_GELU, EPI_BIAS_RESID, EPI_DGELU, EPI_ACCUM_F32 = 0, 1, 2, 3, 4
+
+
+def _ld(t: torch.Tensor) -> int:
+    assert t.dim() == 2 and t.stride(1) == 1, "operands must be 2-D with unit inner stride"
+    return int(t.stride(0))
+
+
+def gemm(
+    layout: int,
+    epilogue: int,
+    a: torch.Tensor,
+    b: torch.Tensor,
+    c: torch.Tensor,
+    *,
+    c2: torch.Tensor | None = None,
+    bias: torch.Tensor | None = None,
+    r: torch.Tensor | None = None,
+) -> torch.Tensor:
+    """Run one GEMM on the current stream; ``c`` (and ``c2``) are written in place."""
+    m, n = c.shape
+    k = a.shape[1] if layout != TN else a.shape[0]
+    fn = native.lib().llmtrain_b200_gemm
+    status = fn(
+        ctypes.c_int(layout), ctypes.c_int(epilogue), ctypes.c_int(m), ctypes.c_int(n),
+        ctypes.c_int(k), native.ptr(a), ctypes.c_int(_ld(a)), native.ptr(b), ctypes.c_int(_ld(b)),
+        native.ptr(c), ctypes.c_int(_ld(c)), native.ptr(c2),
+        ctypes.c_int(_ld(c2) if c2 is not None else 0), native.ptr(bias), native.ptr(r),
+        ctypes.c_int(_ld(r) if r is not None else 0), native.stream_handle(),
+    )
+    native.check(status, "gemm")
+    return c
+
+
+def linear_forward(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None = None) -> torch.Tensor:
+    """``x @ w.T + bias`` with bf16 operands, fp32 accumulate, bf16 result."""
+    out = torch.empty(x.shape[0], w.shape[0], dtype=torch.bfloat16, device=x.device)
+    return gemm(NT, EPI_BIAS, x, w, out, bias=bias)

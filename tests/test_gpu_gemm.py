@@ -1,0 +1,97 @@
+"""tcgen05 GEMM vs an fp32 torch reference of the same op (run on the B200 box)."""
+
+from __future__ import annotations
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _rand(shape, scale=1.0, dtype=torch.bfloat16):
+    return (torch.randn(*shape, device="cuda", dtype=torch.float32) * scale).to(dtype)
+
+
+def _close(got: torch.Tensor, want: torch.Tensor, tol: float) -> None:
+    got = got.float()
+    err = (got - want).abs().max().item()
+    ref = want.abs().max().item() + 1e-6
+    assert err / ref < tol, f"max abs err {err:.4e} vs ref scale {ref:.4e}"
+
+
+SHAPES = [(256, 256, 128), (384, 512, 768), (1000, 320, 1600), (128, 2304, 64), (4096, 768, 3072)]
+
+
+@pytest.mark.parametrize("m,n,k", SHAPES)
+def test_nt_bias(m: int, n: int, k: int) -> None:
+    from llmtrain.ops import gemm as G
+
+    x, w = _rand((m, k)), _rand((n, k), 0.05)
+    bias = torch.randn(n, device="cuda")
+    out = torch.empty(m, n, device="cuda", dtype=torch.bfloat16)
+    G.gemm(G.NT, G.EPI_BIAS, x, w, out, bias=bias)
+    _close(out, x.float() @ w.float().t() + bias, 1e-2)
+    out2 = torch.empty_like(out)
+    G.gemm(G.NT, G.EPI_BIAS, x, w, out2)  # no bias
+    _close(out2, x.float() @ w.float().t(), 1e-2)
+
+
+@pytest.mark.parametrize("m,n,k", SHAPES[:3])
+def test_nt_gelu_and_resid(m: int, n: int, k: int) -> None:
+    from llmtrain.ops import gemm as G
+
+    x, w = _rand((m, k)), _rand((n, k), 0.05)
+    bias = torch.randn(n, device="cuda") * 0.1
+    pre = torch.empty(m, n, device="cuda", dtype=torch.bfloat16)
+    act = torch.empty_like(pre)
+    G.gemm(G.NT, G.EPI_BIAS_GELU, x, w, act, c2=pre, bias=bias)
+    want_pre = x.float() @ w.float().t() + bias
+    _close(pre, want_pre, 1e-2)
+    _close(act, torch.nn.functional.gelu(want_pre), 1e-2)
+
+    resid = _rand((m, n))
+    out = torch.empty_like(pre)
+    G.gemm(G.NT, G.EPI_BIAS_RESID, x, w, out, bias=bias, r=resid)
+    _close(out, want_pre + resid.float(), 1e-2)
+
+
+@pytest.mark.parametrize("m,n,k", SHAPES[:4])
+def test_nn_dgrad(m: int, n: int, k: int) -> None:
+    from llmtrain.ops import gemm as G
+
+    dy, w = _rand((m, k)), _rand((k, n), 0.05)  # C[M,N] = dy[M,K] @ w[K,N]
+    out = torch.empty(m, n, device="cuda", dtype=torch.bfloat16)
+    G.gemm(G.NN, G.EPI_BIAS, dy, w, out)
+    want = dy.float() @ w.float()
+    _close(out, want, 1e-2)
+
+    pre = _rand((m, n))
+    out2 = torch.empty_like(out)
+    G.gemm(G.NN, G.EPI_DGELU, dy, w, out2, r=pre)
+    p = pre.float().requires_grad_(True)
+    torch.nn.functional.gelu(p).backward(want)
+    _close(out2, p.grad, 1e-2)
+
+
+@pytest.mark.parametrize("m,n,k", [(256, 256, 512), (768, 2304, 4096), (320, 1600, 1000), (50304, 768, 2048)])
+def test_tn_wgrad_accumulates(m: int, n: int, k: int) -> None:
+    from llmtrain.ops import gemm as G
+
+    dy, x = _rand((k, m), 0.1), _rand((k, n))  # C[M,N] += dy^T @ x
+    base = torch.randn(m, n, device="cuda")
+    out = base.clone()
+    G.gemm(G.TN, G.EPI_ACCUM_F32, dy, x, out)
+    _close(out, base + dy.float().t() @ x.float(), 5e-3)
+
+
+def test_strided_views() -> None:
+    """Operands may be column slices of a wider matrix (q/k/v inside the fused qkv buffer)."""
+    from llmtrain.ops import gemm as G
+
+    wide = _rand((512, 3 * 256))
+    a = wide[:, 256:512]
+    w = _rand((384, 256), 0.05)
+    out_wide = torch.zeros(512, 1024, device="cuda", dtype=torch.bfloat16)
+    G.gemm(G.NT, G.EPI_BIAS, a, w, out_wide[:, 128:512])
+    _close(out_wide[:, 128:512], a.float() @ w.float().t(), 1e-2)
+    assert out_wide[:, :128].abs().max().item() == 0 and out_wide[:, 512:].abs().max().item() == 0
