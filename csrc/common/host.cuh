@@ -91,6 +91,34 @@ inline int make_tmap_2d(CUtensorMap* out, const T* base, uint64_t rows, uint64_t
   return 0;
 }
 
+// 3-D tensor [d2, d1, d0] (d0 contiguous) with byte-free element pitches ld1 (between d1 rows) and
+// ld2 (between d2 slabs); box = [1, box1, box0].  Used for per-sequence views [B, T, C] so that
+// rows past T are zero-filled on load and clipped on store instead of bleeding into the next
+// sequence.
+template <typename T>
+inline int make_tmap_3d(CUtensorMap* out, const T* base, uint64_t d2, uint64_t d1, uint64_t d0,
+                        uint64_t ld1, uint64_t ld2, uint32_t box1, uint32_t box0, Swz swz) {
+  EncodeTiledFn enc = encode_tiled_fn();
+  B200_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled is unavailable (no CUDA driver?)");
+  CUtensorMapDataType dt =
+      sizeof(T) == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+  cuuint64_t dims[3] = {d0, d1, d2};
+  cuuint64_t strides[2] = {ld1 * sizeof(T), ld2 * sizeof(T)};
+  cuuint32_t box[3] = {box0, box1, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  B200_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "TMA base must be 16-byte aligned");
+  B200_REQUIRE((ld1 * sizeof(T)) % 16 == 0 && (ld2 * sizeof(T)) % 16 == 0,
+               "TMA pitches must be multiples of 16 bytes");
+  CUresult r = enc(out, dt, 3, const_cast<T*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   swz == Swz::B128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    return fail("cuTensorMapEncodeTiled(3d) failed with CUresult " + std::to_string(int(r)));
+  }
+  return 0;
+}
+
 inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 
 inline int sm_count() {

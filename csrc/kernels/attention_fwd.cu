@@ -1,0 +1,314 @@
+// Causal flash attention forward on tcgen05 (head_dim 64, bf16 in/out, fp32 softmax state).
+//
+// Replaces the reference's materialised attention (`src/llmtrain/models/gpt.py:56-70`: scores
+// (B,H,T,T) fp32, masked_fill, softmax, P@V — SURVEY §2.5 K4, work item W2).  Nothing of size T^2
+// ever reaches HBM: per (batch, head, 128-query tile) one CTA walks the key/value tiles up to the
+// diagonal.
+//
+//   TMA warp   : Q once, then K_j / V_j through a 2-stage ring (3-D tensor maps over the fused
+//                [B, T, 3d] QKV buffer, so no permute/copy is ever made and rows past T read 0)
+//   MMA warp   : S = Q K_j^T   (SS, 128x128x64, accumulator in TMEM cols [0,128))
+//                PV = P_j V_j  (SS, 128x64x128, TMEM cols [128,192)), P_j read from smem (bf16),
+//                V_j consumed as an MN-major operand straight from its [kv, hd] layout
+//   4 softmax warps: thread i owns query row i (= TMEM lane i): two passes over S (max, then
+//                exp2 + row-sum + bf16 pack into the swizzled P tile), then folds PV into the
+//                register-resident output with the usual online-softmax rescale.
+//
+// Masking follows the reference's semantics: causal (col > row) and optional key padding are
+// excluded from the softmax; a query whose keys are ALL excluded yields zeros (the reference
+// zeroes such rows after out_proj, `gpt.py:73-74`).  LSE (natural log) is saved for backward.
+//
+// ~113 KB smem and 256 TMEM columns per CTA => two CTAs per SM, so one CTA's softmax overlaps
+// the other's tensor-core work.
+
+#include "../common/host.cuh"
+#include "../common/ptx.cuh"
+#include "../../include/llmtrain_b200.h"
+
+namespace b200 {
+namespace attn {
+
+constexpr int BQ = 128;
+constexpr int BKV = 128;
+constexpr int HD = 64;
+constexpr int TILE_BYTES = 128 * HD * 2;  // 16 KB: 128 rows x 128 B
+constexpr int FWD_THREADS = 192;
+constexpr int FWD_TMEM_COLS = 256;
+constexpr int OFF_Q = 0;
+constexpr int OFF_K = OFF_Q + TILE_BYTES;
+constexpr int OFF_V = OFF_K + 2 * TILE_BYTES;
+constexpr int OFF_P = OFF_V + 2 * TILE_BYTES;
+constexpr int OFF_BAR = OFF_P + 2 * TILE_BYTES;
+constexpr int FWD_SMEM = OFF_BAR + 256;
+
+struct FwdParams {
+  int B, T, H;
+  float scale_log2;              // head_dim^-0.5 * log2(e)
+  const uint8_t* key_mask;       // [B, T] (1 = attend) or nullptr
+  float* lse;                    // [B, H, T]
+};
+
+__global__ void __launch_bounds__(FWD_THREADS, 2)
+fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmO,
+           const FwdParams p) {
+  // No static smem in this kernel, so the dynamic window starts at the (1024 B aligned) base of
+  // the CTA's shared memory; relying on that instead of padding keeps two CTAs resident per SM.
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
+  if ((smem_u32(smem) & 1023u) != 0) __trap();
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
+  uint64_t* q_full = bars + 0;
+  uint64_t* k_full = bars + 1;    // [2]
+  uint64_t* v_full = bars + 3;    // [2]
+  uint64_t* kv_empty = bars + 5;  // [2]
+  uint64_t* s_full = bars + 7;
+  uint64_t* p_full = bars + 8;
+  uint64_t* pv_done = bars + 9;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 10);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nq = (p.T + BQ - 1) / BQ;
+  const int qt = nq - 1 - int(blockIdx.x);  // heaviest (most kv tiles) first
+  const int h = blockIdx.y, b = blockIdx.z;
+  const int q0 = qt * BQ;
+  const int d = p.H * HD;
+  const int n_kv = qt + 1;
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tmQKV);
+    tma_prefetch_desc(&tmO);
+    mbar_init(q_full, 1);
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&k_full[s], 1);
+      mbar_init(&v_full[s], 1);
+      mbar_init(&kv_empty[s], 1);
+    }
+    mbar_init(s_full, 1);
+    mbar_init(p_full, 4);
+    mbar_init(pv_done, 1);
+    fence_barrier_init();
+  }
+  if (warp == 5) {
+    tmem_alloc(tmem_slot, FWD_TMEM_COLS);
+    tmem_relinquish();
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tmem = *tmem_slot;
+  const uint32_t tmem_S = tmem;
+  const uint32_t tmem_PV = tmem + 128;
+
+  if (warp == 4) {
+    // ------------------------------- TMA producer -------------------------------------------
+    if (lane == 0) {
+      mbar_expect_tx(q_full, TILE_BYTES);
+      tma_load_3d(smem + OFF_Q, &tmQKV, q_full, h * HD, q0, b);
+      for (int j = 0; j < n_kv; ++j) {
+        const int st = j & 1;
+        const uint32_t ph = (j >> 1) & 1;
+        mbar_wait(&kv_empty[st], ph ^ 1);
+        mbar_expect_tx(&k_full[st], TILE_BYTES);
+        tma_load_3d(smem + OFF_K + st * TILE_BYTES, &tmQKV, &k_full[st], d + h * HD, j * BKV, b);
+        mbar_expect_tx(&v_full[st], TILE_BYTES);
+        tma_load_3d(smem + OFF_V + st * TILE_BYTES, &tmQKV, &v_full[st], 2 * d + h * HD, j * BKV,
+                    b);
+      }
+    }
+  } else if (warp == 5) {
+    // ------------------------------- MMA issuer ---------------------------------------------
+    if (lane == 0) {
+      constexpr uint32_t idesc_s = umma_idesc_bf16(BQ, BKV, false, false);
+      constexpr uint32_t idesc_pv = umma_idesc_bf16(BQ, HD, false, true);
+      const uint32_t sQ = smem_u32(smem + OFF_Q);
+      const uint32_t sP = smem_u32(smem + OFF_P);
+      mbar_wait(q_full, 0);
+      for (int j = 0; j < n_kv; ++j) {
+        const int st = j & 1;
+        const uint32_t ph = (j >> 1) & 1;
+        const uint32_t sK = smem_u32(smem + OFF_K + st * TILE_BYTES);
+        const uint32_t sV = smem_u32(smem + OFF_V + st * TILE_BYTES);
+        // S_j = Q K_j^T.  The S columns are free: the softmax warps signalled p_full(j-1) only
+        // after their last read of S_{j-1}, and we waited on it below before getting here.
+        mbar_wait(&k_full[st], ph);
+        tc_fence_after_sync();
+#pragma unroll
+        for (int k = 0; k < HD / 16; ++k)
+          umma_ss(tmem_S, umma_smem_desc(sQ + k * 32, 0, 1024), umma_smem_desc(sK + k * 32, 0, 1024),
+                  idesc_s, k > 0);
+        umma_commit(s_full);
+        // PV_j = P_j V_j  (fresh accumulator every tile; folded into registers by the softmax warps)
+        mbar_wait(p_full, j & 1);
+        mbar_wait(&v_full[st], ph);
+        tc_fence_after_sync();
+#pragma unroll
+        for (int k = 0; k < BKV / 16; ++k)
+          umma_ss(tmem_PV, umma_smem_desc(sP + (k >> 2) * TILE_BYTES + (k & 3) * 32, 0, 1024),
+                  umma_smem_desc(sV + k * 2048, TILE_BYTES, 1024), idesc_pv, k > 0);
+        umma_commit(&kv_empty[st]);
+        umma_commit(pv_done);
+      }
+    }
+  } else {
+    // ------------------------------- softmax / output ---------------------------------------
+    const int r = threadIdx.x;  // 0..127: query row inside the tile == TMEM lane
+    const int qrow = q0 + r;
+    const uint32_t lane_base = uint32_t(warp * 32) << 16;
+    float m_run = -INFINITY, l_run = 0.f;
+    float o[HD];
+#pragma unroll
+    for (int i = 0; i < HD; ++i) o[i] = 0.f;
+    const uint8_t* kmask = p.key_mask ? p.key_mask + size_t(b) * p.T : nullptr;
+
+    for (int j = 0; j < n_kv; ++j) {
+      const int kv0 = j * BKV;
+      const bool need_mask = (j == qt) || (kmask != nullptr);
+      mbar_wait(s_full, j & 1);
+      tc_fence_after_sync();
+
+      // pass 1: row max
+      float mx = -INFINITY;
+#pragma unroll 1
+      for (int c = 0; c < BKV / 32; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32b_x32(tmem_S + lane_base + c * 32, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          const int col = kv0 + c * 32 + i;
+          bool ok = true;
+          if (need_mask) {
+            ok = col <= qrow;
+            if (kmask != nullptr && col < p.T) ok = ok && (kmask[col] != 0);
+          }
+          if (ok) mx = fmaxf(mx, __uint_as_float(v[i]));
+        }
+      }
+      const float m_new = fmaxf(m_run, mx * p.scale_log2);
+      const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
+      const float alpha = exp2f(m_run - m_use);  // m_run = -inf -> 0
+
+      // pass 2: p = exp2(s*scale - m), row sum, bf16 pack into the K-major swizzled P tile
+      float sum = 0.f;
+#pragma unroll 1
+      for (int c = 0; c < BKV / 32; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32b_x32(tmem_S + lane_base + c * 32, v);
+        tmem_ld_wait();
+        uint32_t packed[16];
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+          float e[2];
+#pragma unroll
+          for (int u = 0; u < 2; ++u) {
+            const int col = kv0 + c * 32 + i + u;
+            bool ok = true;
+            if (need_mask) {
+              ok = col <= qrow;
+              if (kmask != nullptr && col < p.T) ok = ok && (kmask[col] != 0);
+            }
+            e[u] = ok ? exp2f(__uint_as_float(v[i + u]) * p.scale_log2 - m_use) : 0.f;
+          }
+          // sum what the tensor core will actually see (bf16-rounded), keeps rows normalised
+          const uint32_t pk = pack_bf16x2(e[0], e[1]);
+          const float2 back = unpack_bf16x2(pk);
+          sum += back.x + back.y;
+          packed[i >> 1] = pk;
+        }
+        uint8_t* region = smem + OFF_P + (c >> 1) * TILE_BYTES;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const uint32_t off = swizzle128(r * 128 + ((c & 1) * 4 + q) * 16);
+          *reinterpret_cast<uint4*>(region + off) =
+              make_uint4(packed[4 * q], packed[4 * q + 1], packed[4 * q + 2], packed[4 * q + 3]);
+        }
+      }
+      l_run = l_run * alpha + sum;
+      m_run = m_new;
+
+      fence_proxy_async_smem();
+      tc_fence_before_sync();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(p_full);
+
+      // fold PV_j into the running output
+      mbar_wait(pv_done, j & 1);
+      tc_fence_after_sync();
+#pragma unroll
+      for (int c = 0; c < HD / 32; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32b_x32(tmem_PV + lane_base + c * 32, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) o[c * 32 + i] = o[c * 32 + i] * alpha + __uint_as_float(v[i]);
+      }
+      tc_fence_before_sync();
+    }
+
+    // normalise, stage as bf16 (swizzled 128 B rows) in the P buffer, one TMA store per CTA
+    const float inv_l = l_run > 0.f ? 1.0f / l_run : 0.f;
+    uint8_t* stage = smem + OFF_P;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      uint32_t w[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        w[u] = pack_bf16x2(o[q * 8 + 2 * u] * inv_l, o[q * 8 + 2 * u + 1] * inv_l);
+      *reinterpret_cast<uint4*>(stage + swizzle128(r * 128 + q * 16)) =
+          make_uint4(w[0], w[1], w[2], w[3]);
+    }
+    if (qrow < p.T) {
+      p.lse[(size_t(b) * p.H + h) * p.T + qrow] =
+          l_run > 0.f ? (m_run + log2f(l_run)) * 0.6931471805599453f : -INFINITY;
+    }
+    fence_proxy_async_smem();
+    named_bar_sync(1, 128);
+    if (threadIdx.x == 0) {
+      tma_store_3d(&tmO, stage, h * HD, q0, b);
+      tma_store_commit();
+      tma_store_wait<0>();
+    }
+  }
+
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 5) tmem_dealloc(tmem, FWD_TMEM_COLS);
+}
+
+}  // namespace attn
+}  // namespace b200
+
+using namespace b200;
+
+// qkv: [B, T, 3*H*64] bf16 (q | k | v, head-major inside each third).  out: [B, T, H*64] bf16.
+// lse: [B, H, T] fp32.  key_mask: [B, T] uint8 or NULL.
+extern "C" int llmtrain_b200_attention_fwd(const void* qkv, void* out, float* lse,
+                                           const uint8_t* key_mask, int B, int T, int H,
+                                           int head_dim, cudaStream_t stream) {
+  B200_REQUIRE(head_dim == attn::HD, "attention: the tcgen05 kernel is specialised for head_dim 64");
+  B200_REQUIRE(B > 0 && T > 0 && H > 0, "attention: empty problem");
+  const int d = H * attn::HD;
+  CUtensorMap tQKV, tO;
+  if (make_tmap_3d(&tQKV, static_cast<const __nv_bfloat16*>(qkv), B, T, 3 * d, 3 * d,
+                   uint64_t(T) * 3 * d, 128, attn::HD, Swz::B128))
+    return 1;
+  if (make_tmap_3d(&tO, static_cast<__nv_bfloat16*>(out), B, T, d, d, uint64_t(T) * d, 128,
+                   attn::HD, Swz::B128))
+    return 1;
+  attn::FwdParams p;
+  p.B = B; p.T = T; p.H = H;
+  p.scale_log2 = 1.4426950408889634f / std::sqrt(float(head_dim));
+  p.key_mask = key_mask;
+  p.lse = lse;
+  static bool configured = false;
+  if (!configured) {
+    B200_CHECK_CUDA(cudaFuncSetAttribute(attn::fwd_kernel,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         attn::FWD_SMEM));
+    configured = true;
+  }
+  dim3 grid(ceil_div(T, attn::BQ), H, B);
+  attn::fwd_kernel<<<grid, attn::FWD_THREADS, attn::FWD_SMEM, stream>>>(tQKV, tO, p);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

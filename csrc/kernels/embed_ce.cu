@@ -1,0 +1,370 @@
+// Embedding forward/backward, fused softmax-cross-entropy (forward + dlogits in one pass), bias
+// gradient (column sums) and dtype casts.
+//
+// Reference sites: token+position embedding `src/llmtrain/models/gpt.py:176-179` (K1);
+// cross-entropy + (masked) mean `src/llmtrain/models/gpt.py:256-269` (K11); the bias gradients
+// are the autograd of the four nn.Linear biases (K12).  All of these are HBM-bound, so every
+// kernel makes exactly one pass over its large operand with 128-bit accesses.
+
+#include "../common/host.cuh"
+#include "../common/ptx.cuh"
+#include "../../include/llmtrain_b200.h"
+
+namespace b200 {
+namespace ew {
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// ------------------------------------------------------------------------------------------------
+// x[m,:] = wte[ids[m],:] + wpe[m % T,:]        (bf16 tables, bf16 out; one warp per row)
+// ------------------------------------------------------------------------------------------------
+__global__ void embed_fwd_kernel(const int64_t* __restrict__ ids,
+                                 const __nv_bfloat16* __restrict__ wte,
+                                 const __nv_bfloat16* __restrict__ wpe,
+                                 __nv_bfloat16* __restrict__ x, int rows, int T, int d, int vocab) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int lane = threadIdx.x & 31;
+  int64_t tok = ids[row];
+  tok = tok < 0 ? 0 : (tok >= vocab ? vocab - 1 : tok);  // never read out of bounds
+  const uint4* te = reinterpret_cast<const uint4*>(wte + size_t(tok) * d);
+  const uint4* pe = reinterpret_cast<const uint4*>(wpe + size_t(row % T) * d);
+  uint4* out = reinterpret_cast<uint4*>(x + size_t(row) * d);
+  for (int c = lane; c < (d >> 3); c += 32) {
+    const uint4 a = __ldg(te + c), b = __ldg(pe + c);
+    const float2 a0 = unpack_bf16x2(a.x), a1 = unpack_bf16x2(a.y), a2 = unpack_bf16x2(a.z),
+                 a3 = unpack_bf16x2(a.w);
+    const float2 b0 = unpack_bf16x2(b.x), b1 = unpack_bf16x2(b.y), b2 = unpack_bf16x2(b.z),
+                 b3 = unpack_bf16x2(b.w);
+    out[c] = make_uint4(pack_bf16x2(a0.x + b0.x, a0.y + b0.y), pack_bf16x2(a1.x + b1.x, a1.y + b1.y),
+                        pack_bf16x2(a2.x + b2.x, a2.y + b2.y), pack_bf16x2(a3.x + b3.x, a3.y + b3.y));
+  }
+}
+
+// dwte[ids[m],:] += dx[m,:]   (fp32 arena; vector red.add — rows of one token may collide)
+__global__ void embed_bwd_wte_kernel(const int64_t* __restrict__ ids,
+                                     const __nv_bfloat16* __restrict__ dx,
+                                     float* __restrict__ dwte, int rows, int d, int vocab) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int lane = threadIdx.x & 31;
+  int64_t tok = ids[row];
+  if (tok < 0 || tok >= vocab) return;
+  const uint2* src = reinterpret_cast<const uint2*>(dx + size_t(row) * d);
+  float* dst = dwte + size_t(tok) * d;
+  for (int c = lane; c < (d >> 2); c += 32) {
+    const uint2 u = __ldg(src + c);
+    const float2 f0 = unpack_bf16x2(u.x), f1 = unpack_bf16x2(u.y);
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + 4 * c), "f"(f0.x),
+                 "f"(f0.y), "f"(f1.x), "f"(f1.y)
+                 : "memory");
+  }
+}
+
+// dwpe[t,:] += sum_b dx[b*T + t,:]   (one thread per (t, 4 columns); fixed order over b)
+__global__ void embed_bwd_wpe_kernel(const __nv_bfloat16* __restrict__ dx,
+                                     float* __restrict__ dwpe, int B, int T, int d) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  const int per_row = d >> 2;
+  if (idx >= T * per_row) return;
+  const int t = idx / per_row, c = idx - t * per_row;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int b = 0; b < B; ++b) {
+    const uint2 u = __ldg(reinterpret_cast<const uint2*>(dx + (size_t(b) * T + t) * d) + c);
+    const float2 f0 = unpack_bf16x2(u.x), f1 = unpack_bf16x2(u.y);
+    acc.x += f0.x; acc.y += f0.y; acc.z += f1.x; acc.w += f1.y;
+  }
+  float4* out = reinterpret_cast<float4*>(dwpe + size_t(t) * d) + c;
+  float4 cur = *out;
+  cur.x += acc.x; cur.y += acc.y; cur.z += acc.z; cur.w += acc.w;
+  *out = cur;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Fused cross-entropy: one CTA per row, the whole (padded) vocabulary row is read ONCE into
+// registers, loss_row = lse - logit[label], and (optionally) the row is overwritten in place with
+// dlogits = (softmax - onehot) * grad_scale * row_weight.  Padded columns [V, ldv) get zero.
+// ------------------------------------------------------------------------------------------------
+constexpr int CE_THREADS = 512;
+constexpr int CE_MAX_VEC = 16;  // uint4 per thread -> ld up to 512*16*8 = 65536 columns
+
+template <bool WRITE_GRAD>
+__global__ void __launch_bounds__(CE_THREADS)
+ce_kernel(__nv_bfloat16* __restrict__ logits, const int64_t* __restrict__ labels,
+          const uint8_t* __restrict__ row_valid, float* __restrict__ loss_rows, int V, int ldv,
+          float grad_scale) {
+  __shared__ float red[CE_THREADS / 32];
+  __shared__ float bcast;
+  const int row = blockIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  uint4* rp = reinterpret_cast<uint4*>(logits + size_t(row) * ldv);
+  const int nvec = ldv >> 3;
+  const bool valid = row_valid == nullptr || row_valid[row] != 0;
+  const int label = static_cast<int>(labels[row]);
+
+  uint4 v[CE_MAX_VEC];
+  float mx = -INFINITY;
+#pragma unroll
+  for (int i = 0; i < CE_MAX_VEC; ++i) {
+    const int c = tid + i * CE_THREADS;
+    if (c < nvec) {
+      v[i] = rp[c];
+      const uint32_t w[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 f = unpack_bf16x2(w[j]);
+        const int col = c * 8 + 2 * j;
+        if (col < V) mx = fmaxf(mx, f.x);
+        if (col + 1 < V) mx = fmaxf(mx, f.y);
+      }
+    }
+  }
+  mx = warp_max(mx);
+  if (lane == 0) red[warp] = mx;
+  __syncthreads();
+  if (warp == 0) {
+    float t = lane < CE_THREADS / 32 ? red[lane] : -INFINITY;
+    t = warp_max(t);
+    if (lane == 0) bcast = t;
+  }
+  __syncthreads();
+  mx = bcast;
+  __syncthreads();
+
+  float sum = 0.f, picked = 0.f;
+#pragma unroll
+  for (int i = 0; i < CE_MAX_VEC; ++i) {
+    const int c = tid + i * CE_THREADS;
+    if (c < nvec) {
+      const uint32_t w[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 f = unpack_bf16x2(w[j]);
+        const int col = c * 8 + 2 * j;
+        if (col < V) { sum += __expf(f.x - mx); if (col == label) picked = f.x; }
+        if (col + 1 < V) { sum += __expf(f.y - mx); if (col + 1 == label) picked = f.y; }
+      }
+    }
+  }
+  sum = warp_sum(sum);
+  picked = warp_sum(picked);
+  if (lane == 0) red[warp] = sum;
+  __syncthreads();
+  float total = 0.f;
+  if (warp == 0) {
+    float t = lane < CE_THREADS / 32 ? red[lane] : 0.f;
+    t = warp_sum(t);
+    if (lane == 0) bcast = t;
+  }
+  __syncthreads();
+  total = bcast;
+  __syncthreads();
+  if (lane == 0) red[warp] = picked;
+  __syncthreads();
+  if (warp == 0) {
+    float t = lane < CE_THREADS / 32 ? red[lane] : 0.f;
+    t = warp_sum(t);
+    if (lane == 0) loss_rows[row] = valid ? (__logf(total) + mx - t) : 0.f;
+  }
+
+  if (WRITE_GRAD) {
+    const float inv = valid ? grad_scale / total : 0.f;
+    const float hot = valid ? grad_scale : 0.f;
+#pragma unroll
+    for (int i = 0; i < CE_MAX_VEC; ++i) {
+      const int c = tid + i * CE_THREADS;
+      if (c < nvec) {
+        const uint32_t w[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
+        uint32_t o[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float2 f = unpack_bf16x2(w[j]);
+          const int col = c * 8 + 2 * j;
+          float g0 = 0.f, g1 = 0.f;
+          if (col < V) g0 = __expf(f.x - mx) * inv - (col == label ? hot : 0.f);
+          if (col + 1 < V) g1 = __expf(f.y - mx) * inv - (col + 1 == label ? hot : 0.f);
+          o[j] = pack_bf16x2(g0, g1);
+        }
+        rp[c] = make_uint4(o[0], o[1], o[2], o[3]);
+      }
+    }
+  }
+}
+
+// loss_acc[0] += scale * sum(loss_rows)  — single CTA, fixed order => deterministic.
+__global__ void loss_reduce_kernel(const float* __restrict__ loss_rows, int rows, float scale,
+                                   float* __restrict__ loss_acc) {
+  __shared__ float red[32];
+  float acc = 0.f;
+  for (int i = threadIdx.x; i < rows; i += blockDim.x) acc += loss_rows[i];
+  acc = warp_sum(acc);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    float t = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.f;
+    t = warp_sum(t);
+    if (threadIdx.x == 0) loss_acc[0] += t * scale;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Column sums: db[n] += sum_m dy[m,n].  Grid (ceil(N/64), splits); each warp streams rows, a lane
+// owns two adjacent columns; warps combine through smem; splits combine through scratch in a
+// fixed order (second kernel).
+// ------------------------------------------------------------------------------------------------
+constexpr int CS_WARPS = 8;
+__global__ void __launch_bounds__(CS_WARPS * 32)
+colsum_partial_kernel(const __nv_bfloat16* __restrict__ dy, int ld, int M, int N,
+                      float* __restrict__ partial /* [splits][N] */) {
+  __shared__ float2 sh[CS_WARPS][32];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int col = blockIdx.x * 64 + lane * 2;
+  const int rows_per = (M + gridDim.y - 1) / gridDim.y;
+  const int r0 = blockIdx.y * rows_per;
+  const int r1 = min(M, r0 + rows_per);
+  float2 acc = make_float2(0.f, 0.f);
+  if (col < N) {
+    for (int r = r0 + warp; r < r1; r += CS_WARPS) {
+      const float2 f = unpack_bf16x2(
+          __ldg(reinterpret_cast<const uint32_t*>(dy + size_t(r) * ld + col)));
+      acc.x += f.x; acc.y += f.y;
+    }
+  }
+  sh[warp][lane] = acc;
+  __syncthreads();
+  if (warp == 0 && col < N) {
+    float2 t = sh[0][lane];
+#pragma unroll
+    for (int w = 1; w < CS_WARPS; ++w) { t.x += sh[w][lane].x; t.y += sh[w][lane].y; }
+    partial[size_t(blockIdx.y) * N + col] = t.x;
+    if (col + 1 < N) partial[size_t(blockIdx.y) * N + col + 1] = t.y;
+  }
+}
+__global__ void colsum_finish_kernel(const float* __restrict__ partial, int splits, int N,
+                                     float* __restrict__ out) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  float acc = 0.f;
+  for (int s = 0; s < splits; ++s) acc += partial[size_t(s) * N + n];
+  out[n] += acc;
+}
+inline int colsum_splits(int M, int N) {
+  const int col_blocks = ceil_div(N, 64);
+  int s = ceil_div(4 * sm_count(), col_blocks);
+  const int max_s = ceil_div(M, 64);
+  if (s > max_s) s = max_s;
+  if (s > 64) s = 64;
+  return s < 1 ? 1 : s;
+}
+
+// ------------------------------------------------------------------------------------------------
+// fp32 -> bf16 cast (weight shadow refresh), 8 elements per thread.
+// ------------------------------------------------------------------------------------------------
+__global__ void cast_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst,
+                            size_t n) {
+  const size_t i = (size_t(blockIdx.x) * blockDim.x + threadIdx.x) * 8;
+  if (i + 8 <= n) {
+    const float4 a = __ldg(reinterpret_cast<const float4*>(src + i));
+    const float4 b = __ldg(reinterpret_cast<const float4*>(src + i) + 1);
+    *reinterpret_cast<uint4*>(dst + i) = make_uint4(pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w),
+                                                    pack_bf16x2(b.x, b.y), pack_bf16x2(b.z, b.w));
+  } else {
+    for (size_t j = i; j < n; ++j) dst[j] = __float2bfloat16(src[j]);
+  }
+}
+
+}  // namespace ew
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int llmtrain_b200_embed_fwd(const int64_t* ids, const void* wte, const void* wpe,
+                                       void* x, int B, int T, int d, int vocab,
+                                       cudaStream_t stream) {
+  B200_REQUIRE(d % 8 == 0, "embed: d must be a multiple of 8");
+  const int rows = B * T;
+  if (rows == 0) return 0;
+  ew::embed_fwd_kernel<<<ceil_div(rows, 8), 256, 0, stream>>>(
+      ids, static_cast<const __nv_bfloat16*>(wte), static_cast<const __nv_bfloat16*>(wpe),
+      static_cast<__nv_bfloat16*>(x), rows, T, d, vocab);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int llmtrain_b200_embed_bwd(const int64_t* ids, const void* dx, float* dwte,
+                                       float* dwpe, int B, int T, int d, int vocab,
+                                       cudaStream_t stream) {
+  B200_REQUIRE(d % 8 == 0, "embed: d must be a multiple of 8");
+  const int rows = B * T;
+  if (rows == 0) return 0;
+  ew::embed_bwd_wte_kernel<<<ceil_div(rows, 8), 256, 0, stream>>>(
+      ids, static_cast<const __nv_bfloat16*>(dx), dwte, rows, d, vocab);
+  B200_CHECK_CUDA(cudaGetLastError());
+  ew::embed_bwd_wpe_kernel<<<ceil_div(T * (d / 4), 256), 256, 0, stream>>>(
+      static_cast<const __nv_bfloat16*>(dx), dwpe, B, T, d);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int llmtrain_b200_cross_entropy(void* logits, const int64_t* labels,
+                                           const uint8_t* row_valid, float* loss_rows,
+                                           float* loss_acc, int rows, int V, int ldv,
+                                           float loss_scale, float grad_scale, int write_grad,
+                                           cudaStream_t stream) {
+  B200_REQUIRE(ldv % 8 == 0 && ldv >= V, "cross_entropy: row pitch must be >= V and a multiple of 8");
+  B200_REQUIRE(ldv <= ew::CE_THREADS * ew::CE_MAX_VEC * 8, "cross_entropy: vocabulary too large");
+  if (rows == 0) return 0;
+  auto* lg = static_cast<__nv_bfloat16*>(logits);
+  if (write_grad) {
+    ew::ce_kernel<true><<<rows, ew::CE_THREADS, 0, stream>>>(lg, labels, row_valid, loss_rows, V,
+                                                             ldv, grad_scale);
+  } else {
+    ew::ce_kernel<false><<<rows, ew::CE_THREADS, 0, stream>>>(lg, labels, row_valid, loss_rows, V,
+                                                              ldv, grad_scale);
+  }
+  B200_CHECK_CUDA(cudaGetLastError());
+  if (loss_acc != nullptr) {
+    ew::loss_reduce_kernel<<<1, 1024, 0, stream>>>(loss_rows, rows, loss_scale, loss_acc);
+    B200_CHECK_CUDA(cudaGetLastError());
+  }
+  return 0;
+}
+
+extern "C" size_t llmtrain_b200_bias_grad_scratch_bytes(int M, int N) {
+  return size_t(ew::colsum_splits(M, N)) * N * sizeof(float);
+}
+
+extern "C" int llmtrain_b200_bias_grad(const void* dy, int ld, int M, int N, float* dbias,
+                                       void* scratch, size_t scratch_bytes, cudaStream_t stream) {
+  B200_REQUIRE(ld % 2 == 0, "bias_grad: row pitch must be even");
+  if (M == 0 || N == 0) return 0;
+  const int splits = ew::colsum_splits(M, N);
+  B200_REQUIRE(scratch_bytes >= size_t(splits) * N * sizeof(float), "bias_grad: scratch too small");
+  dim3 grid(ceil_div(N, 64), splits);
+  ew::colsum_partial_kernel<<<grid, ew::CS_WARPS * 32, 0, stream>>>(
+      static_cast<const __nv_bfloat16*>(dy), ld, M, N, static_cast<float*>(scratch));
+  B200_CHECK_CUDA(cudaGetLastError());
+  ew::colsum_finish_kernel<<<ceil_div(N, 256), 256, 0, stream>>>(static_cast<float*>(scratch),
+                                                                 splits, N, dbias);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int llmtrain_b200_cast_f32_to_bf16(const float* src, void* dst, size_t n,
+                                              cudaStream_t stream) {
+  if (n == 0) return 0;
+  const size_t threads = (n + 7) / 8;
+  ew::cast_kernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, stream>>>(
+      src, static_cast<__nv_bfloat16*>(dst), n);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

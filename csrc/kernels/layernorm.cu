@@ -1,0 +1,263 @@
+// LayerNorm forward / backward over bf16 activations (fp32 statistics and parameters).
+//
+// Replaces nn.LayerNorm at `src/llmtrain/models/gpt.py:86,93,142` (used at :100,102,183) and
+// its autograd backward (work item W4).  Memory-bound: one warp owns one row,
+// the row is held in registers between the statistics pass and the normalise pass, all global
+// traffic is 128-bit.  Backward also carries the residual-stream gradient: the block structure
+// x_{l+1} = x_l + f(LN(x_l)) means d x_l = d x_{l+1} + LN'(…), so the kernel adds its result
+// into the running residual gradient in place.  dgamma / dbeta use a deterministic two-stage
+// reduction (per-CTA partial rows in scratch, then a fixed-order column sum) — no float atomics.
+
+#include "../common/host.cuh"
+#include "../common/ptx.cuh"
+#include "../../include/llmtrain_b200.h"
+
+namespace b200 {
+namespace ln {
+
+constexpr int MAX_VEC = 8;  // uint4 (8 bf16) chunks per lane -> d <= 2048
+constexpr int WARPS = 8;
+constexpr float EPS = 1e-5f;
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+__device__ __forceinline__ void unpack8(const uint4& u, float (&f)[8]) {
+  float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z),
+         d = unpack_bf16x2(u.w);
+  f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
+}
+__device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
+  return make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]),
+                    pack_bf16x2(f[6], f[7]));
+}
+
+__global__ void __launch_bounds__(WARPS * 32)
+fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
+           const float* __restrict__ beta, __nv_bfloat16* __restrict__ y,
+           float* __restrict__ mean_out, float* __restrict__ rstd_out, int rows, int d) {
+  const int row = blockIdx.x * WARPS + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int lane = threadIdx.x & 31;
+  const int nvec = d >> 3;
+  const uint4* xr = reinterpret_cast<const uint4*>(x + size_t(row) * d);
+  float v[MAX_VEC][8];
+  float sum = 0.f;
+#pragma unroll
+  for (int i = 0; i < MAX_VEC; ++i) {
+    const int c = lane + i * 32;
+    if (c < nvec) {
+      unpack8(__ldg(xr + c), v[i]);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) sum += v[i][j];
+    }
+  }
+  const float mean = warp_sum(sum) / d;
+  float sq = 0.f;
+#pragma unroll
+  for (int i = 0; i < MAX_VEC; ++i) {
+    if (lane + i * 32 < nvec) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { const float t = v[i][j] - mean; sq += t * t; }
+    }
+  }
+  const float rstd = rsqrtf(warp_sum(sq) / d + EPS);
+  uint4* yr = reinterpret_cast<uint4*>(y + size_t(row) * d);
+#pragma unroll
+  for (int i = 0; i < MAX_VEC; ++i) {
+    const int c = lane + i * 32;
+    if (c < nvec) {
+      const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma) + 2 * c);
+      const float4 g1 = __ldg(reinterpret_cast<const float4*>(gamma) + 2 * c + 1);
+      const float4 b0 = __ldg(reinterpret_cast<const float4*>(beta) + 2 * c);
+      const float4 b1 = __ldg(reinterpret_cast<const float4*>(beta) + 2 * c + 1);
+      const float g[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+      const float b[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+      float o[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = (v[i][j] - mean) * rstd * g[j] + b[j];
+      yr[c] = pack8(o);
+    }
+  }
+  if (lane == 0) {
+    if (mean_out) mean_out[row] = mean;
+    if (rstd_out) rstd_out[row] = rstd;
+  }
+}
+
+// Backward.  Each CTA walks rows blockIdx.x, blockIdx.x + gridDim.x, ... ; every lane keeps the
+// dgamma/dbeta partial sums of the columns it owns in registers, warps are combined through
+// shared memory in a fixed order, and the CTA writes ONE partial row to scratch.
+// NV = uint4 chunks per lane (ceil(d / 256)); inputs stay packed (bf16) between the two passes.
+template <int NV>
+__global__ void __launch_bounds__(WARPS * 32)
+bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
+           const float* __restrict__ gamma, const float* __restrict__ mean,
+           const float* __restrict__ rstd, __nv_bfloat16* __restrict__ dresid,
+           float* __restrict__ partial /* [gridDim.x][2][d] */, int rows, int d) {
+  extern __shared__ float sh[];  // [WARPS][2][d]
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int nvec = d >> 3;
+  float dg[NV][8], db[NV][8];
+#pragma unroll
+  for (int i = 0; i < NV; ++i)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { dg[i][j] = 0.f; db[i][j] = 0.f; }
+
+  for (int row = blockIdx.x * WARPS + warp; row < rows; row += gridDim.x * WARPS) {
+    const uint4* dyr = reinterpret_cast<const uint4*>(dy + size_t(row) * d);
+    const uint4* xr = reinterpret_cast<const uint4*>(x + size_t(row) * d);
+    const float mu = mean[row], rs = rstd[row];
+    uint4 pa[NV], pb[NV];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = lane + i * 32;
+      if (c < nvec) { pa[i] = __ldg(dyr + c); pb[i] = __ldg(xr + c); }
+    }
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = lane + i * 32;
+      if (c < nvec) {
+        float a[8], b[8];
+        unpack8(pa[i], a);
+        unpack8(pb[i], b);
+        const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma) + 2 * c);
+        const float4 g1 = __ldg(reinterpret_cast<const float4*>(gamma) + 2 * c + 1);
+        const float g[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float h = (b[j] - mu) * rs;
+          dg[i][j] += a[j] * h;
+          db[i][j] += a[j];
+          const float w = a[j] * g[j];
+          s1 += w;
+          s2 += w * h;
+        }
+      }
+    }
+    s1 = warp_sum(s1) / d;
+    s2 = warp_sum(s2) / d;
+    uint4* drr = reinterpret_cast<uint4*>(dresid + size_t(row) * d);
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = lane + i * 32;
+      if (c < nvec) {
+        float a[8], b[8], r[8];
+        unpack8(pa[i], a);
+        unpack8(pb[i], b);
+        unpack8(drr[c], r);
+        const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma) + 2 * c);
+        const float4 g1 = __ldg(reinterpret_cast<const float4*>(gamma) + 2 * c + 1);
+        const float g[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float h = (b[j] - mu) * rs;
+          r[j] += rs * (a[j] * g[j] - s1 - h * s2);
+        }
+        drr[c] = pack8(r);
+      }
+    }
+  }
+
+  float* my = sh + size_t(warp) * 2 * d;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int c = lane + i * 32;
+    if (c < nvec) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { my[c * 8 + j] = dg[i][j]; my[d + c * 8 + j] = db[i][j]; }
+    }
+  }
+  __syncthreads();
+  float* out = partial + size_t(blockIdx.x) * 2 * d;
+  for (int idx = threadIdx.x; idx < 2 * d; idx += blockDim.x) {
+    float acc = 0.f;
+#pragma unroll
+    for (int w = 0; w < WARPS; ++w) acc += sh[size_t(w) * 2 * d + idx];
+    out[idx] = acc;
+  }
+}
+
+// Fixed-order column sum of `nparts` partial rows, accumulated into the fp32 gradient arena.
+__global__ void finish_kernel(const float* __restrict__ partial, int nparts, int d,
+                              float* __restrict__ dgamma, float* __restrict__ dbeta) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= 2 * d) return;
+  float acc = 0.f;
+  for (int p = 0; p < nparts; ++p) acc += partial[size_t(p) * 2 * d + idx];
+  if (idx < d) dgamma[idx] += acc; else dbeta[idx - d] += acc;
+}
+
+inline int bwd_grid(int rows) {
+  int g = 2 * sm_count();
+  const int need = ceil_div(rows, WARPS);
+  return g < need ? g : need;
+}
+
+}  // namespace ln
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int llmtrain_b200_layernorm_fwd(const void* x, const float* gamma, const float* beta,
+                                           void* y, float* mean, float* rstd, int rows, int d,
+                                           cudaStream_t stream) {
+  B200_REQUIRE(d % 8 == 0 && d <= ln::MAX_VEC * 256, "layernorm: d must be a multiple of 8, <= 2048");
+  if (rows == 0) return 0;
+  ln::fwd_kernel<<<ceil_div(rows, ln::WARPS), ln::WARPS * 32, 0, stream>>>(
+      static_cast<const __nv_bfloat16*>(x), gamma, beta, static_cast<__nv_bfloat16*>(y), mean,
+      rstd, rows, d);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" size_t llmtrain_b200_layernorm_bwd_scratch_bytes(int rows, int d) {
+  return size_t(ln::bwd_grid(rows)) * 2 * d * sizeof(float);
+}
+
+extern "C" int llmtrain_b200_layernorm_bwd(const void* dy, const void* x, const float* gamma,
+                                           const float* mean, const float* rstd, void* dresid,
+                                           float* dgamma, float* dbeta, void* scratch,
+                                           size_t scratch_bytes, int rows, int d,
+                                           cudaStream_t stream) {
+  B200_REQUIRE(d % 8 == 0 && d <= ln::MAX_VEC * 256, "layernorm: d must be a multiple of 8, <= 2048");
+  if (rows == 0) return 0;
+  const int grid = ln::bwd_grid(rows);
+  B200_REQUIRE(scratch_bytes >= size_t(grid) * 2 * d * sizeof(float),
+               "layernorm_bwd: scratch too small (see llmtrain_b200_layernorm_bwd_scratch_bytes)");
+  const size_t smem = size_t(ln::WARPS) * 2 * d * sizeof(float);
+  const auto* dy_ = static_cast<const __nv_bfloat16*>(dy);
+  const auto* x_ = static_cast<const __nv_bfloat16*>(x);
+  auto* dr_ = static_cast<__nv_bfloat16*>(dresid);
+  auto* part_ = static_cast<float*>(scratch);
+  const int nv = ceil_div(d, 256);
+#define B200_LN_BWD(NV)                                                                        \
+  case NV: {                                                                                   \
+    static bool configured = false;                                                            \
+    if (!configured) {                                                                         \
+      B200_CHECK_CUDA(cudaFuncSetAttribute(ln::bwd_kernel<NV>,                                 \
+                                           cudaFuncAttributeMaxDynamicSharedMemorySize,        \
+                                           160 * 1024));                                       \
+      configured = true;                                                                       \
+    }                                                                                          \
+    ln::bwd_kernel<NV><<<grid, ln::WARPS * 32, smem, stream>>>(dy_, x_, gamma, mean, rstd, dr_, \
+                                                               part_, rows, d);                \
+    break;                                                                                     \
+  }
+  switch (nv) {
+    B200_LN_BWD(1) B200_LN_BWD(2) B200_LN_BWD(3) B200_LN_BWD(4)
+    B200_LN_BWD(5) B200_LN_BWD(6) B200_LN_BWD(7) B200_LN_BWD(8)
+    default: return fail("layernorm_bwd: unsupported width");
+  }
+#undef B200_LN_BWD
+  B200_CHECK_CUDA(cudaGetLastError());
+  ln::finish_kernel<<<ceil_div(2 * d, 256), 256, 0, stream>>>(static_cast<float*>(scratch), grid,
+                                                              d, dgamma, dbeta);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

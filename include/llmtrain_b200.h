@@ -14,6 +14,7 @@
 #ifndef LLMTRAIN_B200_H_
 #define LLMTRAIN_B200_H_
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -40,6 +41,74 @@ int llmtrain_b200_abi_version(void);
 int llmtrain_b200_gemm(int layout, int epilogue, int M, int N, int K, const void* A, int lda,
                        const void* B, int ldb, void* C, int ldc, void* C2, int ldc2,
                        const float* bias, const void* R, int ldr, llm_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * LayerNorm (eps 1e-5).  Replaces nn.LayerNorm at src/llmtrain/models/gpt.py:86,93,142.
+ *   fwd: y = (x-mean)*rstd*gamma+beta, x/y bf16 [rows,d], gamma/beta fp32; mean/rstd fp32 [rows]
+ *        (may be NULL when no backward follows).
+ *   bwd: dresid[rows,d] (bf16, in place) += LN'(dy);  dgamma/dbeta (fp32) += column sums.
+ *        Deterministic two-stage reduction through `scratch` (size from *_scratch_bytes).
+ * ------------------------------------------------------------------------------------------- */
+int llmtrain_b200_layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y,
+                                float* mean, float* rstd, int rows, int d, llm_stream_t stream);
+size_t llmtrain_b200_layernorm_bwd_scratch_bytes(int rows, int d);
+int llmtrain_b200_layernorm_bwd(const void* dy, const void* x, const float* gamma,
+                                const float* mean, const float* rstd, void* dresid, float* dgamma,
+                                float* dbeta, void* scratch, size_t scratch_bytes, int rows, int d,
+                                llm_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Embedding.  Replaces src/llmtrain/models/gpt.py:176-179 and its backward.
+ *   fwd: x[b*T+t,:] = wte[ids[b,t],:] + wpe[t,:]   (bf16 tables, bf16 out)
+ *   bwd: dwte[ids,:] += dx (vector red.add), dwpe[t,:] += sum_b dx[b,t,:]   (fp32 arenas)
+ * ------------------------------------------------------------------------------------------- */
+int llmtrain_b200_embed_fwd(const int64_t* ids, const void* wte, const void* wpe, void* x, int B,
+                            int T, int d, int vocab, llm_stream_t stream);
+int llmtrain_b200_embed_bwd(const int64_t* ids, const void* dx, float* dwte, float* dwpe, int B,
+                            int T, int d, int vocab, llm_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Fused softmax cross-entropy.  Replaces F.cross_entropy(reduction="none") + (masked) mean at
+ * src/llmtrain/models/gpt.py:256-269.  One read of the bf16 logits row [V valid of ldv columns];
+ * loss_rows[r] = lse - logit[label] (0 for rows with row_valid==0); when write_grad != 0 the row
+ * is overwritten in place with (softmax - onehot) * grad_scale (0 for invalid rows / pad columns).
+ * If loss_acc != NULL: loss_acc[0] += loss_scale * sum(loss_rows)   (deterministic).
+ * ------------------------------------------------------------------------------------------- */
+int llmtrain_b200_cross_entropy(void* logits, const int64_t* labels, const uint8_t* row_valid,
+                                float* loss_rows, float* loss_acc, int rows, int V, int ldv,
+                                float loss_scale, float grad_scale, int write_grad,
+                                llm_stream_t stream);
+
+/* dbias[n] (fp32) += sum_m dy[m,n] (bf16, pitch ld).  Autograd of the nn.Linear biases. */
+size_t llmtrain_b200_bias_grad_scratch_bytes(int M, int N);
+int llmtrain_b200_bias_grad(const void* dy, int ld, int M, int N, float* dbias, void* scratch,
+                            size_t scratch_bytes, llm_stream_t stream);
+
+int llmtrain_b200_cast_f32_to_bf16(const float* src, void* dst, size_t n, llm_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Optimizer.  Replaces clip_grad_norm_ + AdamW.step + zero_grad
+ * (src/llmtrain/training/trainer.py:362,390-394).
+ *   grad_sumsq: out[0] = (accumulate ? out[0] : 0) + sum g^2  (two-stage, deterministic).
+ *   adamw: g_eff = g * grad_scale * min(1, max_norm / (sqrt(sumsq)*grad_scale + 1e-6)); decoupled
+ *          weight decay; bias-corrected moments (step counts from 1); optionally refreshes the
+ *          bf16 shadow, writes the pre-clip norm to norm_out, and zeroes g.
+ * ------------------------------------------------------------------------------------------- */
+size_t llmtrain_b200_grad_sumsq_scratch_bytes(size_t n);
+int llmtrain_b200_grad_sumsq(const float* g, size_t n, float* out, int accumulate, void* scratch,
+                             size_t scratch_bytes, llm_stream_t stream);
+int llmtrain_b200_adamw(float* p, float* m, float* v, float* g, void* p_bf16, size_t n,
+                        const float* sumsq, float* norm_out, float lr, float beta1, float beta2,
+                        float eps, float weight_decay, int step, float grad_scale, float max_norm,
+                        int zero_grad, llm_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Causal flash attention (tcgen05, head_dim 64).  Replaces src/llmtrain/models/gpt.py:56-70.
+ *   qkv [B,T,3*H*64] bf16 (q|k|v thirds, head-major), out [B,T,H*64] bf16, lse [B,H,T] fp32,
+ *   key_mask [B,T] uint8 (1 = attend) or NULL.
+ * ------------------------------------------------------------------------------------------- */
+int llmtrain_b200_attention_fwd(const void* qkv, void* out, float* lse, const uint8_t* key_mask,
+                                int B, int T, int H, int head_dim, llm_stream_t stream);
 
 #ifdef __cplusplus
 }

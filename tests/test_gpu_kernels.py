@@ -1,0 +1,186 @@
+"""Memory-bound kernels + attention forward vs fp32 torch references (B200 box)."""
+
+from __future__ import annotations
+
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _bf(shape, scale=1.0):
+    return (torch.randn(*shape, device="cuda") * scale).to(torch.bfloat16)
+
+
+def _rel(got, want):
+    return ((got.float() - want.float()).abs().max() / (want.float().abs().max() + 1e-6)).item()
+
+
+@pytest.mark.parametrize("rows,d", [(64, 768), (1000, 1600), (37, 64), (4096, 1024)])
+def test_layernorm_fwd_bwd(rows: int, d: int) -> None:
+    from llmtrain.ops import kernels as K
+
+    x = _bf((rows, d), 2.0)
+    gamma = torch.randn(d, device="cuda") * 0.5 + 1.0
+    beta = torch.randn(d, device="cuda") * 0.1
+    mean = torch.empty(rows, device="cuda")
+    rstd = torch.empty(rows, device="cuda")
+    y = K.layernorm_fwd(x, gamma, beta, mean=mean, rstd=rstd)
+
+    xr = x.float().requires_grad_(True)
+    g32, b32 = gamma.clone().requires_grad_(True), beta.clone().requires_grad_(True)
+    want = F.layer_norm(xr, (d,), g32, b32, 1e-5)
+    assert _rel(y, want) < 1e-2
+    assert _rel(mean, xr.mean(-1)) < 1e-3
+
+    dy = _bf((rows, d))
+    resid0 = _bf((rows, d))
+    dresid = resid0.clone()
+    dgamma = torch.zeros(d, device="cuda")
+    dbeta = torch.zeros(d, device="cuda")
+    K.layernorm_bwd(dy, x, gamma, mean, rstd, dresid, dgamma, dbeta)
+    want.backward(dy.float())
+    assert _rel(dresid, resid0.float() + xr.grad) < 2e-2
+    assert _rel(dgamma, g32.grad) < 1e-2
+    assert _rel(dbeta, b32.grad) < 1e-2
+    # accumulation semantics of the parameter gradients
+    K.layernorm_bwd(dy, x, gamma, mean, rstd, dresid, dgamma, dbeta)
+    assert _rel(dgamma, 2 * g32.grad) < 1e-2
+
+
+def test_embedding_fwd_bwd() -> None:
+    from llmtrain.ops import kernels as K
+
+    b, t, d, v = 3, 50, 128, 1000
+    ids = torch.randint(0, v, (b, t), device="cuda")
+    wte, wpe = _bf((v, d)), _bf((64, d))
+    x = K.embed_fwd(ids, wte, wpe)
+    want = wte.float()[ids] + wpe.float()[:t][None]
+    assert _rel(x.view(b, t, d), want) < 1e-2
+
+    dx = _bf((b * t, d))
+    dwte = torch.zeros(v, d, device="cuda")
+    dwpe = torch.zeros(64, d, device="cuda")
+    K.embed_bwd(ids, dx, dwte, dwpe)
+    ref_wte = torch.zeros(v, d, device="cuda").index_add_(0, ids.flatten(), dx.float())
+    assert _rel(dwte, ref_wte) < 1e-4
+    assert _rel(dwpe[:t], dx.float().view(b, t, d).sum(0)) < 1e-4
+    assert dwpe[t:].abs().max().item() == 0
+
+
+@pytest.mark.parametrize("rows,v,ldv", [(64, 1000, 1024), (33, 50257, 50304), (8, 16, 16)])
+def test_cross_entropy_loss_and_grad(rows: int, v: int, ldv: int) -> None:
+    from llmtrain.ops import kernels as K
+
+    logits = torch.zeros(rows, ldv, device="cuda", dtype=torch.bfloat16)
+    logits[:, :v] = _bf((rows, v), 3.0)
+    logits[:, v:] = 77.0  # padding columns must be ignored
+    labels = torch.randint(0, v, (rows,), device="cuda")
+    valid = torch.ones(rows, dtype=torch.uint8, device="cuda")
+    valid[::5] = 0
+    ref_in = logits[:, :v].float().requires_grad_(True)
+    per_tok = F.cross_entropy(ref_in, labels, reduction="none")
+    n_valid = int(valid.sum())
+    (per_tok * valid.float()).sum().div(n_valid).backward()
+
+    acc = torch.zeros(1, device="cuda")
+    work = logits.clone()
+    rows_loss = K.cross_entropy(work, labels, vocab=v, row_valid=valid, loss_acc=acc,
+                                loss_scale=1.0 / n_valid, grad_scale=1.0 / n_valid)
+    assert _rel(rows_loss, per_tok * valid.float()) < 1e-3
+    assert abs(acc.item() - (per_tok * valid.float()).sum().item() / n_valid) < 1e-3
+    assert _rel(work[:, :v], ref_in.grad) < 2e-2
+    assert work[:, v:].abs().max().item() == 0 if ldv > v else True
+
+    untouched = logits.clone()
+    K.cross_entropy(untouched, labels, vocab=v, write_grad=False)
+    assert torch.equal(untouched, logits)
+
+
+@pytest.mark.parametrize("m,n", [(4096, 768), (1000, 2304), (130, 50)])
+def test_bias_grad(m: int, n: int) -> None:
+    from llmtrain.ops import kernels as K
+
+    dy = _bf((m, n))
+    db = torch.ones(n, device="cuda")
+    K.bias_grad(dy, db)
+    assert _rel(db, 1.0 + dy.float().sum(0)) < 1e-3
+
+
+def test_cast_and_sumsq_and_adamw_match_torch() -> None:
+    from llmtrain.ops import kernels as K
+
+    n = 1_000_003
+    p = torch.randn(n, device="cuda")
+    g = torch.randn(n, device="cuda") * 3
+    shadow = torch.empty(n, device="cuda", dtype=torch.bfloat16)
+    K.cast_bf16(p, shadow)
+    assert torch.equal(shadow, p.to(torch.bfloat16))
+
+    sumsq = torch.zeros(1, device="cuda")
+    K.grad_sumsq(g, sumsq)
+    assert abs(sumsq.item() / g.double().pow(2).sum().item() - 1) < 1e-5
+
+    ref_p = torch.nn.Parameter(p.clone())
+    opt = torch.optim.AdamW([ref_p], lr=1e-2, weight_decay=0.1)
+    m = torch.zeros(n, device="cuda")
+    v = torch.zeros(n, device="cuda")
+    ours = p.clone()
+    norm = torch.zeros(1, device="cuda")
+    for step in (1, 2, 3):
+        g_step = g * step
+        ref_p.grad = g_step.clone()
+        ref_norm = torch.nn.utils.clip_grad_norm_([ref_p], 1.0)
+        opt.step()
+        work = g_step.clone()
+        K.grad_sumsq(work, sumsq)
+        K.adamw(ours, m, v, work, shadow, sumsq=sumsq, norm_out=norm, lr=1e-2, beta1=0.9,
+                beta2=0.999, eps=1e-8, weight_decay=0.1, step=step, max_norm=1.0)
+        assert abs(norm.item() / ref_norm.item() - 1) < 1e-4
+        assert work.abs().max().item() == 0  # gradients zeroed for the next step
+        assert (ours - ref_p.detach()).abs().max().item() < 1e-5
+    assert torch.equal(shadow, ours.to(torch.bfloat16))
+    assert _rel(m, opt.state[ref_p]["exp_avg"]) < 1e-5
+    assert _rel(v, opt.state[ref_p]["exp_avg_sq"]) < 1e-5
+
+
+def _ref_attention(qkv: torch.Tensor, h: int, key_mask: torch.Tensor | None):
+    b, t, three_d = qkv.shape
+    d = three_d // 3
+    hd = d // h
+    q, k, v = qkv.float().view(b, t, 3, h, hd).permute(2, 0, 3, 1, 4)
+    s = (q @ k.transpose(-1, -2)) / math.sqrt(hd)
+    lowest = torch.finfo(s.dtype).min
+    s = s.masked_fill(torch.ones(t, t, dtype=torch.bool, device=qkv.device).triu_(1), lowest)
+    if key_mask is not None:
+        s = s.masked_fill(~key_mask.bool()[:, None, None, :], lowest)
+    p = s.softmax(-1)
+    return (p @ v).transpose(1, 2).reshape(b, t, d), torch.logsumexp(s, -1)
+
+
+@pytest.mark.parametrize("b,t,h", [(2, 128, 2), (1, 256, 3), (2, 1024, 4), (3, 200, 2), (2, 8, 1)])
+def test_attention_fwd(b: int, t: int, h: int) -> None:
+    from llmtrain.ops import kernels as K
+
+    qkv = _bf((b, t, 3 * h * 64))
+    out, lse = K.attention_fwd(qkv, h)
+    want, want_lse = _ref_attention(qkv, h, None)
+    assert _rel(out, want) < 2e-2
+    assert (lse - want_lse).abs().max().item() < 2e-2
+
+
+def test_attention_fwd_key_padding() -> None:
+    from llmtrain.ops import kernels as K
+
+    b, t, h = 2, 300, 2
+    qkv = _bf((b, t, 3 * h * 64))
+    mask = torch.ones(b, t, dtype=torch.uint8, device="cuda")
+    mask[0, 250:] = 0
+    mask[1, 100:140] = 0
+    out, _ = K.attention_fwd(qkv, h, key_mask=mask)
+    want, _ = _ref_attention(qkv, h, mask)
+    keep = mask.bool()[:, :, None]
+    assert _rel(out * keep, want * keep) < 2e-2
