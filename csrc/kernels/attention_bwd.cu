@@ -1,0 +1,396 @@
+// Causal flash attention backward on tcgen05 (head_dim 64).
+//
+// Autograd of `src/llmtrain/models/gpt.py:56-70` without ever storing P (work
+// item W3).  One CTA owns a 128-row key/value tile j of one (batch, head) and walks the query
+// tiles i >= j.  Five tensor-core products per (i, j) pair, all accumulating in TMEM:
+//
+//   S   = Q_i K_j^T                (128x128x64)      dP  = dO_i V_j^T              (128x128x64)
+//   dV += P^T  dO_i                (128x64x128)      dK += dS^T Q_i               (128x64x128)
+//   dQ_i = dS  K_j                 (128x64x128)   -> fp32 TMA reduce-add into the dQ buffer
+//
+// with P = exp2(S*scale*log2e - LSE_i*log2e) and dS = P o (dP - D_i) * scale computed by four
+// warps that own one query row each (TMEM lane == row).  P and dS are written once to shared
+// memory as bf16 in the 128-byte-swizzled K-major tile layout and are then consumed twice by the
+// tensor core through two different descriptors: K-major (dQ = dS K) and MN-major (P^T, dS^T) —
+// no transposes are materialised.  V_j, dO_i, Q_i, K_j are likewise used both K-major and
+// MN-major straight from their TMA-loaded tiles.
+//
+// D_i = rowsum(dO o O) comes from a small pre-kernel.  dK/dV leave through one TMA store each into
+// the fused [B, T, 3d] gradient buffer; dQ contributions from different kv tiles meet in an fp32
+// buffer that a post-kernel converts into the q third of that same gradient buffer.
+
+#include "../common/host.cuh"
+#include "../common/ptx.cuh"
+#include "../../include/llmtrain_b200.h"
+
+namespace b200 {
+namespace attn_bwd {
+
+constexpr int BQ = 128;
+constexpr int BKV = 128;
+constexpr int HD = 64;
+constexpr int TILE = 128 * HD * 2;  // 16 KB
+constexpr int THREADS = 192;
+constexpr int TMEM_COLS = 512;
+constexpr int COL_S = 0, COL_DP = 128, COL_DV = 256, COL_DK = 320, COL_DQ = 384;
+constexpr int OFF_K = 0;
+constexpr int OFF_V = OFF_K + TILE;
+constexpr int OFF_Q = OFF_V + TILE;        // [2]
+constexpr int OFF_DO = OFF_Q + 2 * TILE;   // [2]
+constexpr int OFF_P = OFF_DO + 2 * TILE;   // 32 KB
+constexpr int OFF_DS = OFF_P + 2 * TILE;   // 32 KB
+constexpr int OFF_DQ = OFF_DS + 2 * TILE;  // 32 KB fp32 staging
+constexpr int OFF_BAR = OFF_DQ + 2 * TILE;
+constexpr int SMEM = OFF_BAR + 256 + 1024;
+
+struct Params {
+  int B, T, H;
+  float scale;       // head_dim^-0.5
+  float scale_log2;  // scale * log2(e)
+  const float* lse;  // [B, H, T]
+  const float* dsum; // [B, H, T]   D = rowsum(dO o O)
+  const uint8_t* key_mask;
+};
+
+__global__ void __launch_bounds__(THREADS, 1)
+bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
+           const __grid_constant__ CUtensorMap tmDQKV, const __grid_constant__ CUtensorMap tmDQ32,
+           const Params p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
+  uint64_t* kv_full = bars + 0;
+  uint64_t* q_full = bars + 1;   // [2]
+  uint64_t* q_empty = bars + 3;  // [2]
+  uint64_t* s_full = bars + 5;
+  uint64_t* pds_full = bars + 6;
+  uint64_t* dq_full = bars + 7;
+  uint64_t* dkv_full = bars + 8;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nq = (p.T + BQ - 1) / BQ;
+  const int jt = blockIdx.x;  // kv tile; tile 0 has the most query tiles and is scheduled first
+  const int h = blockIdx.y, b = blockIdx.z;
+  const int kv0 = jt * BKV;
+  const int d = p.H * HD;
+  const int n_iter = nq - jt;
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tmQKV);
+    tma_prefetch_desc(&tmDO);
+    tma_prefetch_desc(&tmDQKV);
+    tma_prefetch_desc(&tmDQ32);
+    mbar_init(kv_full, 1);
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&q_full[s], 1);
+      mbar_init(&q_empty[s], 1);
+    }
+    mbar_init(s_full, 1);
+    mbar_init(pds_full, 4);
+    mbar_init(dq_full, 1);
+    mbar_init(dkv_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 5) {
+    tmem_alloc(tmem_slot, TMEM_COLS);
+    tmem_relinquish();
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp == 4) {
+    // ------------------------------- TMA producer -------------------------------------------
+    if (lane == 0) {
+      mbar_expect_tx(kv_full, 2 * TILE);
+      tma_load_3d(smem + OFF_K, &tmQKV, kv_full, d + h * HD, kv0, b);
+      tma_load_3d(smem + OFF_V, &tmQKV, kv_full, 2 * d + h * HD, kv0, b);
+      for (int it = 0; it < n_iter; ++it) {
+        const int st = it & 1;
+        const uint32_t ph = (it >> 1) & 1;
+        const int q0 = (jt + it) * BQ;
+        mbar_wait(&q_empty[st], ph ^ 1);
+        mbar_expect_tx(&q_full[st], 2 * TILE);
+        tma_load_3d(smem + OFF_Q + st * TILE, &tmQKV, &q_full[st], h * HD, q0, b);
+        tma_load_3d(smem + OFF_DO + st * TILE, &tmDO, &q_full[st], h * HD, q0, b);
+      }
+    }
+  } else if (warp == 5) {
+    // ------------------------------- MMA issuer ---------------------------------------------
+    if (lane == 0) {
+      constexpr uint32_t id_s = umma_idesc_bf16(128, 128, false, false);   // Q K^T, dO V^T
+      constexpr uint32_t id_t = umma_idesc_bf16(128, 64, true, true);     // P^T dO, dS^T Q
+      constexpr uint32_t id_dq = umma_idesc_bf16(128, 64, false, true);   // dS K
+      const uint32_t sK = smem_u32(smem + OFF_K), sV = smem_u32(smem + OFF_V);
+      const uint32_t sP = smem_u32(smem + OFF_P), sDS = smem_u32(smem + OFF_DS);
+      mbar_wait(kv_full, 0);
+      for (int it = 0; it < n_iter; ++it) {
+        const int st = it & 1;
+        const uint32_t ph = (it >> 1) & 1;
+        const uint32_t sQ = smem_u32(smem + OFF_Q + st * TILE);
+        const uint32_t sDO = smem_u32(smem + OFF_DO + st * TILE);
+        mbar_wait(&q_full[st], ph);
+        tc_fence_after_sync();
+#pragma unroll
+        for (int k = 0; k < HD / 16; ++k)
+          umma_ss(tmem + COL_S, umma_smem_desc(sQ + k * 32, 0, 1024),
+                  umma_smem_desc(sK + k * 32, 0, 1024), id_s, k > 0);
+#pragma unroll
+        for (int k = 0; k < HD / 16; ++k)
+          umma_ss(tmem + COL_DP, umma_smem_desc(sDO + k * 32, 0, 1024),
+                  umma_smem_desc(sV + k * 32, 0, 1024), id_s, k > 0);
+        umma_commit(s_full);
+
+        mbar_wait(pds_full, it & 1);
+        tc_fence_after_sync();
+        // dV += P^T dO ; dK += dS^T Q   (A, B both MN-major: 16 q-rows = 2048 B per K step)
+#pragma unroll
+        for (int k = 0; k < BQ / 16; ++k)
+          umma_ss(tmem + COL_DV, umma_smem_desc(sP + k * 2048, TILE, 1024),
+                  umma_smem_desc(sDO + k * 2048, TILE, 1024), id_t, (it > 0) || (k > 0));
+#pragma unroll
+        for (int k = 0; k < BQ / 16; ++k)
+          umma_ss(tmem + COL_DK, umma_smem_desc(sDS + k * 2048, TILE, 1024),
+                  umma_smem_desc(sQ + k * 2048, TILE, 1024), id_t, (it > 0) || (k > 0));
+        umma_commit(&q_empty[st]);
+        // dQ_i = dS K  (A K-major over 128 kv = two 64-wide regions; B = K_j MN-major)
+#pragma unroll
+        for (int k = 0; k < BKV / 16; ++k)
+          umma_ss(tmem + COL_DQ, umma_smem_desc(sDS + (k >> 2) * TILE + (k & 3) * 32, 0, 1024),
+                  umma_smem_desc(sK + k * 2048, TILE, 1024), id_dq, k > 0);
+        umma_commit(dq_full);
+      }
+      umma_commit(dkv_full);
+    }
+  } else {
+    // ------------------------------- softmax-grad / epilogue warps --------------------------
+    const int r = threadIdx.x;  // 0..127
+    const uint32_t lane_base = uint32_t(warp * 32) << 16;
+    const uint8_t* kmask = p.key_mask ? p.key_mask + size_t(b) * p.T : nullptr;
+    const size_t stat_base = (size_t(b) * p.H + h) * p.T;
+
+    for (int it = 0; it < n_iter; ++it) {
+      const int qt = jt + it;
+      const int q0 = qt * BQ;
+      const int qrow = q0 + r;
+      const bool row_ok = qrow < p.T;
+      float lse2 = 0.f, dsum = 0.f;
+      if (row_ok) {
+        const float l = p.lse[stat_base + qrow];
+        lse2 = l * 1.4426950408889634f;
+        dsum = p.dsum[stat_base + qrow];
+      }
+      const bool dead_row = !row_ok || (lse2 == -INFINITY);
+      const bool need_mask = (it == 0) || (kmask != nullptr);
+
+      mbar_wait(s_full, it & 1);
+      tc_fence_after_sync();
+#pragma unroll 1
+      for (int c = 0; c < BKV / 32; ++c) {
+        uint32_t sv[32], dv[32];
+        tmem_ld_32x32b_x32(tmem + COL_S + lane_base + c * 32, sv);
+        tmem_ld_32x32b_x32(tmem + COL_DP + lane_base + c * 32, dv);
+        tmem_ld_wait();
+        uint32_t pk[16], dk[16];
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+          float pe[2], de[2];
+#pragma unroll
+          for (int u = 0; u < 2; ++u) {
+            const int col = kv0 + c * 32 + i + u;
+            bool ok = !dead_row;
+            if (need_mask) {
+              ok = ok && (col <= qrow);
+              if (kmask != nullptr && col < p.T) ok = ok && (kmask[col] != 0);
+            }
+            const float pv = ok ? exp2f(__uint_as_float(sv[i + u]) * p.scale_log2 - lse2) : 0.f;
+            pe[u] = pv;
+            de[u] = pv * (__uint_as_float(dv[i + u]) - dsum) * p.scale;
+          }
+          pk[i >> 1] = pack_bf16x2(pe[0], pe[1]);
+          dk[i >> 1] = pack_bf16x2(de[0], de[1]);
+        }
+        uint8_t* rp = smem + OFF_P + (c >> 1) * TILE;
+        uint8_t* rd = smem + OFF_DS + (c >> 1) * TILE;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const uint32_t off = swizzle128(r * 128 + ((c & 1) * 4 + q) * 16);
+          *reinterpret_cast<uint4*>(rp + off) =
+              make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
+          *reinterpret_cast<uint4*>(rd + off) =
+              make_uint4(dk[4 * q], dk[4 * q + 1], dk[4 * q + 2], dk[4 * q + 3]);
+        }
+      }
+      fence_proxy_async_smem();
+      tc_fence_before_sync();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(pds_full);
+
+      // dQ_i: TMEM -> fp32 staging (two 128 B-row boxes of 32 columns) -> TMA reduce-add
+      mbar_wait(dq_full, it & 1);
+      tc_fence_after_sync();
+      if (threadIdx.x == 0) tma_store_wait_read<0>();  // previous iteration's staging drained
+      named_bar_sync(1, 128);
+#pragma unroll
+      for (int c = 0; c < HD / 32; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32b_x32(tmem + COL_DQ + lane_base + c * 32, v);
+        tmem_ld_wait();
+        uint8_t* box = smem + OFF_DQ + c * TILE;
+#pragma unroll
+        for (int q = 0; q < 8; ++q)
+          *reinterpret_cast<uint4*>(box + swizzle128(r * 128 + q * 16)) =
+              make_uint4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+      }
+      tc_fence_before_sync();
+      fence_proxy_async_smem();
+      named_bar_sync(1, 128);
+      if (threadIdx.x == 0) {
+        tma_reduce_add_3d(&tmDQ32, smem + OFF_DQ, h * HD, q0, b);
+        tma_reduce_add_3d(&tmDQ32, smem + OFF_DQ + TILE, h * HD + 32, q0, b);
+        tma_store_commit();
+      }
+    }
+
+    // dV, dK: TMEM -> bf16 -> swizzled staging (P / dS buffers are free now) -> TMA store
+    mbar_wait(dkv_full, 0);
+    tc_fence_after_sync();
+#pragma unroll
+    for (int which = 0; which < 2; ++which) {
+      uint8_t* stage = smem + (which == 0 ? OFF_P : OFF_DS);
+      const uint32_t col_base = which == 0 ? COL_DV : COL_DK;
+#pragma unroll
+      for (int c = 0; c < HD / 32; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32b_x32(tmem + col_base + lane_base + c * 32, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          uint32_t w[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u)
+            w[u] = pack_bf16x2(__uint_as_float(v[q * 8 + 2 * u]),
+                               __uint_as_float(v[q * 8 + 2 * u + 1]));
+          *reinterpret_cast<uint4*>(stage + swizzle128(r * 128 + (c * 4 + q) * 16)) =
+              make_uint4(w[0], w[1], w[2], w[3]);
+        }
+      }
+    }
+    tc_fence_before_sync();
+    fence_proxy_async_smem();
+    named_bar_sync(1, 128);
+    if (threadIdx.x == 0) {
+      tma_store_3d(&tmDQKV, smem + OFF_P, 2 * d + h * HD, kv0, b);   // dV
+      tma_store_3d(&tmDQKV, smem + OFF_DS, d + h * HD, kv0, b);      // dK
+      tma_store_commit();
+      tma_store_wait<0>();
+    }
+  }
+
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 5) tmem_dealloc(tmem, TMEM_COLS);
+}
+
+// D[b,h,t] = sum_c dO[b,t,h*64+c] * O[b,t,h*64+c]; one warp per (row, head).
+__global__ void dsum_kernel(const __nv_bfloat16* __restrict__ dO,
+                            const __nv_bfloat16* __restrict__ O, float* __restrict__ dsum, int B,
+                            int T, int H) {
+  const int gw = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  const int total = B * T * H;
+  if (gw >= total) return;
+  const int row = gw / H, h = gw - row * H;
+  const size_t off = size_t(row) * H * HD + h * HD + lane * 2;
+  const float2 a = unpack_bf16x2(__ldg(reinterpret_cast<const uint32_t*>(dO + off)));
+  const float2 o = unpack_bf16x2(__ldg(reinterpret_cast<const uint32_t*>(O + off)));
+  float v = a.x * o.x + a.y * o.y;
+#pragma unroll
+  for (int s = 16; s > 0; s >>= 1) v += __shfl_xor_sync(0xffffffffu, v, s);
+  if (lane == 0) {
+    const int b = row / T, t = row - b * T;
+    dsum[(size_t(b) * H + h) * T + t] = v;
+  }
+}
+
+// dqkv[row, 0:d] = bf16(dq32[row, :])   (q third of the fused gradient buffer)
+__global__ void dq_convert_kernel(const float* __restrict__ dq32, __nv_bfloat16* __restrict__ dqkv,
+                                  int rows, int d) {
+  const size_t idx = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  const int per_row = d >> 3;
+  if (idx >= size_t(rows) * per_row) return;
+  const int row = int(idx / per_row), c = int(idx - size_t(row) * per_row);
+  const float4 a = __ldg(reinterpret_cast<const float4*>(dq32 + size_t(row) * d) + 2 * c);
+  const float4 b = __ldg(reinterpret_cast<const float4*>(dq32 + size_t(row) * d) + 2 * c + 1);
+  *reinterpret_cast<uint4*>(dqkv + size_t(row) * 3 * d + c * 8) = make_uint4(
+      pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w), pack_bf16x2(b.x, b.y), pack_bf16x2(b.z, b.w));
+}
+
+}  // namespace attn_bwd
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" size_t llmtrain_b200_attention_bwd_scratch_bytes(int B, int T, int H, int head_dim) {
+  // fp32 dQ accumulator [B,T,d] followed by D [B,H,T]
+  return size_t(B) * T * H * head_dim * sizeof(float) + size_t(B) * H * T * sizeof(float);
+}
+
+// qkv [B,T,3d], out/dout [B,T,d] bf16, lse [B,H,T]  ->  dqkv [B,T,3d] bf16.
+extern "C" int llmtrain_b200_attention_bwd(const void* qkv, const void* out, const void* dout,
+                                           const float* lse, const uint8_t* key_mask, void* dqkv,
+                                           void* scratch, size_t scratch_bytes, int B, int T,
+                                           int H, int head_dim, cudaStream_t stream) {
+  namespace ab = attn_bwd;
+  B200_REQUIRE(head_dim == ab::HD, "attention_bwd: specialised for head_dim 64");
+  B200_REQUIRE(B > 0 && T > 0 && H > 0, "attention_bwd: empty problem");
+  const int d = H * ab::HD;
+  const size_t dq_bytes = size_t(B) * T * d * sizeof(float);
+  B200_REQUIRE(scratch_bytes >= llmtrain_b200_attention_bwd_scratch_bytes(B, T, H, head_dim),
+               "attention_bwd: scratch too small");
+  B200_REQUIRE((reinterpret_cast<uintptr_t>(scratch) & 255) == 0, "attention_bwd: scratch alignment");
+  float* dq32 = static_cast<float*>(scratch);
+  float* dsum = reinterpret_cast<float*>(static_cast<uint8_t*>(scratch) + dq_bytes);
+  B200_CHECK_CUDA(cudaMemsetAsync(dq32, 0, dq_bytes, stream));
+
+  const int rows = B * T;
+  ab::dsum_kernel<<<ceil_div(rows * H, 8), 256, 0, stream>>>(
+      static_cast<const __nv_bfloat16*>(dout), static_cast<const __nv_bfloat16*>(out), dsum, B, T,
+      H);
+  B200_CHECK_CUDA(cudaGetLastError());
+
+  CUtensorMap tQKV, tDO, tDQKV, tDQ32;
+  if (make_tmap_3d(&tQKV, static_cast<const __nv_bfloat16*>(qkv), B, T, 3 * d, 3 * d,
+                   uint64_t(T) * 3 * d, 128, ab::HD, Swz::B128)) return 1;
+  if (make_tmap_3d(&tDO, static_cast<const __nv_bfloat16*>(dout), B, T, d, d, uint64_t(T) * d, 128,
+                   ab::HD, Swz::B128)) return 1;
+  if (make_tmap_3d(&tDQKV, static_cast<__nv_bfloat16*>(dqkv), B, T, 3 * d, 3 * d,
+                   uint64_t(T) * 3 * d, 128, ab::HD, Swz::B128)) return 1;
+  if (make_tmap_3d(&tDQ32, dq32, B, T, d, d, uint64_t(T) * d, 128, 32, Swz::B128)) return 1;
+
+  ab::Params p;
+  p.B = B; p.T = T; p.H = H;
+  p.scale = 1.0f / std::sqrt(float(head_dim));
+  p.scale_log2 = p.scale * 1.4426950408889634f;
+  p.lse = lse;
+  p.dsum = dsum;
+  p.key_mask = key_mask;
+  static bool configured = false;
+  if (!configured) {
+    B200_CHECK_CUDA(cudaFuncSetAttribute(ab::bwd_kernel,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, ab::SMEM));
+    configured = true;
+  }
+  dim3 grid(ceil_div(T, ab::BKV), H, B);
+  ab::bwd_kernel<<<grid, ab::THREADS, ab::SMEM, stream>>>(tQKV, tDO, tDQKV, tDQ32, p);
+  B200_CHECK_CUDA(cudaGetLastError());
+
+  const size_t n = size_t(rows) * (d / 8);
+  ab::dq_convert_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, stream>>>(
+      dq32, static_cast<__nv_bfloat16*>(dqkv), rows, d);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

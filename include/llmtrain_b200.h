@@ -110,6 +110,15 @@ int llmtrain_b200_adamw(float* p, float* m, float* v, float* g, void* p_bf16, si
 int llmtrain_b200_attention_fwd(const void* qkv, void* out, float* lse, const uint8_t* key_mask,
                                 int B, int T, int H, int head_dim, llm_stream_t stream);
 
+/* Backward of the above (autograd of gpt.py:56-70).  dout [B,T,H*64] bf16 -> dqkv [B,T,3*H*64]
+ * bf16 (all three thirds fully overwritten).  `scratch` (256-byte aligned, size from
+ * *_scratch_bytes) holds the fp32 dQ accumulator and the row statistics D = rowsum(dO o O). */
+size_t llmtrain_b200_attention_bwd_scratch_bytes(int B, int T, int H, int head_dim);
+int llmtrain_b200_attention_bwd(const void* qkv, const void* out, const void* dout,
+                                const float* lse, const uint8_t* key_mask, void* dqkv,
+                                void* scratch, size_t scratch_bytes, int B, int T, int H,
+                                int head_dim, llm_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -39,6 +39,7 @@ def _lib():
             "llmtrain_b200_layernorm_bwd_scratch_bytes",
             "llmtrain_b200_bias_grad_scratch_bytes",
             "llmtrain_b200_grad_sumsq_scratch_bytes",
+            "llmtrain_b200_attention_bwd_scratch_bytes",
         ):
             getattr(lib, name).restype = ctypes.c_size_t
         lib._llm_typed = True
@@ -178,6 +179,26 @@ def attention_fwd(qkv, n_heads, *, key_mask=None, out=None, lse=None):
         "attention_fwd",
     )
     return out, lse
+
+
+def attention_bwd(qkv, out, dout, lse, n_heads, *, key_mask=None, dqkv=None):
+    """Gradient of :func:`attention_fwd` w.r.t. the fused ``qkv`` buffer."""
+    b, t, three_d = qkv.shape
+    hd = three_d // 3 // n_heads
+    dqkv = torch.empty_like(qkv) if dqkv is None else dqkv
+    lib = _lib()
+    need = lib.llmtrain_b200_attention_bwd_scratch_bytes(_c_int(b), _c_int(t), _c_int(n_heads),
+                                                         _c_int(hd))
+    buf = scratch(need, qkv.device)
+    check(
+        lib.llmtrain_b200_attention_bwd(
+            ptr(qkv), ptr(out), ptr(dout), ptr(lse), ptr(key_mask), ptr(dqkv), ptr(buf),
+            _c_size(buf.numel()), _c_int(b), _c_int(t), _c_int(n_heads), _c_int(hd),
+            stream_handle(),
+        ),
+        "attention_bwd",
+    )
+    return dqkv
 
 
 def softmax_scale(head_dim: int) -> float:

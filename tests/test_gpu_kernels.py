@@ -184,3 +184,39 @@ def test_attention_fwd_key_padding() -> None:
     want, _ = _ref_attention(qkv, h, mask)
     keep = mask.bool()[:, :, None]
     assert _rel(out * keep, want * keep) < 2e-2
+
+
+@pytest.mark.parametrize("b,t,h", [(1, 128, 1), (2, 256, 2), (2, 1024, 3), (2, 200, 2), (1, 8, 2)])
+def test_attention_bwd(b: int, t: int, h: int) -> None:
+    from llmtrain.ops import kernels as K
+
+    qkv = _bf((b, t, 3 * h * 64))
+    out, lse = K.attention_fwd(qkv, h)
+    dout = _bf((b, t, h * 64))
+    dqkv = K.attention_bwd(qkv, out, dout, lse, h)
+
+    ref_in = qkv.float().requires_grad_(True)
+    want, _ = _ref_attention(ref_in, h, None)
+    want.backward(dout.float())
+    d = h * 64
+    for name, sl in (("dq", slice(0, d)), ("dk", slice(d, 2 * d)), ("dv", slice(2 * d, 3 * d))):
+        err = _rel(dqkv[..., sl], ref_in.grad[..., sl])
+        assert err < 3e-2, f"{name}: {err}"
+
+
+def test_attention_bwd_key_padding() -> None:
+    from llmtrain.ops import kernels as K
+
+    b, t, h = 2, 300, 2
+    qkv = _bf((b, t, 3 * h * 64))
+    mask = torch.ones(b, t, dtype=torch.uint8, device="cuda")
+    mask[0, 250:] = 0
+    mask[1, 100:140] = 0
+    keep = mask.bool()[:, :, None]
+    out, lse = K.attention_fwd(qkv, h, key_mask=mask)
+    dout = (_bf((b, t, h * 64)).float() * keep).to(torch.bfloat16)  # padded queries get no grad
+    dqkv = K.attention_bwd(qkv, out, dout, lse, h, key_mask=mask)
+    ref_in = qkv.float().requires_grad_(True)
+    want, _ = _ref_attention(ref_in, h, mask)
+    want.backward(dout.float())
+    assert _rel(dqkv, ref_in.grad) < 3e-2
