@@ -4,3 +4,6 @@
 
 extern "C" const char* llmtrain_b200_last_error(void) { return b200::last_error_slot().c_str(); }
 extern "C" int llmtrain_b200_abi_version(void) { return 1000; }
+extern "C" long long llmtrain_b200_launch_count(void) {
+  return b200::launch_counter().load(std::memory_order_relaxed);
+}

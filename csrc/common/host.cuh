@@ -6,6 +6,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <atomic>
 #include <cstdio>
 #include <cstring>
 #include <mutex>
@@ -118,6 +119,14 @@ inline int make_tmap_3d(CUtensorMap* out, const T* base, uint64_t d2, uint64_t d
   }
   return 0;
 }
+
+// Number of kernels this library has launched (all threads); bench.py reports the delta over its
+// timed region as "gpu_launches".
+inline std::atomic<long long>& launch_counter() {
+  static std::atomic<long long> counter{0};
+  return counter;
+}
+#define B200_COUNT_LAUNCH(n) ::b200::launch_counter().fetch_add((n), std::memory_order_relaxed)
 
 inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 

@@ -1,0 +1,385 @@
+// GPT training runtime: owns the memory plan (flat parameter / gradient / activation arenas) and
+// sequences the sm_100a kernels for a full forward, fused loss, and backward pass.
+//
+// This is the C++ replacement for what the reference delegates to torch autograd when
+// `GPTAdapter.compute_loss` runs `GPT.forward` and `.backward()`
+// (`src/llmtrain/models/gpt.py:167-184,214-271`, `src/llmtrain/training/trainer.py:385-387`):
+// there is no graph, no per-op allocation and no Python in the loop — one call launches ~20
+// kernels per layer on a caller-provided stream, every intermediate lives at a fixed offset of
+// one activation arena sized for (max_batch x max_seq), and weight gradients accumulate in fp32
+// straight into the flat gradient arena that the bucket engine reduces.
+//
+// Arena order (elements, every tensor 64-element aligned):
+//   wpe | layer 0 .. L-1 {ln1.w ln1.b qkv.w qkv.b out.w out.b ln2.w ln2.b fc.w fc.b proj.w proj.b}
+//   | ln_f.w ln_f.b | [token_embedding.w if untied] | <LM-head matrix>
+// The LM-head matrix (token_embedding when tied) is LAST so that its bf16 shadow can carry zero
+// rows up to the padded vocabulary (multiple of 128) without disturbing any other offset; backward
+// finishes gradient regions from the end of the arena towards the front, which is the bucket
+// order the comm engine wants.
+
+#include <vector>
+
+#include "../common/host.cuh"
+#include "../../include/llmtrain_b200.h"
+
+namespace b200 {
+namespace engine {
+
+constexpr size_t ALIGN_ELEMS = 64;
+inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+struct LayerOffsets {
+  size_t ln1_w, ln1_b, qkv_w, qkv_b, out_w, out_b, ln2_w, ln2_b, fc_w, fc_b, proj_w, proj_b;
+};
+
+struct LayerActs {
+  size_t ln1, ln1_mean, ln1_rstd, qkv, atty, lse, resid1, ln2, ln2_mean, ln2_rstd, fch_pre,
+      fch_act, resid2;
+};
+
+struct Gpt {
+  int V = 0, Vp = 0, block = 0, d = 0, L = 0, H = 0, F = 0, tied = 1;
+  int maxB = 0, maxT = 0;
+  // parameter plan
+  size_t wpe = 0, lnf_w = 0, lnf_b = 0, wte = 0, head = 0;
+  std::vector<LayerOffsets> layer;
+  size_t n_params = 0;   // elements in p32 / m / v / g32 (incl. alignment gaps)
+  size_t n_shadow = 0;   // elements in the bf16 shadow (n_params + vocabulary padding rows)
+  // activation plan (byte offsets)
+  std::vector<LayerActs> acts;
+  size_t a_x0 = 0, a_lnf = 0, a_lnf_mean = 0, a_lnf_rstd = 0, a_logits = 0, a_loss_rows = 0;
+  size_t a_dresid = 0, a_dtmp = 0, a_dqkv = 0, a_dfc = 0, a_attn_scratch = 0, a_red_scratch = 0;
+  size_t attn_scratch_bytes = 0, red_scratch_bytes = 0, act_bytes = 0;
+  // bound memory
+  float *p32 = nullptr, *g32 = nullptr;
+  __nv_bfloat16* p16 = nullptr;
+  uint8_t* act = nullptr;
+  // state of the last forward (needed by backward)
+  int B = 0, T = 0;
+  const int64_t* ids = nullptr;
+  const uint8_t* key_mask = nullptr;
+  bool have_forward = false;
+};
+
+inline size_t take(size_t& cursor, size_t n) {
+  const size_t at = cursor;
+  cursor = align_up(cursor + n, ALIGN_ELEMS);
+  return at;
+}
+inline size_t take_bytes(size_t& cursor, size_t n) {
+  const size_t at = cursor;
+  cursor = align_up(cursor + n, 256);
+  return at;
+}
+
+void plan_params(Gpt& g) {
+  size_t c = 0;
+  const size_t d = g.d, F = g.F;
+  g.wpe = take(c, size_t(g.block) * d);
+  g.layer.resize(g.L);
+  for (int l = 0; l < g.L; ++l) {
+    LayerOffsets& o = g.layer[l];
+    o.ln1_w = take(c, d);          o.ln1_b = take(c, d);
+    o.qkv_w = take(c, 3 * d * d);  o.qkv_b = take(c, 3 * d);
+    o.out_w = take(c, d * d);      o.out_b = take(c, d);
+    o.ln2_w = take(c, d);          o.ln2_b = take(c, d);
+    o.fc_w = take(c, F * d);       o.fc_b = take(c, F);
+    o.proj_w = take(c, d * F);     o.proj_b = take(c, d);
+  }
+  g.lnf_w = take(c, d);
+  g.lnf_b = take(c, d);
+  if (g.tied) {
+    g.wte = take(c, size_t(g.V) * d);
+    g.head = g.wte;
+  } else {
+    g.wte = take(c, size_t(g.V) * d);
+    g.head = take(c, size_t(g.V) * d);
+  }
+  g.n_params = c;
+  g.n_shadow = align_up(g.head + size_t(g.Vp) * d, ALIGN_ELEMS);
+  if (g.n_shadow < g.n_params) g.n_shadow = g.n_params;
+}
+
+void plan_acts(Gpt& g) {
+  const size_t M = size_t(g.maxB) * g.maxT, d = g.d, F = g.F;
+  size_t c = 0;
+  g.a_x0 = take_bytes(c, M * d * 2);
+  g.acts.resize(g.L);
+  for (int l = 0; l < g.L; ++l) {
+    LayerActs& a = g.acts[l];
+    a.ln1 = take_bytes(c, M * d * 2);
+    a.ln1_mean = take_bytes(c, M * 4);
+    a.ln1_rstd = take_bytes(c, M * 4);
+    a.qkv = take_bytes(c, M * 3 * d * 2);
+    a.atty = take_bytes(c, M * d * 2);
+    a.lse = take_bytes(c, size_t(g.maxB) * g.H * g.maxT * 4);
+    a.resid1 = take_bytes(c, M * d * 2);
+    a.ln2 = take_bytes(c, M * d * 2);
+    a.ln2_mean = take_bytes(c, M * 4);
+    a.ln2_rstd = take_bytes(c, M * 4);
+    a.fch_pre = take_bytes(c, M * F * 2);
+    a.fch_act = take_bytes(c, M * F * 2);
+    a.resid2 = take_bytes(c, M * d * 2);
+  }
+  g.a_lnf = take_bytes(c, M * d * 2);
+  g.a_lnf_mean = take_bytes(c, M * 4);
+  g.a_lnf_rstd = take_bytes(c, M * 4);
+  g.a_logits = take_bytes(c, M * size_t(g.Vp) * 2);
+  g.a_loss_rows = take_bytes(c, M * 4);
+  g.a_dresid = take_bytes(c, M * d * 2);
+  g.a_dtmp = take_bytes(c, M * d * 2);
+  g.a_dqkv = take_bytes(c, M * 3 * d * 2);
+  g.a_dfc = take_bytes(c, M * F * 2);
+  g.attn_scratch_bytes =
+      llmtrain_b200_attention_bwd_scratch_bytes(g.maxB, g.maxT, g.H, g.d / g.H);
+  g.a_attn_scratch = take_bytes(c, g.attn_scratch_bytes);
+  size_t red = llmtrain_b200_layernorm_bwd_scratch_bytes(int(M), g.d);
+  const int widths[4] = {g.d, 3 * g.d, g.F, g.d};
+  for (int w : widths) {
+    const size_t need = llmtrain_b200_bias_grad_scratch_bytes(int(M), w);
+    if (need > red) red = need;
+  }
+  g.red_scratch_bytes = red;
+  g.a_red_scratch = take_bytes(c, red);
+  g.act_bytes = c;
+}
+
+// ---- thin typed views -------------------------------------------------------------------------
+struct View {
+  Gpt& g;
+  explicit View(Gpt& g_) : g(g_) {}
+  __nv_bfloat16* bf(size_t off) const { return reinterpret_cast<__nv_bfloat16*>(g.act + off); }
+  float* f32(size_t off) const { return reinterpret_cast<float*>(g.act + off); }
+  const __nv_bfloat16* w(size_t off) const { return g.p16 + off; }
+  const float* p(size_t off) const { return g.p32 + off; }
+  float* grad(size_t off) const { return g.g32 + off; }
+};
+
+#define B200_TRY(call)      \
+  do {                      \
+    if ((call) != 0) return 1; \
+  } while (0)
+
+inline int linear_fwd(int epi, int M, int N, int K, const void* x, const void* w, void* y, void* y2,
+                      const float* bias, const void* r, cudaStream_t s) {
+  return llmtrain_b200_gemm(0, epi, M, N, K, x, K, w, K, y, N, y2, N, bias, r, N,
+                            reinterpret_cast<llm_stream_t>(s));
+}
+// dX[M,K] = dY[M,N] @ W[N,K]
+inline int linear_dgrad(int epi, int M, int N, int K, const void* dy, const void* w, void* dx,
+                        const void* r, cudaStream_t s) {
+  return llmtrain_b200_gemm(1, epi, M, K, N, dy, N, w, K, dx, K, nullptr, 0, nullptr, r, K,
+                            reinterpret_cast<llm_stream_t>(s));
+}
+// dW[N,K] += dY[M,N]^T @ X[M,K]
+inline int linear_wgrad(int M, int N, int K, const void* dy, int ld_dy, const void* x, float* dw,
+                        cudaStream_t s) {
+  return llmtrain_b200_gemm(2, 4, N, K, M, dy, ld_dy, x, K, dw, K, nullptr, 0, nullptr, nullptr, 0,
+                            reinterpret_cast<llm_stream_t>(s));
+}
+
+int forward(Gpt& g, const int64_t* ids, const uint8_t* key_mask, int B, int T, cudaStream_t s) {
+  View v(g);
+  const int M = B * T, d = g.d, F = g.F, hd = g.d / g.H;
+  auto st = reinterpret_cast<llm_stream_t>(s);
+  B200_TRY(llmtrain_b200_embed_fwd(ids, v.w(g.wte), v.w(g.wpe), v.bf(g.a_x0), B, T, d, g.V, st));
+  const __nv_bfloat16* x = v.bf(g.a_x0);
+  for (int l = 0; l < g.L; ++l) {
+    const LayerOffsets& o = g.layer[l];
+    const LayerActs& a = g.acts[l];
+    B200_TRY(llmtrain_b200_layernorm_fwd(x, v.p(o.ln1_w), v.p(o.ln1_b), v.bf(a.ln1),
+                                         v.f32(a.ln1_mean), v.f32(a.ln1_rstd), M, d, st));
+    B200_TRY(linear_fwd(0, M, 3 * d, d, v.bf(a.ln1), v.w(o.qkv_w), v.bf(a.qkv), nullptr,
+                        v.p(o.qkv_b), nullptr, s));
+    B200_TRY(llmtrain_b200_attention_fwd(v.bf(a.qkv), v.bf(a.atty), v.f32(a.lse), key_mask, B, T,
+                                         g.H, hd, st));
+    B200_TRY(linear_fwd(2, M, d, d, v.bf(a.atty), v.w(o.out_w), v.bf(a.resid1), nullptr,
+                        v.p(o.out_b), x, s));
+    B200_TRY(llmtrain_b200_layernorm_fwd(v.bf(a.resid1), v.p(o.ln2_w), v.p(o.ln2_b), v.bf(a.ln2),
+                                         v.f32(a.ln2_mean), v.f32(a.ln2_rstd), M, d, st));
+    B200_TRY(linear_fwd(1, M, F, d, v.bf(a.ln2), v.w(o.fc_w), v.bf(a.fch_act), v.bf(a.fch_pre),
+                        v.p(o.fc_b), nullptr, s));
+    B200_TRY(linear_fwd(2, M, d, F, v.bf(a.fch_act), v.w(o.proj_w), v.bf(a.resid2), nullptr,
+                        v.p(o.proj_b), v.bf(a.resid1), s));
+    x = v.bf(a.resid2);
+  }
+  B200_TRY(llmtrain_b200_layernorm_fwd(x, v.p(g.lnf_w), v.p(g.lnf_b), v.bf(g.a_lnf),
+                                       v.f32(g.a_lnf_mean), v.f32(g.a_lnf_rstd), M, d, st));
+  // logits[M, Vp] = lnf @ head^T   (pad rows of the shadow are zero -> pad logits are 0, ignored)
+  B200_TRY(llmtrain_b200_gemm(0, 0, M, g.Vp, d, v.bf(g.a_lnf), d, v.w(g.head), d,
+                              v.bf(g.a_logits), g.Vp, nullptr, 0, nullptr, nullptr, 0, st));
+  g.B = B; g.T = T; g.ids = ids; g.key_mask = key_mask;
+  g.have_forward = true;
+  return 0;
+}
+
+int backward(Gpt& g, cudaStream_t s) {
+  B200_REQUIRE(g.have_forward, "gpt_backward: no forward pass to differentiate");
+  View v(g);
+  const int B = g.B, T = g.T, M = B * T, d = g.d, F = g.F, hd = g.d / g.H;
+  auto st = reinterpret_cast<llm_stream_t>(s);
+  void* red = g.act + g.a_red_scratch;
+  const size_t red_bytes = g.red_scratch_bytes;
+  __nv_bfloat16* dlogits = v.bf(g.a_logits);
+  __nv_bfloat16* dtmp = v.bf(g.a_dtmp);
+  __nv_bfloat16* dresid = v.bf(g.a_dresid);
+  __nv_bfloat16* dqkv = v.bf(g.a_dqkv);
+  __nv_bfloat16* dfc = v.bf(g.a_dfc);
+
+  // LM head: dlnf = dlogits @ head ; dhead += dlogits^T @ lnf   (only the V real rows)
+  B200_TRY(llmtrain_b200_gemm(1, 0, M, d, g.Vp, dlogits, g.Vp, v.w(g.head), d, dtmp, d, nullptr, 0,
+                              nullptr, nullptr, 0, st));
+  B200_TRY(llmtrain_b200_gemm(2, 4, g.V, d, M, dlogits, g.Vp, v.bf(g.a_lnf), d, v.grad(g.head), d,
+                              nullptr, 0, nullptr, nullptr, 0, st));
+  B200_CHECK_CUDA(cudaMemsetAsync(dresid, 0, size_t(M) * d * 2, s));
+  const __nv_bfloat16* x_last = g.L > 0 ? v.bf(g.acts[g.L - 1].resid2) : v.bf(g.a_x0);
+  B200_TRY(llmtrain_b200_layernorm_bwd(dtmp, x_last, v.p(g.lnf_w), v.f32(g.a_lnf_mean),
+                                       v.f32(g.a_lnf_rstd), dresid, v.grad(g.lnf_w),
+                                       v.grad(g.lnf_b), red, red_bytes, M, d, st));
+
+  for (int l = g.L - 1; l >= 0; --l) {
+    const LayerOffsets& o = g.layer[l];
+    const LayerActs& a = g.acts[l];
+    const __nv_bfloat16* x_in = l > 0 ? v.bf(g.acts[l - 1].resid2) : v.bf(g.a_x0);
+    // ---- MLP: resid2 = gelu(ln2 @ Wfc^T + bfc) @ Wproj^T + bproj + resid1
+    B200_TRY(llmtrain_b200_bias_grad(dresid, d, M, d, v.grad(o.proj_b), red, red_bytes, st));
+    B200_TRY(linear_wgrad(M, d, F, dresid, d, v.bf(a.fch_act), v.grad(o.proj_w), s));
+    B200_TRY(linear_dgrad(3, M, d, F, dresid, v.w(o.proj_w), dfc, v.bf(a.fch_pre), s));
+    B200_TRY(llmtrain_b200_bias_grad(dfc, F, M, F, v.grad(o.fc_b), red, red_bytes, st));
+    B200_TRY(linear_wgrad(M, F, d, dfc, F, v.bf(a.ln2), v.grad(o.fc_w), s));
+    B200_TRY(linear_dgrad(0, M, F, d, dfc, v.w(o.fc_w), dtmp, nullptr, s));
+    B200_TRY(llmtrain_b200_layernorm_bwd(dtmp, v.bf(a.resid1), v.p(o.ln2_w), v.f32(a.ln2_mean),
+                                         v.f32(a.ln2_rstd), dresid, v.grad(o.ln2_w),
+                                         v.grad(o.ln2_b), red, red_bytes, M, d, st));
+    // ---- attention: resid1 = attn(ln1 @ Wqkv^T + bqkv) @ Wo^T + bo + x_in
+    B200_TRY(llmtrain_b200_bias_grad(dresid, d, M, d, v.grad(o.out_b), red, red_bytes, st));
+    B200_TRY(linear_wgrad(M, d, d, dresid, d, v.bf(a.atty), v.grad(o.out_w), s));
+    B200_TRY(linear_dgrad(0, M, d, d, dresid, v.w(o.out_w), dtmp, nullptr, s));
+    B200_TRY(llmtrain_b200_attention_bwd(v.bf(a.qkv), v.bf(a.atty), dtmp, v.f32(a.lse), g.key_mask,
+                                         dqkv, g.act + g.a_attn_scratch, g.attn_scratch_bytes, B, T,
+                                         g.H, hd, st));
+    B200_TRY(llmtrain_b200_bias_grad(dqkv, 3 * d, M, 3 * d, v.grad(o.qkv_b), red, red_bytes, st));
+    B200_TRY(linear_wgrad(M, 3 * d, d, dqkv, 3 * d, v.bf(a.ln1), v.grad(o.qkv_w), s));
+    B200_TRY(linear_dgrad(0, M, 3 * d, d, dqkv, v.w(o.qkv_w), dtmp, nullptr, s));
+    B200_TRY(llmtrain_b200_layernorm_bwd(dtmp, x_in, v.p(o.ln1_w), v.f32(a.ln1_mean),
+                                         v.f32(a.ln1_rstd), dresid, v.grad(o.ln1_w),
+                                         v.grad(o.ln1_b), red, red_bytes, M, d, st));
+  }
+  B200_TRY(llmtrain_b200_embed_bwd(g.ids, dresid, v.grad(g.wte), v.grad(g.wpe), B, T, d, g.V, st));
+  g.have_forward = false;
+  return 0;
+}
+
+}  // namespace engine
+}  // namespace b200
+
+using namespace b200;
+using b200::engine::Gpt;
+
+extern "C" int llmtrain_b200_gpt_create(int vocab, int block_size, int d_model, int n_layers,
+                                        int n_heads, int d_ff, int tied, int max_batch,
+                                        int max_seq, void** handle) {
+  B200_REQUIRE(handle != nullptr, "gpt_create: null handle");
+  B200_REQUIRE(d_model % n_heads == 0 && d_model / n_heads == 64,
+               "gpt_create: the sm_100a attention kernels need head_dim == 64");
+  B200_REQUIRE(d_model % 8 == 0 && d_ff % 8 == 0 && d_model <= 2048,
+               "gpt_create: d_model/d_ff must be multiples of 8 and d_model <= 2048");
+  B200_REQUIRE(max_seq <= block_size && max_batch > 0 && max_seq > 0, "gpt_create: bad batch plan");
+  auto* g = new Gpt();
+  g->V = vocab;
+  g->Vp = int(engine::align_up(size_t(vocab), 128));
+  g->block = block_size; g->d = d_model; g->L = n_layers; g->H = n_heads; g->F = d_ff;
+  g->tied = tied ? 1 : 0;
+  g->maxB = max_batch; g->maxT = max_seq;
+  engine::plan_params(*g);
+  engine::plan_acts(*g);
+  *handle = g;
+  return 0;
+}
+
+extern "C" void llmtrain_b200_gpt_destroy(void* handle) { delete static_cast<Gpt*>(handle); }
+
+extern "C" size_t llmtrain_b200_gpt_param_elems(void* h) { return static_cast<Gpt*>(h)->n_params; }
+extern "C" size_t llmtrain_b200_gpt_shadow_elems(void* h) { return static_cast<Gpt*>(h)->n_shadow; }
+extern "C" size_t llmtrain_b200_gpt_activation_bytes(void* h) { return static_cast<Gpt*>(h)->act_bytes; }
+extern "C" int llmtrain_b200_gpt_padded_vocab(void* h) { return static_cast<Gpt*>(h)->Vp; }
+extern "C" size_t llmtrain_b200_gpt_logits_offset(void* h) { return static_cast<Gpt*>(h)->a_logits; }
+extern "C" size_t llmtrain_b200_gpt_loss_rows_offset(void* h) { return static_cast<Gpt*>(h)->a_loss_rows; }
+
+// Offset (elements) of a named tensor inside the fp32 arenas.  layer < 0 for the globals
+// (0 wpe, 1 ln_f.w, 2 ln_f.b, 3 token_embedding, 4 lm_head); otherwise which in [0,12) follows
+// the LayerOffsets field order.
+extern "C" long long llmtrain_b200_gpt_param_offset(void* h, int layer, int which) {
+  Gpt& g = *static_cast<Gpt*>(h);
+  if (layer < 0) {
+    switch (which) {
+      case 0: return (long long)g.wpe;
+      case 1: return (long long)g.lnf_w;
+      case 2: return (long long)g.lnf_b;
+      case 3: return (long long)g.wte;
+      case 4: return (long long)g.head;
+      default: return -1;
+    }
+  }
+  if (layer >= g.L || which < 0 || which >= 12) return -1;
+  const size_t* fields = reinterpret_cast<const size_t*>(&g.layer[layer]);
+  return (long long)fields[which];
+}
+
+extern "C" int llmtrain_b200_gpt_bind(void* h, float* p32, float* g32, void* p16, void* act,
+                                      size_t act_bytes) {
+  Gpt& g = *static_cast<Gpt*>(h);
+  B200_REQUIRE(act_bytes >= g.act_bytes, "gpt_bind: activation arena too small");
+  B200_REQUIRE(((reinterpret_cast<uintptr_t>(p32) | reinterpret_cast<uintptr_t>(g32) |
+                 reinterpret_cast<uintptr_t>(p16) | reinterpret_cast<uintptr_t>(act)) & 255) == 0,
+               "gpt_bind: arenas must be 256-byte aligned");
+  g.p32 = p32; g.g32 = g32;
+  g.p16 = static_cast<__nv_bfloat16*>(p16);
+  g.act = static_cast<uint8_t*>(act);
+  g.have_forward = false;
+  return 0;
+}
+
+// bf16 shadow <- fp32 master (after init / checkpoint load); zero the vocabulary padding rows.
+extern "C" int llmtrain_b200_gpt_refresh_shadow(void* h, llm_stream_t stream) {
+  Gpt& g = *static_cast<Gpt*>(h);
+  B200_REQUIRE(g.p32 != nullptr && g.p16 != nullptr, "gpt_refresh_shadow: arenas not bound");
+  auto s = reinterpret_cast<cudaStream_t>(stream);
+  if (llmtrain_b200_cast_f32_to_bf16(g.p32, g.p16, g.n_params, stream)) return 1;
+  if (g.n_shadow > g.n_params) {
+    B200_CHECK_CUDA(cudaMemsetAsync(g.p16 + g.n_params, 0, (g.n_shadow - g.n_params) * 2, s));
+  }
+  const size_t head_end = g.head + size_t(g.V) * g.d;
+  if (g.n_params > head_end) {  // alignment gap after the head inside n_params
+    B200_CHECK_CUDA(cudaMemsetAsync(g.p16 + head_end, 0, (g.n_params - head_end) * 2, s));
+  }
+  return 0;
+}
+
+// Forward pass.  mode 0: logits only (left in the arena as bf16 [B*T, Vp]).
+// mode 1: + per-row loss, loss_acc[0] += loss_scale * sum(rows).   mode 2: as 1, and the logits
+// are replaced by dlogits * grad_scale so that llmtrain_b200_gpt_backward can follow.
+extern "C" int llmtrain_b200_gpt_forward(void* h, const int64_t* ids, const int64_t* labels,
+                                         const uint8_t* key_mask, int B, int T, int mode,
+                                         float* loss_acc, float loss_scale, float grad_scale,
+                                         llm_stream_t stream) {
+  Gpt& g = *static_cast<Gpt*>(h);
+  B200_REQUIRE(g.act != nullptr, "gpt_forward: arenas not bound");
+  B200_REQUIRE(B >= 1 && B <= g.maxB && T >= 1 && T <= g.maxT, "gpt_forward: batch exceeds plan");
+  auto s = reinterpret_cast<cudaStream_t>(stream);
+  if (engine::forward(g, ids, key_mask, B, T, s)) return 1;
+  if (mode >= 1) {
+    B200_REQUIRE(labels != nullptr, "gpt_forward: labels required for the loss");
+    if (llmtrain_b200_cross_entropy(g.act + g.a_logits, labels, key_mask,
+                                    reinterpret_cast<float*>(g.act + g.a_loss_rows), loss_acc,
+                                    B * T, g.V, g.Vp, loss_scale, grad_scale, mode == 2 ? 1 : 0,
+                                    stream))
+      return 1;
+  }
+  if (mode != 2) g.have_forward = false;
+  return 0;
+}
+
+extern "C" int llmtrain_b200_gpt_backward(void* h, llm_stream_t stream) {
+  return engine::backward(*static_cast<Gpt*>(h), reinterpret_cast<cudaStream_t>(stream));
+}

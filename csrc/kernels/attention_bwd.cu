@@ -361,6 +361,7 @@ extern "C" int llmtrain_b200_attention_bwd(const void* qkv, const void* out, con
       static_cast<const __nv_bfloat16*>(dout), static_cast<const __nv_bfloat16*>(out), dsum, B, T,
       H);
   B200_CHECK_CUDA(cudaGetLastError());
+  B200_COUNT_LAUNCH(1);
 
   CUtensorMap tQKV, tDO, tDQKV, tDQ32;
   if (make_tmap_3d(&tQKV, static_cast<const __nv_bfloat16*>(qkv), B, T, 3 * d, 3 * d,
@@ -387,10 +388,12 @@ extern "C" int llmtrain_b200_attention_bwd(const void* qkv, const void* out, con
   dim3 grid(ceil_div(T, ab::BKV), H, B);
   ab::bwd_kernel<<<grid, ab::THREADS, ab::SMEM, stream>>>(tQKV, tDO, tDQKV, tDQ32, p);
   B200_CHECK_CUDA(cudaGetLastError());
+  B200_COUNT_LAUNCH(1);
 
   const size_t n = size_t(rows) * (d / 8);
   ab::dq_convert_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, stream>>>(
       dq32, static_cast<__nv_bfloat16*>(dqkv), rows, d);
   B200_CHECK_CUDA(cudaGetLastError());
+  B200_COUNT_LAUNCH(1);
   return 0;
 }

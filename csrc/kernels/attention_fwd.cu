@@ -310,5 +310,6 @@ extern "C" int llmtrain_b200_attention_fwd(const void* qkv, void* out, float* ls
   dim3 grid(ceil_div(T, attn::BQ), H, B);
   attn::fwd_kernel<<<grid, attn::FWD_THREADS, attn::FWD_SMEM, stream>>>(tQKV, tO, p);
   B200_CHECK_CUDA(cudaGetLastError());
+  B200_COUNT_LAUNCH(1);
   return 0;
 }

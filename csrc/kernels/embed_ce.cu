@@ -297,6 +297,7 @@ extern "C" int llmtrain_b200_embed_fwd(const int64_t* ids, const void* wte, cons
       ids, static_cast<const __nv_bfloat16*>(wte), static_cast<const __nv_bfloat16*>(wpe),
       static_cast<__nv_bfloat16*>(x), rows, T, d, vocab);
   B200_CHECK_CUDA(cudaGetLastError());
+  B200_COUNT_LAUNCH(1);
   return 0;
 }
 
@@ -309,9 +310,11 @@ extern "C" int llmtrain_b200_embed_bwd(const int64_t* ids, const void* dx, float
   ew::embed_bwd_wte_kernel<<<ceil_div(rows, 8), 256, 0, stream>>>(
       ids, static_cast<const __nv_bfloat16*>(dx), dwte, rows, d, vocab);
   B200_CHECK_CUDA(cudaGetLastError());
+  B200_COUNT_LAUNCH(1);
   ew::embed_bwd_wpe_kernel<<<ceil_div(T * (d / 4), 256), 256, 0, stream>>>(
       static_cast<const __nv_bfloat16*>(dx), dwpe, B, T, d);
   B200_CHECK_CUDA(cudaGetLastError());
+  B200_COUNT_LAUNCH(1);
   return 0;
 }
 
@@ -332,9 +335,11 @@ extern "C" int llmtrain_b200_cross_entropy(void* logits, const int64_t* labels,
                                                               ldv, grad_scale);
   }
   B200_CHECK_CUDA(cudaGetLastError());
+  B200_COUNT_LAUNCH(1);
   if (loss_acc != nullptr) {
     ew::loss_reduce_kernel<<<1, 1024, 0, stream>>>(loss_rows, rows, loss_scale, loss_acc);
     B200_CHECK_CUDA(cudaGetLastError());
+  B200_COUNT_LAUNCH(1);
   }
   return 0;
 }
@@ -353,9 +358,11 @@ extern "C" int llmtrain_b200_bias_grad(const void* dy, int ld, int M, int N, flo
   ew::colsum_partial_kernel<<<grid, ew::CS_WARPS * 32, 0, stream>>>(
       static_cast<const __nv_bfloat16*>(dy), ld, M, N, static_cast<float*>(scratch));
   B200_CHECK_CUDA(cudaGetLastError());
+  B200_COUNT_LAUNCH(1);
   ew::colsum_finish_kernel<<<ceil_div(N, 256), 256, 0, stream>>>(static_cast<float*>(scratch),
                                                                  splits, N, dbias);
   B200_CHECK_CUDA(cudaGetLastError());
+  B200_COUNT_LAUNCH(1);
   return 0;
 }
 
@@ -366,5 +373,6 @@ extern "C" int llmtrain_b200_cast_f32_to_bf16(const float* src, void* dst, size_
   ew::cast_kernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, stream>>>(
       src, static_cast<__nv_bfloat16*>(dst), n);
   B200_CHECK_CUDA(cudaGetLastError());
+  B200_COUNT_LAUNCH(1);
   return 0;
 }

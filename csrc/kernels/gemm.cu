@@ -339,6 +339,7 @@ int launch(const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tC,
   const int grid = tiles < sm_count() ? tiles : sm_count();
   kern<<<grid, NUM_THREADS, SMEM_BYTES, stream>>>(tA, tB, tC, tC2, p);
   B200_CHECK_CUDA(cudaGetLastError());
+  B200_COUNT_LAUNCH(1);
   return 0;
 }
 

@@ -213,6 +213,7 @@ extern "C" int llmtrain_b200_layernorm_fwd(const void* x, const float* gamma, co
       static_cast<const __nv_bfloat16*>(x), gamma, beta, static_cast<__nv_bfloat16*>(y), mean,
       rstd, rows, d);
   B200_CHECK_CUDA(cudaGetLastError());
+  B200_COUNT_LAUNCH(1);
   return 0;
 }
 
@@ -256,8 +257,10 @@ extern "C" int llmtrain_b200_layernorm_bwd(const void* dy, const void* x, const 
   }
 #undef B200_LN_BWD
   B200_CHECK_CUDA(cudaGetLastError());
+  B200_COUNT_LAUNCH(1);
   ln::finish_kernel<<<ceil_div(2 * d, 256), 256, 0, stream>>>(static_cast<float*>(scratch), grid,
                                                               d, dgamma, dbeta);
   B200_CHECK_CUDA(cudaGetLastError());
+  B200_COUNT_LAUNCH(1);
   return 0;
 }

@@ -155,9 +155,11 @@ extern "C" int llmtrain_b200_grad_sumsq(const float* g, size_t n, float* out, in
   optim::sumsq_partial_kernel<<<grid, optim::THREADS, 0, stream>>>(g, n,
                                                                    static_cast<float*>(scratch));
   B200_CHECK_CUDA(cudaGetLastError());
+  B200_COUNT_LAUNCH(1);
   optim::sumsq_finish_kernel<<<1, optim::THREADS, 0, stream>>>(static_cast<float*>(scratch), grid,
                                                                out, accumulate);
   B200_CHECK_CUDA(cudaGetLastError());
+  B200_COUNT_LAUNCH(1);
   return 0;
 }
 
@@ -183,5 +185,6 @@ extern "C" int llmtrain_b200_adamw(float* p, float* m, float* v, float* g, void*
   optim::adamw_kernel<<<grid, optim::THREADS, 0, stream>>>(
       p, m, v, g, static_cast<__nv_bfloat16*>(p_bf16), n, sumsq, norm_out, a, zero_grad);
   B200_CHECK_CUDA(cudaGetLastError());
+  B200_COUNT_LAUNCH(1);
   return 0;
 }

@@ -26,6 +26,8 @@ typedef struct CUstream_st* llm_stream_t;
 const char* llmtrain_b200_last_error(void);
 /* 1000*major + 10*minor of the library ABI. */
 int llmtrain_b200_abi_version(void);
+/* Kernels launched by this library so far in this process (monotonic). */
+long long llmtrain_b200_launch_count(void);
 
 /* ---------------------------------------------------------------------------------------------
  * GEMM (tcgen05 + TMEM + TMA).  Replaces nn.Linear forward and its autograd dgrad/wgrad:
@@ -118,6 +120,41 @@ int llmtrain_b200_attention_bwd(const void* qkv, const void* out, const void* do
                                 const float* lse, const uint8_t* key_mask, void* dqkv,
                                 void* scratch, size_t scratch_bytes, int B, int T, int H,
                                 int head_dim, llm_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * GPT runtime (csrc/engine/gpt_engine.cu).  Replaces autograd over GPT.forward + compute_loss
+ * (src/llmtrain/models/gpt.py:167-184,214-271; src/llmtrain/training/trainer.py:385-387).
+ *
+ * The engine plans memory but owns none: the caller allocates (e.g. as torch tensors, so that
+ * nn.Parameters can alias the master weights) and binds
+ *   p32 / g32 : fp32 [gpt_param_elems]      master weights / accumulated gradients
+ *   p16       : bf16 [gpt_shadow_elems]     weight shadow consumed by the GEMMs
+ *   act       : bytes [gpt_activation_bytes] activations + backward temporaries + scratch
+ * gpt_param_offset maps tensors to arena offsets: layer < 0 -> which = 0 position_embedding,
+ * 1 ln_f.weight, 2 ln_f.bias, 3 token_embedding, 4 lm_head (== 3 when tied); layer >= 0 ->
+ * which = 0..11 = ln_1.w ln_1.b qkv.w qkv.b out.w out.b ln_2.w ln_2.b fc.w fc.b proj.w proj.b.
+ * ------------------------------------------------------------------------------------------- */
+int llmtrain_b200_gpt_create(int vocab, int block_size, int d_model, int n_layers, int n_heads,
+                             int d_ff, int tied, int max_batch, int max_seq, void** handle);
+void llmtrain_b200_gpt_destroy(void* handle);
+size_t llmtrain_b200_gpt_param_elems(void* handle);
+size_t llmtrain_b200_gpt_shadow_elems(void* handle);
+size_t llmtrain_b200_gpt_activation_bytes(void* handle);
+int llmtrain_b200_gpt_padded_vocab(void* handle);
+size_t llmtrain_b200_gpt_logits_offset(void* handle);
+size_t llmtrain_b200_gpt_loss_rows_offset(void* handle);
+long long llmtrain_b200_gpt_param_offset(void* handle, int layer, int which);
+int llmtrain_b200_gpt_bind(void* handle, float* p32, float* g32, void* p16, void* act,
+                           size_t act_bytes);
+int llmtrain_b200_gpt_refresh_shadow(void* handle, llm_stream_t stream);
+/* mode 0: logits (bf16 [B*T, padded_vocab] at logits_offset).  mode 1: + loss rows and
+ * loss_acc[0] += loss_scale * sum.  mode 2: as 1 and logits := dlogits * grad_scale (then call
+ * gpt_backward).  key_mask [B,T] uint8 (1 = real token) or NULL; ids/labels int64 [B,T]. */
+int llmtrain_b200_gpt_forward(void* handle, const int64_t* ids, const int64_t* labels,
+                              const uint8_t* key_mask, int B, int T, int mode, float* loss_acc,
+                              float loss_scale, float grad_scale, llm_stream_t stream);
+/* g32 += d loss / d params for the last mode-2 forward. */
+int llmtrain_b200_gpt_backward(void* handle, llm_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -45,6 +45,8 @@ class TorchEngine(TrainEngine):
         self._adapter = adapter
         self._device = device
         self._max_grad_norm = max_grad_norm
+        if hasattr(model, "prefer_native"):
+            model.prefer_native = False  # this engine differentiates through torch ops
         self.model = model
         if data_parallel:
             ids = [device.index] if device.type == "cuda" and device.index is not None else None

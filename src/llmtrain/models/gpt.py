@@ -12,9 +12,12 @@ checkpoints interchange with the reference in both directions.
 * CPU (or MPS): plain torch ops, fp32 — this is the numerical oracle and the plumbing path.
 * CUDA (B200, sm_100a): the module hands its parameters to :class:`llmtrain.engine.b200.GPTEngine`,
   a C++ runtime that owns flat parameter/gradient/activation arenas and launches this repo's
-  hand-written tcgen05/TMA kernels (``csrc/``).  ``forward`` then returns logits produced by
-  those kernels and ``GPTAdapter.compute_loss`` runs the fused forward+backward.  There is no
-  silent eager fallback on CUDA: a missing native library is an error.
+  hand-written tcgen05/TMA kernels (``csrc/``).  ``forward`` (under ``no_grad``) returns logits
+  produced by those kernels and ``GPTAdapter.compute_loss`` runs the fused forward+backward.
+  A missing native library is an error, never a silent fallback.  The torch-op path remains
+  reachable on CUDA on purpose (``prefer_native = False`` / ``trainer.extra.engine: torch``):
+  it is the on-device oracle for the equivalence tests and the path taken for shapes the kernels
+  do not cover (head_dim != 64) or training with dropout > 0.
 
 The causal mask is never materialised on the device (the attention kernel applies it
 implicitly); the ``causal_mask`` tensors exist only inside ``state_dict()`` for format parity,
@@ -175,6 +178,8 @@ class GPT(nn.Module):
             self.lm_head.weight = self.token_embedding.weight
         self.reset_parameters()
         self._engine: Any | None = None  # created lazily once parameters sit on a CUDA device
+        #: engines that want the torch-op (autograd) path on CUDA, e.g. the oracle, clear this
+        self.prefer_native = True
 
     def reset_parameters(self) -> None:
         """GPT-2 style init; residual-path projections get the depth-scaled std."""
@@ -192,6 +197,20 @@ class GPT(nn.Module):
     @property
     def on_cuda(self) -> bool:
         return self.token_embedding.weight.is_cuda
+
+    def use_native(self) -> bool:
+        """True when calls should run on the sm_100a runtime instead of torch ops.
+
+        Dropout is not implemented in the native kernels yet, so a module that is in training
+        mode with ``dropout > 0`` stays on the torch path (the trainer logs this choice).
+        """
+        if not (self.on_cuda and self.prefer_native):
+            return False
+        if self.training and self.dropout_p > 0.0:
+            return False
+        from llmtrain.engine.b200 import supports
+
+        return supports(self)
 
     def native_engine(self, **options: Any) -> Any:
         """The C++/CUDA runtime bound to this module's parameters (CUDA only)."""
@@ -215,7 +234,7 @@ class GPT(nn.Module):
         _, seq = input_ids.shape
         if seq > self.block_size:
             raise ValueError(f"Input sequence length {seq} exceeds block size {self.block_size}.")
-        if self.on_cuda:
+        if self.use_native() and not torch.is_grad_enabled():
             return self.native_engine().logits(input_ids, attention_mask)
         positions = torch.arange(seq, device=input_ids.device)
         x = self.drop(self.token_embedding(input_ids) + self.position_embedding(positions)[None])
@@ -255,7 +274,7 @@ class GPTAdapter(ModelAdapter):
     ) -> tuple[torch.Tensor, dict[str, float]]:
         ids, labels, mask = validate_lm_batch(batch, min_seq_len=2)
         inner = getattr(model, "module", model)  # tolerate a DDP wrapper
-        if isinstance(inner, GPT) and inner.on_cuda:
+        if isinstance(inner, GPT) and inner.use_native():
             # Fused path: logits are never materialised; loss keeps an autograd edge to params.
             loss = inner.native_engine().loss(ids, labels, mask)
             return loss, {"loss": float(loss.item())}

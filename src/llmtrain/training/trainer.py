@@ -132,12 +132,18 @@ class Trainer:
         if self._device.type == "cuda" and choice in ("auto", "b200"):
             from llmtrain.engine.b200 import B200TrainEngine, supports
 
-            if supports(model):
+            blocker = None
+            if not supports(model):
+                blocker = f"model {type(model).__name__} is outside the kernels' shape coverage"
+            elif cfg.model.dropout > 0.0:
+                blocker = "model.dropout > 0 (the native kernels do not implement dropout yet)"
+            if blocker is None:
                 return B200TrainEngine(
                     model, cfg, device=self._device, ddp_state=self._ddp_state
                 )
             if choice == "b200":
-                raise ValueError(f"engine 'b200' does not support model {type(model).__name__}")
+                raise ValueError(f"engine 'b200' unavailable: {blocker}")
+            logger.warning("native B200 engine not used (%s); training on torch CUDA ops", blocker)
         return TorchEngine(
             model,
             self._adapter,

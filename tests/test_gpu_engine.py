@@ -1,0 +1,174 @@
+"""Native GPT runtime vs the torch-op oracle, and the CUDA trainer path end to end (B200 box)."""
+
+from __future__ import annotations
+
+import copy
+import math
+from pathlib import Path
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _cfg(tmp: Path | None = None, **over):
+    from llmtrain.config.schemas import RunConfig
+
+    payload = {
+        "run": {"name": "gpu-engine", "device": "cuda"},
+        "model": {"name": "gpt", "block_size": 128, "d_model": 128, "n_layers": 2, "n_heads": 2,
+                  "d_ff": 512, "dropout": 0.0, "vocab_size": 1000},
+        "data": {"name": "synthetic_text", "extra": {"pattern": "arith", "val_examples": 8}},
+        "trainer": {"max_steps": 30, "micro_batch_size": 4, "grad_accum_steps": 1,
+                    "warmup_steps": 0, "lr": 3e-3, "weight_decay": 0.0, "log_every_steps": 10,
+                    "eval_every_steps": 30, "save_every_steps": 10},
+        "ddp": {}, "mlflow": {"enabled": False}, "logging": {"log_to_file": False},
+        "output": {"root_dir": str(tmp) if tmp else "runs"},
+    }
+    for section, values in over.items():
+        payload[section].update(values)
+    return RunConfig.model_validate(payload)
+
+
+def _model(tie: bool = True, **kw):
+    from llmtrain.models.gpt import GPT
+
+    torch.manual_seed(0)
+    args = dict(vocab_size=1000, block_size=128, d_model=128, n_layers=2, n_heads=2, d_ff=512,
+                dropout=0.0, tie_embeddings=tie)
+    args.update(kw)
+    return GPT(**args)
+
+
+@pytest.mark.parametrize("tie", [True, False])
+@pytest.mark.parametrize("b,t", [(2, 128), (3, 50)])
+def test_native_loss_and_grads_match_torch_ops(tie: bool, b: int, t: int) -> None:
+    from llmtrain.models.gpt import GPTAdapter
+
+    oracle = _model(tie).cuda()
+    oracle.prefer_native = False
+    native = copy.deepcopy(oracle)
+    native.prefer_native = True
+    adapter = GPTAdapter()
+    ids = torch.randint(0, 1000, (b, t), device="cuda")
+    labels = torch.randint(0, 1000, (b, t), device="cuda")
+    batch = {"input_ids": ids, "labels": labels}
+
+    want, _ = adapter.compute_loss(oracle, batch)
+    want.backward()
+    got, metrics = adapter.compute_loss(native, batch)
+    assert native._engine is not None, "native runtime was not used"
+    got.backward()
+    assert abs(got.item() - want.item()) < 2e-2 * max(1.0, abs(want.item()))
+    assert abs(metrics["loss"] - got.item()) < 1e-6
+
+    ref = dict(oracle.named_parameters())
+    for name, p in native.named_parameters():
+        assert p.grad is not None, name
+        g_ref = ref[name].grad
+        denom = g_ref.abs().max().item() + 1e-8
+        err = (p.grad - g_ref).abs().max().item() / denom
+        assert err < 6e-2, f"{name}: rel err {err:.3e}"
+
+
+def test_native_logits_and_mask_path() -> None:
+    from llmtrain.models.gpt import GPTAdapter
+
+    oracle = _model().cuda().eval()
+    oracle.prefer_native = False
+    native = copy.deepcopy(oracle)
+    native.prefer_native = True
+    ids = torch.randint(0, 1000, (2, 100), device="cuda")
+    with torch.no_grad():
+        want = oracle(ids)
+        got = native(ids)
+    assert got.shape == want.shape == (2, 100, 1000)
+    assert (got - want).abs().max().item() < 5e-2 * want.abs().max().item()
+
+    mask = torch.ones(2, 100, dtype=torch.long, device="cuda")
+    mask[0, 70:] = 0
+    labels = torch.randint(0, 1000, (2, 100), device="cuda")
+    batch = {"input_ids": ids, "labels": labels, "attention_mask": mask}
+    adapter = GPTAdapter()
+    with torch.no_grad():
+        want_loss, _ = adapter.compute_loss(oracle, batch)
+        got_loss, _ = adapter.compute_loss(native, batch)
+    assert abs(got_loss.item() - want_loss.item()) < 2e-2 * abs(want_loss.item())
+
+
+def test_state_dict_keys_match_cpu_model_and_alias_is_kept() -> None:
+    cpu = _model()
+    gpu = copy.deepcopy(cpu).cuda()
+    gpu.native_engine()
+    assert list(gpu.state_dict().keys()) == list(cpu.state_dict().keys())
+    assert gpu.lm_head.weight is gpu.token_embedding.weight
+    gpu.load_state_dict(cpu.state_dict())
+    assert gpu._engine.bound_to(gpu)
+    for (n1, a), (n2, b_) in zip(cpu.state_dict().items(), gpu.state_dict().items(), strict=True):
+        assert n1 == n2 and torch.equal(a, b_.cpu()), n1
+
+
+def test_trainer_native_engine_learns_and_resumes(tmp_path: Path) -> None:
+    from llmtrain.engine.b200 import B200TrainEngine
+    from llmtrain.training import Trainer
+
+    cfg = _cfg(tmp_path)
+    trainer = Trainer(cfg, run_dir=tmp_path / "run")
+    assert isinstance(trainer._engine, B200TrainEngine)
+    result = trainer.fit()
+    assert result.first_step_loss is not None and math.isfinite(result.final_loss)
+    assert result.final_loss < 0.7 * result.first_step_loss
+    assert result.final_val_loss is not None and result.final_val_loss < result.first_step_loss
+    assert result.peak_memory > 0
+    ckpts = sorted((tmp_path / "run" / "checkpoints").glob("step_*.pt"))
+    assert [c.name for c in ckpts] == ["step_000010.pt", "step_000020.pt", "step_000030.pt"]
+
+    payload = torch.load(ckpts[-1], weights_only=False)
+    assert all(not v.is_cuda for v in payload["model_state_dict"].values())
+    state0 = payload["optimizer_state_dict"]["state"][0]
+    assert set(state0) == {"step", "exp_avg", "exp_avg_sq"} and float(state0["step"]) == 30.0
+
+    # resume from step 20 and land (almost) where the uninterrupted run landed
+    again = Trainer(cfg, run_dir=tmp_path / "run2")
+    resumed = again.fit(resume_from=ckpts[1])
+    assert resumed.resumed_from_step == 20
+    assert abs(resumed.final_loss - result.final_loss) < 5e-2 * max(1.0, result.final_loss)
+
+
+def test_checkpoint_from_gpu_loads_into_cpu_model(tmp_path: Path) -> None:
+    from llmtrain.training import Trainer
+
+    cfg = _cfg(tmp_path, trainer={"max_steps": 2, "save_every_steps": 2})
+    Trainer(cfg, run_dir=tmp_path / "r").fit()
+    payload = torch.load(tmp_path / "r" / "checkpoints" / "step_000002.pt", weights_only=False)
+    cpu = _model()
+    cpu.load_state_dict(payload["model_state_dict"])  # strict: includes causal_mask keys
+    opt = torch.optim.AdamW(cpu.parameters())
+    opt.load_state_dict(payload["optimizer_state_dict"])
+
+
+def test_grad_accumulation_matches_big_batch() -> None:
+    """accum k over k micro-batches == one batch k times larger (same tokens)."""
+    from llmtrain.engine.b200 import GPTEngine
+
+    base = _model().cuda()
+    ids = torch.randint(0, 1000, (4, 64), device="cuda")
+    labels = torch.randint(0, 1000, (4, 64), device="cuda")
+
+    def grads(chunks: int) -> torch.Tensor:
+        m = copy.deepcopy(base)
+        eng: GPTEngine = m.native_engine(max_batch=4, max_seq=64)
+        g = eng.ensure_grad_arena()
+        eng.refresh_shadow()
+        acc = torch.zeros(1, device="cuda")
+        for part_ids, part_lab in zip(ids.chunk(chunks), labels.chunk(chunks), strict=True):
+            scale = 1.0 / (part_ids.numel() * chunks)
+            eng.run_forward(part_ids.contiguous(), part_lab.contiguous(), None, mode=2,
+                            loss_acc=acc, loss_scale=scale, grad_scale=scale)
+            eng.run_backward()
+        torch.cuda.synchronize()
+        return g.clone()
+
+    g1, g2 = grads(1), grads(2)
+    assert (g1 - g2).abs().max().item() < 2e-2 * g1.abs().max().item()
