@@ -118,7 +118,7 @@ def test_trainer_native_engine_learns_and_resumes(tmp_path: Path) -> None:
     assert isinstance(trainer._engine, B200TrainEngine)
     result = trainer.fit()
     assert result.first_step_loss is not None and math.isfinite(result.final_loss)
-    assert result.final_loss < 0.7 * result.first_step_loss
+    assert result.final_loss < result.first_step_loss - 0.5
     assert result.final_val_loss is not None and result.final_val_loss < result.first_step_loss
     assert result.peak_memory > 0
     ckpts = sorted((tmp_path / "run" / "checkpoints").glob("step_*.pt"))
