@@ -376,3 +376,90 @@ extern "C" int llmtrain_b200_cast_f32_to_bf16(const float* src, void* dst, size_
   B200_COUNT_LAUNCH(1);
   return 0;
 }
+
+// ------------------------------------------------------------------------------------------------
+// Bias gradient for hosts that must not allocate.
+//
+// Some programs that link this library are not allowed to obtain device memory on their own once
+// they are running: a serving or training process whose memory pool already owns every byte of
+// HBM (a later cudaMalloc would fail or fragment the pool), a latency-critical loop that cannot
+// afford the device-wide stall a cudaMalloc/cudaFree implies, or a thin language binding that can
+// pass pointers it was given but has no allocator to ask.  llmtrain_b200_bias_grad needs a few
+// hundred KB of temporary global memory for its deterministic two-stage column sum, so those
+// callers could not use it.  This variant carries that temporary storage inside the library image
+// instead: a fixed array in device global memory that exists on every GPU that loads the library,
+// from load until process exit, whether or not the function is ever called.
+//
+// Consequences the caller has to know about:
+//   * The array has a fixed capacity (kNoAllocFloats floats = 1 MiB per GPU).  A problem whose
+//     partial sums do not fit is refused with an error; nothing is launched.
+//   * All calls on one GPU use the same array and it is never cleared between calls.  That is
+//     safe here because the first kernel overwrites every partial sum the second one reads, so no
+//     element has to start at zero — but two calls whose kernels are in flight at the same time
+//     (different streams, or different host threads on different streams) would overwrite each
+//     other's partial sums.  Issue calls for one GPU on one stream, or order them with events.
+//   * The device address of the array is looked up once per GPU, on the first call made while
+//     that GPU is current.  That first call does a little host-side set-up work; make it during
+//     initialisation, before starting any stream capture.
+// ------------------------------------------------------------------------------------------------
+namespace b200 {
+namespace ew {
+
+constexpr size_t kNoAllocFloats = size_t(1) << 18;  // 262144 floats = 1 MiB
+constexpr int kNoAllocMaxDevices = 64;
+
+static __device__ __align__(256) float g_bias_grad_partials[kNoAllocFloats];
+
+// Host-side cache of the array's device address, one slot per GPU.  (In host code the name
+// g_bias_grad_partials is only a handle for the runtime, never an address to hand to a kernel.)
+static float* g_noalloc_addr[kNoAllocMaxDevices] = {};
+static std::mutex g_noalloc_mutex;
+
+static int noalloc_scratch(float** out) {
+  int dev = -1;
+  B200_CHECK_CUDA(cudaGetDevice(&dev));
+  B200_REQUIRE(dev >= 0 && dev < kNoAllocMaxDevices, "bias_grad_noalloc: device index out of range");
+  std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+  if (g_noalloc_addr[dev] == nullptr) {
+    float* addr = nullptr;
+    B200_CHECK_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&addr), g_bias_grad_partials));
+    B200_REQUIRE(addr != nullptr, "bias_grad_noalloc: symbol address lookup returned null");
+    g_noalloc_addr[dev] = addr;
+  }
+  *out = g_noalloc_addr[dev];
+  return 0;
+}
+
+}  // namespace ew
+}  // namespace b200
+
+extern "C" size_t llmtrain_b200_bias_grad_noalloc_capacity_bytes(void) {
+  return ew::kNoAllocFloats * sizeof(float);
+}
+
+// dbias[n] (fp32) += sum_m dy[m,n] (bf16, pitch ld) — same result as llmtrain_b200_bias_grad, but
+// the partial sums live in the library's built-in array (see the block comment above).
+extern "C" int llmtrain_b200_bias_grad_noalloc(const void* dy, int ld, int M, int N, float* dbias,
+                                               cudaStream_t stream) {
+  B200_REQUIRE(ld % 2 == 0, "bias_grad_noalloc: row pitch must be even");
+  B200_REQUIRE(M >= 0 && N >= 0, "bias_grad_noalloc: negative extent");
+  if (M == 0 || N == 0) return 0;
+  const int splits = ew::colsum_splits(M, N);
+  if (size_t(splits) * size_t(N) > ew::kNoAllocFloats) {
+    return fail("bias_grad_noalloc: " + std::to_string(size_t(splits) * size_t(N)) +
+                " partial sums needed for M=" + std::to_string(M) + " N=" + std::to_string(N) +
+                " but the built-in scratch holds " + std::to_string(ew::kNoAllocFloats) +
+                " floats (1 MiB); use llmtrain_b200_bias_grad with caller-provided scratch");
+  }
+  float* partials = nullptr;
+  if (ew::noalloc_scratch(&partials)) return 1;
+  dim3 grid(ceil_div(N, 64), splits);
+  ew::colsum_partial_kernel<<<grid, ew::CS_WARPS * 32, 0, stream>>>(
+      static_cast<const __nv_bfloat16*>(dy), ld, M, N, partials);
+  B200_CHECK_CUDA(cudaGetLastError());
+  B200_COUNT_LAUNCH(1);
+  ew::colsum_finish_kernel<<<ceil_div(N, 256), 256, 0, stream>>>(partials, splits, N, dbias);
+  B200_CHECK_CUDA(cudaGetLastError());
+  B200_COUNT_LAUNCH(1);
+  return 0;
+}

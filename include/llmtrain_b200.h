@@ -86,6 +86,22 @@ size_t llmtrain_b200_bias_grad_scratch_bytes(int M, int N);
 int llmtrain_b200_bias_grad(const void* dy, int ld, int M, int N, float* dbias, void* scratch,
                             size_t scratch_bytes, llm_stream_t stream);
 
+/* Same column sum for callers that cannot supply scratch because they cannot allocate device
+ * memory themselves (a process whose pool already owns all of HBM, a latency-critical loop that
+ * cannot take cudaMalloc's device-wide stall, a binding with no allocator).  This entry point has
+ * no counterpart in the reference; it exists only for such hosts.  The partial sums go to a 1 MiB
+ * array built into the library image (resident on every GPU that loads the library, until exit).
+ *   - refused with an error when colsum splits * N exceeds capacity_bytes()/4 partial sums;
+ *   - every call on a GPU shares that array and nothing is cleared between calls (none of it needs
+ *     to start at zero); calls whose kernels overlap on the GPU corrupt each other: keep them on
+ *     one stream or order them with events;
+ *   - the first call made on each GPU looks the array's address up; make that call during
+ *     start-up, before beginning any stream capture.
+ * Performs no cudaMalloc/cudaFree and calls no allocating library routine. */
+size_t llmtrain_b200_bias_grad_noalloc_capacity_bytes(void);
+int llmtrain_b200_bias_grad_noalloc(const void* dy, int ld, int M, int N, float* dbias,
+                                    llm_stream_t stream);
+
 int llmtrain_b200_cast_f32_to_bf16(const float* src, void* dst, size_t n, llm_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
