@@ -172,6 +172,30 @@ int llmtrain_b200_gpt_forward(void* handle, const int64_t* ids, const int64_t* l
 /* g32 += d loss / d params for the last mode-2 forward. */
 int llmtrain_b200_gpt_backward(void* handle, llm_stream_t stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * NVLink peer-memory communicator (csrc/comm/nvl.cu).  Replaces DistributedDataParallel's bucketed
+ * all-reduce + clip_grad_norm_ + AdamW.step (src/llmtrain/training/trainer.py:87-91,377-394).
+ * One process per GPU, 2..8 ranks on one NVLink domain.  create() cudaMallocs symmetric buffers
+ * for an arena of n fp32 elements (n % 8 == 0); export() writes 3 cudaIpcMemHandle_t (192 bytes)
+ * to host memory; the caller all-gathers those rank-major and passes them to connect().
+ *   nvl_step:      g (fp32 local gradient sum) -> bf16 wire -> rank-ordered reduce-scatter ->
+ *                  gather fused with *grad_scale, global-norm clip, AdamW on p/m/v, bf16 shadow
+ *                  refresh, g := 0.  Replicas stay bit-identical.
+ *   nvl_allreduce: out = scale * sum_r bf16(in_r)   (tests, bandwidth sweep)
+ * A peer that never arrives trips a wall-clock watchdog (timeout_sec) and traps with a message.
+ * ------------------------------------------------------------------------------------------- */
+int llmtrain_b200_nvl_create(int rank, int world, size_t n, double timeout_sec, void** handle);
+int llmtrain_b200_nvl_export(void* handle, void* h_out_192_bytes);
+int llmtrain_b200_nvl_connect(void* handle, const void* h_all_handles);
+void llmtrain_b200_nvl_destroy(void* handle);
+int llmtrain_b200_nvl_barrier(void* handle, llm_stream_t stream);
+int llmtrain_b200_nvl_step(void* handle, float* g, float* p, float* m, float* v, void* p16,
+                           float* norm_out, float lr, float beta1, float beta2, float eps,
+                           float weight_decay, int step, float grad_scale, float max_norm,
+                           llm_stream_t stream);
+int llmtrain_b200_nvl_allreduce(void* handle, float* in, float* out, float scale,
+                                llm_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,12 +1,19 @@
 """Gradient reduction + optimiser step across ranks.
 
-``NcclFallback`` is the transport used across nodes (or whenever peer mapping is impossible):
-one NCCL all-reduce over the flat fp32 gradient arena followed by the fused clip + AdamW pass.
-The NVLink peer-memory path (``try_create``) replaces both with this repo's own kernels.
+* :class:`NvlComm` — this repo's NVLink / NVSwitch peer-memory path (``csrc/comm/nvl.cu``): CUDA-IPC
+  mapped symmetric buffers, flag barriers, rank-ordered reduce-scatter, and an all-gather that is
+  fused with average + global-norm clip + AdamW + bf16 shadow refresh.  It replaces the c10d
+  Reducer + ProcessGroup all-reduce the reference rents through ``DistributedDataParallel``
+  (`src/llmtrain/training/trainer.py:87-91,377-394`).  The torch process group is used only to
+  exchange the IPC handles.
+* :class:`NcclFallback` — the transport across nodes, or whenever peers cannot map each other (pods
+  without a shared IPC namespace, no P2P): one NCCL all-reduce over the flat fp32 gradient arena
+  followed by the same fused optimiser kernel.
 """
 
 from __future__ import annotations
 
+import ctypes
 import logging
 from typing import Any
 
@@ -14,9 +21,12 @@ import torch
 import torch.distributed as dist
 
 from llmtrain.ops import kernels as K
+from llmtrain.ops import native
+from llmtrain.ops.native import check, ptr, stream_handle
 
 logger = logging.getLogger(__name__)
 
+_IPC_HANDLE_BYTES = 64
 _live: list[Any] = []
 
 
@@ -37,12 +47,123 @@ class NcclFallback:
         K.adamw(g.p32, m, v, g.g32, g.p16, sumsq=sumsq, norm_out=norm,
                 grad_scale=1.0 / self._world, **hyper)
 
+    def close(self) -> None:
+        return None
+
+
+def _peers_reachable(world: int) -> bool:
+    """All ranks on this host, each with P2P access to every other visible device?"""
+    count = torch.cuda.device_count()
+    if count < world:
+        return False
+    me = torch.cuda.current_device()
+    return all(d == me or torch.cuda.can_device_access_peer(me, d) for d in range(world))
+
+
+class NvlComm:
+    """Peer-memory communicator over an arena of ``n`` fp32 elements."""
+
+    name = "nvl-p2p(pack-bf16 -> reduce-scatter -> gather+adamw)"
+
+    def __init__(self, n: int, *, rank: int, world: int, timeout_s: float) -> None:
+        self._lib = native.lib()
+        self._n = n
+        self.rank, self.world = rank, world
+        handle = ctypes.c_void_p()
+        check(
+            self._lib.llmtrain_b200_nvl_create(
+                ctypes.c_int(rank), ctypes.c_int(world), ctypes.c_size_t(n),
+                ctypes.c_double(float(timeout_s)), ctypes.byref(handle),
+            ),
+            "nvl_create",
+        )
+        self._handle = handle
+        mine = (ctypes.c_ubyte * (3 * _IPC_HANDLE_BYTES))()
+        check(self._lib.llmtrain_b200_nvl_export(handle, mine), "nvl_export")
+        gathered: list[bytes | None] = [None] * world
+        dist.all_gather_object(gathered, bytes(mine))
+        blob = b"".join(g for g in gathered if g is not None)
+        if len(blob) != world * 3 * _IPC_HANDLE_BYTES:
+            raise RuntimeError("nvl: IPC handle exchange returned an unexpected payload size")
+        everyone = (ctypes.c_ubyte * len(blob)).from_buffer_copy(blob)
+        check(self._lib.llmtrain_b200_nvl_connect(handle, everyone), "nvl_connect")
+        dist.barrier()  # every rank has mapped every peer before the first kernel runs
+        _live.append(self)
+
+    def barrier(self) -> None:
+        check(self._lib.llmtrain_b200_nvl_barrier(self._handle, stream_handle()), "nvl_barrier")
+
+    def allreduce(self, src: torch.Tensor, dst: torch.Tensor, scale: float = 1.0) -> None:
+        """``dst = scale * sum_r bf16(src_r)`` (fp32 in/out, bf16 on the wire)."""
+        assert src.numel() == self._n and dst.numel() == self._n
+        check(
+            self._lib.llmtrain_b200_nvl_allreduce(self._handle, ptr(src), ptr(dst),
+                                                  ctypes.c_float(scale), stream_handle()),
+            "nvl_allreduce",
+        )
+
+    def step(self, g: torch.Tensor, p: torch.Tensor, m: torch.Tensor, v: torch.Tensor,
+             p16: torch.Tensor, norm: torch.Tensor | None, hyper: dict[str, Any]) -> None:
+        check(
+            self._lib.llmtrain_b200_nvl_step(
+                self._handle, ptr(g), ptr(p), ptr(m), ptr(v), ptr(p16), ptr(norm),
+                ctypes.c_float(hyper["lr"]), ctypes.c_float(hyper["beta1"]),
+                ctypes.c_float(hyper["beta2"]), ctypes.c_float(hyper["eps"]),
+                ctypes.c_float(hyper["weight_decay"]), ctypes.c_int(hyper["step"]),
+                ctypes.c_float(1.0 / self.world), ctypes.c_float(hyper["max_norm"]),
+                stream_handle(),
+            ),
+            "nvl_step",
+        )
+
+    def close(self) -> None:
+        if self._handle:
+            self._lib.llmtrain_b200_nvl_destroy.argtypes = [ctypes.c_void_p]
+            self._lib.llmtrain_b200_nvl_destroy.restype = None
+            self._lib.llmtrain_b200_nvl_destroy(self._handle)
+            self._handle = ctypes.c_void_p()
+
+
+class _NvlTrainComm:
+    """Adapter with the ``reduce_and_step`` face the train engine expects."""
+
+    def __init__(self, gpt: Any, comm: NvlComm) -> None:
+        self._gpt, self._comm = gpt, comm
+        self.name = comm.name
+
+    def reduce_and_step(self, m: torch.Tensor, v: torch.Tensor, sumsq: torch.Tensor,
+                        norm: torch.Tensor, hyper: dict[str, Any]) -> None:
+        del sumsq  # the global norm is assembled from the owners' slice partials on the device
+        g = self._gpt
+        self._comm.step(g.g32, g.p32, m, v, g.p16, norm, hyper)
+
+    def close(self) -> None:
+        self._comm.close()
+
 
 def try_create(gpt: Any, m: torch.Tensor, v: torch.Tensor, *, rank: int, world: int,
                device: torch.device, timeout_s: int) -> Any | None:
     """Build the peer-memory communicator, or ``None`` when the ranks cannot map each other."""
-    del gpt, m, v, rank, world, device, timeout_s
-    return None
+    del m, v, device
+    if not 2 <= world <= 8:
+        return None
+    ok = torch.tensor([1 if _peers_reachable(world) else 0], device="cuda")
+    dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+    if int(ok.item()) == 0:
+        return None
+    try:
+        comm = NvlComm(gpt.n_params, rank=rank, world=world, timeout_s=timeout_s)
+    except Exception as exc:
+        logger.warning("nvl communicator could not be created: %s", exc)
+        failed = torch.tensor([1], device="cuda")
+        dist.all_reduce(failed, op=dist.ReduceOp.MAX)
+        return None
+    failed = torch.tensor([0], device="cuda")
+    dist.all_reduce(failed, op=dist.ReduceOp.MAX)
+    if int(failed.item()):
+        comm.close()
+        return None
+    return _NvlTrainComm(gpt, comm)
 
 
 def shutdown() -> None:

@@ -1,0 +1,122 @@
+"""Worker for the multi-GPU NVLink tests (run under torch.distributed.run, one rank per GPU)."""
+
+from __future__ import annotations
+
+import os
+import sys
+from pathlib import Path
+
+import torch
+import torch.distributed as dist
+
+ROOT = Path(__file__).resolve().parents[1]
+sys.path.insert(0, str(ROOT / "src"))
+
+
+def _check_allreduce(comm, rank: int, world: int) -> None:
+    n = comm._n
+    torch.manual_seed(100 + rank)
+    src = torch.randn(n, device="cuda") * (rank + 1)
+    out = torch.empty(n, device="cuda")
+    for scale in (1.0, 1.0 / world):  # twice in a row: epochs / buffer reuse
+        comm.allreduce(src, out, scale)
+        torch.cuda.synchronize()
+        rounded = src.to(torch.bfloat16).float()
+        parts = [torch.empty_like(rounded) for _ in range(world)]
+        dist.all_gather(parts, rounded)
+        want = torch.zeros_like(rounded)
+        for part in parts:  # rank order, fp32 — exactly what the kernel does
+            want += part
+        want *= scale
+        assert torch.equal(out, want), f"rank {rank}: allreduce mismatch {(out - want).abs().max()}"
+
+
+def _check_step(comm, rank: int, world: int) -> None:
+    from llmtrain.ops import kernels as K
+
+    n = comm._n
+    torch.manual_seed(7)
+    p0 = torch.randn(n, device="cuda")
+    p, m, v = p0.clone(), torch.zeros(n, device="cuda"), torch.zeros(n, device="cuda")
+    p16 = torch.empty(n, device="cuda", dtype=torch.bfloat16)
+    norm = torch.zeros(1, device="cuda")
+    ref_p, ref_m, ref_v = p0.clone(), torch.zeros(n, device="cuda"), torch.zeros(n, device="cuda")
+    ref_p16 = torch.empty_like(p16)
+    sumsq, ref_norm = torch.zeros(1, device="cuda"), torch.zeros(1, device="cuda")
+    for step in (1, 2, 3):
+        torch.manual_seed(1000 * step + rank)
+        g = torch.randn(n, device="cuda") * 0.01 * (rank + 1)
+        hyper = dict(lr=1e-2, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=0.1, step=step,
+                     max_norm=1.0)
+        # reference: gather everyone's bf16-rounded gradient, average, single-GPU fused AdamW
+        rounded = g.to(torch.bfloat16).float()
+        parts = [torch.empty_like(rounded) for _ in range(world)]
+        dist.all_gather(parts, rounded)
+        total = torch.zeros_like(rounded)
+        for part in parts:
+            total += part
+        K.grad_sumsq(total, sumsq)
+        K.adamw(ref_p, ref_m, ref_v, total, ref_p16, sumsq=sumsq, norm_out=ref_norm,
+                grad_scale=1.0 / world, **hyper)
+        comm.step(g, p, m, v, p16, norm, hyper)
+        torch.cuda.synchronize()
+        assert g.abs().max().item() == 0.0, "gradient arena was not zeroed"
+        assert abs(norm.item() / ref_norm.item() - 1) < 1e-4, (norm.item(), ref_norm.item())
+        assert (p - ref_p).abs().max().item() < 1e-5
+        assert torch.equal(p16, p.to(torch.bfloat16))
+    # replicas must be bit-identical
+    mine = p.clone()
+    others = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(others, mine)
+    assert all(torch.equal(others[0], o) for o in others), "replicas diverged"
+
+
+def _check_trainer(rank: int, world: int) -> None:
+    from llmtrain.config.schemas import RunConfig
+    from llmtrain.distributed import DDPState
+    from llmtrain.training import Trainer
+
+    cfg = RunConfig.model_validate({
+        "run": {"name": "nvl-trainer", "device": "cuda"},
+        "model": {"name": "gpt", "block_size": 128, "d_model": 128, "n_layers": 2, "n_heads": 2,
+                  "d_ff": 512, "dropout": 0.0, "vocab_size": 1000},
+        "data": {"name": "synthetic_text", "extra": {"pattern": "arith"}},
+        "trainer": {"max_steps": 20, "micro_batch_size": 4, "grad_accum_steps": 2,
+                    "warmup_steps": 0, "lr": 3e-3, "weight_decay": 0.0, "log_every_steps": 5},
+        "ddp": {"enabled": True, "backend": "nvl"},
+        "mlflow": {"enabled": False}, "logging": {"log_to_file": False}, "output": {},
+    })
+    state = DDPState(rank=rank, world_size=world, local_rank=rank, is_main=rank == 0)
+    trainer = Trainer(cfg, ddp_state=state)
+    comm = trainer._engine._comm
+    assert comm is not None and comm.name.startswith("nvl"), getattr(comm, "name", None)
+    result = trainer.fit()
+    assert result.final_loss < result.first_step_loss - 0.3, (result.first_step_loss, result.final_loss)
+    flat = trainer._engine._gpt.p32.clone()
+    others = [torch.empty_like(flat) for _ in range(world)]
+    dist.all_gather(others, flat)
+    assert all(torch.equal(others[0], o) for o in others), "replicas diverged after training"
+
+
+def main() -> int:
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
+    dist.init_process_group("cpu:gloo,cuda:nccl")
+    try:
+        from llmtrain.parallel.nvl import NvlComm, shutdown
+
+        comm = NvlComm(8 * 1024 * 1024 + 64, rank=rank, world=world, timeout_s=60)
+        _check_allreduce(comm, rank, world)
+        _check_step(comm, rank, world)
+        _check_trainer(rank, world)
+        shutdown()
+        dist.barrier()
+        if rank == 0:
+            print("NVL_WORKER_OK")
+    finally:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

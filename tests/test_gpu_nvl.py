@@ -1,0 +1,33 @@
+"""NVLink peer-memory communicator: needs >= 2 GPUs on the box (skipped otherwise)."""
+
+from __future__ import annotations
+
+import socket
+import subprocess
+import sys
+from pathlib import Path
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _free_port() -> int:
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return int(s.getsockname()[1])
+
+
+@pytest.mark.parametrize("world", [2])
+def test_nvl_allreduce_step_and_trainer(world: int) -> None:
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    worker = Path(__file__).with_name("_nvl_worker.py")
+    proc = subprocess.run(
+        [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+         "--master-addr", "127.0.0.1", "--master-port", str(_free_port()), str(worker)],
+        capture_output=True, text=True, timeout=600, check=False,
+    )
+    assert proc.returncode == 0, proc.stdout[-3000:] + proc.stderr[-3000:]
+    assert "NVL_WORKER_OK" in proc.stdout
