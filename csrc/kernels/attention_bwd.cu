@@ -295,23 +295,34 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
   if (warp == 5) tmem_dealloc(tmem, TMEM_COLS);
 }
 
-// D[b,h,t] = sum_c dO[b,t,h*64+c] * O[b,t,h*64+c]; one warp per (row, head).
+// D[b,h,t] = sum_c dO[b,t,h*64+c] * O[b,t,h*64+c]; 8 lanes x 16 B cover one head (64 bf16), so a
+// warp handles 4 (row, head) pairs per load instruction.
 __global__ void dsum_kernel(const __nv_bfloat16* __restrict__ dO,
                             const __nv_bfloat16* __restrict__ O, float* __restrict__ dsum, int B,
                             int T, int H) {
-  const int gw = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  const int lane = threadIdx.x & 31;
-  const int total = B * T * H;
-  if (gw >= total) return;
-  const int row = gw / H, h = gw - row * H;
-  const size_t off = size_t(row) * H * HD + h * HD + lane * 2;
-  const float2 a = unpack_bf16x2(__ldg(reinterpret_cast<const uint32_t*>(dO + off)));
-  const float2 o = unpack_bf16x2(__ldg(reinterpret_cast<const uint32_t*>(O + off)));
-  float v = a.x * o.x + a.y * o.y;
+  const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long pair = gid >> 3;  // (row, head) index
+  const int sub = int(gid & 7);
+  const long long total = (long long)B * T * H;
+  float v = 0.f;
+  if (pair < total) {
+    const size_t off = size_t(pair) * HD + sub * 8;  // [row][h][64] is contiguous in (row, h)
+    const uint4 a = __ldg(reinterpret_cast<const uint4*>(dO + off));
+    const uint4 o = __ldg(reinterpret_cast<const uint4*>(O + off));
+    const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, ow[4] = {o.x, o.y, o.z, o.w};
 #pragma unroll
-  for (int s = 16; s > 0; s >>= 1) v += __shfl_xor_sync(0xffffffffu, v, s);
-  if (lane == 0) {
-    const int b = row / T, t = row - b * T;
+    for (int j = 0; j < 4; ++j) {
+      const float2 x = unpack_bf16x2(aw[j]), y = unpack_bf16x2(ow[j]);
+      v += x.x * y.x + x.y * y.y;
+    }
+  }
+  v += __shfl_xor_sync(0xffffffffu, v, 4);
+  v += __shfl_xor_sync(0xffffffffu, v, 2);
+  v += __shfl_xor_sync(0xffffffffu, v, 1);
+  if (sub == 0 && pair < total) {
+    const long long row = pair / H;
+    const int h = int(pair - row * H);
+    const int b = int(row / T), t = int(row - (long long)b * T);
     dsum[(size_t(b) * H + h) * T + t] = v;
   }
 }
@@ -357,7 +368,7 @@ extern "C" int llmtrain_b200_attention_bwd(const void* qkv, const void* out, con
   B200_CHECK_CUDA(cudaMemsetAsync(dq32, 0, dq_bytes, stream));
 
   const int rows = B * T;
-  ab::dsum_kernel<<<ceil_div(rows * H, 8), 256, 0, stream>>>(
+  ab::dsum_kernel<<<ceil_div(rows * H * 8, 256), 256, 0, stream>>>(
       static_cast<const __nv_bfloat16*>(dout), static_cast<const __nv_bfloat16*>(out), dsum, B, T,
       H);
   B200_CHECK_CUDA(cudaGetLastError());

@@ -90,20 +90,29 @@ __global__ void embed_bwd_wpe_kernel(const __nv_bfloat16* __restrict__ dx,
 }
 
 // ------------------------------------------------------------------------------------------------
-// Fused cross-entropy: one CTA per row, the whole (padded) vocabulary row is read ONCE into
-// registers, loss_row = lse - logit[label], and (optionally) the row is overwritten in place with
-// dlogits = (softmax - onehot) * grad_scale * row_weight.  Padded columns [V, ldv) get zero.
+// Fused cross-entropy: one CTA per row.  Pass 1 streams the (padded) vocabulary row once from HBM
+// keeping an online (max, sum-exp) pair per thread; loss_row = lse - logit[label].  Pass 2
+// (training only) re-reads the row — 100 KB, still L2-resident — and overwrites it in place with
+// dlogits = (softmax - onehot) * grad_scale.  Padded columns [V, ldv) get zero.  Few registers and
+// 256-thread CTAs keep 8 rows in flight per SM so the loads of one row hide the math of another.
 // ------------------------------------------------------------------------------------------------
-constexpr int CE_THREADS = 512;
-constexpr int CE_MAX_VEC = 16;  // uint4 per thread -> ld up to 512*16*8 = 65536 columns
+constexpr int CE_THREADS = 256;
+
+__device__ __forceinline__ void online_merge(float& m, float& s, float m2, float s2) {
+  const float mn = fmaxf(m, m2);
+  const float a = (m == -INFINITY) ? 0.f : __expf(m - mn);
+  const float b = (m2 == -INFINITY) ? 0.f : __expf(m2 - mn);
+  s = s * a + s2 * b;
+  m = mn;
+}
 
 template <bool WRITE_GRAD>
 __global__ void __launch_bounds__(CE_THREADS)
 ce_kernel(__nv_bfloat16* __restrict__ logits, const int64_t* __restrict__ labels,
           const uint8_t* __restrict__ row_valid, float* __restrict__ loss_rows, int V, int ldv,
           float grad_scale) {
-  __shared__ float red[CE_THREADS / 32];
-  __shared__ float bcast;
+  __shared__ float red_m[CE_THREADS / 32], red_s[CE_THREADS / 32];
+  __shared__ float bc_m, bc_s;
   const int row = blockIdx.x;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   uint4* rp = reinterpret_cast<uint4*>(logits + size_t(row) * ldv);
@@ -111,92 +120,71 @@ ce_kernel(__nv_bfloat16* __restrict__ logits, const int64_t* __restrict__ labels
   const bool valid = row_valid == nullptr || row_valid[row] != 0;
   const int label = static_cast<int>(labels[row]);
 
-  uint4 v[CE_MAX_VEC];
-  float mx = -INFINITY;
+  float m = -INFINITY, ssum = 0.f;
+  for (int c = tid; c < nvec; c += CE_THREADS) {
+    const uint4 u = rp[c];
+    const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+    float f[8];
 #pragma unroll
-  for (int i = 0; i < CE_MAX_VEC; ++i) {
-    const int c = tid + i * CE_THREADS;
-    if (c < nvec) {
-      v[i] = rp[c];
-      const uint32_t w[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
+    for (int j = 0; j < 4; ++j) {
+      const float2 t = unpack_bf16x2(w[j]);
+      const int col = c * 8 + 2 * j;
+      f[2 * j] = col < V ? t.x : -INFINITY;
+      f[2 * j + 1] = col + 1 < V ? t.y : -INFINITY;
+    }
+    float cm = f[0];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const float2 f = unpack_bf16x2(w[j]);
-        const int col = c * 8 + 2 * j;
-        if (col < V) mx = fmaxf(mx, f.x);
-        if (col + 1 < V) mx = fmaxf(mx, f.y);
-      }
+    for (int j = 1; j < 8; ++j) cm = fmaxf(cm, f[j]);
+    if (cm > -INFINITY) {
+      float cs = 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) cs += __expf(f[j] - cm);  // exp(-inf) = 0 for padding
+      online_merge(m, ssum, cm, cs);
     }
   }
-  mx = warp_max(mx);
-  if (lane == 0) red[warp] = mx;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float m2 = __shfl_xor_sync(0xffffffffu, m, o);
+    const float s2 = __shfl_xor_sync(0xffffffffu, ssum, o);
+    online_merge(m, ssum, m2, s2);
+  }
+  if (lane == 0) { red_m[warp] = m; red_s[warp] = ssum; }
   __syncthreads();
   if (warp == 0) {
-    float t = lane < CE_THREADS / 32 ? red[lane] : -INFINITY;
-    t = warp_max(t);
-    if (lane == 0) bcast = t;
-  }
-  __syncthreads();
-  mx = bcast;
-  __syncthreads();
-
-  float sum = 0.f, picked = 0.f;
+    float mm = lane < CE_THREADS / 32 ? red_m[lane] : -INFINITY;
+    float ss = lane < CE_THREADS / 32 ? red_s[lane] : 0.f;
 #pragma unroll
-  for (int i = 0; i < CE_MAX_VEC; ++i) {
-    const int c = tid + i * CE_THREADS;
-    if (c < nvec) {
-      const uint32_t w[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const float2 f = unpack_bf16x2(w[j]);
-        const int col = c * 8 + 2 * j;
-        if (col < V) { sum += __expf(f.x - mx); if (col == label) picked = f.x; }
-        if (col + 1 < V) { sum += __expf(f.y - mx); if (col + 1 == label) picked = f.y; }
-      }
+    for (int o = 16; o > 0; o >>= 1) {
+      const float m2 = __shfl_xor_sync(0xffffffffu, mm, o);
+      const float s2 = __shfl_xor_sync(0xffffffffu, ss, o);
+      online_merge(mm, ss, m2, s2);
+    }
+    if (lane == 0) {
+      bc_m = mm; bc_s = ss;
+      const float picked = (label >= 0 && label < V)
+                               ? __bfloat162float(logits[size_t(row) * ldv + label]) : 0.f;
+      loss_rows[row] = valid ? (__logf(ss) + mm - picked) : 0.f;
     }
   }
-  sum = warp_sum(sum);
-  picked = warp_sum(picked);
-  if (lane == 0) red[warp] = sum;
+  if (!WRITE_GRAD) return;
   __syncthreads();
-  float total = 0.f;
-  if (warp == 0) {
-    float t = lane < CE_THREADS / 32 ? red[lane] : 0.f;
-    t = warp_sum(t);
-    if (lane == 0) bcast = t;
-  }
-  __syncthreads();
-  total = bcast;
-  __syncthreads();
-  if (lane == 0) red[warp] = picked;
-  __syncthreads();
-  if (warp == 0) {
-    float t = lane < CE_THREADS / 32 ? red[lane] : 0.f;
-    t = warp_sum(t);
-    if (lane == 0) loss_rows[row] = valid ? (__logf(total) + mx - t) : 0.f;
-  }
-
-  if (WRITE_GRAD) {
-    const float inv = valid ? grad_scale / total : 0.f;
-    const float hot = valid ? grad_scale : 0.f;
+  const float mx = bc_m;
+  const float inv = valid ? grad_scale / bc_s : 0.f;
+  const float hot = valid ? grad_scale : 0.f;
+  for (int c = tid; c < nvec; c += CE_THREADS) {
+    const uint4 u = rp[c];
+    const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+    uint32_t o[4];
 #pragma unroll
-    for (int i = 0; i < CE_MAX_VEC; ++i) {
-      const int c = tid + i * CE_THREADS;
-      if (c < nvec) {
-        const uint32_t w[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
-        uint32_t o[4];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const float2 f = unpack_bf16x2(w[j]);
-          const int col = c * 8 + 2 * j;
-          float g0 = 0.f, g1 = 0.f;
-          if (col < V) g0 = __expf(f.x - mx) * inv - (col == label ? hot : 0.f);
-          if (col + 1 < V) g1 = __expf(f.y - mx) * inv - (col + 1 == label ? hot : 0.f);
-          o[j] = pack_bf16x2(g0, g1);
-        }
-        rp[c] = make_uint4(o[0], o[1], o[2], o[3]);
-      }
+    for (int j = 0; j < 4; ++j) {
+      const float2 f = unpack_bf16x2(w[j]);
+      const int col = c * 8 + 2 * j;
+      float g0 = 0.f, g1 = 0.f;
+      if (col < V) g0 = __expf(f.x - mx) * inv - (col == label ? hot : 0.f);
+      if (col + 1 < V) g1 = __expf(f.y - mx) * inv - (col + 1 == label ? hot : 0.f);
+      o[j] = pack_bf16x2(g0, g1);
     }
+    rp[c] = make_uint4(o[0], o[1], o[2], o[3]);
   }
 }
 
@@ -324,7 +312,6 @@ extern "C" int llmtrain_b200_cross_entropy(void* logits, const int64_t* labels,
                                            float loss_scale, float grad_scale, int write_grad,
                                            cudaStream_t stream) {
   B200_REQUIRE(ldv % 8 == 0 && ldv >= V, "cross_entropy: row pitch must be >= V and a multiple of 8");
-  B200_REQUIRE(ldv <= ew::CE_THREADS * ew::CE_MAX_VEC * 8, "cross_entropy: vocabulary too large");
   if (rows == 0) return 0;
   auto* lg = static_cast<__nv_bfloat16*>(logits);
   if (write_grad) {

@@ -15,8 +15,8 @@
 // residual add, x GELU'(pre) for the MLP dgrad, fp32 accumulate.
 //
 // Tile: 128 x 256 x 64, UMMA 128x256x16 (cta_group::1), 4-stage smem ring (48 KB / stage),
-// 2 x 256 TMEM columns.  6 warps: 0 = TMA producer, 1 = MMA issuer + TMEM owner, 2..5 = epilogue
-// (warp w reads TMEM lanes 32*(w%4)..+31).  Grid = #SMs, static round-robin tile schedule with M
+// 2 x 256 TMEM columns.  10 warps: 0 = TMA producer, 1 = MMA issuer + TMEM owner, 2..9 = epilogue
+// (warp w reads TMEM lanes 32*(w%4)..+31; two warps per lane quarter split the 256 columns).  Grid = #SMs, static round-robin tile schedule with M
 // fastest so concurrently running CTAs share the weight tile through L2.
 
 #include "../common/host.cuh"
@@ -34,9 +34,9 @@ constexpr int STAGES = 4;
 constexpr int A_BYTES = BM * BK * 2;  // 16 KB
 constexpr int B_BYTES = BN * BK * 2;  // 32 KB
 constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-constexpr int EPI_WARPS = 4;
+constexpr int EPI_WARPS = 8;              // two warps per TMEM lane quarter, each owns 128 columns
 constexpr int EPI_BUF_BYTES = 32 * 128;  // 32 rows x 128 B per staging buffer
-constexpr int EPI_BYTES = EPI_WARPS * 2 * EPI_BUF_BYTES;
+constexpr int EPI_BYTES = EPI_WARPS * EPI_BUF_BYTES;
 constexpr int NUM_THREADS = 32 * (2 + EPI_WARPS);
 constexpr int TMEM_COLS = 512;
 constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + 256 /*barriers*/ + 1024 /*align*/;
@@ -57,13 +57,26 @@ struct Params {
   int ldr;
 };
 
-__device__ __forceinline__ float gelu_erf(float x) {
-  return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f));
+// erf via Abramowitz & Stegun 7.1.26 (|abs err| < 1.5e-7 — two orders of magnitude below bf16
+// resolution), sharing one exponential between Phi(x) and phi(x).  The libm erff costs ~3x more
+// instructions and made the GELU epilogues the pacing stage of their GEMMs.
+struct PhiPair { float cdf, pdf; };  // Phi(x), phi(x) of the standard normal
+__device__ __forceinline__ PhiPair normal_cdf_pdf(float x) {
+  const float ax = fabsf(x) * 0.70710678118654752f;             // |x|/sqrt(2)
+  const float t = __fdividef(1.0f, fmaf(0.3275911f, ax, 1.0f));
+  const float e = __expf(-ax * ax);                              // exp(-x^2/2)
+  float poly = fmaf(1.061405429f, t, -1.453152027f);
+  poly = fmaf(poly, t, 1.421413741f);
+  poly = fmaf(poly, t, -0.284496736f);
+  poly = fmaf(poly, t, 0.254829592f);
+  const float erf_abs = 1.0f - poly * t * e;                     // erf(|x|/sqrt(2))
+  const float cdf = 0.5f * (1.0f + copysignf(erf_abs, x));
+  return {cdf, 0.3989422804014327f * e};
 }
+__device__ __forceinline__ float gelu_erf(float x) { return x * normal_cdf_pdf(x).cdf; }
 __device__ __forceinline__ float gelu_erf_grad(float x) {
-  const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752f));
-  const float pdf = 0.3989422804014327f * __expf(-0.5f * x * x);
-  return cdf + x * pdf;
+  const PhiPair n = normal_cdf_pdf(x);
+  return fmaf(x, n.pdf, n.cdf);
 }
 
 template <bool A_MN, bool B_MN, int EPI>
@@ -191,34 +204,34 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
   } else {
     // ===================================== epilogue =========================================
-    const int ew = warp - 2;        // 0..3 : staging-buffer owner
+    // Warp w reads TMEM lanes 32*(w%4)..+31 (hardware restriction) and columns
+    // [128*half, 128*half+128) of the 256-wide accumulator; one 4 KB staging buffer per warp.
+    const int ew = warp - 2;        // 0..7
     const int quarter = warp & 3;   // TMEM lane quarter this warp may access
-    uint8_t* stg0 = epi_smem + (ew * 2 + 0) * EPI_BUF_BYTES;
-    uint8_t* stg1 = epi_smem + (ew * 2 + 1) * EPI_BUF_BYTES;
+    const int half = ew >> 2;       // which 128-column half of the tile
+    uint8_t* stg = epi_smem + ew * EPI_BUF_BYTES;
     int acc = 0;
     uint32_t acc_phase = 0;
-    int buf = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int split = tile / tiles_mn;
       const int mn = tile - split * tiles_mn;
       const int m0 = (mn % num_m) * BM;
-      const int n0 = (mn / num_m) * BN;
+      const int n0 = (mn / num_m) * BN + half * (BN / 2);
       const int row = m0 + quarter * 32 + lane;  // this thread's output row
       const bool row_ok = row < p.M;
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after_sync();
-      const uint32_t t_row = tmem_base + (uint32_t(quarter * 32) << 16) + acc * BN;
+      const uint32_t t_row = tmem_base + (uint32_t(quarter * 32) << 16) + acc * BN + half * (BN / 2);
 
       if (EPI == kAccumF32) {
-        // 8 chunks of 32 fp32 columns (128 B rows), reduce-added into global fp32.
+        // 4 chunks of 32 fp32 columns (128 B rows), reduce-added into global fp32.
 #pragma unroll 1
-        for (int c = 0; c < BN / 32; ++c) {
+        for (int c = 0; c < BN / 64; ++c) {
           if (n0 + c * 32 >= p.N) break;
           uint32_t v[32];
           tmem_ld_32x32b_x32(t_row + c * 32, v);
           tmem_ld_wait();
-          uint8_t* stg = buf ? stg1 : stg0;
-          tma_store_wait_read<1>();  // the buffer used two chunks ago is free again
+          tma_store_wait_read<0>();  // previous chunk's TMA has finished reading the buffer
           __syncwarp();
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
@@ -232,14 +245,36 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             tma_reduce_add_2d(&tmC, stg, n0 + c * 32, m0 + quarter * 32);
             tma_store_commit();
           }
-          buf ^= 1;
         }
       } else {
-        // 4 chunks of 64 bf16 columns (128 B rows).
+        // 2 chunks of 64 bf16 columns (128 B rows).
 #pragma unroll 1
-        for (int c = 0; c < BN / 64; ++c) {
+        for (int c = 0; c < BN / 128; ++c) {
           const int col0 = n0 + c * 64;
           if (col0 >= p.N) break;
+          // Issue the residual / pre-activation reads first (this thread's row, 64 contiguous
+          // bf16 = 8 x 16 B) so they overlap the TMEM loads.
+          uint4 rv[8];
+          const bool full_cols = (col0 + 64 <= p.N);
+          if (EPI == kBiasResid || EPI == kDGelu) {
+#pragma unroll
+            for (int q = 0; q < 8; ++q) rv[q] = make_uint4(0u, 0u, 0u, 0u);
+            if (row_ok) {
+              const __nv_bfloat16* rp = p.R + size_t(row) * p.ldr + col0;
+              if (full_cols) {
+#pragma unroll
+                for (int q = 0; q < 8; ++q) rv[q] = __ldg(reinterpret_cast<const uint4*>(rp) + q);
+              } else {
+                uint32_t* rw = reinterpret_cast<uint32_t*>(rv);
+#pragma unroll
+                for (int j = 0; j < 64; j += 2) {  // static indices keep rv in registers
+                  const float lo = (col0 + j < p.N) ? __bfloat162float(rp[j]) : 0.f;
+                  const float hi = (col0 + j + 1 < p.N) ? __bfloat162float(rp[j + 1]) : 0.f;
+                  rw[j >> 1] = pack_bf16x2(lo, hi);
+                }
+              }
+            }
+          }
           uint32_t v[2][32];
           tmem_ld_32x32b_x32(t_row + c * 64, v[0]);
           tmem_ld_32x32b_x32(t_row + c * 64 + 32, v[1]);
@@ -247,6 +282,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 
           uint32_t out[32];   // 64 bf16 packed
           uint32_t out2[32];  // pre-activation (GELU variant only)
+          const uint32_t* rw = reinterpret_cast<const uint32_t*>(rv);
 #pragma unroll
           for (int h = 0; h < 2; ++h) {
 #pragma unroll
@@ -256,22 +292,19 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               float x1 = __uint_as_float(v[h][j + 1]);
               if (EPI == kBias || EPI == kBiasGelu || EPI == kBiasResid) {
                 if (p.bias != nullptr) {
-                  if (col < p.N) x0 += __ldg(p.bias + col);
-                  if (col + 1 < p.N) x1 += __ldg(p.bias + col + 1);
+                  if (full_cols) {
+                    const float2 bb = __ldg(reinterpret_cast<const float2*>(p.bias + col));
+                    x0 += bb.x; x1 += bb.y;
+                  } else {
+                    if (col < p.N) x0 += __ldg(p.bias + col);
+                    if (col + 1 < p.N) x1 += __ldg(p.bias + col + 1);
+                  }
                 }
               }
               if (EPI == kBiasResid || EPI == kDGelu) {
-                float r0 = 0.f, r1 = 0.f;
-                if (row_ok && col + 1 < p.N) {
-                  const uint32_t rr = __ldg(reinterpret_cast<const uint32_t*>(
-                      p.R + size_t(row) * p.ldr + col));
-                  const float2 f = unpack_bf16x2(rr);
-                  r0 = f.x; r1 = f.y;
-                } else if (row_ok && col < p.N) {
-                  r0 = __bfloat162float(p.R[size_t(row) * p.ldr + col]);
-                }
-                if (EPI == kBiasResid) { x0 += r0; x1 += r1; }
-                else { x0 *= gelu_erf_grad(r0); x1 *= gelu_erf_grad(r1); }
+                const float2 f = unpack_bf16x2(rw[h * 16 + (j >> 1)]);
+                if (EPI == kBiasResid) { x0 += f.x; x1 += f.y; }
+                else { x0 *= gelu_erf_grad(f.x); x1 *= gelu_erf_grad(f.y); }
               }
               if (EPI == kBiasGelu) {
                 out2[h * 16 + j / 2] = pack_bf16x2(x0, x1);
@@ -281,31 +314,37 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             }
           }
 
-          if (EPI == kBiasGelu) {
-            tma_store_wait_read<0>();  // both staging buffers are reused every chunk
-          } else {
-            tma_store_wait_read<1>();
-          }
+          tma_store_wait_read<0>();  // previous chunk's TMA has finished reading the buffer
           __syncwarp();
-          uint8_t* stg = (EPI == kBiasGelu) ? stg0 : (buf ? stg1 : stg0);
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
             const uint32_t off = swizzle128(lane * 128 + j * 16);
             *reinterpret_cast<uint4*>(stg + off) =
                 make_uint4(out[4 * j], out[4 * j + 1], out[4 * j + 2], out[4 * j + 3]);
-            if (EPI == kBiasGelu) {
-              *reinterpret_cast<uint4*>(stg1 + off) =
-                  make_uint4(out2[4 * j], out2[4 * j + 1], out2[4 * j + 2], out2[4 * j + 3]);
-            }
           }
           fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) {
             tma_store_2d(&tmC, stg, col0, m0 + quarter * 32);
-            if (EPI == kBiasGelu) tma_store_2d(&tmC2, stg1, col0, m0 + quarter * 32);
             tma_store_commit();
           }
-          buf ^= 1;
+          if (EPI == kBiasGelu) {
+            // second output (pre-activation) through the same buffer
+            tma_store_wait_read<0>();
+            __syncwarp();
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const uint32_t off = swizzle128(lane * 128 + j * 16);
+              *reinterpret_cast<uint4*>(stg + off) =
+                  make_uint4(out2[4 * j], out2[4 * j + 1], out2[4 * j + 2], out2[4 * j + 3]);
+            }
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+              tma_store_2d(&tmC2, stg, col0, m0 + quarter * 32);
+              tma_store_commit();
+            }
+          }
         }
       }
       // TMEM reads for this accumulator are complete (wait::ld above): hand it back.

@@ -184,13 +184,27 @@ bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict
 }
 
 // Fixed-order column sum of `nparts` partial rows, accumulated into the fp32 gradient arena.
-__global__ void finish_kernel(const float* __restrict__ partial, int nparts, int d,
-                              float* __restrict__ dgamma, float* __restrict__ dbeta) {
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= 2 * d) return;
+// Block = 32 columns x 8 part-lanes: lane py sums parts py, py+8, ... (coalesced 128 B reads per
+// part row), then the 8 partials of a column are combined in a fixed order through smem.
+constexpr int FIN_COLS = 32, FIN_LANES = 8;
+__global__ void __launch_bounds__(FIN_COLS * FIN_LANES)
+finish_kernel(const float* __restrict__ partial, int nparts, int d, float* __restrict__ dgamma,
+              float* __restrict__ dbeta) {
+  __shared__ float sh[FIN_LANES][FIN_COLS];
+  const int cx = threadIdx.x & (FIN_COLS - 1), py = threadIdx.x / FIN_COLS;
+  const int idx = blockIdx.x * FIN_COLS + cx;
   float acc = 0.f;
-  for (int p = 0; p < nparts; ++p) acc += partial[size_t(p) * 2 * d + idx];
-  if (idx < d) dgamma[idx] += acc; else dbeta[idx - d] += acc;
+  if (idx < 2 * d) {
+    for (int p = py; p < nparts; p += FIN_LANES) acc += partial[size_t(p) * 2 * d + idx];
+  }
+  sh[py][cx] = acc;
+  __syncthreads();
+  if (py == 0 && idx < 2 * d) {
+    float t = sh[0][cx];
+#pragma unroll
+    for (int k = 1; k < FIN_LANES; ++k) t += sh[k][cx];
+    if (idx < d) dgamma[idx] += t; else dbeta[idx - d] += t;
+  }
 }
 
 inline int bwd_grid(int rows) {
@@ -258,8 +272,8 @@ extern "C" int llmtrain_b200_layernorm_bwd(const void* dy, const void* x, const 
 #undef B200_LN_BWD
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
-  ln::finish_kernel<<<ceil_div(2 * d, 256), 256, 0, stream>>>(static_cast<float*>(scratch), grid,
-                                                              d, dgamma, dbeta);
+  ln::finish_kernel<<<ceil_div(2 * d, ln::FIN_COLS), ln::FIN_COLS * ln::FIN_LANES, 0, stream>>>(
+      static_cast<float*>(scratch), grid, d, dgamma, dbeta);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   return 0;
