@@ -63,31 +63,42 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
+// try_wait suspends the warp in hardware until the phase completes or the time hint (ns) runs
+// out, so a waiting role (TMA producer, MMA issuer) does not burn issue slots that the math
+// warps on the same SM sub-partition need.
 __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
   uint32_t done;
   asm volatile(
       "{\n\t"
       ".reg .pred P;\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 P, [%1], %2;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 P, [%1], %2, %3;\n\t"
       "selp.u32 %0, 1, 0, P;\n\t"
       "}\n"
       : "=r"(done)
-      : "r"(smem_u32(bar)), "r"(parity)
+      : "r"(smem_u32(bar)), "r"(parity), "r"(0x00100000u)
       : "memory");
   return done != 0;
 }
 
-// Bounded spin: a protocol bug traps (visible as a CUDA error) instead of hanging the GPU box.
-#ifndef B200_MBAR_SPIN_LIMIT
-#define B200_MBAR_SPIN_LIMIT (1u << 28)
+// Bounded wait: a protocol bug traps (visible as a CUDA error) instead of hanging the GPU box.
+// The bound is wall-clock (10 s by %globaltimer) and only evaluated on the slow path.
+#ifndef B200_MBAR_TIMEOUT_NS
+#define B200_MBAR_TIMEOUT_NS 10000000000ull
 #endif
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+static __device__ __noinline__ void mbar_timeout_trap() {
+  printf("b200: mbarrier wait timed out (block %d thread %d)\n", blockIdx.x, threadIdx.x);
+  __trap();
+}
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-  uint32_t spins = 0;
+  if (mbar_try_wait(bar, parity)) return;
+  const unsigned long long t0 = global_timer_ns();
   while (!mbar_try_wait(bar, parity)) {
-    if (++spins > B200_MBAR_SPIN_LIMIT) {
-      printf("b200: mbarrier wait timed out (block %d thread %d)\n", blockIdx.x, threadIdx.x);
-      __trap();
-    }
+    if (global_timer_ns() - t0 > B200_MBAR_TIMEOUT_NS) mbar_timeout_trap();
   }
 }
 
@@ -322,6 +333,13 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 __device__ __forceinline__ float2 unpack_bf16x2(uint32_t u) {
   __nv_bfloat162 v = *reinterpret_cast<__nv_bfloat162*>(&u);
   return __bfloat1622float2(v);
+}
+
+// 2^x with the bare MUFU.EX2 (flush-to-zero, no range fix-up code around it).
+__device__ __forceinline__ float fast_exp2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
 }
 
 // 128-byte swizzle: byte offset inside a tile whose rows are 128 B and whose base is 1024 B

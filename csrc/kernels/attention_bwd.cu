@@ -30,7 +30,7 @@ constexpr int BQ = 128;
 constexpr int BKV = 128;
 constexpr int HD = 64;
 constexpr int TILE = 128 * HD * 2;  // 16 KB
-constexpr int THREADS = 192;
+constexpr int THREADS = 320;  // 8 softmax-grad warps + TMA warp + MMA warp
 constexpr int TMEM_COLS = 512;
 constexpr int COL_S = 0, COL_DP = 128, COL_DV = 256, COL_DK = 320, COL_DQ = 384;
 constexpr int OFF_K = 0;
@@ -51,6 +51,49 @@ struct Params {
   const float* dsum; // [B, H, T]   D = rowsum(dO o O)
   const uint8_t* key_mask;
 };
+
+// One thread: 64 columns of its row.  P = exp2(S*scale*log2e - lse*log2e), dS = P (dP - D) scale,
+// both written as bf16 into one 64-column swizzled region (row r, 8 x 16 B chunks).
+template <bool MASK>
+__device__ __forceinline__ void softmax_grad(uint32_t t_row, uint8_t* rp, uint8_t* rd, int r,
+                                             int col0, int qrow, int T, const uint8_t* kmask,
+                                             bool dead_row, float scale_log2, float scale,
+                                             float lse2, float dsum) {
+#pragma unroll 1
+  for (int c = 0; c < 2; ++c) {
+    uint32_t sv[32], dv[32];
+    tmem_ld_32x32b_x32(t_row + COL_S + c * 32, sv);
+    tmem_ld_32x32b_x32(t_row + COL_DP + c * 32, dv);
+    tmem_ld_wait();
+    uint32_t pk[16], dk[16];
+#pragma unroll
+    for (int i = 0; i < 32; i += 2) {
+      float pe[2], de[2];
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        float pv = fast_exp2(fmaf(__uint_as_float(sv[i + u]), scale_log2, -lse2));
+        if (MASK) {
+          const int col = col0 + c * 32 + i + u;
+          bool ok = !dead_row && (col <= qrow);
+          if (kmask != nullptr && col < T) ok = ok && (kmask[col] != 0);
+          if (!ok) pv = 0.f;
+        }
+        pe[u] = pv;
+        de[u] = pv * (__uint_as_float(dv[i + u]) - dsum) * scale;
+      }
+      pk[i >> 1] = pack_bf16x2(pe[0], pe[1]);
+      dk[i >> 1] = pack_bf16x2(de[0], de[1]);
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const uint32_t off = swizzle128(r * 128 + (c * 4 + q) * 16);
+      *reinterpret_cast<uint4*>(rp + off) =
+          make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
+      *reinterpret_cast<uint4*>(rd + off) =
+          make_uint4(dk[4 * q], dk[4 * q + 1], dk[4 * q + 2], dk[4 * q + 3]);
+    }
+  }
+}
 
 __global__ void __launch_bounds__(THREADS, 1)
 bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
@@ -88,12 +131,12 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
       mbar_init(&q_empty[s], 1);
     }
     mbar_init(s_full, 1);
-    mbar_init(pds_full, 4);
+    mbar_init(pds_full, 8);
     mbar_init(dq_full, 1);
     mbar_init(dkv_full, 1);
     fence_barrier_init();
   }
-  if (warp == 5) {
+  if (warp == 9) {
     tmem_alloc(tmem_slot, TMEM_COLS);
     tmem_relinquish();
   }
@@ -102,7 +145,7 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
   tc_fence_after_sync();
   const uint32_t tmem = *tmem_slot;
 
-  if (warp == 4) {
+  if (warp == 8) {
     // ------------------------------- TMA producer -------------------------------------------
     if (lane == 0) {
       mbar_expect_tx(kv_full, 2 * TILE);
@@ -118,7 +161,7 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
         tma_load_3d(smem + OFF_DO + st * TILE, &tmDO, &q_full[st], h * HD, q0, b);
       }
     }
-  } else if (warp == 5) {
+  } else if (warp == 9) {
     // ------------------------------- MMA issuer ---------------------------------------------
     if (lane == 0) {
       constexpr uint32_t id_s = umma_idesc_bf16(128, 128, false, false);   // Q K^T, dO V^T
@@ -167,8 +210,11 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
     }
   } else {
     // ------------------------------- softmax-grad / epilogue warps --------------------------
-    const int r = threadIdx.x;  // 0..127
-    const uint32_t lane_base = uint32_t(warp * 32) << 16;
+    // 8 warps: warp w owns TMEM lanes 32*(w%4)..+31 (query / kv row r) and the 64-column half
+    // (w/4) of every 128-column tile — which is exactly one swizzled smem region of P / dS.
+    const int quarter = warp & 3, half = warp >> 2;
+    const int r = quarter * 32 + lane;  // 0..127
+    const uint32_t lane_base = uint32_t(quarter * 32) << 16;
     const uint8_t* kmask = p.key_mask ? p.key_mask + size_t(b) * p.T : nullptr;
     const size_t stat_base = (size_t(b) * p.H + h) * p.T;
 
@@ -179,67 +225,38 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
       const bool row_ok = qrow < p.T;
       float lse2 = 0.f, dsum = 0.f;
       if (row_ok) {
-        const float l = p.lse[stat_base + qrow];
-        lse2 = l * 1.4426950408889634f;
+        lse2 = p.lse[stat_base + qrow] * 1.4426950408889634f;
         dsum = p.dsum[stat_base + qrow];
       }
       const bool dead_row = !row_ok || (lse2 == -INFINITY);
-      const bool need_mask = (it == 0) || (kmask != nullptr);
+      const bool need_mask = (it == 0) || (kmask != nullptr) || dead_row;
 
       mbar_wait(s_full, it & 1);
       tc_fence_after_sync();
-#pragma unroll 1
-      for (int c = 0; c < BKV / 32; ++c) {
-        uint32_t sv[32], dv[32];
-        tmem_ld_32x32b_x32(tmem + COL_S + lane_base + c * 32, sv);
-        tmem_ld_32x32b_x32(tmem + COL_DP + lane_base + c * 32, dv);
-        tmem_ld_wait();
-        uint32_t pk[16], dk[16];
-#pragma unroll
-        for (int i = 0; i < 32; i += 2) {
-          float pe[2], de[2];
-#pragma unroll
-          for (int u = 0; u < 2; ++u) {
-            const int col = kv0 + c * 32 + i + u;
-            bool ok = !dead_row;
-            if (need_mask) {
-              ok = ok && (col <= qrow);
-              if (kmask != nullptr && col < p.T) ok = ok && (kmask[col] != 0);
-            }
-            const float pv = ok ? exp2f(__uint_as_float(sv[i + u]) * p.scale_log2 - lse2) : 0.f;
-            pe[u] = pv;
-            de[u] = pv * (__uint_as_float(dv[i + u]) - dsum) * p.scale;
-          }
-          pk[i >> 1] = pack_bf16x2(pe[0], pe[1]);
-          dk[i >> 1] = pack_bf16x2(de[0], de[1]);
-        }
-        uint8_t* rp = smem + OFF_P + (c >> 1) * TILE;
-        uint8_t* rd = smem + OFF_DS + (c >> 1) * TILE;
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const uint32_t off = swizzle128(r * 128 + ((c & 1) * 4 + q) * 16);
-          *reinterpret_cast<uint4*>(rp + off) =
-              make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
-          *reinterpret_cast<uint4*>(rd + off) =
-              make_uint4(dk[4 * q], dk[4 * q + 1], dk[4 * q + 2], dk[4 * q + 3]);
-        }
+      uint8_t* rp = smem + OFF_P + half * TILE;
+      uint8_t* rd = smem + OFF_DS + half * TILE;
+      if (need_mask) {
+        softmax_grad<true>(tmem + lane_base + half * 64, rp, rd, r, kv0 + half * 64, qrow, p.T,
+                           kmask, dead_row, p.scale_log2, p.scale, lse2, dsum);
+      } else {
+        softmax_grad<false>(tmem + lane_base + half * 64, rp, rd, r, kv0 + half * 64, qrow, p.T,
+                            kmask, dead_row, p.scale_log2, p.scale, lse2, dsum);
       }
       fence_proxy_async_smem();
       tc_fence_before_sync();
       __syncwarp();
       if (lane == 0) mbar_arrive(pds_full);
 
-      // dQ_i: TMEM -> fp32 staging (two 128 B-row boxes of 32 columns) -> TMA reduce-add
+      // dQ_i: TMEM -> fp32 staging (this half's 32 columns = one 128 B-row box) -> TMA reduce-add
       mbar_wait(dq_full, it & 1);
       tc_fence_after_sync();
       if (threadIdx.x == 0) tma_store_wait_read<0>();  // previous iteration's staging drained
-      named_bar_sync(1, 128);
-#pragma unroll
-      for (int c = 0; c < HD / 32; ++c) {
+      named_bar_sync(1, 256);
+      {
         uint32_t v[32];
-        tmem_ld_32x32b_x32(tmem + COL_DQ + lane_base + c * 32, v);
+        tmem_ld_32x32b_x32(tmem + COL_DQ + lane_base + half * 32, v);
         tmem_ld_wait();
-        uint8_t* box = smem + OFF_DQ + c * TILE;
+        uint8_t* box = smem + OFF_DQ + half * TILE;
 #pragma unroll
         for (int q = 0; q < 8; ++q)
           *reinterpret_cast<uint4*>(box + swizzle128(r * 128 + q * 16)) =
@@ -247,7 +264,7 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
       }
       tc_fence_before_sync();
       fence_proxy_async_smem();
-      named_bar_sync(1, 128);
+      named_bar_sync(1, 256);
       if (threadIdx.x == 0) {
         tma_reduce_add_3d(&tmDQ32, smem + OFF_DQ, h * HD, q0, b);
         tma_reduce_add_3d(&tmDQ32, smem + OFF_DQ + TILE, h * HD + 32, q0, b);
@@ -255,33 +272,30 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
       }
     }
 
-    // dV, dK: TMEM -> bf16 -> swizzled staging (P / dS buffers are free now) -> TMA store
+    // dV, dK: TMEM -> bf16 -> swizzled staging (P / dS buffers are free now) -> TMA store.
+    // Each warp converts its 32-column half of both accumulators.
     mbar_wait(dkv_full, 0);
     tc_fence_after_sync();
 #pragma unroll
     for (int which = 0; which < 2; ++which) {
       uint8_t* stage = smem + (which == 0 ? OFF_P : OFF_DS);
       const uint32_t col_base = which == 0 ? COL_DV : COL_DK;
+      uint32_t v[32];
+      tmem_ld_32x32b_x32(tmem + col_base + lane_base + half * 32, v);
+      tmem_ld_wait();
 #pragma unroll
-      for (int c = 0; c < HD / 32; ++c) {
-        uint32_t v[32];
-        tmem_ld_32x32b_x32(tmem + col_base + lane_base + c * 32, v);
-        tmem_ld_wait();
+      for (int q = 0; q < 4; ++q) {
+        uint32_t w[4];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          uint32_t w[4];
-#pragma unroll
-          for (int u = 0; u < 4; ++u)
-            w[u] = pack_bf16x2(__uint_as_float(v[q * 8 + 2 * u]),
-                               __uint_as_float(v[q * 8 + 2 * u + 1]));
-          *reinterpret_cast<uint4*>(stage + swizzle128(r * 128 + (c * 4 + q) * 16)) =
-              make_uint4(w[0], w[1], w[2], w[3]);
-        }
+        for (int u = 0; u < 4; ++u)
+          w[u] = pack_bf16x2(__uint_as_float(v[q * 8 + 2 * u]), __uint_as_float(v[q * 8 + 2 * u + 1]));
+        *reinterpret_cast<uint4*>(stage + swizzle128(r * 128 + (half * 4 + q) * 16)) =
+            make_uint4(w[0], w[1], w[2], w[3]);
       }
     }
     tc_fence_before_sync();
     fence_proxy_async_smem();
-    named_bar_sync(1, 128);
+    named_bar_sync(1, 256);
     if (threadIdx.x == 0) {
       tma_store_3d(&tmDQKV, smem + OFF_P, 2 * d + h * HD, kv0, b);   // dV
       tma_store_3d(&tmDQKV, smem + OFF_DS, d + h * HD, kv0, b);      // dK
@@ -292,7 +306,7 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
 
   tc_fence_before_sync();
   __syncthreads();
-  if (warp == 5) tmem_dealloc(tmem, TMEM_COLS);
+  if (warp == 9) tmem_dealloc(tmem, TMEM_COLS);
 }
 
 // D[b,h,t] = sum_c dO[b,t,h*64+c] * O[b,t,h*64+c]; 8 lanes x 16 B cover one head (64 bf16), so a

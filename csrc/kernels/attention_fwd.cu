@@ -48,6 +48,66 @@ struct FwdParams {
   float* lse;                    // [B, H, T]
 };
 
+template <bool MASK>
+__device__ __forceinline__ bool keep(int col, int qrow, int T, const uint8_t* kmask) {
+  if (!MASK) return true;
+  bool ok = col <= qrow;
+  if (kmask != nullptr && col < T) ok = ok && (kmask[col] != 0);
+  return ok;
+}
+
+// max over this thread's row of the 128-column S tile
+template <bool MASK>
+__device__ __forceinline__ float row_max(uint32_t t_row, int kv0, int qrow, int T,
+                                         const uint8_t* kmask) {
+  float mx = -INFINITY;
+#pragma unroll 1
+  for (int c = 0; c < BKV / 32; ++c) {
+    uint32_t v[32];
+    tmem_ld_32x32b_x32(t_row + c * 32, v);
+    tmem_ld_wait();
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+      if (keep<MASK>(kv0 + c * 32 + i, qrow, T, kmask)) mx = fmaxf(mx, __uint_as_float(v[i]));
+    }
+  }
+  return mx;
+}
+
+// p = exp2(s*scale - m) -> bf16 into the K-major 128B-swizzled P tile; returns the row sum
+template <bool MASK>
+__device__ __forceinline__ float exp_pack(uint32_t t_row, uint8_t* sP, int r, int kv0, int qrow,
+                                          int T, const uint8_t* kmask, float scale_log2,
+                                          float m_use) {
+  float sum = 0.f;
+#pragma unroll 1
+  for (int c = 0; c < BKV / 32; ++c) {
+    uint32_t v[32];
+    tmem_ld_32x32b_x32(t_row + c * 32, v);
+    tmem_ld_wait();
+    uint32_t packed[16];
+#pragma unroll
+    for (int i = 0; i < 32; i += 2) {
+      float e0 = fast_exp2(fmaf(__uint_as_float(v[i]), scale_log2, -m_use));
+      float e1 = fast_exp2(fmaf(__uint_as_float(v[i + 1]), scale_log2, -m_use));
+      if (MASK) {
+        if (!keep<MASK>(kv0 + c * 32 + i, qrow, T, kmask)) e0 = 0.f;
+        if (!keep<MASK>(kv0 + c * 32 + i + 1, qrow, T, kmask)) e1 = 0.f;
+      }
+      sum += e0 + e1;
+      packed[i >> 1] = pack_bf16x2(e0, e1);
+    }
+    uint8_t* region = sP + (c >> 1) * TILE_BYTES;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const uint32_t off = swizzle128(r * 128 + ((c & 1) * 4 + q) * 16);
+      *reinterpret_cast<uint4*>(region + off) =
+          make_uint4(packed[4 * q], packed[4 * q + 1], packed[4 * q + 2], packed[4 * q + 3]);
+    }
+  }
+  return sum;
+}
+
 __global__ void __launch_bounds__(FWD_THREADS, 2)
 fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmO,
            const FwdParams p) {
@@ -166,63 +226,19 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
       mbar_wait(s_full, j & 1);
       tc_fence_after_sync();
 
-      // pass 1: row max
-      float mx = -INFINITY;
-#pragma unroll 1
-      for (int c = 0; c < BKV / 32; ++c) {
-        uint32_t v[32];
-        tmem_ld_32x32b_x32(tmem_S + lane_base + c * 32, v);
-        tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          const int col = kv0 + c * 32 + i;
-          bool ok = true;
-          if (need_mask) {
-            ok = col <= qrow;
-            if (kmask != nullptr && col < p.T) ok = ok && (kmask[col] != 0);
-          }
-          if (ok) mx = fmaxf(mx, __uint_as_float(v[i]));
-        }
-      }
+      // Two passes over S in TMEM (max, then exp2 + pack).  The masked variant is only
+      // instantiated for the diagonal tile / key-padding case, so off-diagonal tiles execute no
+      // per-element integer or predicate instructions at all.
+      float mx = need_mask ? row_max<true>(tmem_S + lane_base, kv0, qrow, p.T, kmask)
+                           : row_max<false>(tmem_S + lane_base, kv0, qrow, p.T, kmask);
       const float m_new = fmaxf(m_run, mx * p.scale_log2);
       const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
-      const float alpha = exp2f(m_run - m_use);  // m_run = -inf -> 0
-
-      // pass 2: p = exp2(s*scale - m), row sum, bf16 pack into the K-major swizzled P tile
-      float sum = 0.f;
-#pragma unroll 1
-      for (int c = 0; c < BKV / 32; ++c) {
-        uint32_t v[32];
-        tmem_ld_32x32b_x32(tmem_S + lane_base + c * 32, v);
-        tmem_ld_wait();
-        uint32_t packed[16];
-#pragma unroll
-        for (int i = 0; i < 32; i += 2) {
-          float e[2];
-#pragma unroll
-          for (int u = 0; u < 2; ++u) {
-            const int col = kv0 + c * 32 + i + u;
-            bool ok = true;
-            if (need_mask) {
-              ok = col <= qrow;
-              if (kmask != nullptr && col < p.T) ok = ok && (kmask[col] != 0);
-            }
-            e[u] = ok ? exp2f(__uint_as_float(v[i + u]) * p.scale_log2 - m_use) : 0.f;
-          }
-          // sum what the tensor core will actually see (bf16-rounded), keeps rows normalised
-          const uint32_t pk = pack_bf16x2(e[0], e[1]);
-          const float2 back = unpack_bf16x2(pk);
-          sum += back.x + back.y;
-          packed[i >> 1] = pk;
-        }
-        uint8_t* region = smem + OFF_P + (c >> 1) * TILE_BYTES;
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const uint32_t off = swizzle128(r * 128 + ((c & 1) * 4 + q) * 16);
-          *reinterpret_cast<uint4*>(region + off) =
-              make_uint4(packed[4 * q], packed[4 * q + 1], packed[4 * q + 2], packed[4 * q + 3]);
-        }
-      }
+      const float alpha = fast_exp2(m_run - m_use);  // m_run = -inf -> 0
+      const float sum =
+          need_mask ? exp_pack<true>(tmem_S + lane_base, smem + OFF_P, r, kv0, qrow, p.T, kmask,
+                                     p.scale_log2, m_use)
+                    : exp_pack<false>(tmem_S + lane_base, smem + OFF_P, r, kv0, qrow, p.T, kmask,
+                                      p.scale_log2, m_use);
       l_run = l_run * alpha + sum;
       m_run = m_new;
 
