@@ -229,7 +229,9 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
         dsum = p.dsum[stat_base + qrow];
       }
       const bool dead_row = !row_ok || (lse2 == -INFINITY);
-      const bool need_mask = (it == 0) || (kmask != nullptr) || dead_row;
+      // warp-uniform on purpose: the two variants contain .sync.aligned TMEM loads
+      const bool need_mask =
+          (it == 0) || (kmask != nullptr) || (__any_sync(0xffffffffu, dead_row) != 0);
 
       mbar_wait(s_full, it & 1);
       tc_fence_after_sync();
