@@ -205,36 +205,52 @@ __global__ void loss_reduce_kernel(const float* __restrict__ loss_rows, int rows
 }
 
 // ------------------------------------------------------------------------------------------------
-// Column sums: db[n] += sum_m dy[m,n].  Grid (ceil(N/64), splits); each warp streams rows, a lane
-// owns two adjacent columns; warps combine through smem; splits combine through scratch in a
-// fixed order (second kernel).
+// Column sums: db[n] += sum_m dy[m,n].  Grid (ceil(N/256), splits); a warp streams whole rows with
+// 16-byte loads (a lane owns 8 adjacent columns, a warp 256); warps combine through smem; splits
+// combine through scratch in a fixed order (second kernel).
 // ------------------------------------------------------------------------------------------------
 constexpr int CS_WARPS = 8;
+constexpr int CS_COLS = 256;
 __global__ void __launch_bounds__(CS_WARPS * 32)
 colsum_partial_kernel(const __nv_bfloat16* __restrict__ dy, int ld, int M, int N,
                       float* __restrict__ partial /* [splits][N] */) {
-  __shared__ float2 sh[CS_WARPS][32];
+  __shared__ float sh[CS_WARPS][CS_COLS];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int col = blockIdx.x * 64 + lane * 2;
+  const int col = blockIdx.x * CS_COLS + lane * 8;
   const int rows_per = (M + gridDim.y - 1) / gridDim.y;
   const int r0 = blockIdx.y * rows_per;
   const int r1 = min(M, r0 + rows_per);
-  float2 acc = make_float2(0.f, 0.f);
-  if (col < N) {
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  const bool vec_ok = (col + 8 <= N) && ((ld & 7) == 0) &&
+                      ((reinterpret_cast<uintptr_t>(dy) & 15) == 0);
+  if (vec_ok) {
+#pragma unroll 4
     for (int r = r0 + warp; r < r1; r += CS_WARPS) {
-      const float2 f = unpack_bf16x2(
-          __ldg(reinterpret_cast<const uint32_t*>(dy + size_t(r) * ld + col)));
-      acc.x += f.x; acc.y += f.y;
+      const uint4 u = __ldg(reinterpret_cast<const uint4*>(dy + size_t(r) * ld + col));
+      const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 f = unpack_bf16x2(w[j]);
+        acc[2 * j] += f.x;
+        acc[2 * j + 1] += f.y;
+      }
+    }
+  } else if (col < N) {
+    for (int r = r0 + warp; r < r1; r += CS_WARPS) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (col + j < N) acc[j] += __bfloat162float(dy[size_t(r) * ld + col + j]);
     }
   }
-  sh[warp][lane] = acc;
-  __syncthreads();
-  if (warp == 0 && col < N) {
-    float2 t = sh[0][lane];
 #pragma unroll
-    for (int w = 1; w < CS_WARPS; ++w) { t.x += sh[w][lane].x; t.y += sh[w][lane].y; }
-    partial[size_t(blockIdx.y) * N + col] = t.x;
-    if (col + 1 < N) partial[size_t(blockIdx.y) * N + col + 1] = t.y;
+  for (int j = 0; j < 8; ++j) sh[warp][lane * 8 + j] = acc[j];
+  __syncthreads();
+  const int c = threadIdx.x;  // 256 threads <-> 256 columns
+  if (blockIdx.x * CS_COLS + c < N) {
+    float t = sh[0][c];
+#pragma unroll
+    for (int w = 1; w < CS_WARPS; ++w) t += sh[w][c];
+    partial[size_t(blockIdx.y) * N + blockIdx.x * CS_COLS + c] = t;
   }
 }
 __global__ void colsum_finish_kernel(const float* __restrict__ partial, int splits, int N,
@@ -246,7 +262,7 @@ __global__ void colsum_finish_kernel(const float* __restrict__ partial, int spli
   out[n] += acc;
 }
 inline int colsum_splits(int M, int N) {
-  const int col_blocks = ceil_div(N, 64);
+  const int col_blocks = ceil_div(N, CS_COLS);
   int s = ceil_div(4 * sm_count(), col_blocks);
   const int max_s = ceil_div(M, 64);
   if (s > max_s) s = max_s;
@@ -341,7 +357,7 @@ extern "C" int llmtrain_b200_bias_grad(const void* dy, int ld, int M, int N, flo
   if (M == 0 || N == 0) return 0;
   const int splits = ew::colsum_splits(M, N);
   B200_REQUIRE(scratch_bytes >= size_t(splits) * N * sizeof(float), "bias_grad: scratch too small");
-  dim3 grid(ceil_div(N, 64), splits);
+  dim3 grid(ceil_div(N, ew::CS_COLS), splits);
   ew::colsum_partial_kernel<<<grid, ew::CS_WARPS * 32, 0, stream>>>(
       static_cast<const __nv_bfloat16*>(dy), ld, M, N, static_cast<float*>(scratch));
   B200_CHECK_CUDA(cudaGetLastError());
@@ -440,7 +456,7 @@ extern "C" int llmtrain_b200_bias_grad_noalloc(const void* dy, int ld, int M, in
   }
   float* partials = nullptr;
   if (ew::noalloc_scratch(&partials)) return 1;
-  dim3 grid(ceil_div(N, 64), splits);
+  dim3 grid(ceil_div(N, ew::CS_COLS), splits);
   ew::colsum_partial_kernel<<<grid, ew::CS_WARPS * 32, 0, stream>>>(
       static_cast<const __nv_bfloat16*>(dy), ld, M, N, partials);
   B200_CHECK_CUDA(cudaGetLastError());
