@@ -219,3 +219,27 @@ def test_dummy_gpt_is_small_and_ignores_mask_in_loss() -> None:
     model.eval()
     a, _ = adapter.compute_loss(model, {"input_ids": ids, "labels": ids})
     assert torch.isfinite(a)
+
+
+def test_generation_greedy_sampling_and_checkpoint_loader(tmp_path: Path) -> None:
+    from llmtrain.generation import generate, load_model_from_checkpoint
+    from llmtrain.training import Trainer
+
+    cfg = config(tmp_path, model=TINY_GPT,
+                 trainer={"max_steps": 60, "micro_batch_size": 4, "lr": 3e-3, "weight_decay": 0.0,
+                          "save_every_steps": 60, "log_every_steps": 60, "eval_every_steps": 60})
+    Trainer(cfg, run_dir=tmp_path / "g").fit()
+    model, loaded_cfg = load_model_from_checkpoint(tmp_path / "g" / "checkpoints" / "step_000060.pt")
+    assert loaded_cfg.model.vocab_size == 16 and not model.training
+    prompt = torch.tensor([[3, 7]])
+    greedy = generate(model, prompt, max_new_tokens=5, temperature=0.0)
+    assert greedy.shape == (1, 7) and torch.equal(greedy[:, :2], prompt)
+    # the copy task teaches "repeat the current token": greedy continuation repeats the last one
+    assert greedy[0, 2:].tolist() == [7] * 5
+    g1 = generate(model, prompt, max_new_tokens=12, temperature=1.0, top_k=3,
+                  generator=torch.Generator().manual_seed(0))
+    g2 = generate(model, prompt, max_new_tokens=12, temperature=1.0, top_k=3,
+                  generator=torch.Generator().manual_seed(0))
+    assert torch.equal(g1, g2) and g1.shape == (1, 14) and int(g1.max()) < 16
+    with pytest.raises(ValueError, match="batch, time"):
+        generate(model, torch.tensor([1, 2]), max_new_tokens=1)
