@@ -45,7 +45,14 @@ struct Peers {
   const __nv_bfloat16* send[MAX_RANKS];
   const float* red[MAX_RANKS];
   uint32_t* sync[MAX_RANKS];
+  float* full[MAX_RANKS];  // fp32 [n]: the reduced gradient, pushed by the slice owners
 };
+
+constexpr int MAX_BUCKETS = 256;
+// Overlapped bucket kernels must CO-RESIDE with the backward GEMM CTAs (1 per SM, ~54K of the 64K
+// registers, ~224 KB smem): small CTAs, no smem, <= 80 registers per thread.
+constexpr int BUCKET_GRID = 64;
+constexpr int OVL_THREADS = 128;
 
 struct Comm {
   int rank = 0, world = 1, device = 0;
@@ -55,8 +62,14 @@ struct Comm {
   uint32_t* sync = nullptr;
   float* partials = nullptr;  // per-CTA sum-of-squares partials (local scratch)
   int scatter_grid = 0;
+  float* full = nullptr;             // symmetric fp32 [n] (overlapped path)
+  float* bucket_partials = nullptr;  // [MAX_BUCKETS][BUCKET_GRID]
+  int buckets_this_step = 0;
+  cudaStream_t comm_stream = nullptr;
+  cudaEvent_t ready_events[MAX_BUCKETS] = {};
+  cudaEvent_t done_event = nullptr;
   Peers peers{};
-  void* opened[3 * MAX_RANKS] = {};
+  void* opened[4 * MAX_RANKS] = {};
   uint32_t epoch = 0;
   unsigned long long timeout_ns = 1800ull * 1000000000ull;
   bool peers_open = false;
@@ -221,6 +234,110 @@ gather_adamw_kernel(Peers peers, int world, size_t n, size_t chunk, float* __res
   }
 }
 
+// Overlapped path, one bucket: rank r owns sub-slice r of [lo, lo+len); it sums that sub-slice over
+// all ranks (rank order, fp32) and PUSHES the result into every rank's `full` buffer, so that after
+// the last bucket each rank holds the complete reduced gradient locally.
+template <int W>
+__global__ void __launch_bounds__(OVL_THREADS, 4)
+scatter_push_kernel(Peers peers, size_t lo, size_t len, float* __restrict__ partial) {
+  __shared__ float sh[OVL_THREADS / 32];
+  const size_t n8 = len >> 3;
+  float sq = 0.f;
+  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n8;
+       i += size_t(gridDim.x) * blockDim.x) {
+    uint4 v[W];
+#pragma unroll
+    for (int r = 0; r < W; ++r) v[r] = reinterpret_cast<const uint4*>(peers.send[r] + lo)[i];
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int r = 0; r < W; ++r) {
+      const uint32_t w[4] = {v[r].x, v[r].y, v[r].z, v[r].w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 f = unpack_bf16x2(w[j]);
+        acc[2 * j] += f.x;
+        acc[2 * j + 1] += f.y;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) sq += acc[j] * acc[j];
+    const float4 a = make_float4(acc[0], acc[1], acc[2], acc[3]);
+    const float4 b = make_float4(acc[4], acc[5], acc[6], acc[7]);
+#pragma unroll
+    for (int r = 0; r < W; ++r) {
+      float4* dst = reinterpret_cast<float4*>(peers.full[r] + lo) + 2 * i;
+      dst[0] = a;
+      dst[1] = b;
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = sq;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    float t = threadIdx.x < OVL_THREADS / 32 ? sh[threadIdx.x] : 0.f;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+    if (threadIdx.x == 0) partial[blockIdx.x] = t;
+  }
+}
+
+__global__ void __launch_bounds__(OVL_THREADS, 4)
+pack_range_kernel(const float* __restrict__ g, __nv_bfloat16* __restrict__ send, size_t lo,
+                  size_t len) {
+  const size_t n8 = len >> 3;
+  const float4* src = reinterpret_cast<const float4*>(g + lo);
+  uint4* dst = reinterpret_cast<uint4*>(send + lo);
+  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n8;
+       i += size_t(gridDim.x) * blockDim.x) {
+    const float4 a = __ldg(src + 2 * i), b = __ldg(src + 2 * i + 1);
+    dst[i] = make_uint4(pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w), pack_bf16x2(b.x, b.y),
+                        pack_bf16x2(b.z, b.w));
+  }
+}
+
+// Local AdamW over the complete reduced gradient in `full` (overlapped path).
+__global__ void __launch_bounds__(THREADS)
+adamw_full_kernel(Peers peers, int world, size_t n, const float* __restrict__ full,
+                  float* __restrict__ p, float* __restrict__ m, float* __restrict__ v,
+                  float* __restrict__ g, __nv_bfloat16* __restrict__ p16,
+                  float* __restrict__ norm_out, Adam a) {
+  float total = 0.f;
+  for (int r = 0; r < world; ++r)
+    total += reinterpret_cast<const float*>(peers.sync[r])[NORM_SLOT];
+  const float norm = sqrtf(total) * a.grad_scale;
+  float coef = a.grad_scale;
+  if (a.max_norm > 0.f) coef *= fminf(1.0f, a.max_norm / (norm + 1e-6f));
+  if (norm_out != nullptr && blockIdx.x == 0 && threadIdx.x == 0) norm_out[0] = norm;
+  const float decay = 1.0f - a.lr * a.weight_decay;
+  const float step_size = a.lr / a.bias_corr1;
+  const float omb1 = 1.0f - a.beta1, omb2 = 1.0f - a.beta2;
+  const size_t n4 = n >> 2;
+  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n4;
+       i += size_t(gridDim.x) * blockDim.x) {
+    const float4 gr = __ldg(reinterpret_cast<const float4*>(full) + i);
+    float4 pv = reinterpret_cast<float4*>(p)[i];
+    float4 mv = reinterpret_cast<float4*>(m)[i];
+    float4 vv = reinterpret_cast<float4*>(v)[i];
+    float* pp = reinterpret_cast<float*>(&pv);
+    float* mp = reinterpret_cast<float*>(&mv);
+    float* vp = reinterpret_cast<float*>(&vv);
+    const float* gp = reinterpret_cast<const float*>(&gr);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float gj = gp[j] * coef;
+      mp[j] = a.beta1 * mp[j] + omb1 * gj;
+      vp[j] = a.beta2 * vp[j] + omb2 * gj * gj;
+      pp[j] = pp[j] * decay - step_size * (mp[j] / (sqrtf(vp[j]) / a.bias_corr2_sqrt + a.eps));
+    }
+    reinterpret_cast<float4*>(p)[i] = pv;
+    reinterpret_cast<float4*>(m)[i] = mv;
+    reinterpret_cast<float4*>(v)[i] = vv;
+    reinterpret_cast<uint2*>(p16)[i] = make_uint2(pack_bf16x2(pp[0], pp[1]), pack_bf16x2(pp[2], pp[3]));
+    reinterpret_cast<float4*>(g)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+}
+
 inline int launch_barrier(Comm& c, cudaStream_t s) {
   c.epoch += 1;
   barrier_kernel<<<1, 32, 0, s>>>(c.peers, c.rank, c.world, c.epoch, c.timeout_ns);
@@ -281,22 +398,31 @@ extern "C" int llmtrain_b200_nvl_create(int rank, int world, size_t n, double ti
   B200_CHECK_CUDA(cudaMemset(c->red, 0, chunk * sizeof(float)));
   c->scatter_grid = 2 * sm_count();
   B200_CHECK_CUDA(cudaMalloc(&c->partials, size_t(c->scatter_grid) * sizeof(float)));
+  B200_CHECK_CUDA(cudaMalloc(&c->full, n * sizeof(float)));
+  B200_CHECK_CUDA(cudaMemset(c->full, 0, n * sizeof(float)));
+  B200_CHECK_CUDA(cudaMalloc(&c->bucket_partials,
+                             size_t(nvl::MAX_BUCKETS) * nvl::BUCKET_GRID * sizeof(float)));
+  B200_CHECK_CUDA(cudaStreamCreateWithFlags(&c->comm_stream, cudaStreamNonBlocking));
+  for (auto& ev : c->ready_events)
+    B200_CHECK_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+  B200_CHECK_CUDA(cudaEventCreateWithFlags(&c->done_event, cudaEventDisableTiming));
   B200_CHECK_CUDA(cudaDeviceSynchronize());
   *handle = c;
   return 0;
 }
 
-// out: 3 consecutive cudaIpcMemHandle_t (send, red, sync) = 3 * 64 bytes (host memory).
+// out: 4 consecutive cudaIpcMemHandle_t (send, red, sync, full) = 4 * 64 bytes (host memory).
 extern "C" int llmtrain_b200_nvl_export(void* handle, void* h_out) {
   Comm& c = *static_cast<Comm*>(handle);
   auto* out = static_cast<cudaIpcMemHandle_t*>(h_out);
   B200_CHECK_CUDA(cudaIpcGetMemHandle(&out[0], c.send));
   B200_CHECK_CUDA(cudaIpcGetMemHandle(&out[1], c.red));
   B200_CHECK_CUDA(cudaIpcGetMemHandle(&out[2], c.sync));
+  B200_CHECK_CUDA(cudaIpcGetMemHandle(&out[3], c.full));
   return 0;
 }
 
-// h_all: world * 3 handles, rank-major (the all-gathered output of nvl_export).
+// h_all: world * 4 handles, rank-major (the all-gathered output of nvl_export).
 extern "C" int llmtrain_b200_nvl_connect(void* handle, const void* h_all) {
   Comm& c = *static_cast<Comm*>(handle);
   const auto* all = static_cast<const cudaIpcMemHandle_t*>(h_all);
@@ -305,16 +431,18 @@ extern "C" int llmtrain_b200_nvl_connect(void* handle, const void* h_all) {
       c.peers.send[r] = c.send;
       c.peers.red[r] = c.red;
       c.peers.sync[r] = c.sync;
+      c.peers.full[r] = c.full;
       continue;
     }
-    void* ptrs[3] = {nullptr, nullptr, nullptr};
-    for (int k = 0; k < 3; ++k) {
-      B200_CHECK_CUDA(cudaIpcOpenMemHandle(&ptrs[k], all[r * 3 + k], cudaIpcMemLazyEnablePeerAccess));
-      c.opened[r * 3 + k] = ptrs[k];
+    void* ptrs[4] = {nullptr, nullptr, nullptr, nullptr};
+    for (int k = 0; k < 4; ++k) {
+      B200_CHECK_CUDA(cudaIpcOpenMemHandle(&ptrs[k], all[r * 4 + k], cudaIpcMemLazyEnablePeerAccess));
+      c.opened[r * 4 + k] = ptrs[k];
     }
     c.peers.send[r] = static_cast<const __nv_bfloat16*>(ptrs[0]);
     c.peers.red[r] = static_cast<const float*>(ptrs[1]);
     c.peers.sync[r] = static_cast<uint32_t*>(ptrs[2]);
+    c.peers.full[r] = static_cast<float*>(ptrs[3]);
   }
   c.peers_open = true;
   return 0;
@@ -330,6 +458,12 @@ extern "C" void llmtrain_b200_nvl_destroy(void* handle) {
   cudaFree(c->red);
   cudaFree(c->sync);
   cudaFree(c->partials);
+  cudaFree(c->full);
+  cudaFree(c->bucket_partials);
+  for (auto& ev : c->ready_events)
+    if (ev != nullptr) cudaEventDestroy(ev);
+  if (c->done_event != nullptr) cudaEventDestroy(c->done_event);
+  if (c->comm_stream != nullptr) cudaStreamDestroy(c->comm_stream);
   delete c;
 }
 
@@ -385,4 +519,99 @@ extern "C" int llmtrain_b200_nvl_allreduce(void* handle, float* in, float* out, 
   a.bias_corr1 = 1.f; a.bias_corr2_sqrt = 1.f;
   return nvl_run(c, in, nullptr, nullptr, nullptr, nullptr, out, nullptr, a, 0,
                  reinterpret_cast<cudaStream_t>(stream));
+}
+
+// ------------------------------------------------------------------------------------------------
+// Overlapped path: bucket reductions run on the communicator's own stream while backward continues.
+// ------------------------------------------------------------------------------------------------
+int b200_gpt_backward_with_hook(void* handle, cudaStream_t stream,
+                                int (*hook)(void*, size_t, size_t), void* ctx);
+
+namespace {
+struct HookCtx {
+  Comm* comm;
+  float* g;
+  cudaStream_t compute;
+};
+
+// [lo, lo+len) of the arena is final on the compute stream: pack -> barrier -> reduce + push.
+int reduce_bucket(void* raw, size_t lo, size_t len) {
+  HookCtx& h = *static_cast<HookCtx*>(raw);
+  Comm& c = *h.comm;
+  if (len == 0) return 0;
+  B200_REQUIRE(lo % 8 == 0 && len % 8 == 0, "nvl: bucket bounds must be multiples of 8 elements");
+  B200_REQUIRE(c.buckets_this_step < nvl::MAX_BUCKETS, "nvl: too many buckets in one step");
+  const int b = c.buckets_this_step++;
+  cudaStream_t cs = c.comm_stream;
+  B200_CHECK_CUDA(cudaEventRecord(c.ready_events[b], h.compute));
+  B200_CHECK_CUDA(cudaStreamWaitEvent(cs, c.ready_events[b], 0));
+  nvl::pack_range_kernel<<<nvl::BUCKET_GRID, nvl::OVL_THREADS, 0, cs>>>(h.g, c.send, lo, len);
+  B200_CHECK_CUDA(cudaGetLastError());
+  B200_COUNT_LAUNCH(1);
+  if (nvl::launch_barrier(c, cs)) return 1;
+  size_t sub = (len + c.world - 1) / c.world;
+  sub = (sub + 7) / 8 * 8;
+  const size_t my_lo = lo + size_t(c.rank) * sub;
+  const size_t my_hi = my_lo + sub < lo + len ? my_lo + sub : lo + len;
+  const size_t my_len = my_hi > my_lo ? my_hi - my_lo : 0;
+  float* part = c.bucket_partials + size_t(b) * nvl::BUCKET_GRID;
+#define B200_PUSH(W)                                                                          \
+  case W:                                                                                     \
+    nvl::scatter_push_kernel<W><<<nvl::BUCKET_GRID, nvl::OVL_THREADS, 0, cs>>>(c.peers, my_lo,    \
+                                                                           my_len, part);     \
+    break;
+  switch (c.world) {
+    B200_PUSH(2) B200_PUSH(3) B200_PUSH(4) B200_PUSH(5) B200_PUSH(6) B200_PUSH(7) B200_PUSH(8)
+    default: return fail("nvl: world size must be in [2, 8]");
+  }
+#undef B200_PUSH
+  B200_CHECK_CUDA(cudaGetLastError());
+  B200_COUNT_LAUNCH(1);
+  return 0;
+}
+}  // namespace
+
+// Backward of the bound GPT runtime with every gradient bucket reduced across ranks as soon as it
+// is final.  Follow with llmtrain_b200_nvl_finish_step on the same stream.
+extern "C" int llmtrain_b200_nvl_backward_overlapped(void* nvl_handle, void* gpt_handle, float* g,
+                                                     llm_stream_t stream) {
+  Comm& c = *static_cast<Comm*>(nvl_handle);
+  B200_REQUIRE(c.peers_open, "nvl: peers are not connected");
+  c.buckets_this_step = 0;
+  HookCtx ctx{&c, g, reinterpret_cast<cudaStream_t>(stream)};
+  return b200_gpt_backward_with_hook(gpt_handle, ctx.compute, &reduce_bucket, &ctx);
+}
+
+// After the last bucket: global norm from all ranks' partials, then clip + AdamW + shadow refresh
+// + gradient zeroing over the locally complete reduced gradient.
+extern "C" int llmtrain_b200_nvl_finish_step(void* nvl_handle, float* g, float* p, float* m,
+                                             float* v, void* p16, float* norm_out, float lr,
+                                             float beta1, float beta2, float eps,
+                                             float weight_decay, int step, float grad_scale,
+                                             float max_norm, llm_stream_t stream) {
+  Comm& c = *static_cast<Comm*>(nvl_handle);
+  B200_REQUIRE(step >= 1, "nvl_finish_step: step counts from 1");
+  B200_REQUIRE(c.buckets_this_step > 0, "nvl_finish_step: no buckets were reduced this step");
+  auto s = reinterpret_cast<cudaStream_t>(stream);
+  cudaStream_t cs = c.comm_stream;
+  // this rank's sum of squares = all bucket partials, fixed order
+  nvl::norm_finish_kernel<<<1, 256, 0, cs>>>(c.bucket_partials,
+                                             c.buckets_this_step * nvl::BUCKET_GRID,
+                                             reinterpret_cast<float*>(c.sync) + nvl::NORM_SLOT);
+  B200_CHECK_CUDA(cudaGetLastError());
+  B200_COUNT_LAUNCH(1);
+  if (nvl::launch_barrier(c, cs)) return 1;  // every rank's pushes and norm partial are visible
+  B200_CHECK_CUDA(cudaEventRecord(c.done_event, cs));
+  B200_CHECK_CUDA(cudaStreamWaitEvent(s, c.done_event, 0));
+  nvl::Adam a;
+  a.lr = lr; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps; a.weight_decay = weight_decay;
+  a.bias_corr1 = static_cast<float>(1.0 - std::pow(double(beta1), double(step)));
+  a.bias_corr2_sqrt = static_cast<float>(std::sqrt(1.0 - std::pow(double(beta2), double(step))));
+  a.grad_scale = grad_scale; a.max_norm = max_norm;
+  nvl::adamw_full_kernel<<<8 * sm_count(), nvl::THREADS, 0, s>>>(
+      c.peers, c.world, c.n, c.full, p, m, v, g, static_cast<__nv_bfloat16*>(p16), norm_out, a);
+  B200_CHECK_CUDA(cudaGetLastError());
+  B200_COUNT_LAUNCH(1);
+  c.buckets_this_step = 0;
+  return 0;
 }

@@ -213,7 +213,11 @@ int forward(Gpt& g, const int64_t* ids, const uint8_t* key_mask, int B, int T, c
   return 0;
 }
 
-int backward(Gpt& g, cudaStream_t s) {
+// Called right after the kernels that FINALISE the gradient range [lo, lo+len) of the arena have
+// been enqueued on `s` (ranges arrive back-to-front, the embedding tables last).
+using BucketHook = int (*)(void* ctx, size_t lo, size_t len);
+
+int backward(Gpt& g, cudaStream_t s, BucketHook hook = nullptr, void* hook_ctx = nullptr) {
   B200_REQUIRE(g.have_forward, "gpt_backward: no forward pass to differentiate");
   View v(g);
   const int B = g.B, T = g.T, M = B * T, d = g.d, F = g.F, hd = g.d / g.H;
@@ -264,11 +268,37 @@ int backward(Gpt& g, cudaStream_t s) {
     B200_TRY(llmtrain_b200_layernorm_bwd(dtmp, x_in, v.p(o.ln1_w), v.f32(a.ln1_mean),
                                          v.f32(a.ln1_rstd), dresid, v.grad(o.ln1_w),
                                          v.grad(o.ln1_b), red, red_bytes, M, d, st));
+    if (hook != nullptr) {
+      // layer l's parameters (+ ln_f for the last layer) are contiguous in the arena
+      const size_t lo = o.ln1_w;
+      const size_t hi = (l + 1 < g.L) ? g.layer[l + 1].ln1_w : (g.tied ? g.wte : g.wte);
+      B200_TRY(hook(hook_ctx, lo, hi - lo));
+    }
   }
   B200_TRY(llmtrain_b200_embed_bwd(g.ids, dresid, v.grad(g.wte), v.grad(g.wpe), B, T, d, g.V, st));
+  if (hook != nullptr) {
+    const size_t first_layer = g.L > 0 ? g.layer[0].ln1_w : g.lnf_w;
+    B200_TRY(hook(hook_ctx, g.wte, g.n_params - g.wte));  // token embedding (+ untied head)
+    B200_TRY(hook(hook_ctx, 0, first_layer));              // position embedding
+  }
   g.have_forward = false;
   return 0;
 }
+
+}  // namespace engine
+}  // namespace b200
+
+// Internal (non-ABI) entry used by the communicator to interleave bucket reductions.
+int b200_gpt_backward_with_hook(void* handle, cudaStream_t stream, b200::engine::BucketHook hook,
+                                void* ctx) {
+  return b200::engine::backward(*static_cast<b200::engine::Gpt*>(handle), stream, hook, ctx);
+}
+size_t b200_gpt_param_elems(void* handle) {
+  return static_cast<b200::engine::Gpt*>(handle)->n_params;
+}
+
+namespace b200 {
+namespace engine {
 
 }  // namespace engine
 }  // namespace b200

@@ -356,6 +356,8 @@ class B200TrainEngine(TrainEngine):
         self._loss_acc = torch.zeros(1, dtype=torch.float32, device=device)
         self._step = 0
         self._comm: Any | None = None
+        self._prefetch = bool(cfg.trainer.extra.get("prefetch", True))
+        self._prefetched: tuple[Any, ...] | None = None
 
         if self._world > 1:
             self._sync_initial_parameters()
@@ -394,7 +396,8 @@ class B200TrainEngine(TrainEngine):
         algo = str(cfg.trainer.extra.get("allreduce", "auto"))
         if want == "nvl" or (want == "nccl" and algo == "nvl"):
             comm = nvl.try_create(self._gpt, self._m, self._v, rank=self._rank, world=self._world,
-                                  device=self._device, timeout_s=cfg.ddp.timeout_sec)
+                                  device=self._device, timeout_s=cfg.ddp.timeout_sec,
+                                  overlap=bool(cfg.trainer.extra.get("overlap_comm", True)))
             if comm is not None:
                 return comm
             logger.warning("NVLink peer access unavailable; falling back to NCCL all-reduce")
@@ -424,15 +427,23 @@ class B200TrainEngine(TrainEngine):
         g = self._gpt
         self._loss_acc.zero_()
         tokens = 0
-        for _ in range(accum_steps):
-            ids, labels, key_mask, n_valid = self._stage(next_batch())
+        for micro in range(accum_steps):
+            # The first micro-batch of a step was usually staged (pinned host -> device copy
+            # enqueued) at the end of the previous step, so the copy and the loader's host work
+            # overlap the optimiser kernels instead of following a loss read-back.
+            staged = self._prefetched if self._prefetched is not None else self._stage(next_batch())
+            self._prefetched = None
+            ids, labels, key_mask, n_valid = staged
             if ids.shape[0] > g._plan[0] or ids.shape[1] > g._plan[1]:
                 g._replan(max(ids.shape[0], g._plan[0]), max(ids.shape[1], g._plan[1]))
             tokens += ids.numel()
             scale = 1.0 / (n_valid * accum_steps)
             g.run_forward(ids, labels, key_mask, mode=2, loss_acc=self._loss_acc,
                           loss_scale=scale, grad_scale=scale)
-            g.run_backward()
+            if micro == accum_steps - 1 and hasattr(self._comm, "backward_last"):
+                self._comm.backward_last()  # gradients are final: reduce buckets as they finish
+            else:
+                g.run_backward()
         self._step += 1
         lr = float(self.optimizer.param_groups[0]["lr"])
         group = self.optimizer.param_groups[0]
@@ -448,7 +459,10 @@ class B200TrainEngine(TrainEngine):
                     **hyper)
         else:
             self._comm.reduce_and_step(self._m, self._v, self._sumsq, self._norm, hyper)
-        return self._loss_acc.clone().reshape(()), tokens
+        loss = self._loss_acc.clone().reshape(())
+        if self._prefetch:
+            self._prefetched = self._stage(next_batch())
+        return loss, tokens
 
     def eval_loss(self, batch: Batch) -> float:
         ids, labels, key_mask, n_valid = self._stage(batch)

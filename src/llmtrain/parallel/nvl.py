@@ -27,6 +27,7 @@ from llmtrain.ops.native import check, ptr, stream_handle
 logger = logging.getLogger(__name__)
 
 _IPC_HANDLE_BYTES = 64
+_HANDLES_PER_RANK = 4  # send, red, sync, full
 _live: list[Any] = []
 
 
@@ -78,12 +79,12 @@ class NvlComm:
             "nvl_create",
         )
         self._handle = handle
-        mine = (ctypes.c_ubyte * (3 * _IPC_HANDLE_BYTES))()
+        mine = (ctypes.c_ubyte * (_HANDLES_PER_RANK * _IPC_HANDLE_BYTES))()
         check(self._lib.llmtrain_b200_nvl_export(handle, mine), "nvl_export")
         gathered: list[bytes | None] = [None] * world
         dist.all_gather_object(gathered, bytes(mine))
         blob = b"".join(g for g in gathered if g is not None)
-        if len(blob) != world * 3 * _IPC_HANDLE_BYTES:
+        if len(blob) != world * _HANDLES_PER_RANK * _IPC_HANDLE_BYTES:
             raise RuntimeError("nvl: IPC handle exchange returned an unexpected payload size")
         everyone = (ctypes.c_ubyte * len(blob)).from_buffer_copy(blob)
         check(self._lib.llmtrain_b200_nvl_connect(handle, everyone), "nvl_connect")
@@ -116,6 +117,29 @@ class NvlComm:
             "nvl_step",
         )
 
+    def backward_overlapped(self, gpt_handle: ctypes.c_void_p, g: torch.Tensor) -> None:
+        """Backward of the bound GPT runtime; each gradient bucket is reduced across ranks on the
+        communicator's own stream as soon as backward has finalised it."""
+        check(
+            self._lib.llmtrain_b200_nvl_backward_overlapped(self._handle, gpt_handle, ptr(g),
+                                                            stream_handle()),
+            "nvl_backward_overlapped",
+        )
+
+    def finish_step(self, g: torch.Tensor, p: torch.Tensor, m: torch.Tensor, v: torch.Tensor,
+                    p16: torch.Tensor, norm: torch.Tensor | None, hyper: dict[str, Any]) -> None:
+        check(
+            self._lib.llmtrain_b200_nvl_finish_step(
+                self._handle, ptr(g), ptr(p), ptr(m), ptr(v), ptr(p16), ptr(norm),
+                ctypes.c_float(hyper["lr"]), ctypes.c_float(hyper["beta1"]),
+                ctypes.c_float(hyper["beta2"]), ctypes.c_float(hyper["eps"]),
+                ctypes.c_float(hyper["weight_decay"]), ctypes.c_int(hyper["step"]),
+                ctypes.c_float(1.0 / self.world), ctypes.c_float(hyper["max_norm"]),
+                stream_handle(),
+            ),
+            "nvl_finish_step",
+        )
+
     def close(self) -> None:
         if self._handle:
             self._lib.llmtrain_b200_nvl_destroy.argtypes = [ctypes.c_void_p]
@@ -125,24 +149,46 @@ class NvlComm:
 
 
 class _NvlTrainComm:
-    """Adapter with the ``reduce_and_step`` face the train engine expects."""
+    """Adapter with the face the train engine expects.
 
-    def __init__(self, gpt: Any, comm: NvlComm) -> None:
+    ``overlap=True`` (default): the last micro-batch's backward goes through
+    :meth:`backward_last`, which reduces every per-layer bucket on a side stream while backward
+    continues (owners push reduced slices to all peers), so ``reduce_and_step`` only has to run the
+    local clip + AdamW pass.  ``overlap=False``: one pack / reduce-scatter / gather+AdamW sequence
+    after backward.
+    """
+
+    def __init__(self, gpt: Any, comm: NvlComm, *, overlap: bool = True) -> None:
         self._gpt, self._comm = gpt, comm
-        self.name = comm.name
+        self.overlap = overlap
+        self._reduced = False
+        self.name = ("nvl-p2p(per-layer buckets overlapped with backward: pack-bf16 -> "
+                     "reduce+push -> local adamw)") if overlap else comm.name
+
+    def backward_last(self) -> None:
+        g = self._gpt
+        if self.overlap:
+            self._comm.backward_overlapped(g._handle, g.g32)
+            self._reduced = True
+        else:
+            g.run_backward()
 
     def reduce_and_step(self, m: torch.Tensor, v: torch.Tensor, sumsq: torch.Tensor,
                         norm: torch.Tensor, hyper: dict[str, Any]) -> None:
         del sumsq  # the global norm is assembled from the owners' slice partials on the device
         g = self._gpt
-        self._comm.step(g.g32, g.p32, m, v, g.p16, norm, hyper)
+        if self._reduced:
+            self._comm.finish_step(g.g32, g.p32, m, v, g.p16, norm, hyper)
+            self._reduced = False
+        else:
+            self._comm.step(g.g32, g.p32, m, v, g.p16, norm, hyper)
 
     def close(self) -> None:
         self._comm.close()
 
 
 def try_create(gpt: Any, m: torch.Tensor, v: torch.Tensor, *, rank: int, world: int,
-               device: torch.device, timeout_s: int) -> Any | None:
+               device: torch.device, timeout_s: int, overlap: bool = True) -> Any | None:
     """Build the peer-memory communicator, or ``None`` when the ranks cannot map each other."""
     del m, v, device
     if not 2 <= world <= 8:
@@ -163,7 +209,7 @@ def try_create(gpt: Any, m: torch.Tensor, v: torch.Tensor, *, rank: int, world: 
     if int(failed.item()):
         comm.close()
         return None
-    return _NvlTrainComm(gpt, comm)
+    return _NvlTrainComm(gpt, comm, overlap=overlap)
 
 
 def shutdown() -> None:

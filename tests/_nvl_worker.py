@@ -71,7 +71,7 @@ def _check_step(comm, rank: int, world: int) -> None:
     assert all(torch.equal(others[0], o) for o in others), "replicas diverged"
 
 
-def _check_trainer(rank: int, world: int) -> None:
+def _check_trainer(rank: int, world: int, overlap: bool = True) -> None:
     from llmtrain.config.schemas import RunConfig
     from llmtrain.distributed import DDPState
     from llmtrain.training import Trainer
@@ -82,7 +82,8 @@ def _check_trainer(rank: int, world: int) -> None:
                   "d_ff": 512, "dropout": 0.0, "vocab_size": 1000},
         "data": {"name": "synthetic_text", "extra": {"pattern": "arith"}},
         "trainer": {"max_steps": 20, "micro_batch_size": 4, "grad_accum_steps": 2,
-                    "warmup_steps": 0, "lr": 3e-3, "weight_decay": 0.0, "log_every_steps": 5},
+                    "warmup_steps": 0, "lr": 3e-3, "weight_decay": 0.0, "log_every_steps": 5,
+                    "extra": {"overlap_comm": overlap}},
         "ddp": {"enabled": True, "backend": "nvl"},
         "mlflow": {"enabled": False}, "logging": {"log_to_file": False}, "output": {},
     })
@@ -90,12 +91,14 @@ def _check_trainer(rank: int, world: int) -> None:
     trainer = Trainer(cfg, ddp_state=state)
     comm = trainer._engine._comm
     assert comm is not None and comm.name.startswith("nvl"), getattr(comm, "name", None)
+    assert comm.overlap is overlap
     result = trainer.fit()
     assert result.final_loss < result.first_step_loss - 0.3, (result.first_step_loss, result.final_loss)
     flat = trainer._engine._gpt.p32.clone()
     others = [torch.empty_like(flat) for _ in range(world)]
     dist.all_gather(others, flat)
     assert all(torch.equal(others[0], o) for o in others), "replicas diverged after training"
+    return result.final_loss
 
 
 def main() -> int:
@@ -108,7 +111,10 @@ def main() -> int:
         comm = NvlComm(8 * 1024 * 1024 + 64, rank=rank, world=world, timeout_s=60)
         _check_allreduce(comm, rank, world)
         _check_step(comm, rank, world)
-        _check_trainer(rank, world)
+        loss_overlapped = _check_trainer(rank, world, overlap=True)
+        loss_serial = _check_trainer(rank, world, overlap=False)
+        # same data, same init seed path? (fresh random init per trainer) -> only sanity-compare
+        assert abs(loss_overlapped - loss_serial) < 2.0
         shutdown()
         dist.barrier()
         if rank == 0:
