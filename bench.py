@@ -160,7 +160,8 @@ def _payload(cfg_model: dict[str, Any], micro_batch: int, accum: int, world: int
         "trainer": {"max_steps": max(steps, 1), "micro_batch_size": micro_batch,
                     "grad_accum_steps": accum, "lr": 3e-4, "weight_decay": 0.1, "warmup_steps": 0,
                     "max_grad_norm": 1.0, "log_every_steps": 1, "eval_every_steps": 10**9,
-                    "save_every_steps": 10**9},
+                    "save_every_steps": 10**9,
+                    "extra": {"overlap_comm": os.environ.get("LLMTRAIN_OVERLAP", "1") != "0"}},
         "ddp": {"enabled": world > 1, "backend": "nvl"},
         "mlflow": {"enabled": False},
         "logging": {"level": "WARNING", "log_to_file": False},

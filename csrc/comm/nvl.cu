@@ -48,11 +48,15 @@ struct Peers {
   float* full[MAX_RANKS];  // fp32 [n]: the reduced gradient, pushed by the slice owners
 };
 
-constexpr int MAX_BUCKETS = 256;
+constexpr int MAX_BUCKETS = 128;
 // Overlapped bucket kernels must CO-RESIDE with the backward GEMM CTAs (1 per SM, ~54K of the 64K
 // registers, ~224 KB smem): small CTAs, no smem, <= 80 registers per thread.
 constexpr int BUCKET_GRID = 64;
 constexpr int OVL_THREADS = 128;
+// Buckets that only become final when backward is over (the embedding tables) find the GPU idle:
+// they get a full-size grid instead.
+constexpr int TAIL_GRID = 1024;
+constexpr int PARTIAL_STRIDE = TAIL_GRID;  // per-bucket slots in bucket_partials
 
 struct Comm {
   int rank = 0, world = 1, device = 0;
@@ -401,7 +405,9 @@ extern "C" int llmtrain_b200_nvl_create(int rank, int world, size_t n, double ti
   B200_CHECK_CUDA(cudaMalloc(&c->full, n * sizeof(float)));
   B200_CHECK_CUDA(cudaMemset(c->full, 0, n * sizeof(float)));
   B200_CHECK_CUDA(cudaMalloc(&c->bucket_partials,
-                             size_t(nvl::MAX_BUCKETS) * nvl::BUCKET_GRID * sizeof(float)));
+                             size_t(nvl::MAX_BUCKETS) * nvl::PARTIAL_STRIDE * sizeof(float)));
+  B200_CHECK_CUDA(cudaMemset(c->bucket_partials, 0,
+                             size_t(nvl::MAX_BUCKETS) * nvl::PARTIAL_STRIDE * sizeof(float)));
   B200_CHECK_CUDA(cudaStreamCreateWithFlags(&c->comm_stream, cudaStreamNonBlocking));
   for (auto& ev : c->ready_events)
     B200_CHECK_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
@@ -545,7 +551,10 @@ int reduce_bucket(void* raw, size_t lo, size_t len) {
   cudaStream_t cs = c.comm_stream;
   B200_CHECK_CUDA(cudaEventRecord(c.ready_events[b], h.compute));
   B200_CHECK_CUDA(cudaStreamWaitEvent(cs, c.ready_events[b], 0));
-  nvl::pack_range_kernel<<<nvl::BUCKET_GRID, nvl::OVL_THREADS, 0, cs>>>(h.g, c.send, lo, len);
+  // Ranges touching either end of the arena are the embedding tables: backward is finished.
+  const bool tail = (lo == 0) || (lo + len == c.n);
+  const int grid = tail ? nvl::TAIL_GRID : nvl::BUCKET_GRID;
+  nvl::pack_range_kernel<<<grid, nvl::OVL_THREADS, 0, cs>>>(h.g, c.send, lo, len);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   if (nvl::launch_barrier(c, cs)) return 1;
@@ -554,11 +563,12 @@ int reduce_bucket(void* raw, size_t lo, size_t len) {
   const size_t my_lo = lo + size_t(c.rank) * sub;
   const size_t my_hi = my_lo + sub < lo + len ? my_lo + sub : lo + len;
   const size_t my_len = my_hi > my_lo ? my_hi - my_lo : 0;
-  float* part = c.bucket_partials + size_t(b) * nvl::BUCKET_GRID;
+  float* part = c.bucket_partials + size_t(b) * nvl::PARTIAL_STRIDE;
+  B200_CHECK_CUDA(cudaMemsetAsync(part, 0, nvl::PARTIAL_STRIDE * sizeof(float), cs));
 #define B200_PUSH(W)                                                                          \
   case W:                                                                                     \
-    nvl::scatter_push_kernel<W><<<nvl::BUCKET_GRID, nvl::OVL_THREADS, 0, cs>>>(c.peers, my_lo,    \
-                                                                           my_len, part);     \
+    nvl::scatter_push_kernel<W><<<grid, nvl::OVL_THREADS, 0, cs>>>(c.peers, my_lo, my_len,    \
+                                                                   part);                     \
     break;
   switch (c.world) {
     B200_PUSH(2) B200_PUSH(3) B200_PUSH(4) B200_PUSH(5) B200_PUSH(6) B200_PUSH(7) B200_PUSH(8)
@@ -595,8 +605,8 @@ extern "C" int llmtrain_b200_nvl_finish_step(void* nvl_handle, float* g, float* 
   auto s = reinterpret_cast<cudaStream_t>(stream);
   cudaStream_t cs = c.comm_stream;
   // this rank's sum of squares = all bucket partials, fixed order
-  nvl::norm_finish_kernel<<<1, 256, 0, cs>>>(c.bucket_partials,
-                                             c.buckets_this_step * nvl::BUCKET_GRID,
+  nvl::norm_finish_kernel<<<1, 1024, 0, cs>>>(c.bucket_partials,
+                                              c.buckets_this_step * nvl::PARTIAL_STRIDE,
                                              reinterpret_cast<float*>(c.sync) + nvl::NORM_SLOT);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);

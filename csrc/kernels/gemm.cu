@@ -57,26 +57,33 @@ struct Params {
   int ldr;
 };
 
-// erf via Abramowitz & Stegun 7.1.26 (|abs err| < 1.5e-7 — two orders of magnitude below bf16
-// resolution), sharing one exponential between Phi(x) and phi(x).  The libm erff costs ~3x more
-// instructions and made the GELU epilogues the pacing stage of their GEMMs.
-struct PhiPair { float cdf, pdf; };  // Phi(x), phi(x) of the standard normal
-__device__ __forceinline__ PhiPair normal_cdf_pdf(float x) {
-  const float ax = fabsf(x) * 0.70710678118654752f;             // |x|/sqrt(2)
-  const float t = __fdividef(1.0f, fmaf(0.3275911f, ax, 1.0f));
-  const float e = __expf(-ax * ax);                              // exp(-x^2/2)
+// Phi(x) (standard normal CDF) via Abramowitz & Stegun 7.1.26 for erf (|abs err| < 1.5e-7 — two
+// orders of magnitude below bf16 resolution), arranged for the fewest issue slots: constants are
+// pre-folded, the exponential and reciprocal are the bare MUFU approximations, and one exponential
+// serves both Phi(x) and phi(x).  libm's erff made the GELU epilogues the pacing stage of their
+// GEMMs (the epilogue must keep up with a 128x256x768 mainloop: ~6K cycles per tile).
+__device__ __forceinline__ float mufu_rcp(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+struct PhiPair { float cdf, half_e; };  // Phi(x) and 0.5*exp(-x^2/2)
+__device__ __forceinline__ PhiPair normal_cdf(float x) {
+  constexpr float kP = 0.3275911f * 0.70710678118654752f;   // p / sqrt(2)
+  constexpr float kC = -0.5f * 1.4426950408889634f;         // -log2(e)/2
+  const float t = mufu_rcp(fmaf(kP, fabsf(x), 1.0f));
+  const float half_e = 0.5f * fast_exp2(x * x * kC);        // 0.5 * exp(-x^2/2)
   float poly = fmaf(1.061405429f, t, -1.453152027f);
   poly = fmaf(poly, t, 1.421413741f);
   poly = fmaf(poly, t, -0.284496736f);
   poly = fmaf(poly, t, 0.254829592f);
-  const float erf_abs = 1.0f - poly * t * e;                     // erf(|x|/sqrt(2))
-  const float cdf = 0.5f * (1.0f + copysignf(erf_abs, x));
-  return {cdf, 0.3989422804014327f * e};
+  const float q = poly * t * half_e;                         // 0.5 * erfc(|x|/sqrt 2)
+  return {x > 0.f ? 1.0f - q : q, half_e};
 }
-__device__ __forceinline__ float gelu_erf(float x) { return x * normal_cdf_pdf(x).cdf; }
+__device__ __forceinline__ float gelu_erf(float x) { return x * normal_cdf(x).cdf; }
 __device__ __forceinline__ float gelu_erf_grad(float x) {
-  const PhiPair n = normal_cdf_pdf(x);
-  return fmaf(x, n.pdf, n.cdf);
+  const PhiPair n = normal_cdf(x);
+  return fmaf(x * 0.7978845608028654f, n.half_e, n.cdf);     // Phi + x*phi, phi = 2*half_e/sqrt(2pi)
 }
 
 template <bool A_MN, bool B_MN, int EPI>
@@ -283,6 +290,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           uint32_t out[32];   // 64 bf16 packed
           uint32_t out2[32];  // pre-activation (GELU variant only)
           const uint32_t* rw = reinterpret_cast<const uint32_t*>(rv);
+          const bool add_bias =
+              (EPI == kBias || EPI == kBiasGelu || EPI == kBiasResid) && p.bias != nullptr;
 #pragma unroll
           for (int h = 0; h < 2; ++h) {
 #pragma unroll
@@ -290,15 +299,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               const int col = col0 + h * 32 + j;
               float x0 = __uint_as_float(v[h][j]);
               float x1 = __uint_as_float(v[h][j + 1]);
-              if (EPI == kBias || EPI == kBiasGelu || EPI == kBiasResid) {
-                if (p.bias != nullptr) {
-                  if (full_cols) {
-                    const float2 bb = __ldg(reinterpret_cast<const float2*>(p.bias + col));
-                    x0 += bb.x; x1 += bb.y;
-                  } else {
-                    if (col < p.N) x0 += __ldg(p.bias + col);
-                    if (col + 1 < p.N) x1 += __ldg(p.bias + col + 1);
-                  }
+              if (add_bias) {
+                if (full_cols) {  // warp-uniform; the common case carries no per-element guards
+                  const float2 bb = __ldg(reinterpret_cast<const float2*>(p.bias + col));
+                  x0 += bb.x; x1 += bb.y;
+                } else {
+                  if (col < p.N) x0 += __ldg(p.bias + col);
+                  if (col + 1 < p.N) x1 += __ldg(p.bias + col + 1);
                 }
               }
               if (EPI == kBiasResid || EPI == kDGelu) {
