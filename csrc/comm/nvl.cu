@@ -56,7 +56,7 @@ constexpr int OVL_THREADS = 128;
 // Buckets that only become final when backward is over (the embedding tables) find the GPU idle:
 // they get a full-size grid instead.
 constexpr int TAIL_GRID = 1024;
-constexpr int PARTIAL_STRIDE = TAIL_GRID;  // per-bucket slots in bucket_partials
+constexpr int PARTIAL_STRIDE = TAIL_GRID * (OVL_THREADS / 32);  // one slot per warp per bucket
 
 struct Comm {
   int rank = 0, world = 1, device = 0;
@@ -244,7 +244,6 @@ gather_adamw_kernel(Peers peers, int world, size_t n, size_t chunk, float* __res
 template <int W>
 __global__ void __launch_bounds__(OVL_THREADS, 4)
 scatter_push_kernel(Peers peers, size_t lo, size_t len, float* __restrict__ partial) {
-  __shared__ float sh[OVL_THREADS / 32];
   const size_t n8 = len >> 3;
   float sq = 0.f;
   for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n8;
@@ -276,14 +275,10 @@ scatter_push_kernel(Peers peers, size_t lo, size_t len, float* __restrict__ part
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
-  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = sq;
-  __syncthreads();
-  if (threadIdx.x < 32) {
-    float t = threadIdx.x < OVL_THREADS / 32 ? sh[threadIdx.x] : 0.f;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
-    if (threadIdx.x == 0) partial[blockIdx.x] = t;
-  }
+  // No shared memory on purpose (see OVL_THREADS): one partial per warp, summed later in a fixed
+  // order by norm_finish_kernel.
+  if ((threadIdx.x & 31) == 0)
+    partial[blockIdx.x * (OVL_THREADS / 32) + (threadIdx.x >> 5)] = sq;
 }
 
 __global__ void __launch_bounds__(OVL_THREADS, 4)

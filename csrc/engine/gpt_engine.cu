@@ -17,6 +17,8 @@
 // finishes gradient regions from the end of the arena towards the front, which is the bucket
 // order the comm engine wants.
 
+#include <nvtx3/nvToolsExt.h>  // header-only NVTX3: no link dependency, no cost without a tool
+
 #include <vector>
 
 #include "../common/host.cuh"
@@ -160,6 +162,12 @@ struct View {
     if ((call) != 0) return 1; \
   } while (0)
 
+// Phase / layer ranges for Nsight timelines (the reference has no tracing at all).
+struct NvtxRange {
+  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+};
+
 inline int linear_fwd(int epi, int M, int N, int K, const void* x, const void* w, void* y, void* y2,
                       const float* bias, const void* r, cudaStream_t s) {
   return llmtrain_b200_gemm(0, epi, M, N, K, x, K, w, K, y, N, y2, N, bias, r, N,
@@ -180,11 +188,13 @@ inline int linear_wgrad(int M, int N, int K, const void* dy, int ld_dy, const vo
 
 int forward(Gpt& g, const int64_t* ids, const uint8_t* key_mask, int B, int T, cudaStream_t s) {
   View v(g);
+  NvtxRange phase("gpt.forward");
   const int M = B * T, d = g.d, F = g.F, hd = g.d / g.H;
   auto st = reinterpret_cast<llm_stream_t>(s);
   B200_TRY(llmtrain_b200_embed_fwd(ids, v.w(g.wte), v.w(g.wpe), v.bf(g.a_x0), B, T, d, g.V, st));
   const __nv_bfloat16* x = v.bf(g.a_x0);
   for (int l = 0; l < g.L; ++l) {
+    NvtxRange layer_range("layer.fwd");
     const LayerOffsets& o = g.layer[l];
     const LayerActs& a = g.acts[l];
     B200_TRY(llmtrain_b200_layernorm_fwd(x, v.p(o.ln1_w), v.p(o.ln1_b), v.bf(a.ln1),
@@ -220,6 +230,7 @@ using BucketHook = int (*)(void* ctx, size_t lo, size_t len);
 int backward(Gpt& g, cudaStream_t s, BucketHook hook = nullptr, void* hook_ctx = nullptr) {
   B200_REQUIRE(g.have_forward, "gpt_backward: no forward pass to differentiate");
   View v(g);
+  NvtxRange phase("gpt.backward");
   const int B = g.B, T = g.T, M = B * T, d = g.d, F = g.F, hd = g.d / g.H;
   auto st = reinterpret_cast<llm_stream_t>(s);
   void* red = g.act + g.a_red_scratch;
@@ -242,6 +253,7 @@ int backward(Gpt& g, cudaStream_t s, BucketHook hook = nullptr, void* hook_ctx =
                                        v.grad(g.lnf_b), red, red_bytes, M, d, st));
 
   for (int l = g.L - 1; l >= 0; --l) {
+    NvtxRange layer_range("layer.bwd");
     const LayerOffsets& o = g.layer[l];
     const LayerActs& a = g.acts[l];
     const __nv_bfloat16* x_in = l > 0 ? v.bf(g.acts[l - 1].resid2) : v.bf(g.a_x0);

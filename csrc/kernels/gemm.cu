@@ -39,7 +39,10 @@ constexpr int EPI_BUF_BYTES = 32 * 128;  // 32 rows x 128 B per staging buffer
 constexpr int EPI_BYTES = EPI_WARPS * EPI_BUF_BYTES;
 constexpr int NUM_THREADS = 32 * (2 + EPI_WARPS);
 constexpr int TMEM_COLS = 512;
-constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + 256 /*barriers*/ + 1024 /*align*/;
+// No alignment slack: the kernel has no static shared memory, so its dynamic window starts at the
+// 1024 B-aligned base of the CTA's allocation.  Staying under 225 KB leaves room for one of the
+// communicator's small, smem-free CTAs to share the SM during the overlapped bucket reduction.
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + 256 /*barriers*/;
 
 enum Epi : int {
   kBias = 0,      // C = acc (+ bias)
@@ -91,9 +94,9 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
             const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmC2,
             const Params p) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                             ~uintptr_t(1023));
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
+  if ((smem_u32(smem) & 1023u) != 0) __trap();
   uint8_t* epi_smem = smem + STAGES * STAGE_BYTES;
   uint64_t* bars = reinterpret_cast<uint64_t*>(epi_smem + EPI_BYTES);
   uint64_t* full_bar = bars;                  // [STAGES]
