@@ -218,12 +218,14 @@ def run_ours(args: argparse.Namespace) -> dict[str, Any]:
                 engine.train_step(next_device_batch, accum)
 
         steps_device(args.warmup)
+        engine.collect_phase_timing()  # drop warm-up samples
         launches_before = int(lib.llmtrain_b200_launch_count())
         with ClockSampler(torch.cuda.current_device()) as clocks:
             ms = _timed(lambda: steps_device(args.steps), world)
         launches = int(lib.llmtrain_b200_launch_count()) - launches_before
         ms = _max_over_ranks(ms, world)
         value = tokens_per_step * args.steps / (ms / 1e3)
+        phases = engine.collect_phase_timing()
 
         # ---- end-to-end arm: Trainer.fit, pinned-host inputs every step, loss read every step ---
         trainer.fit(max_steps_override=args.warmup)
@@ -274,6 +276,8 @@ def run_ours(args: argparse.Namespace) -> dict[str, Any]:
             "gpu_launches": launches,
             "peak_memory_gb": torch.cuda.max_memory_allocated() / 2**30,
         }
+        if phases:
+            result["phase_ms_rank0"] = phases
         return result if rank == 0 else {}
     finally:
         if ddp_state is not None:

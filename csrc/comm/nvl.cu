@@ -27,6 +27,7 @@
 // first barrier, which a peer only signals once its gather has finished.
 
 #include <cmath>
+#include <cstdlib>
 #include <vector>
 
 #include "../common/host.cuh"
@@ -69,6 +70,7 @@ struct Comm {
   float* full = nullptr;             // symmetric fp32 [n] (overlapped path)
   float* bucket_partials = nullptr;  // [MAX_BUCKETS][BUCKET_GRID]
   int buckets_this_step = 0;
+  int bucket_grid = BUCKET_GRID;
   cudaStream_t comm_stream = nullptr;
   cudaEvent_t ready_events[MAX_BUCKETS] = {};
   cudaEvent_t done_event = nullptr;
@@ -403,7 +405,17 @@ extern "C" int llmtrain_b200_nvl_create(int rank, int world, size_t n, double ti
                              size_t(nvl::MAX_BUCKETS) * nvl::PARTIAL_STRIDE * sizeof(float)));
   B200_CHECK_CUDA(cudaMemset(c->bucket_partials, 0,
                              size_t(nvl::MAX_BUCKETS) * nvl::PARTIAL_STRIDE * sizeof(float)));
-  B200_CHECK_CUDA(cudaStreamCreateWithFlags(&c->comm_stream, cudaStreamNonBlocking));
+  {
+    // Highest priority: the few small comm CTAs should win any CTA slot that frees up, otherwise
+    // a bucket's reduction trails far behind the backward pass it is meant to overlap.
+    int least = 0, greatest = 0;
+    B200_CHECK_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+    B200_CHECK_CUDA(cudaStreamCreateWithPriority(&c->comm_stream, cudaStreamNonBlocking, greatest));
+  }
+  if (const char* env = std::getenv("LLMTRAIN_NVL_BUCKET_GRID")) {
+    const int v = std::atoi(env);
+    if (v >= 1 && v <= nvl::TAIL_GRID) c->bucket_grid = v;
+  }
   for (auto& ev : c->ready_events)
     B200_CHECK_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
   B200_CHECK_CUDA(cudaEventCreateWithFlags(&c->done_event, cudaEventDisableTiming));
@@ -548,7 +560,7 @@ int reduce_bucket(void* raw, size_t lo, size_t len) {
   B200_CHECK_CUDA(cudaStreamWaitEvent(cs, c.ready_events[b], 0));
   // Ranges touching either end of the arena are the embedding tables: backward is finished.
   const bool tail = (lo == 0) || (lo + len == c.n);
-  const int grid = tail ? nvl::TAIL_GRID : nvl::BUCKET_GRID;
+  const int grid = tail ? nvl::TAIL_GRID : c.bucket_grid;
   nvl::pack_range_kernel<<<grid, nvl::OVL_THREADS, 0, cs>>>(h.g, c.send, lo, len);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);

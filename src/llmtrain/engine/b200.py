@@ -358,6 +358,13 @@ class B200TrainEngine(TrainEngine):
         self._comm: Any | None = None
         self._prefetch = bool(cfg.trainer.extra.get("prefetch", True))
         self._prefetched: tuple[Any, ...] | None = None
+        # Optional CUDA-event phase timeline (LLMTRAIN_PHASE_TIMING=1): forward / backward(+bucket
+        # reductions) / reduce+optimiser, averaged per step in ``phase_ms``.
+        import os
+
+        self._phase_timing = os.environ.get("LLMTRAIN_PHASE_TIMING", "0") == "1"
+        self._phase_events: list[list[torch.cuda.Event]] = []
+        self.phase_ms: dict[str, float] = {}
 
         if self._world > 1:
             self._sync_initial_parameters()
@@ -438,12 +445,15 @@ class B200TrainEngine(TrainEngine):
                 g._replan(max(ids.shape[0], g._plan[0]), max(ids.shape[1], g._plan[1]))
             tokens += ids.numel()
             scale = 1.0 / (n_valid * accum_steps)
+            marks = self._mark()
             g.run_forward(ids, labels, key_mask, mode=2, loss_acc=self._loss_acc,
                           loss_scale=scale, grad_scale=scale)
+            self._mark(marks)
             if micro == accum_steps - 1 and hasattr(self._comm, "backward_last"):
                 self._comm.backward_last()  # gradients are final: reduce buckets as they finish
             else:
                 g.run_backward()
+            self._mark(marks)
         self._step += 1
         lr = float(self.optimizer.param_groups[0]["lr"])
         group = self.optimizer.param_groups[0]
@@ -459,10 +469,36 @@ class B200TrainEngine(TrainEngine):
                     **hyper)
         else:
             self._comm.reduce_and_step(self._m, self._v, self._sumsq, self._norm, hyper)
+        self._mark(marks, final=True)
         loss = self._loss_acc.clone().reshape(())
         if self._prefetch:
             self._prefetched = self._stage(next_batch())
         return loss, tokens
+
+    def _mark(self, marks: list[torch.cuda.Event] | None = None, *, final: bool = False):
+        if not self._phase_timing:
+            return None
+        ev = torch.cuda.Event(enable_timing=True)
+        ev.record()
+        if marks is None:
+            return [ev]
+        marks.append(ev)
+        if final:
+            self._phase_events.append(marks)
+        return marks
+
+    def collect_phase_timing(self, skip: int = 0) -> dict[str, float]:
+        """Average milliseconds per step of (forward, backward, reduce+optimiser), last micro-batch."""
+        torch.cuda.synchronize()
+        rows = self._phase_events[skip:]
+        if rows:
+            names = ("forward_ms", "backward_ms", "reduce_optim_ms")
+            self.phase_ms = {
+                n: sum(r[i].elapsed_time(r[i + 1]) for r in rows) / len(rows)
+                for i, n in enumerate(names)
+            }
+        self._phase_events = []
+        return self.phase_ms
 
     def eval_loss(self, batch: Batch) -> float:
         ids, labels, key_mask, n_valid = self._stage(batch)

@@ -172,3 +172,28 @@ def test_grad_accumulation_matches_big_batch() -> None:
 
     g1, g2 = grads(1), grads(2)
     assert (g1 - g2).abs().max().item() < 2e-2 * g1.abs().max().item()
+
+
+def test_native_matches_oracle_on_gpt2_xl_shaped_layer() -> None:
+    """d=1600 / 25 heads / F=6400: none of the GEMM extents is a multiple of the 128x256 tile."""
+    from llmtrain.models.gpt import GPTAdapter
+
+    oracle = _model(vocab_size=1000, block_size=256, d_model=1600, n_layers=1, n_heads=25,
+                    d_ff=6400).cuda()
+    oracle.prefer_native = False
+    native = copy.deepcopy(oracle)
+    native.prefer_native = True
+    adapter = GPTAdapter()
+    ids = torch.randint(0, 1000, (2, 200), device="cuda")
+    labels = torch.randint(0, 1000, (2, 200), device="cuda")
+    batch = {"input_ids": ids, "labels": labels}
+    want, _ = adapter.compute_loss(oracle, batch)
+    want.backward()
+    got, _ = adapter.compute_loss(native, batch)
+    got.backward()
+    assert abs(got.item() - want.item()) < 2e-2 * abs(want.item())
+    ref = dict(oracle.named_parameters())
+    for name, p in native.named_parameters():
+        g_ref = ref[name].grad
+        err = (p.grad - g_ref).abs().max().item() / (g_ref.abs().max().item() + 1e-8)
+        assert err < 8e-2, f"{name}: rel err {err:.3e}"
