@@ -71,6 +71,7 @@ struct Comm {
   float* bucket_partials = nullptr;  // [MAX_BUCKETS][BUCKET_GRID]
   int buckets_this_step = 0;
   int bucket_grid = BUCKET_GRID;
+  bool dma_gather = true;  // push reduced slices with cudaMemcpyAsync (copy engines) vs SM stores
   cudaStream_t comm_stream = nullptr;
   cudaEvent_t ready_events[MAX_BUCKETS] = {};
   cudaEvent_t done_event = nullptr;
@@ -245,7 +246,8 @@ gather_adamw_kernel(Peers peers, int world, size_t n, size_t chunk, float* __res
 // the last bucket each rank holds the complete reduced gradient locally.
 template <int W>
 __global__ void __launch_bounds__(OVL_THREADS, 4)
-scatter_push_kernel(Peers peers, size_t lo, size_t len, float* __restrict__ partial) {
+scatter_push_kernel(Peers peers, size_t lo, size_t len, float* __restrict__ partial,
+                    int only_rank /* >= 0: store to that rank's buffer only (DMA does the rest) */) {
   const size_t n8 = len >> 3;
   float sq = 0.f;
   for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n8;
@@ -268,11 +270,17 @@ scatter_push_kernel(Peers peers, size_t lo, size_t len, float* __restrict__ part
     for (int j = 0; j < 8; ++j) sq += acc[j] * acc[j];
     const float4 a = make_float4(acc[0], acc[1], acc[2], acc[3]);
     const float4 b = make_float4(acc[4], acc[5], acc[6], acc[7]);
-#pragma unroll
-    for (int r = 0; r < W; ++r) {
-      float4* dst = reinterpret_cast<float4*>(peers.full[r] + lo) + 2 * i;
+    if (only_rank >= 0) {
+      float4* dst = reinterpret_cast<float4*>(peers.full[only_rank] + lo) + 2 * i;
       dst[0] = a;
       dst[1] = b;
+    } else {
+#pragma unroll
+      for (int r = 0; r < W; ++r) {
+        float4* dst = reinterpret_cast<float4*>(peers.full[r] + lo) + 2 * i;
+        dst[0] = a;
+        dst[1] = b;
+      }
     }
   }
 #pragma unroll
@@ -412,6 +420,7 @@ extern "C" int llmtrain_b200_nvl_create(int rank, int world, size_t n, double ti
     B200_CHECK_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
     B200_CHECK_CUDA(cudaStreamCreateWithPriority(&c->comm_stream, cudaStreamNonBlocking, greatest));
   }
+  if (const char* env = std::getenv("LLMTRAIN_NVL_DMA_GATHER")) c->dma_gather = std::atoi(env) != 0;
   if (const char* env = std::getenv("LLMTRAIN_NVL_BUCKET_GRID")) {
     const int v = std::atoi(env);
     if (v >= 1 && v <= nvl::TAIL_GRID) c->bucket_grid = v;
@@ -574,8 +583,8 @@ int reduce_bucket(void* raw, size_t lo, size_t len) {
   B200_CHECK_CUDA(cudaMemsetAsync(part, 0, nvl::PARTIAL_STRIDE * sizeof(float), cs));
 #define B200_PUSH(W)                                                                          \
   case W:                                                                                     \
-    nvl::scatter_push_kernel<W><<<grid, nvl::OVL_THREADS, 0, cs>>>(c.peers, my_lo, my_len,    \
-                                                                   part);                     \
+    nvl::scatter_push_kernel<W><<<grid, nvl::OVL_THREADS, 0, cs>>>(                            \
+        c.peers, my_lo, my_len, part, c.dma_gather ? c.rank : -1);                            \
     break;
   switch (c.world) {
     B200_PUSH(2) B200_PUSH(3) B200_PUSH(4) B200_PUSH(5) B200_PUSH(6) B200_PUSH(7) B200_PUSH(8)
@@ -584,6 +593,15 @@ int reduce_bucket(void* raw, size_t lo, size_t len) {
 #undef B200_PUSH
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
+  if (c.dma_gather && my_len > 0) {
+    // All-gather by the copy engines: the owner's reduced sub-slice goes to every peer's `full`
+    // buffer without occupying issue slots on SMs that are busy with backward GEMMs.
+    for (int r = 0; r < c.world; ++r) {
+      if (r == c.rank) continue;
+      B200_CHECK_CUDA(cudaMemcpyAsync(c.peers.full[r] + my_lo, c.full + my_lo,
+                                      my_len * sizeof(float), cudaMemcpyDeviceToDevice, cs));
+    }
+  }
   return 0;
 }
 }  // namespace
