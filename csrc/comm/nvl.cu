@@ -52,7 +52,7 @@ struct Peers {
 constexpr int MAX_BUCKETS = 128;
 // Overlapped bucket kernels must CO-RESIDE with the backward GEMM CTAs (1 per SM, ~54K of the 64K
 // registers, ~224 KB smem): small CTAs, no smem, <= 80 registers per thread.
-constexpr int BUCKET_GRID = 64;
+constexpr int BUCKET_GRID = 148;
 constexpr int OVL_THREADS = 128;
 // Buckets that only become final when backward is over (the embedding tables) find the GPU idle:
 // they get a full-size grid instead.

@@ -290,8 +290,8 @@ int backward(Gpt& g, cudaStream_t s, BucketHook hook = nullptr, void* hook_ctx =
   B200_TRY(llmtrain_b200_embed_bwd(g.ids, dresid, v.grad(g.wte), v.grad(g.wpe), B, T, d, g.V, st));
   if (hook != nullptr) {
     const size_t first_layer = g.L > 0 ? g.layer[0].ln1_w : g.lnf_w;
+    B200_TRY(hook(hook_ctx, 0, first_layer));              // position embedding (small, first)
     B200_TRY(hook(hook_ctx, g.wte, g.n_params - g.wte));  // token embedding (+ untied head)
-    B200_TRY(hook(hook_ctx, 0, first_layer));              // position embedding
   }
   g.have_forward = false;
   return 0;
