@@ -58,6 +58,8 @@ struct Params {
   const float* bias;     // [N] fp32 or nullptr
   const __nv_bfloat16* R;  // residual / saved pre-activation, row pitch ldr
   int ldr;
+  __nv_bfloat16* C2;       // second output of the GELU epilogue (pre-activation), row pitch ldc2
+  int ldc2;
 };
 
 // Phi(x) (standard normal CDF) via Abramowitz & Stegun 7.1.26 for erf (|abs err| < 1.5e-7 — two
@@ -119,7 +121,6 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
     tma_prefetch_desc(&tmC);
-    if (EPI == kBiasGelu) tma_prefetch_desc(&tmC2);
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
@@ -229,6 +230,32 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       const int n0 = (mn / num_m) * BN + half * (BN / 2);
       const int row = m0 + quarter * 32 + lane;  // this thread's output row
       const bool row_ok = row < p.M;
+      // Residual / saved pre-activation for this thread's row (2 chunks x 64 bf16): issued BEFORE
+      // waiting for the accumulator so the HBM latency hides behind this tile's mainloop.
+      uint4 rv[2][8];
+      if (EPI == kBiasResid || EPI == kDGelu) {
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+#pragma unroll
+          for (int q = 0; q < 8; ++q) rv[c][q] = make_uint4(0u, 0u, 0u, 0u);
+          const int col0 = n0 + c * 64;
+          if (row_ok && col0 < p.N) {
+            const __nv_bfloat16* rp = p.R + size_t(row) * p.ldr + col0;
+            if (col0 + 64 <= p.N) {
+#pragma unroll
+              for (int q = 0; q < 8; ++q) rv[c][q] = __ldg(reinterpret_cast<const uint4*>(rp) + q);
+            } else {
+              uint32_t* rw = reinterpret_cast<uint32_t*>(rv[c]);
+#pragma unroll
+              for (int j = 0; j < 64; j += 2) {  // static indices keep rv in registers
+                const float lo = (col0 + j < p.N) ? __bfloat162float(rp[j]) : 0.f;
+                const float hi = (col0 + j + 1 < p.N) ? __bfloat162float(rp[j + 1]) : 0.f;
+                rw[j >> 1] = pack_bf16x2(lo, hi);
+              }
+            }
+          }
+        }
+      }
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after_sync();
       const uint32_t t_row = tmem_base + (uint32_t(quarter * 32) << 16) + acc * BN + half * (BN / 2);
@@ -258,33 +285,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         }
       } else {
         // 2 chunks of 64 bf16 columns (128 B rows).
-#pragma unroll 1
+#pragma unroll
         for (int c = 0; c < BN / 128; ++c) {
           const int col0 = n0 + c * 64;
           if (col0 >= p.N) break;
-          // Issue the residual / pre-activation reads first (this thread's row, 64 contiguous
-          // bf16 = 8 x 16 B) so they overlap the TMEM loads.
-          uint4 rv[8];
           const bool full_cols = (col0 + 64 <= p.N);
-          if (EPI == kBiasResid || EPI == kDGelu) {
-#pragma unroll
-            for (int q = 0; q < 8; ++q) rv[q] = make_uint4(0u, 0u, 0u, 0u);
-            if (row_ok) {
-              const __nv_bfloat16* rp = p.R + size_t(row) * p.ldr + col0;
-              if (full_cols) {
-#pragma unroll
-                for (int q = 0; q < 8; ++q) rv[q] = __ldg(reinterpret_cast<const uint4*>(rp) + q);
-              } else {
-                uint32_t* rw = reinterpret_cast<uint32_t*>(rv);
-#pragma unroll
-                for (int j = 0; j < 64; j += 2) {  // static indices keep rv in registers
-                  const float lo = (col0 + j < p.N) ? __bfloat162float(rp[j]) : 0.f;
-                  const float hi = (col0 + j + 1 < p.N) ? __bfloat162float(rp[j + 1]) : 0.f;
-                  rw[j >> 1] = pack_bf16x2(lo, hi);
-                }
-              }
-            }
-          }
           uint32_t v[2][32];
           tmem_ld_32x32b_x32(t_row + c * 64, v[0]);
           tmem_ld_32x32b_x32(t_row + c * 64 + 32, v[1]);
@@ -292,7 +297,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 
           uint32_t out[32];   // 64 bf16 packed
           uint32_t out2[32];  // pre-activation (GELU variant only)
-          const uint32_t* rw = reinterpret_cast<const uint32_t*>(rv);
+          const uint32_t* rw = reinterpret_cast<const uint32_t*>(rv[c]);
           const bool add_bias =
               (EPI == kBias || EPI == kBiasGelu || EPI == kBiasResid) && p.bias != nullptr;
 #pragma unroll
@@ -339,20 +344,24 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             tma_store_commit();
           }
           if (EPI == kBiasGelu) {
-            // second output (pre-activation) through the same buffer
-            tma_store_wait_read<0>();
-            __syncwarp();
+            // Second output (pre-activation, needed by backward): straight from registers with
+            // 16-byte stores — this thread's row, 128 contiguous bytes.  Pushing it through the
+            // staging buffer as well would serialise two TMA round trips per chunk.
+            if (row_ok) {
+              __nv_bfloat16* dst = p.C2 + size_t(row) * p.ldc2 + col0;
+              if (full_cols) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const uint32_t off = swizzle128(lane * 128 + j * 16);
-              *reinterpret_cast<uint4*>(stg + off) =
-                  make_uint4(out2[4 * j], out2[4 * j + 1], out2[4 * j + 2], out2[4 * j + 3]);
-            }
-            fence_proxy_async_smem();
-            __syncwarp();
-            if (lane == 0) {
-              tma_store_2d(&tmC2, stg, col0, m0 + quarter * 32);
-              tma_store_commit();
+                for (int j = 0; j < 8; ++j)
+                  reinterpret_cast<uint4*>(dst)[j] =
+                      make_uint4(out2[4 * j], out2[4 * j + 1], out2[4 * j + 2], out2[4 * j + 3]);
+              } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                  const float2 f = unpack_bf16x2(out2[j]);
+                  if (col0 + 2 * j < p.N) dst[2 * j] = __float2bfloat16(f.x);
+                  if (col0 + 2 * j + 1 < p.N) dst[2 * j + 1] = __float2bfloat16(f.y);
+                }
+              }
             }
           }
         }
@@ -421,6 +430,8 @@ extern "C" int llmtrain_b200_gemm(int layout, int epilogue, int M, int N, int K,
   p.bias = bias;
   p.R = static_cast<const __nv_bfloat16*>(R);
   p.ldr = ldr;
+  p.C2 = static_cast<__nv_bfloat16*>(C2);
+  p.ldc2 = ldc2;
   const auto* a = static_cast<const __nv_bfloat16*>(A);
   const auto* b = static_cast<const __nv_bfloat16*>(B);
   CUtensorMap tA, tB, tC, tC2;
@@ -441,8 +452,8 @@ extern "C" int llmtrain_b200_gemm(int layout, int epilogue, int M, int N, int K,
     if (make_tmap_2d(&tC, static_cast<__nv_bfloat16*>(C), M, N, ldc, 32, 64, Swz::B128)) return 1;
     if (epilogue == kBiasGelu) {
       B200_REQUIRE(C2 != nullptr, "gemm: GELU epilogue needs the pre-activation output C2");
-      if (make_tmap_2d(&tC2, static_cast<__nv_bfloat16*>(C2), M, N, ldc2, 32, 64, Swz::B128))
-        return 1;
+      B200_REQUIRE(ldc2 % 8 == 0 && (reinterpret_cast<uintptr_t>(C2) & 15) == 0,
+                   "gemm: C2 must be 16-byte aligned with a pitch that is a multiple of 8");
     }
     if (epilogue == kBiasResid || epilogue == kDGelu)
       B200_REQUIRE(R != nullptr, "gemm: this epilogue needs R");
