@@ -207,6 +207,7 @@ int forward(Gpt& g, const int64_t* ids, const uint8_t* key_mask, int B, int T, c
                         v.p(o.out_b), x, s));
     B200_TRY(llmtrain_b200_layernorm_fwd(v.bf(a.resid1), v.p(o.ln2_w), v.p(o.ln2_b), v.bf(a.ln2),
                                          v.f32(a.ln2_mean), v.f32(a.ln2_rstd), M, d, st));
+    // fch_pre receives gelu'(pre-activation): all that backward needs from this GEMM
     B200_TRY(linear_fwd(1, M, F, d, v.bf(a.ln2), v.w(o.fc_w), v.bf(a.fch_act), v.bf(a.fch_pre),
                         v.p(o.fc_b), nullptr, s));
     B200_TRY(linear_fwd(2, M, d, F, v.bf(a.fch_act), v.w(o.proj_w), v.bf(a.resid2), nullptr,

@@ -46,9 +46,9 @@ constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + 256 /*barriers*/;
 
 enum Epi : int {
   kBias = 0,      // C = acc (+ bias)
-  kBiasGelu = 1,  // C2 = acc + bias ; C = gelu(C2)
+  kBiasGelu = 1,  // x = acc + bias ; C = gelu(x) ; C2 = gelu'(x)   (C2 is what backward needs)
   kBiasResid = 2, // C = acc (+ bias) + R
-  kDGelu = 3,     // C = acc * gelu'(R)          (R holds the saved pre-activation)
+  kDGelu = 3,     // C = acc * R                 (R holds gelu'(pre-activation) saved by forward)
   kAccumF32 = 4,  // C(fp32) += acc              (TMA reduce-add)
 };
 
@@ -85,10 +85,12 @@ __device__ __forceinline__ PhiPair normal_cdf(float x) {
   const float q = poly * t * half_e;                         // 0.5 * erfc(|x|/sqrt 2)
   return {x > 0.f ? 1.0f - q : q, half_e};
 }
-__device__ __forceinline__ float gelu_erf(float x) { return x * normal_cdf(x).cdf; }
-__device__ __forceinline__ float gelu_erf_grad(float x) {
+// gelu(x) = x Phi(x) and gelu'(x) = Phi(x) + x phi(x) from ONE evaluation: forward stores the
+// derivative (bf16) instead of the pre-activation, so the MLP dgrad epilogue is a single multiply.
+struct GeluPair { float y, dy; };
+__device__ __forceinline__ GeluPair gelu_erf_both(float x) {
   const PhiPair n = normal_cdf(x);
-  return fmaf(x * 0.7978845608028654f, n.half_e, n.cdf);     // Phi + x*phi, phi = 2*half_e/sqrt(2pi)
+  return {x * n.cdf, fmaf(x * 0.7978845608028654f, n.half_e, n.cdf)};  // phi = 2*half_e/sqrt(2pi)
 }
 
 template <bool A_MN, bool B_MN, int EPI>
@@ -256,6 +258,22 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           }
         }
       }
+      // Bias for this warp's 128 columns: lane l keeps columns 4l..4l+3 (one coalesced 16-byte
+      // load, issued before the accumulator wait); values reach their consumers by shuffle, so
+      // no memory latency sits inside the math loop.
+      float4 bias4 = make_float4(0.f, 0.f, 0.f, 0.f);
+      const bool add_bias =
+          (EPI == kBias || EPI == kBiasGelu || EPI == kBiasResid) && p.bias != nullptr;
+      if (add_bias) {
+        const int bc = n0 + lane * 4;
+        if (bc + 4 <= p.N) {
+          bias4 = __ldg(reinterpret_cast<const float4*>(p.bias + bc));
+        } else {
+          if (bc < p.N) bias4.x = __ldg(p.bias + bc);
+          if (bc + 1 < p.N) bias4.y = __ldg(p.bias + bc + 1);
+          if (bc + 2 < p.N) bias4.z = __ldg(p.bias + bc + 2);
+        }
+      }
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after_sync();
       const uint32_t t_row = tmem_base + (uint32_t(quarter * 32) << 16) + acc * BN + half * (BN / 2);
@@ -298,32 +316,31 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           uint32_t out[32];   // 64 bf16 packed
           uint32_t out2[32];  // pre-activation (GELU variant only)
           const uint32_t* rw = reinterpret_cast<const uint32_t*>(rv[c]);
-          const bool add_bias =
-              (EPI == kBias || EPI == kBiasGelu || EPI == kBiasResid) && p.bias != nullptr;
 #pragma unroll
           for (int h = 0; h < 2; ++h) {
 #pragma unroll
             for (int j = 0; j < 32; j += 2) {
-              const int col = col0 + h * 32 + j;
               float x0 = __uint_as_float(v[h][j]);
               float x1 = __uint_as_float(v[h][j + 1]);
               if (add_bias) {
-                if (full_cols) {  // warp-uniform; the common case carries no per-element guards
-                  const float2 bb = __ldg(reinterpret_cast<const float2*>(p.bias + col));
-                  x0 += bb.x; x1 += bb.y;
-                } else {
-                  if (col < p.N) x0 += __ldg(p.bias + col);
-                  if (col + 1 < p.N) x1 += __ldg(p.bias + col + 1);
-                }
+                // column inside this warp's 128 = c*64 + h*32 + j  ->  lane (col/4), component col%4
+                constexpr int kUnused = 0;
+                (void)kUnused;
+                const int cc = c * 64 + h * 32 + j;
+                const float lo = (cc & 2) ? bias4.z : bias4.x;   // j is even: component 0 or 2
+                const float hi = (cc & 2) ? bias4.w : bias4.y;
+                x0 += __shfl_sync(0xffffffffu, lo, cc >> 2);
+                x1 += __shfl_sync(0xffffffffu, hi, cc >> 2);
               }
               if (EPI == kBiasResid || EPI == kDGelu) {
                 const float2 f = unpack_bf16x2(rw[h * 16 + (j >> 1)]);
                 if (EPI == kBiasResid) { x0 += f.x; x1 += f.y; }
-                else { x0 *= gelu_erf_grad(f.x); x1 *= gelu_erf_grad(f.y); }
+                else { x0 *= f.x; x1 *= f.y; }
               }
               if (EPI == kBiasGelu) {
-                out2[h * 16 + j / 2] = pack_bf16x2(x0, x1);
-                x0 = gelu_erf(x0); x1 = gelu_erf(x1);
+                const GeluPair g0 = gelu_erf_both(x0), g1 = gelu_erf_both(x1);
+                out2[h * 16 + j / 2] = pack_bf16x2(g0.dy, g1.dy);
+                x0 = g0.y; x1 = g1.y;
               }
               out[h * 16 + j / 2] = pack_bf16x2(x0, x1);
             }

@@ -35,8 +35,9 @@ long long llmtrain_b200_launch_count(void);
  *   layout 0 (NT): C[M,N]  = A[M,K]   * B[N,K]^T
  *   layout 1 (NN): C[M,N]  = A[M,K]   * B[K,N]
  *   layout 2 (TN): C[M,N] += A[K,M]^T * B[K,N]      (C is fp32; split-K; TMA reduce-add)
- *   epilogue 0: C = acc (+bias)            1: C2 = acc+bias, C = gelu_erf(C2)
- *            2: C = acc (+bias) + R        3: C = acc * gelu_erf'(R)      4: fp32 accumulate
+ *   epilogue 0: C = acc (+bias)            1: x = acc+bias, C = gelu_erf(x), C2 = gelu_erf'(x)
+ *            2: C = acc (+bias) + R        3: C = acc * R  (R = the C2 saved by 1)
+ *            4: fp32 accumulate
  *   A, B, C(bf16), C2, R are bf16 with row pitches lda/ldb/ldc/ldc2/ldr in elements (each pitch
  *   a multiple of 8); bias is fp32 [N] or NULL.
  * ------------------------------------------------------------------------------------------- */

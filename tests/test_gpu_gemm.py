@@ -42,12 +42,15 @@ def test_nt_gelu_and_resid(m: int, n: int, k: int) -> None:
 
     x, w = _rand((m, k)), _rand((n, k), 0.05)
     bias = torch.randn(n, device="cuda") * 0.1
-    pre = torch.empty(m, n, device="cuda", dtype=torch.bfloat16)
-    act = torch.empty_like(pre)
-    G.gemm(G.NT, G.EPI_BIAS_GELU, x, w, act, c2=pre, bias=bias)
-    want_pre = x.float() @ w.float().t() + bias
-    _close(pre, want_pre, 1e-2)
-    _close(act, torch.nn.functional.gelu(want_pre), 1e-2)
+    dact = torch.empty(m, n, device="cuda", dtype=torch.bfloat16)
+    act = torch.empty_like(dact)
+    G.gemm(G.NT, G.EPI_BIAS_GELU, x, w, act, c2=dact, bias=bias)
+    want_pre = (x.float() @ w.float().t() + bias).requires_grad_(True)
+    want_act = torch.nn.functional.gelu(want_pre)  # exact (erf) GELU
+    want_act.sum().backward()
+    _close(act, want_act.detach(), 1e-2)
+    _close(dact, want_pre.grad, 1e-2)  # second output: gelu'(pre), consumed by the MLP dgrad
+    want_pre = want_pre.detach()
 
     resid = _rand((m, n))
     out = torch.empty_like(pre)
@@ -65,12 +68,10 @@ def test_nn_dgrad(m: int, n: int, k: int) -> None:
     want = dy.float() @ w.float()
     _close(out, want, 1e-2)
 
-    pre = _rand((m, n))
+    factor = _rand((m, n))  # gelu'(pre) as saved by the forward GELU epilogue
     out2 = torch.empty_like(out)
-    G.gemm(G.NN, G.EPI_DGELU, dy, w, out2, r=pre)
-    p = pre.float().requires_grad_(True)
-    torch.nn.functional.gelu(p).backward(want)
-    _close(out2, p.grad, 1e-2)
+    G.gemm(G.NN, G.EPI_DGELU, dy, w, out2, r=factor)
+    _close(out2, want * factor.float(), 1e-2)
 
 
 @pytest.mark.parametrize("m,n,k", [(256, 256, 512), (768, 2304, 4096), (320, 1600, 1000), (50304, 768, 2048)])
