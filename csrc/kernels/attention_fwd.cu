@@ -5,14 +5,17 @@
 // ever reaches HBM: per (batch, head, 128-query tile) one CTA walks the key/value tiles up to the
 // diagonal.
 //
-//   TMA warp   : Q once, then K_j / V_j through a 2-stage ring (3-D tensor maps over the fused
-//                [B, T, 3d] QKV buffer, so no permute/copy is ever made and rows past T read 0)
+//   TMA warp   : Q once, then K_j / V_j (3-D tensor maps over the fused [B, T, 3d] QKV buffer, so
+//                no permute/copy is ever made and rows past T read 0); K is reloaded as soon as
+//                S_j has consumed it, V as soon as PV_j has.
 //   MMA warp   : S = Q K_j^T   (SS, 128x128x64, accumulator in TMEM cols [0,128))
-//                PV = P_j V_j  (SS, 128x64x128, TMEM cols [128,192)), P_j read from smem (bf16),
-//                V_j consumed as an MN-major operand straight from its [kv, hd] layout
+//                PV = P_j V_j  (SS, 128x64x128, two TMEM accumulators of 64 cols), P_j read from a
+//                double-buffered bf16 smem tile, V_j consumed as an MN-major operand straight from
+//                its [kv, hd] layout.  Issue order: p_full(j) -> S_{j+1} -> PV_j.
 //   4 softmax warps: thread i owns query row i (= TMEM lane i): two passes over S (max, then
-//                exp2 + row-sum + bf16 pack into the swizzled P tile), then folds PV into the
-//                register-resident output with the usual online-softmax rescale.
+//                exp2 + row-sum + bf16 pack into the swizzled P tile); PV_{j-1} is folded into the
+//                register-resident output AFTER P_j has been handed over, so the tensor-core
+//                latency of PV hides behind the next tile's softmax.
 //
 // Masking follows the reference's semantics: causal (col > row) and optional key padding are
 // excluded from the softmax; a query whose keys are ALL excluded yields zeros (the reference
@@ -35,10 +38,11 @@ constexpr int TILE_BYTES = 128 * HD * 2;  // 16 KB: 128 rows x 128 B
 constexpr int FWD_THREADS = 192;
 constexpr int FWD_TMEM_COLS = 256;
 constexpr int OFF_Q = 0;
-constexpr int OFF_K = OFF_Q + TILE_BYTES;
-constexpr int OFF_V = OFF_K + 2 * TILE_BYTES;
-constexpr int OFF_P = OFF_V + 2 * TILE_BYTES;
-constexpr int OFF_BAR = OFF_P + 2 * TILE_BYTES;
+constexpr int OFF_K = OFF_Q + TILE_BYTES;          // single stage (reloaded once S_j has read it)
+constexpr int OFF_V = OFF_K + TILE_BYTES;          // single stage (reloaded once PV_j has read it)
+constexpr int OFF_P = OFF_V + TILE_BYTES;          // 2 x 32 KB: P_j is written while PV_{j-1} runs
+constexpr int P_BYTES = 2 * TILE_BYTES;
+constexpr int OFF_BAR = OFF_P + 2 * P_BYTES;
 constexpr int FWD_SMEM = OFF_BAR + 256;
 
 struct FwdParams {
@@ -118,13 +122,14 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
   if ((smem_u32(smem) & 1023u) != 0) __trap();
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
   uint64_t* q_full = bars + 0;
-  uint64_t* k_full = bars + 1;    // [2]
-  uint64_t* v_full = bars + 3;    // [2]
-  uint64_t* kv_empty = bars + 5;  // [2]
-  uint64_t* s_full = bars + 7;
-  uint64_t* p_full = bars + 8;
-  uint64_t* pv_done = bars + 9;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 10);
+  uint64_t* k_full = bars + 1;
+  uint64_t* k_empty = bars + 2;
+  uint64_t* v_full = bars + 3;
+  uint64_t* v_empty = bars + 4;
+  uint64_t* s_full = bars + 5;
+  uint64_t* p_full = bars + 6;
+  uint64_t* pv_done = bars + 7;   // [2], one per PV accumulator
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nq = (p.T + BQ - 1) / BQ;
@@ -138,14 +143,14 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
     tma_prefetch_desc(&tmQKV);
     tma_prefetch_desc(&tmO);
     mbar_init(q_full, 1);
-    for (int s = 0; s < 2; ++s) {
-      mbar_init(&k_full[s], 1);
-      mbar_init(&v_full[s], 1);
-      mbar_init(&kv_empty[s], 1);
-    }
+    mbar_init(k_full, 1);
+    mbar_init(k_empty, 1);
+    mbar_init(v_full, 1);
+    mbar_init(v_empty, 1);
     mbar_init(s_full, 1);
     mbar_init(p_full, 4);
-    mbar_init(pv_done, 1);
+    mbar_init(&pv_done[0], 1);
+    mbar_init(&pv_done[1], 1);
     fence_barrier_init();
   }
   if (warp == 5) {
@@ -156,8 +161,8 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
   __syncthreads();
   tc_fence_after_sync();
   const uint32_t tmem = *tmem_slot;
-  const uint32_t tmem_S = tmem;
-  const uint32_t tmem_PV = tmem + 128;
+  const uint32_t tmem_S = tmem;           // 128 columns
+  const uint32_t tmem_PV = tmem + 128;    // 2 x 64 columns
 
   if (warp == 4) {
     // ------------------------------- TMA producer -------------------------------------------
@@ -165,48 +170,49 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
       mbar_expect_tx(q_full, TILE_BYTES);
       tma_load_3d(smem + OFF_Q, &tmQKV, q_full, h * HD, q0, b);
       for (int j = 0; j < n_kv; ++j) {
-        const int st = j & 1;
-        const uint32_t ph = (j >> 1) & 1;
-        mbar_wait(&kv_empty[st], ph ^ 1);
-        mbar_expect_tx(&k_full[st], TILE_BYTES);
-        tma_load_3d(smem + OFF_K + st * TILE_BYTES, &tmQKV, &k_full[st], d + h * HD, j * BKV, b);
-        mbar_expect_tx(&v_full[st], TILE_BYTES);
-        tma_load_3d(smem + OFF_V + st * TILE_BYTES, &tmQKV, &v_full[st], 2 * d + h * HD, j * BKV,
-                    b);
+        if (j > 0) mbar_wait(k_empty, (j - 1) & 1);   // S_{j-1} has consumed K
+        mbar_expect_tx(k_full, TILE_BYTES);
+        tma_load_3d(smem + OFF_K, &tmQKV, k_full, d + h * HD, j * BKV, b);
+        if (j > 0) mbar_wait(v_empty, (j - 1) & 1);   // PV_{j-1} has consumed V
+        mbar_expect_tx(v_full, TILE_BYTES);
+        tma_load_3d(smem + OFF_V, &tmQKV, v_full, 2 * d + h * HD, j * BKV, b);
       }
     }
   } else if (warp == 5) {
     // ------------------------------- MMA issuer ---------------------------------------------
+    // Issue order per tile: ... p_full(j) -> S_{j+1} -> PV_j.  S_{j+1} goes first because the
+    // softmax warps need it next; PV_j is only folded one iteration later.
     if (lane == 0) {
       constexpr uint32_t idesc_s = umma_idesc_bf16(BQ, BKV, false, false);
       constexpr uint32_t idesc_pv = umma_idesc_bf16(BQ, HD, false, true);
       const uint32_t sQ = smem_u32(smem + OFF_Q);
-      const uint32_t sP = smem_u32(smem + OFF_P);
-      mbar_wait(q_full, 0);
-      for (int j = 0; j < n_kv; ++j) {
-        const int st = j & 1;
-        const uint32_t ph = (j >> 1) & 1;
-        const uint32_t sK = smem_u32(smem + OFF_K + st * TILE_BYTES);
-        const uint32_t sV = smem_u32(smem + OFF_V + st * TILE_BYTES);
-        // S_j = Q K_j^T.  The S columns are free: the softmax warps signalled p_full(j-1) only
-        // after their last read of S_{j-1}, and we waited on it below before getting here.
-        mbar_wait(&k_full[st], ph);
+      const uint32_t sK = smem_u32(smem + OFF_K);
+      const uint32_t sV = smem_u32(smem + OFF_V);
+      auto issue_s = [&](int j) {
+        mbar_wait(k_full, j & 1);
         tc_fence_after_sync();
 #pragma unroll
         for (int k = 0; k < HD / 16; ++k)
           umma_ss(tmem_S, umma_smem_desc(sQ + k * 32, 0, 1024), umma_smem_desc(sK + k * 32, 0, 1024),
                   idesc_s, k > 0);
+        umma_commit(k_empty);
         umma_commit(s_full);
-        // PV_j = P_j V_j  (fresh accumulator every tile; folded into registers by the softmax warps)
-        mbar_wait(p_full, j & 1);
-        mbar_wait(&v_full[st], ph);
+      };
+      mbar_wait(q_full, 0);
+      issue_s(0);
+      for (int j = 0; j < n_kv; ++j) {
+        mbar_wait(p_full, j & 1);  // P_j is in smem and S_j has been read out of TMEM
+        if (j + 1 < n_kv) issue_s(j + 1);
+        mbar_wait(v_full, j & 1);
         tc_fence_after_sync();
+        const uint32_t sP = smem_u32(smem + OFF_P + (j & 1) * P_BYTES);
+        const uint32_t acc = tmem_PV + (j & 1) * HD;
 #pragma unroll
         for (int k = 0; k < BKV / 16; ++k)
-          umma_ss(tmem_PV, umma_smem_desc(sP + (k >> 2) * TILE_BYTES + (k & 3) * 32, 0, 1024),
+          umma_ss(acc, umma_smem_desc(sP + (k >> 2) * TILE_BYTES + (k & 3) * 32, 0, 1024),
                   umma_smem_desc(sV + k * 2048, TILE_BYTES, 1024), idesc_pv, k > 0);
-        umma_commit(&kv_empty[st]);
-        umma_commit(pv_done);
+        umma_commit(v_empty);
+        umma_commit(&pv_done[j & 1]);
       }
     }
   } else {
@@ -214,15 +220,31 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
     const int r = threadIdx.x;  // 0..127: query row inside the tile == TMEM lane
     const int qrow = q0 + r;
     const uint32_t lane_base = uint32_t(warp * 32) << 16;
-    float m_run = -INFINITY, l_run = 0.f;
+    float m_run = -INFINITY, l_run = 0.f, alpha_prev = 0.f;
     float o[HD];
 #pragma unroll
     for (int i = 0; i < HD; ++i) o[i] = 0.f;
     const uint8_t* kmask = p.key_mask ? p.key_mask + size_t(b) * p.T : nullptr;
 
+    // o = o * alpha + PV_j, PV_j read from its TMEM accumulator
+    auto fold = [&](int j, float alpha) {
+      mbar_wait(&pv_done[j & 1], (j >> 1) & 1);
+      tc_fence_after_sync();
+#pragma unroll
+      for (int c = 0; c < HD / 32; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32b_x32(tmem_PV + (j & 1) * HD + lane_base + c * 32, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) o[c * 32 + i] = o[c * 32 + i] * alpha + __uint_as_float(v[i]);
+      }
+      tc_fence_before_sync();
+    };
+
     for (int j = 0; j < n_kv; ++j) {
       const int kv0 = j * BKV;
       const bool need_mask = (j == qt) || (kmask != nullptr);
+      uint8_t* sP = smem + OFF_P + (j & 1) * P_BYTES;
       mbar_wait(s_full, j & 1);
       tc_fence_after_sync();
 
@@ -235,9 +257,9 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
       const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
       const float alpha = fast_exp2(m_run - m_use);  // m_run = -inf -> 0
       const float sum =
-          need_mask ? exp_pack<true>(tmem_S + lane_base, smem + OFF_P, r, kv0, qrow, p.T, kmask,
+          need_mask ? exp_pack<true>(tmem_S + lane_base, sP, r, kv0, qrow, p.T, kmask,
                                      p.scale_log2, m_use)
-                    : exp_pack<false>(tmem_S + lane_base, smem + OFF_P, r, kv0, qrow, p.T, kmask,
+                    : exp_pack<false>(tmem_S + lane_base, sP, r, kv0, qrow, p.T, kmask,
                                       p.scale_log2, m_use);
       l_run = l_run * alpha + sum;
       m_run = m_new;
@@ -247,23 +269,16 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
       __syncwarp();
       if (lane == 0) mbar_arrive(p_full);
 
-      // fold PV_j into the running output
-      mbar_wait(pv_done, j & 1);
-      tc_fence_after_sync();
-#pragma unroll
-      for (int c = 0; c < HD / 32; ++c) {
-        uint32_t v[32];
-        tmem_ld_32x32b_x32(tmem_PV + lane_base + c * 32, v);
-        tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < 32; ++i) o[c * 32 + i] = o[c * 32 + i] * alpha + __uint_as_float(v[i]);
-      }
-      tc_fence_before_sync();
+      // Fold the PREVIOUS tile's PV while the tensor core works on S_{j+1} / PV_j: the PV latency
+      // never sits between two softmax passes.
+      if (j > 0) fold(j - 1, alpha_prev);
+      alpha_prev = alpha;
     }
+    fold(n_kv - 1, alpha_prev);
 
-    // normalise, stage as bf16 (swizzled 128 B rows) in the P buffer, one TMA store per CTA
+    // normalise, stage as bf16 (swizzled 128 B rows) in a P buffer, one TMA store per CTA
     const float inv_l = l_run > 0.f ? 1.0f / l_run : 0.f;
-    uint8_t* stage = smem + OFF_P;
+    uint8_t* stage = smem + OFF_P + (n_kv & 1) * P_BYTES;  // the buffer the last PV did NOT use
 #pragma unroll
     for (int q = 0; q < 8; ++q) {
       uint32_t w[4];

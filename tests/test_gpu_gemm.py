@@ -53,7 +53,7 @@ def test_nt_gelu_and_resid(m: int, n: int, k: int) -> None:
     want_pre = want_pre.detach()
 
     resid = _rand((m, n))
-    out = torch.empty_like(pre)
+    out = torch.empty_like(act)
     G.gemm(G.NT, G.EPI_BIAS_RESID, x, w, out, bias=bias, r=resid)
     _close(out, want_pre + resid.float(), 1e-2)
 
