@@ -9,14 +9,13 @@
 //                no permute/copy is ever made and rows past T read 0); K is reloaded as soon as
 //                S_j has consumed it, V as soon as PV_j has.
 //   MMA warp   : S = Q K_j^T   (SS, 128x128x64, accumulator in TMEM cols [0,128))
-//                O += P_j V_j  (SS, 128x64x128, one 64-column TMEM accumulator), P_j read from a
+//                PV = P_j V_j  (SS, 128x64x128, two TMEM accumulators of 64 cols), P_j read from a
 //                double-buffered bf16 smem tile, V_j consumed as an MN-major operand straight from
 //                its [kv, hd] layout.  Issue order: p_full(j) -> S_{j+1} -> PV_j.
-//   4 softmax warps: thread i owns query row i (= TMEM lane i): the S row is pulled from TMEM
-//                once per tile (four loads in flight, one wait), max / exp2 / row-sum / bf16 pack
-//                run on registers, P goes to the swizzled smem tile.  O accumulates in TMEM across
-//                tiles against a lazily raised reference maximum (rescaled only when the row
-//                maximum grows by more than 2^8), so there is no per-tile fold of PV.
+//   4 softmax warps: thread i owns query row i (= TMEM lane i): two passes over S (max, then
+//                exp2 + row-sum + bf16 pack into the swizzled P tile); PV_{j-1} is folded into the
+//                register-resident output AFTER P_j has been handed over, so the tensor-core
+//                latency of PV hides behind the next tile's softmax.
 //
 // Masking follows the reference's semantics: causal (col > row) and optional key padding are
 // excluded from the softmax; a query whose keys are ALL excluded yields zeros (the reference
@@ -61,42 +60,40 @@ __device__ __forceinline__ bool keep(int col, int qrow, int T, const uint8_t* km
   return ok;
 }
 
-// Row of S (128 fp32) from TMEM into registers: four loads in flight, one wait.
-__device__ __forceinline__ void load_s_row(uint32_t t_row, uint32_t (&v)[4][32]) {
-  tmem_ld_32x32b_x32(t_row, v[0]);
-  tmem_ld_32x32b_x32(t_row + 32, v[1]);
-  tmem_ld_32x32b_x32(t_row + 64, v[2]);
-  tmem_ld_32x32b_x32(t_row + 96, v[3]);
-  tmem_ld_wait();
-}
-
+// max over this thread's row of the 128-column S tile
 template <bool MASK>
-__device__ __forceinline__ float row_max(const uint32_t (&v)[4][32], int kv0, int qrow, int T,
+__device__ __forceinline__ float row_max(uint32_t t_row, int kv0, int qrow, int T,
                                          const uint8_t* kmask) {
   float mx = -INFINITY;
-#pragma unroll
-  for (int c = 0; c < 4; ++c) {
+#pragma unroll 1
+  for (int c = 0; c < BKV / 32; ++c) {
+    uint32_t v[32];
+    tmem_ld_32x32b_x32(t_row + c * 32, v);
+    tmem_ld_wait();
 #pragma unroll
     for (int i = 0; i < 32; ++i) {
-      if (keep<MASK>(kv0 + c * 32 + i, qrow, T, kmask)) mx = fmaxf(mx, __uint_as_float(v[c][i]));
+      if (keep<MASK>(kv0 + c * 32 + i, qrow, T, kmask)) mx = fmaxf(mx, __uint_as_float(v[i]));
     }
   }
   return mx;
 }
 
-// p = exp2(s*scale - m_ref) -> bf16 into the K-major 128B-swizzled P tile; returns the row sum
+// p = exp2(s*scale - m) -> bf16 into the K-major 128B-swizzled P tile; returns the row sum
 template <bool MASK>
-__device__ __forceinline__ float exp_pack(const uint32_t (&v)[4][32], uint8_t* sP, int r, int kv0,
-                                          int qrow, int T, const uint8_t* kmask, float scale_log2,
-                                          float m_ref) {
+__device__ __forceinline__ float exp_pack(uint32_t t_row, uint8_t* sP, int r, int kv0, int qrow,
+                                          int T, const uint8_t* kmask, float scale_log2,
+                                          float m_use) {
   float sum = 0.f;
-#pragma unroll
-  for (int c = 0; c < 4; ++c) {
+#pragma unroll 1
+  for (int c = 0; c < BKV / 32; ++c) {
+    uint32_t v[32];
+    tmem_ld_32x32b_x32(t_row + c * 32, v);
+    tmem_ld_wait();
     uint32_t packed[16];
 #pragma unroll
     for (int i = 0; i < 32; i += 2) {
-      float e0 = fast_exp2(fmaf(__uint_as_float(v[c][i]), scale_log2, -m_ref));
-      float e1 = fast_exp2(fmaf(__uint_as_float(v[c][i + 1]), scale_log2, -m_ref));
+      float e0 = fast_exp2(fmaf(__uint_as_float(v[i]), scale_log2, -m_use));
+      float e1 = fast_exp2(fmaf(__uint_as_float(v[i + 1]), scale_log2, -m_use));
       if (MASK) {
         if (!keep<MASK>(kv0 + c * 32 + i, qrow, T, kmask)) e0 = 0.f;
         if (!keep<MASK>(kv0 + c * 32 + i + 1, qrow, T, kmask)) e1 = 0.f;
@@ -131,7 +128,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
   uint64_t* v_empty = bars + 4;
   uint64_t* s_full = bars + 5;
   uint64_t* p_full = bars + 6;
-  uint64_t* pv_done = bars + 7;
+  uint64_t* pv_done = bars + 7;   // [2], one per PV accumulator
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -152,7 +149,8 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
     mbar_init(v_empty, 1);
     mbar_init(s_full, 1);
     mbar_init(p_full, 4);
-    mbar_init(pv_done, 1);
+    mbar_init(&pv_done[0], 1);
+    mbar_init(&pv_done[1], 1);
     fence_barrier_init();
   }
   if (warp == 5) {
@@ -164,7 +162,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
   tc_fence_after_sync();
   const uint32_t tmem = *tmem_slot;
   const uint32_t tmem_S = tmem;           // 128 columns
-  const uint32_t tmem_O = tmem + 128;     // 64 columns: O accumulates across all kv tiles
+  const uint32_t tmem_PV = tmem + 128;    // 2 x 64 columns
 
   if (warp == 4) {
     // ------------------------------- TMA producer -------------------------------------------
@@ -208,27 +206,40 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
         mbar_wait(v_full, j & 1);
         tc_fence_after_sync();
         const uint32_t sP = smem_u32(smem + OFF_P + (j & 1) * P_BYTES);
+        const uint32_t acc = tmem_PV + (j & 1) * HD;
 #pragma unroll
         for (int k = 0; k < BKV / 16; ++k)
-          umma_ss(tmem_O, umma_smem_desc(sP + (k >> 2) * TILE_BYTES + (k & 3) * 32, 0, 1024),
-                  umma_smem_desc(sV + k * 2048, TILE_BYTES, 1024), idesc_pv, (j > 0) || (k > 0));
+          umma_ss(acc, umma_smem_desc(sP + (k >> 2) * TILE_BYTES + (k & 3) * 32, 0, 1024),
+                  umma_smem_desc(sV + k * 2048, TILE_BYTES, 1024), idesc_pv, k > 0);
         umma_commit(v_empty);
-        umma_commit(pv_done);
+        umma_commit(&pv_done[j & 1]);
       }
     }
   } else {
     // ------------------------------- softmax / output ---------------------------------------
-    // O lives in TMEM and is accumulated by the tensor core across kv tiles.  Exponents are taken
-    // relative to a reference maximum m_ref that is only raised when the true row maximum has
-    // outgrown it by more than 2^8 (then O and l are rescaled once); in between, p = 2^(s-m_ref)
-    // stays <= 256, exact in fp32 accumulation and harmless in bf16.  The whole S row is read
-    // from TMEM once per tile (one wait), and no per-tile read-modify-write of O remains.
     const int r = threadIdx.x;  // 0..127: query row inside the tile == TMEM lane
     const int qrow = q0 + r;
     const uint32_t lane_base = uint32_t(warp * 32) << 16;
-    float m_ref = -INFINITY, l_run = 0.f;
+    float m_run = -INFINITY, l_run = 0.f, alpha_prev = 0.f;
+    float o[HD];
+#pragma unroll
+    for (int i = 0; i < HD; ++i) o[i] = 0.f;
     const uint8_t* kmask = p.key_mask ? p.key_mask + size_t(b) * p.T : nullptr;
-    constexpr float kRaise = 8.0f;
+
+    // o = o * alpha + PV_j, PV_j read from its TMEM accumulator
+    auto fold = [&](int j, float alpha) {
+      mbar_wait(&pv_done[j & 1], (j >> 1) & 1);
+      tc_fence_after_sync();
+#pragma unroll
+      for (int c = 0; c < HD / 32; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32b_x32(tmem_PV + (j & 1) * HD + lane_base + c * 32, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) o[c * 32 + i] = o[c * 32 + i] * alpha + __uint_as_float(v[i]);
+      }
+      tc_fence_before_sync();
+    };
 
     for (int j = 0; j < n_kv; ++j) {
       const int kv0 = j * BKV;
@@ -236,58 +247,34 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
       uint8_t* sP = smem + OFF_P + (j & 1) * P_BYTES;
       mbar_wait(s_full, j & 1);
       tc_fence_after_sync();
-      uint32_t v[4][32];
-      load_s_row(tmem_S + lane_base, v);
 
-      const float mx = (need_mask ? row_max<true>(v, kv0, qrow, p.T, kmask)
-                                  : row_max<false>(v, kv0, qrow, p.T, kmask)) * p.scale_log2;
-      const bool raise = mx > m_ref + kRaise || (m_ref == -INFINITY && mx > -INFINITY);
-      // warp-uniform branch: the correction uses .sync.aligned TMEM loads/stores
-      if (__any_sync(0xffffffffu, raise && j > 0)) {
-        const float m_new = raise ? mx : m_ref;
-        const float alpha = (m_ref == -INFINITY) ? 0.f : fast_exp2(m_ref - m_new);
-        l_run *= alpha;
-        mbar_wait(pv_done, (j - 1) & 1);  // PV_{j-1} has landed in O
-        tc_fence_after_sync();
-#pragma unroll
-        for (int c = 0; c < HD / 16; ++c) {
-          uint32_t o[16];
-          tmem_ld_32x32b_x16(tmem_O + lane_base + c * 16, o);
-          tmem_ld_wait();
-#pragma unroll
-          for (int i = 0; i < 16; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
-          tmem_st_32x32b_x16(tmem_O + lane_base + c * 16, o);
-        }
-        tmem_st_wait();
-        m_ref = m_new;
-      } else if (raise) {
-        m_ref = mx;  // first tile: nothing accumulated yet
-      }
-      const float m_use = (m_ref == -INFINITY) ? 0.f : m_ref;
+      // Two passes over S in TMEM (max, then exp2 + pack).  The masked variant is only
+      // instantiated for the diagonal tile / key-padding case, so off-diagonal tiles execute no
+      // per-element integer or predicate instructions at all.
+      float mx = need_mask ? row_max<true>(tmem_S + lane_base, kv0, qrow, p.T, kmask)
+                           : row_max<false>(tmem_S + lane_base, kv0, qrow, p.T, kmask);
+      const float m_new = fmaxf(m_run, mx * p.scale_log2);
+      const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
+      const float alpha = fast_exp2(m_run - m_use);  // m_run = -inf -> 0
       const float sum =
-          need_mask ? exp_pack<true>(v, sP, r, kv0, qrow, p.T, kmask, p.scale_log2, m_use)
-                    : exp_pack<false>(v, sP, r, kv0, qrow, p.T, kmask, p.scale_log2, m_use);
-      l_run += sum;
+          need_mask ? exp_pack<true>(tmem_S + lane_base, sP, r, kv0, qrow, p.T, kmask,
+                                     p.scale_log2, m_use)
+                    : exp_pack<false>(tmem_S + lane_base, sP, r, kv0, qrow, p.T, kmask,
+                                      p.scale_log2, m_use);
+      l_run = l_run * alpha + sum;
+      m_run = m_new;
 
       fence_proxy_async_smem();
       tc_fence_before_sync();
       __syncwarp();
       if (lane == 0) mbar_arrive(p_full);
-    }
 
-    // O is complete once the last PV has landed
-    mbar_wait(pv_done, (n_kv - 1) & 1);
-    tc_fence_after_sync();
-    float o[HD];
-#pragma unroll
-    for (int c = 0; c < HD / 32; ++c) {
-      uint32_t t[32];
-      tmem_ld_32x32b_x32(tmem_O + lane_base + c * 32, t);
-      tmem_ld_wait();
-#pragma unroll
-      for (int i = 0; i < 32; ++i) o[c * 32 + i] = __uint_as_float(t[i]);
+      // Fold the PREVIOUS tile's PV while the tensor core works on S_{j+1} / PV_j: the PV latency
+      // never sits between two softmax passes.
+      if (j > 0) fold(j - 1, alpha_prev);
+      alpha_prev = alpha;
     }
-    const float m_run = m_ref;
+    fold(n_kv - 1, alpha_prev);
 
     // normalise, stage as bf16 (swizzled 128 B rows) in a P buffer, one TMA store per CTA
     const float inv_l = l_run > 0.f ? 1.0f / l_run : 0.f;
