@@ -317,7 +317,7 @@ def main() -> int:
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", choices=("ours", "reference"), default="ours")
-    ap.add_argument("--micro-batch", type=int, default=16, help="sequences per GPU per micro-step")
+    ap.add_argument("--micro-batch", type=int, default=32, help="sequences per GPU per micro-step")
     ap.add_argument("--grad-accum", type=int, default=1)
     ap.add_argument("--seq-len", type=int, default=1024)
     args = ap.parse_args()

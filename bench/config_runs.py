@@ -36,7 +36,8 @@ def run_cli(cfg: dict, gpus: int, run_id: str, extra: list[str], workdir: Path) 
     proc = subprocess.run(cmd, capture_output=True, text=True, env=env, timeout=1500)
     if proc.returncode != 0:
         raise SystemExit(f"{run_id} failed:\n{proc.stderr[-3000:]}")
-    summary = json.loads(proc.stdout)
+    # NCCL may print its version banner on stdout ahead of the summary document
+    summary = json.loads(proc.stdout[proc.stdout.index("{"):])
     rates = [float(m) for m in re.findall(r"tokens_per_sec=([0-9.]+)", proc.stderr)]
     return {"summary": summary["training"], "tokens_per_sec_rank0_last": rates[-1] if rates else None}
 

@@ -35,56 +35,70 @@ __device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
                     pack_bf16x2(f[6], f[7]));
 }
 
+// Forward.  A warp owns one row at a time and walks rows with a grid stride; gamma/beta for the
+// columns a lane owns are loaded ONCE into registers (they were 4x the load instructions of the
+// activations when re-read per row).  NV = uint4 chunks per lane.
+template <int NV>
 __global__ void __launch_bounds__(WARPS * 32)
 fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
            const float* __restrict__ beta, __nv_bfloat16* __restrict__ y,
            float* __restrict__ mean_out, float* __restrict__ rstd_out, int rows, int d) {
-  const int row = blockIdx.x * WARPS + (threadIdx.x >> 5);
-  if (row >= rows) return;
   const int lane = threadIdx.x & 31;
   const int nvec = d >> 3;
-  const uint4* xr = reinterpret_cast<const uint4*>(x + size_t(row) * d);
-  float v[MAX_VEC][8];
-  float sum = 0.f;
+  float g[NV][8], bt[NV][8];
 #pragma unroll
-  for (int i = 0; i < MAX_VEC; ++i) {
-    const int c = lane + i * 32;
-    if (c < nvec) {
-      unpack8(__ldg(xr + c), v[i]);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) sum += v[i][j];
-    }
-  }
-  const float mean = warp_sum(sum) / d;
-  float sq = 0.f;
-#pragma unroll
-  for (int i = 0; i < MAX_VEC; ++i) {
-    if (lane + i * 32 < nvec) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) { const float t = v[i][j] - mean; sq += t * t; }
-    }
-  }
-  const float rstd = rsqrtf(warp_sum(sq) / d + EPS);
-  uint4* yr = reinterpret_cast<uint4*>(y + size_t(row) * d);
-#pragma unroll
-  for (int i = 0; i < MAX_VEC; ++i) {
+  for (int i = 0; i < NV; ++i) {
     const int c = lane + i * 32;
     if (c < nvec) {
       const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma) + 2 * c);
       const float4 g1 = __ldg(reinterpret_cast<const float4*>(gamma) + 2 * c + 1);
       const float4 b0 = __ldg(reinterpret_cast<const float4*>(beta) + 2 * c);
       const float4 b1 = __ldg(reinterpret_cast<const float4*>(beta) + 2 * c + 1);
-      const float g[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
-      const float b[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-      float o[8];
-#pragma unroll
-      for (int j = 0; j < 8; ++j) o[j] = (v[i][j] - mean) * rstd * g[j] + b[j];
-      yr[c] = pack8(o);
+      g[i][0] = g0.x; g[i][1] = g0.y; g[i][2] = g0.z; g[i][3] = g0.w;
+      g[i][4] = g1.x; g[i][5] = g1.y; g[i][6] = g1.z; g[i][7] = g1.w;
+      bt[i][0] = b0.x; bt[i][1] = b0.y; bt[i][2] = b0.z; bt[i][3] = b0.w;
+      bt[i][4] = b1.x; bt[i][5] = b1.y; bt[i][6] = b1.z; bt[i][7] = b1.w;
     }
   }
-  if (lane == 0) {
-    if (mean_out) mean_out[row] = mean;
-    if (rstd_out) rstd_out[row] = rstd;
+  const float inv_d = 1.0f / d;
+  for (int row = blockIdx.x * WARPS + (threadIdx.x >> 5); row < rows; row += gridDim.x * WARPS) {
+    const uint4* xr = reinterpret_cast<const uint4*>(x + size_t(row) * d);
+    float v[NV][8];
+    float sum = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = lane + i * 32;
+      if (c < nvec) {
+        unpack8(__ldg(xr + c), v[i]);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) sum += v[i][j];
+      }
+    }
+    const float mean = warp_sum(sum) * inv_d;
+    float sq = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      if (lane + i * 32 < nvec) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { const float t = v[i][j] - mean; sq += t * t; }
+      }
+    }
+    const float rstd = rsqrtf(warp_sum(sq) * inv_d + EPS);
+    uint4* yr = reinterpret_cast<uint4*>(y + size_t(row) * d);
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = lane + i * 32;
+      if (c < nvec) {
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = (v[i][j] - mean) * rstd * g[i][j] + bt[i][j];
+        yr[c] = pack8(o);
+      }
+    }
+    if (lane == 0) {
+      if (mean_out) mean_out[row] = mean;
+      if (rstd_out) rstd_out[row] = rstd;
+    }
   }
 }
 
@@ -102,11 +116,19 @@ bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int nvec = d >> 3;
-  float dg[NV][8], db[NV][8];
+  float dg[NV][8], db[NV][8], g[NV][8];
 #pragma unroll
-  for (int i = 0; i < NV; ++i)
+  for (int i = 0; i < NV; ++i) {
 #pragma unroll
-    for (int j = 0; j < 8; ++j) { dg[i][j] = 0.f; db[i][j] = 0.f; }
+    for (int j = 0; j < 8; ++j) { dg[i][j] = 0.f; db[i][j] = 0.f; g[i][j] = 0.f; }
+    const int c = lane + i * 32;
+    if (c < nvec) {
+      const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma) + 2 * c);
+      const float4 g1 = __ldg(reinterpret_cast<const float4*>(gamma) + 2 * c + 1);
+      g[i][0] = g0.x; g[i][1] = g0.y; g[i][2] = g0.z; g[i][3] = g0.w;
+      g[i][4] = g1.x; g[i][5] = g1.y; g[i][6] = g1.z; g[i][7] = g1.w;
+    }
+  }
 
   for (int row = blockIdx.x * WARPS + warp; row < rows; row += gridDim.x * WARPS) {
     const uint4* dyr = reinterpret_cast<const uint4*>(dy + size_t(row) * d);
@@ -126,15 +148,12 @@ bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict
         float a[8], b[8];
         unpack8(pa[i], a);
         unpack8(pb[i], b);
-        const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma) + 2 * c);
-        const float4 g1 = __ldg(reinterpret_cast<const float4*>(gamma) + 2 * c + 1);
-        const float g[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           const float h = (b[j] - mu) * rs;
           dg[i][j] += a[j] * h;
           db[i][j] += a[j];
-          const float w = a[j] * g[j];
+          const float w = a[j] * g[i][j];
           s1 += w;
           s2 += w * h;
         }
@@ -151,13 +170,10 @@ bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict
         unpack8(pa[i], a);
         unpack8(pb[i], b);
         unpack8(drr[c], r);
-        const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma) + 2 * c);
-        const float4 g1 = __ldg(reinterpret_cast<const float4*>(gamma) + 2 * c + 1);
-        const float g[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           const float h = (b[j] - mu) * rs;
-          r[j] += rs * (a[j] * g[j] - s1 - h * s2);
+          r[j] += rs * (a[j] * g[i][j] - s1 - h * s2);
         }
         drr[c] = pack8(r);
       }
@@ -223,9 +239,22 @@ extern "C" int llmtrain_b200_layernorm_fwd(const void* x, const float* gamma, co
                                            cudaStream_t stream) {
   B200_REQUIRE(d % 8 == 0 && d <= ln::MAX_VEC * 256, "layernorm: d must be a multiple of 8, <= 2048");
   if (rows == 0) return 0;
-  ln::fwd_kernel<<<ceil_div(rows, ln::WARPS), ln::WARPS * 32, 0, stream>>>(
-      static_cast<const __nv_bfloat16*>(x), gamma, beta, static_cast<__nv_bfloat16*>(y), mean,
-      rstd, rows, d);
+  const auto* x_ = static_cast<const __nv_bfloat16*>(x);
+  auto* y_ = static_cast<__nv_bfloat16*>(y);
+  int grid = 8 * sm_count();
+  const int need = ceil_div(rows, ln::WARPS);
+  if (grid > need) grid = need;
+#define B200_LN_FWD(NV)                                                                         \
+  case NV:                                                                                      \
+    ln::fwd_kernel<NV><<<grid, ln::WARPS * 32, 0, stream>>>(x_, gamma, beta, y_, mean, rstd,    \
+                                                            rows, d);                           \
+    break;
+  switch (ceil_div(d, 256)) {
+    B200_LN_FWD(1) B200_LN_FWD(2) B200_LN_FWD(3) B200_LN_FWD(4)
+    B200_LN_FWD(5) B200_LN_FWD(6) B200_LN_FWD(7) B200_LN_FWD(8)
+    default: return fail("layernorm_fwd: unsupported width");
+  }
+#undef B200_LN_FWD
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   return 0;
