@@ -58,9 +58,16 @@ struct Params {
   const float* bias;     // [N] fp32 or nullptr
   const __nv_bfloat16* R;  // residual / saved pre-activation, row pitch ldr
   int ldr;
-  __nv_bfloat16* C2;       // second output of the GELU epilogue (pre-activation), row pitch ldc2
+  __nv_bfloat16* C2;       // second output of the GELU epilogue, row pitch ldc2
   int ldc2;
+  __nv_bfloat16* Cptr;     // bf16 output for the direct-store epilogue, row pitch ldc
+  int ldc;
 };
+
+#ifndef B200_GEMM_DIRECT_STORE
+#define B200_GEMM_DIRECT_STORE 1
+#endif
+constexpr bool kDirectStore = B200_GEMM_DIRECT_STORE != 0;
 
 // Phi(x) (standard normal CDF) via Abramowitz & Stegun 7.1.26 for erf (|abs err| < 1.5e-7 — two
 // orders of magnitude below bf16 resolution), arranged for the fewest issue slots: constants are
@@ -346,6 +353,27 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             }
           }
 
+          if (kDirectStore) {
+            // This thread's 64 outputs are 128 contiguous bytes of its row: eight 16-byte stores
+            // cover whole cache lines, and nothing goes through shared memory (the smem port is
+            // the mainloop's bottleneck: ~96 B/cycle of operand reads against a 128 B/cycle port).
+            if (row_ok) {
+              __nv_bfloat16* dst = p.Cptr + size_t(row) * p.ldc + col0;
+              if (full_cols) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                  reinterpret_cast<uint4*>(dst)[j] =
+                      make_uint4(out[4 * j], out[4 * j + 1], out[4 * j + 2], out[4 * j + 3]);
+              } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                  const float2 f = unpack_bf16x2(out[j]);
+                  if (col0 + 2 * j < p.N) dst[2 * j] = __float2bfloat16(f.x);
+                  if (col0 + 2 * j + 1 < p.N) dst[2 * j + 1] = __float2bfloat16(f.y);
+                }
+              }
+            }
+          } else {
           tma_store_wait_read<0>();  // previous chunk's TMA has finished reading the buffer
           __syncwarp();
 #pragma unroll
@@ -359,6 +387,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           if (lane == 0) {
             tma_store_2d(&tmC, stg, col0, m0 + quarter * 32);
             tma_store_commit();
+          }
           }
           if (EPI == kBiasGelu) {
             // Second output (pre-activation, needed by backward): straight from registers with
@@ -449,6 +478,8 @@ extern "C" int llmtrain_b200_gemm(int layout, int epilogue, int M, int N, int K,
   p.ldr = ldr;
   p.C2 = static_cast<__nv_bfloat16*>(C2);
   p.ldc2 = ldc2;
+  p.Cptr = static_cast<__nv_bfloat16*>(C);
+  p.ldc = ldc;
   const auto* a = static_cast<const __nv_bfloat16*>(A);
   const auto* b = static_cast<const __nv_bfloat16*>(B);
   CUtensorMap tA, tB, tC, tC2;
@@ -467,6 +498,8 @@ extern "C" int llmtrain_b200_gemm(int layout, int epilogue, int M, int N, int K,
     p.k_splits = pick_splits(M, N, K);
   } else {
     if (make_tmap_2d(&tC, static_cast<__nv_bfloat16*>(C), M, N, ldc, 32, 64, Swz::B128)) return 1;
+    B200_REQUIRE(!gemm::kDirectStore || (ldc % 8 == 0 && (reinterpret_cast<uintptr_t>(C) & 15) == 0),
+                 "gemm: C must be 16-byte aligned with a pitch that is a multiple of 8");
     if (epilogue == kBiasGelu) {
       B200_REQUIRE(C2 != nullptr, "gemm: GELU epilogue needs the pre-activation output C2");
       B200_REQUIRE(ldc2 % 8 == 0 && (reinterpret_cast<uintptr_t>(C2) & 15) == 0,

@@ -281,8 +281,10 @@ class Trainer:
     # ------------------------------------------------------------------ logging blocks
     def _log_train_interval(self, step: int, max_steps: int, window: _Interval,
                             tokens_local_total: int, tokens_global_total: int) -> int:
-        elapsed = time.perf_counter() - window.started
+        # Read the losses back FIRST: on CUDA that is the synchronisation point, and the interval
+        # must not end while the interval's kernels are still in flight.
         loss_sum = window.loss_sum()
+        elapsed = time.perf_counter() - window.started
         mean_loss = loss_sum / window.steps
         step_time = elapsed / window.steps
         rate = window.tokens / elapsed if elapsed > 0 else 0.0
