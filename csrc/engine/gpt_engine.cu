@@ -249,9 +249,13 @@ int backward(Gpt& g, cudaStream_t s, BucketHook hook = nullptr, void* hook_ctx =
                               nullptr, 0, nullptr, nullptr, 0, st));
   B200_CHECK_CUDA(cudaMemsetAsync(dresid, 0, size_t(M) * d * 2, s));
   const __nv_bfloat16* x_last = g.L > 0 ? v.bf(g.acts[g.L - 1].resid2) : v.bf(g.a_x0);
+  // Every LayerNorm backward also emits the column sums of the residual gradient it has just
+  // produced: that is the bias gradient of the projection whose output this residual value is.
   B200_TRY(llmtrain_b200_layernorm_bwd(dtmp, x_last, v.p(g.lnf_w), v.f32(g.a_lnf_mean),
                                        v.f32(g.a_lnf_rstd), dresid, v.grad(g.lnf_w),
-                                       v.grad(g.lnf_b), red, red_bytes, M, d, st));
+                                       v.grad(g.lnf_b),
+                                       g.L > 0 ? v.grad(g.layer[g.L - 1].proj_b) : nullptr, red,
+                                       red_bytes, M, d, st));
 
   for (int l = g.L - 1; l >= 0; --l) {
     NvtxRange layer_range("layer.bwd");
@@ -259,7 +263,6 @@ int backward(Gpt& g, cudaStream_t s, BucketHook hook = nullptr, void* hook_ctx =
     const LayerActs& a = g.acts[l];
     const __nv_bfloat16* x_in = l > 0 ? v.bf(g.acts[l - 1].resid2) : v.bf(g.a_x0);
     // ---- MLP: resid2 = gelu(ln2 @ Wfc^T + bfc) @ Wproj^T + bproj + resid1
-    B200_TRY(llmtrain_b200_bias_grad(dresid, d, M, d, v.grad(o.proj_b), red, red_bytes, st));
     B200_TRY(linear_wgrad(M, d, F, dresid, d, v.bf(a.fch_act), v.grad(o.proj_w), s));
     B200_TRY(linear_dgrad(3, M, d, F, dresid, v.w(o.proj_w), dfc, v.bf(a.fch_pre), s));
     B200_TRY(llmtrain_b200_bias_grad(dfc, F, M, F, v.grad(o.fc_b), red, red_bytes, st));
@@ -267,9 +270,9 @@ int backward(Gpt& g, cudaStream_t s, BucketHook hook = nullptr, void* hook_ctx =
     B200_TRY(linear_dgrad(0, M, F, d, dfc, v.w(o.fc_w), dtmp, nullptr, s));
     B200_TRY(llmtrain_b200_layernorm_bwd(dtmp, v.bf(a.resid1), v.p(o.ln2_w), v.f32(a.ln2_mean),
                                          v.f32(a.ln2_rstd), dresid, v.grad(o.ln2_w),
-                                         v.grad(o.ln2_b), red, red_bytes, M, d, st));
+                                         v.grad(o.ln2_b), v.grad(o.out_b), red, red_bytes, M, d,
+                                         st));
     // ---- attention: resid1 = attn(ln1 @ Wqkv^T + bqkv) @ Wo^T + bo + x_in
-    B200_TRY(llmtrain_b200_bias_grad(dresid, d, M, d, v.grad(o.out_b), red, red_bytes, st));
     B200_TRY(linear_wgrad(M, d, d, dresid, d, v.bf(a.atty), v.grad(o.out_w), s));
     B200_TRY(linear_dgrad(0, M, d, d, dresid, v.w(o.out_w), dtmp, nullptr, s));
     B200_TRY(llmtrain_b200_attention_bwd(v.bf(a.qkv), v.bf(a.atty), dtmp, v.f32(a.lse), g.key_mask,
@@ -280,7 +283,9 @@ int backward(Gpt& g, cudaStream_t s, BucketHook hook = nullptr, void* hook_ctx =
     B200_TRY(linear_dgrad(0, M, 3 * d, d, dqkv, v.w(o.qkv_w), dtmp, nullptr, s));
     B200_TRY(llmtrain_b200_layernorm_bwd(dtmp, x_in, v.p(o.ln1_w), v.f32(a.ln1_mean),
                                          v.f32(a.ln1_rstd), dresid, v.grad(o.ln1_w),
-                                         v.grad(o.ln1_b), red, red_bytes, M, d, st));
+                                         v.grad(o.ln1_b),
+                                         l > 0 ? v.grad(g.layer[l - 1].proj_b) : nullptr, red,
+                                         red_bytes, M, d, st));
     if (hook != nullptr) {
       // layer l's parameters (+ ln_f for the last layer) are contiguous in the arena
       const size_t lo = o.ln1_w;

@@ -65,7 +65,7 @@ struct Params {
 };
 
 #ifndef B200_GEMM_DIRECT_STORE
-#define B200_GEMM_DIRECT_STORE 1
+#define B200_GEMM_DIRECT_STORE 0
 #endif
 constexpr bool kDirectStore = B200_GEMM_DIRECT_STORE != 0;
 
@@ -354,9 +354,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           }
 
           if (kDirectStore) {
-            // This thread's 64 outputs are 128 contiguous bytes of its row: eight 16-byte stores
-            // cover whole cache lines, and nothing goes through shared memory (the smem port is
-            // the mainloop's bottleneck: ~96 B/cycle of operand reads against a 128 B/cycle port).
+            // Alternative epilogue (compile with -DB200_GEMM_DIRECT_STORE=1): eight 16-byte stores
+            // per thread straight to global memory.  MEASURED SLOWER than the staging + TMA-store
+            // path on B200 (fc forward 70 -> 87 us, whole step +7%), so it is off by default.
             if (row_ok) {
               __nv_bfloat16* dst = p.Cptr + size_t(row) * p.ldc + col0;
               if (full_cols) {

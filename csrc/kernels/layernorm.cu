@@ -106,13 +106,23 @@ fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
 // dgamma/dbeta partial sums of the columns it owns in registers, warps are combined through
 // shared memory in a fixed order, and the CTA writes ONE partial row to scratch.
 // NV = uint4 chunks per lane (ceil(d / 256)); inputs stay packed (bf16) between the two passes.
-template <int NV>
+// COLSUM: additionally produce column sums of the UPDATED residual gradient — that tensor is the
+// output gradient of the preceding out_proj / mlp_proj, so its column sum is that layer's bias
+// gradient and the separate reduction pass over it disappears.
+template <int NV, bool COLSUM>
 __global__ void __launch_bounds__(WARPS * 32)
 bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
            const float* __restrict__ gamma, const float* __restrict__ mean,
            const float* __restrict__ rstd, __nv_bfloat16* __restrict__ dresid,
-           float* __restrict__ partial /* [gridDim.x][2][d] */, int rows, int d) {
-  extern __shared__ float sh[];  // [WARPS][2][d]
+           float* __restrict__ partial /* [gridDim.x][NS][d], NS = COLSUM ? 3 : 2 */, int rows,
+           int d) {
+  constexpr int NS = COLSUM ? 3 : 2;
+  extern __shared__ float sh[];  // [WARPS][NS][d]
+  float dc[COLSUM ? NV : 1][8];
+#pragma unroll
+  for (int i = 0; i < (COLSUM ? NV : 1); ++i)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) dc[i][j] = 0.f;
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int nvec = d >> 3;
@@ -174,27 +184,32 @@ bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict
         for (int j = 0; j < 8; ++j) {
           const float h = (b[j] - mu) * rs;
           r[j] += rs * (a[j] * g[i][j] - s1 - h * s2);
+          if (COLSUM) dc[i][j] += r[j];
         }
         drr[c] = pack8(r);
       }
     }
   }
 
-  float* my = sh + size_t(warp) * 2 * d;
+  float* my = sh + size_t(warp) * NS * d;
 #pragma unroll
   for (int i = 0; i < NV; ++i) {
     const int c = lane + i * 32;
     if (c < nvec) {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) { my[c * 8 + j] = dg[i][j]; my[d + c * 8 + j] = db[i][j]; }
+      for (int j = 0; j < 8; ++j) {
+        my[c * 8 + j] = dg[i][j];
+        my[d + c * 8 + j] = db[i][j];
+        if (COLSUM) my[2 * d + c * 8 + j] = dc[i][j];
+      }
     }
   }
   __syncthreads();
-  float* out = partial + size_t(blockIdx.x) * 2 * d;
-  for (int idx = threadIdx.x; idx < 2 * d; idx += blockDim.x) {
+  float* out = partial + size_t(blockIdx.x) * NS * d;
+  for (int idx = threadIdx.x; idx < NS * d; idx += blockDim.x) {
     float acc = 0.f;
 #pragma unroll
-    for (int w = 0; w < WARPS; ++w) acc += sh[size_t(w) * 2 * d + idx];
+    for (int w = 0; w < WARPS; ++w) acc += sh[size_t(w) * NS * d + idx];
     out[idx] = acc;
   }
 }
@@ -204,22 +219,25 @@ bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict
 // part row), then the 8 partials of a column are combined in a fixed order through smem.
 constexpr int FIN_COLS = 32, FIN_LANES = 8;
 __global__ void __launch_bounds__(FIN_COLS * FIN_LANES)
-finish_kernel(const float* __restrict__ partial, int nparts, int d, float* __restrict__ dgamma,
-              float* __restrict__ dbeta) {
+finish_kernel(const float* __restrict__ partial, int nparts, int d, int ns,
+              float* __restrict__ dgamma, float* __restrict__ dbeta,
+              float* __restrict__ dcolsum) {
   __shared__ float sh[FIN_LANES][FIN_COLS];
   const int cx = threadIdx.x & (FIN_COLS - 1), py = threadIdx.x / FIN_COLS;
   const int idx = blockIdx.x * FIN_COLS + cx;
   float acc = 0.f;
-  if (idx < 2 * d) {
-    for (int p = py; p < nparts; p += FIN_LANES) acc += partial[size_t(p) * 2 * d + idx];
+  if (idx < ns * d) {
+    for (int p = py; p < nparts; p += FIN_LANES) acc += partial[size_t(p) * ns * d + idx];
   }
   sh[py][cx] = acc;
   __syncthreads();
-  if (py == 0 && idx < 2 * d) {
+  if (py == 0 && idx < ns * d) {
     float t = sh[0][cx];
 #pragma unroll
     for (int k = 1; k < FIN_LANES; ++k) t += sh[k][cx];
-    if (idx < d) dgamma[idx] += t; else dbeta[idx - d] += t;
+    if (idx < d) dgamma[idx] += t;
+    else if (idx < 2 * d) dbeta[idx - d] += t;
+    else dcolsum[idx - 2 * d] += t;
   }
 }
 
@@ -261,20 +279,21 @@ extern "C" int llmtrain_b200_layernorm_fwd(const void* x, const float* gamma, co
 }
 
 extern "C" size_t llmtrain_b200_layernorm_bwd_scratch_bytes(int rows, int d) {
-  return size_t(ln::bwd_grid(rows)) * 2 * d * sizeof(float);
+  return size_t(ln::bwd_grid(rows)) * 3 * d * sizeof(float);
 }
 
 extern "C" int llmtrain_b200_layernorm_bwd(const void* dy, const void* x, const float* gamma,
                                            const float* mean, const float* rstd, void* dresid,
-                                           float* dgamma, float* dbeta, void* scratch,
-                                           size_t scratch_bytes, int rows, int d,
+                                           float* dgamma, float* dbeta, float* dcolsum,
+                                           void* scratch, size_t scratch_bytes, int rows, int d,
                                            cudaStream_t stream) {
   B200_REQUIRE(d % 8 == 0 && d <= ln::MAX_VEC * 256, "layernorm: d must be a multiple of 8, <= 2048");
   if (rows == 0) return 0;
   const int grid = ln::bwd_grid(rows);
-  B200_REQUIRE(scratch_bytes >= size_t(grid) * 2 * d * sizeof(float),
+  const int ns = dcolsum != nullptr ? 3 : 2;
+  B200_REQUIRE(scratch_bytes >= size_t(grid) * ns * d * sizeof(float),
                "layernorm_bwd: scratch too small (see llmtrain_b200_layernorm_bwd_scratch_bytes)");
-  const size_t smem = size_t(ln::WARPS) * 2 * d * sizeof(float);
+  const size_t smem = size_t(ln::WARPS) * ns * d * sizeof(float);
   const auto* dy_ = static_cast<const __nv_bfloat16*>(dy);
   const auto* x_ = static_cast<const __nv_bfloat16*>(x);
   auto* dr_ = static_cast<__nv_bfloat16*>(dresid);
@@ -284,13 +303,22 @@ extern "C" int llmtrain_b200_layernorm_bwd(const void* dy, const void* x, const 
   case NV: {                                                                                   \
     static bool configured = false;                                                            \
     if (!configured) {                                                                         \
-      B200_CHECK_CUDA(cudaFuncSetAttribute(ln::bwd_kernel<NV>,                                 \
+      B200_CHECK_CUDA(cudaFuncSetAttribute(ln::bwd_kernel<NV, false>,                          \
                                            cudaFuncAttributeMaxDynamicSharedMemorySize,        \
-                                           160 * 1024));                                       \
+                                           200 * 1024));                                       \
+      B200_CHECK_CUDA(cudaFuncSetAttribute(ln::bwd_kernel<NV, true>,                           \
+                                           cudaFuncAttributeMaxDynamicSharedMemorySize,        \
+                                           200 * 1024));                                       \
       configured = true;                                                                       \
     }                                                                                          \
-    ln::bwd_kernel<NV><<<grid, ln::WARPS * 32, smem, stream>>>(dy_, x_, gamma, mean, rstd, dr_, \
-                                                               part_, rows, d);                \
+    if (ns == 3)                                                                               \
+      ln::bwd_kernel<NV, true><<<grid, ln::WARPS * 32, smem, stream>>>(dy_, x_, gamma, mean,   \
+                                                                       rstd, dr_, part_, rows, \
+                                                                       d);                     \
+    else                                                                                       \
+      ln::bwd_kernel<NV, false><<<grid, ln::WARPS * 32, smem, stream>>>(dy_, x_, gamma, mean,  \
+                                                                        rstd, dr_, part_,      \
+                                                                        rows, d);              \
     break;                                                                                     \
   }
   switch (nv) {
@@ -301,8 +329,8 @@ extern "C" int llmtrain_b200_layernorm_bwd(const void* dy, const void* x, const 
 #undef B200_LN_BWD
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
-  ln::finish_kernel<<<ceil_div(2 * d, ln::FIN_COLS), ln::FIN_COLS * ln::FIN_LANES, 0, stream>>>(
-      static_cast<float*>(scratch), grid, d, dgamma, dbeta);
+  ln::finish_kernel<<<ceil_div(ns * d, ln::FIN_COLS), ln::FIN_COLS * ln::FIN_LANES, 0, stream>>>(
+      static_cast<float*>(scratch), grid, d, ns, dgamma, dbeta, dcolsum);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   return 0;

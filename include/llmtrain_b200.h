@@ -49,7 +49,9 @@ int llmtrain_b200_gemm(int layout, int epilogue, int M, int N, int K, const void
  * LayerNorm (eps 1e-5).  Replaces nn.LayerNorm at src/llmtrain/models/gpt.py:86,93,142.
  *   fwd: y = (x-mean)*rstd*gamma+beta, x/y bf16 [rows,d], gamma/beta fp32; mean/rstd fp32 [rows]
  *        (may be NULL when no backward follows).
- *   bwd: dresid[rows,d] (bf16, in place) += LN'(dy);  dgamma/dbeta (fp32) += column sums.
+ *   bwd: dresid[rows,d] (bf16, in place) += LN'(dy);  dgamma/dbeta (fp32) += column sums;
+ *        if dcolsum != NULL: dcolsum[d] (fp32) += column sums of the UPDATED dresid (= the bias
+ *        gradient of the projection that produced this residual-stream value).
  *        Deterministic two-stage reduction through `scratch` (size from *_scratch_bytes).
  * ------------------------------------------------------------------------------------------- */
 int llmtrain_b200_layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y,
@@ -57,8 +59,8 @@ int llmtrain_b200_layernorm_fwd(const void* x, const float* gamma, const float* 
 size_t llmtrain_b200_layernorm_bwd_scratch_bytes(int rows, int d);
 int llmtrain_b200_layernorm_bwd(const void* dy, const void* x, const float* gamma,
                                 const float* mean, const float* rstd, void* dresid, float* dgamma,
-                                float* dbeta, void* scratch, size_t scratch_bytes, int rows, int d,
-                                llm_stream_t stream);
+                                float* dbeta, float* dcolsum, void* scratch, size_t scratch_bytes,
+                                int rows, int d, llm_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Embedding.  Replaces src/llmtrain/models/gpt.py:176-179 and its backward.

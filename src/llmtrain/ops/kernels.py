@@ -59,7 +59,7 @@ def layernorm_fwd(x, gamma, beta, y=None, mean=None, rstd=None):
     return y
 
 
-def layernorm_bwd(dy, x, gamma, mean, rstd, dresid, dgamma, dbeta):
+def layernorm_bwd(dy, x, gamma, mean, rstd, dresid, dgamma, dbeta, dcolsum=None):
     rows, d = x.shape
     lib = _lib()
     need = lib.llmtrain_b200_layernorm_bwd_scratch_bytes(_c_int(rows), _c_int(d))
@@ -67,7 +67,8 @@ def layernorm_bwd(dy, x, gamma, mean, rstd, dresid, dgamma, dbeta):
     check(
         lib.llmtrain_b200_layernorm_bwd(
             ptr(dy), ptr(x), ptr(gamma), ptr(mean), ptr(rstd), ptr(dresid), ptr(dgamma),
-            ptr(dbeta), ptr(buf), _c_size(buf.numel()), _c_int(rows), _c_int(d), stream_handle(),
+            ptr(dbeta), ptr(dcolsum), ptr(buf), _c_size(buf.numel()), _c_int(rows), _c_int(d),
+            stream_handle(),
         ),
         "layernorm_bwd",
     )

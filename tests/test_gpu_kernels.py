@@ -49,6 +49,11 @@ def test_layernorm_fwd_bwd(rows: int, d: int) -> None:
     # accumulation semantics of the parameter gradients
     K.layernorm_bwd(dy, x, gamma, mean, rstd, dresid, dgamma, dbeta)
     assert _rel(dgamma, 2 * g32.grad) < 1e-2
+    # optional third output: column sums of the updated residual gradient
+    dresid2 = resid0.clone()
+    colsum = torch.ones(d, device="cuda")
+    K.layernorm_bwd(dy, x, gamma, mean, rstd, dresid2, dgamma, dbeta, colsum)
+    assert _rel(colsum, 1.0 + (resid0.float() + xr.grad).sum(0)) < 1e-2
 
 
 def test_embedding_fwd_bwd() -> None:
