@@ -80,6 +80,7 @@ struct Comm {
   uint32_t epoch = 0;
   unsigned long long timeout_ns = 1800ull * 1000000000ull;
   bool peers_open = false;
+  uint32_t oneshot_calls = 0;
 };
 
 __device__ __forceinline__ unsigned long long now_ns() {
@@ -344,6 +345,46 @@ adamw_full_kernel(Peers peers, int world, size_t n, const float* __restrict__ fu
     reinterpret_cast<float4*>(v)[i] = vv;
     reinterpret_cast<uint2*>(p16)[i] = make_uint2(pack_bf16x2(pp[0], pp[1]), pack_bf16x2(pp[2], pp[3]));
     reinterpret_cast<float4*>(g)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// One-shot all-reduce for small messages (<= ONESHOT_MAX elements): a single CTA packs the local
+// values to bf16 in its send buffer, exchanges flags with every peer, then every rank reads ALL
+// peers' buffers and reduces locally in rank order.  One launch instead of five: latency-optimal
+// where the two-shot pipeline is launch-bound.  The send buffer alternates between two halves by
+// call parity, so a fast rank's next call cannot overwrite data a slow peer is still reading.
+// ------------------------------------------------------------------------------------------------
+constexpr size_t ONESHOT_MAX = 1u << 18;  // elements (1 MiB of fp32 payload)
+
+template <int W>
+__global__ void __launch_bounds__(1024)
+oneshot_kernel(Peers peers, int rank, uint32_t epoch, size_t half_off, const float* __restrict__ in,
+               float* __restrict__ out, size_t n, float scale, unsigned long long timeout_ns) {
+  __nv_bfloat16* mine = const_cast<__nv_bfloat16*>(peers.send[rank]) + half_off;
+  for (size_t i = threadIdx.x; i < n; i += blockDim.x) mine[i] = __float2bfloat16(in[i]);
+  __syncthreads();
+  if (threadIdx.x < W) {
+    const int p = threadIdx.x;
+    __threadfence_system();
+    st_release_sys(peers.sync[p] + rank, epoch);
+    const uint32_t* flag = peers.sync[rank] + p;
+    const unsigned long long t0 = now_ns();
+    while (static_cast<int32_t>(ld_acquire_sys(flag) - epoch) < 0) {
+      if (now_ns() - t0 > timeout_ns) {
+        printf("llmtrain nvl: rank %d timed out waiting for rank %d (one-shot, epoch %u)\n", rank,
+               p, epoch);
+        __trap();
+      }
+    }
+  }
+  __syncthreads();
+  __threadfence_system();
+  for (size_t i = threadIdx.x; i < n; i += blockDim.x) {
+    float acc = 0.f;
+#pragma unroll
+    for (int r = 0; r < W; ++r) acc += __bfloat162float(peers.send[r][half_off + i]);
+    out[i] = acc * scale;
   }
 }
 
@@ -648,5 +689,53 @@ extern "C" int llmtrain_b200_nvl_finish_step(void* nvl_handle, float* g, float* 
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   c.buckets_this_step = 0;
+  return 0;
+}
+
+// Small-message all-reduce: out[i] = scale * sum_r bf16(in_r[i]) for count <= 262144 elements
+// (count may be smaller than the communicator's arena; the arena must hold 2 * count elements).
+extern "C" int llmtrain_b200_nvl_allreduce_oneshot(void* handle, const float* in, float* out,
+                                                   size_t count, float scale,
+                                                   llm_stream_t stream) {
+  Comm& c = *static_cast<Comm*>(handle);
+  B200_REQUIRE(c.peers_open, "nvl: peers are not connected");
+  B200_REQUIRE(count > 0 && count <= nvl::ONESHOT_MAX, "nvl_allreduce_oneshot: count out of range");
+  B200_REQUIRE(2 * count <= c.n, "nvl_allreduce_oneshot: communicator arena too small");
+  auto s = reinterpret_cast<cudaStream_t>(stream);
+  const size_t half_off = (c.oneshot_calls++ & 1u) ? (c.n / 2) : 0;
+  c.epoch += 1;
+#define B200_ONESHOT(W)                                                                        \
+  case W:                                                                                      \
+    nvl::oneshot_kernel<W><<<1, 1024, 0, s>>>(c.peers, c.rank, c.epoch, half_off, in, out,     \
+                                              count, scale, c.timeout_ns);                     \
+    break;
+  switch (c.world) {
+    B200_ONESHOT(2) B200_ONESHOT(3) B200_ONESHOT(4) B200_ONESHOT(5) B200_ONESHOT(6)
+    B200_ONESHOT(7) B200_ONESHOT(8)
+    default: return fail("nvl: world size must be in [2, 8]");
+  }
+#undef B200_ONESHOT
+  B200_CHECK_CUDA(cudaGetLastError());
+  B200_COUNT_LAUNCH(1);
+  return 0;
+}
+
+// Broadcast `count` fp32 values from `root` to every rank through the symmetric `full` buffer:
+// root stages locally, flag barrier, the others pull with a copy-engine transfer from root's
+// mapped buffer, flag barrier (root may then reuse the buffer).  Replaces the parameter broadcast
+// DistributedDataParallel performs in its constructor.
+extern "C" int llmtrain_b200_nvl_broadcast(void* handle, float* buf, size_t count, int root,
+                                           llm_stream_t stream) {
+  Comm& c = *static_cast<Comm*>(handle);
+  B200_REQUIRE(c.peers_open, "nvl: peers are not connected");
+  B200_REQUIRE(count <= c.n && root >= 0 && root < c.world, "nvl_broadcast: bad arguments");
+  auto s = reinterpret_cast<cudaStream_t>(stream);
+  if (c.rank == root)
+    B200_CHECK_CUDA(cudaMemcpyAsync(c.full, buf, count * sizeof(float), cudaMemcpyDeviceToDevice, s));
+  if (nvl::launch_barrier(c, s)) return 1;
+  if (c.rank != root)
+    B200_CHECK_CUDA(cudaMemcpyAsync(buf, c.peers.full[root], count * sizeof(float),
+                                    cudaMemcpyDeviceToDevice, s));
+  if (nvl::launch_barrier(c, s)) return 1;
   return 0;
 }

@@ -298,10 +298,46 @@ __global__ void cast_kernel(const float* __restrict__ src, __nv_bfloat16* __rest
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Device-resident synthetic token source (work item W13): counter-based generator, one thread per
+// row, ids[b,t] = h(seed, row, t) mod vocab and labels[b,t] = ids[b,t+1] (next-token targets),
+// so benchmark inputs never have to cross PCIe.  splitmix64 finaliser as the hash.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint64_t mix64(uint64_t z) {
+  z += 0x9E3779B97F4A7C15ull;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  return z ^ (z >> 31);
+}
+__global__ void synth_tokens_kernel(int64_t* __restrict__ ids, int64_t* __restrict__ labels,
+                                    int rows, int T, int vocab, uint64_t seed, uint64_t row0) {
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (long long)rows * T) return;
+  const int r = int(idx / T), t = int(idx - (long long)r * T);
+  const uint64_t base = mix64(seed ^ mix64(row0 + uint64_t(r)));
+  const int64_t cur = int64_t(mix64(base + uint64_t(t)) % uint64_t(vocab));
+  const int64_t nxt = int64_t(mix64(base + uint64_t(t) + 1) % uint64_t(vocab));
+  ids[idx] = cur;
+  if (labels != nullptr) labels[idx] = nxt;
+}
+
 }  // namespace ew
 }  // namespace b200
 
 using namespace b200;
+
+extern "C" int llmtrain_b200_synthetic_tokens(int64_t* ids, int64_t* labels, int rows, int T,
+                                              int vocab, uint64_t seed, uint64_t first_row,
+                                              cudaStream_t stream) {
+  B200_REQUIRE(vocab > 0 && rows >= 0 && T > 0, "synthetic_tokens: bad shape");
+  if (rows == 0) return 0;
+  const long long n = (long long)rows * T;
+  ew::synth_tokens_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, stream>>>(
+      ids, labels, rows, T, vocab, seed, first_row);
+  B200_CHECK_CUDA(cudaGetLastError());
+  B200_COUNT_LAUNCH(1);
+  return 0;
+}
 
 extern "C" int llmtrain_b200_embed_fwd(const int64_t* ids, const void* wte, const void* wpe,
                                        void* x, int B, int T, int d, int vocab,

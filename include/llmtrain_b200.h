@@ -105,6 +105,12 @@ size_t llmtrain_b200_bias_grad_noalloc_capacity_bytes(void);
 int llmtrain_b200_bias_grad_noalloc(const void* dy, int ld, int M, int N, float* dbias,
                                     llm_stream_t stream);
 
+/* Device-resident synthetic next-token data: ids[r,t] = hash(seed, first_row + r, t) mod vocab,
+ * labels[r,t] = ids[r,t+1] (labels may be NULL).  Capability of the reference's dummy_text
+ * (src/llmtrain/data/dummy_text.py:33-51) at full sequence length, without host copies. */
+int llmtrain_b200_synthetic_tokens(int64_t* ids, int64_t* labels, int rows, int T, int vocab,
+                                   uint64_t seed, uint64_t first_row, llm_stream_t stream);
+
 int llmtrain_b200_cast_f32_to_bf16(const float* src, void* dst, size_t n, llm_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
@@ -198,6 +204,21 @@ int llmtrain_b200_nvl_step(void* handle, float* g, float* p, float* m, float* v,
                            llm_stream_t stream);
 int llmtrain_b200_nvl_allreduce(void* handle, float* in, float* out, float scale,
                                 llm_stream_t stream);
+/* One launch, every rank reads all peers (latency-optimal, count <= 262144, arena >= 2*count). */
+int llmtrain_b200_nvl_allreduce_oneshot(void* handle, const float* in, float* out, size_t count,
+                                        float scale, llm_stream_t stream);
+/* Copy-engine broadcast of fp32 values from `root` (initial parameter sync). */
+int llmtrain_b200_nvl_broadcast(void* handle, float* buf, size_t count, int root,
+                                llm_stream_t stream);
+/* Overlapped path: backward of a bound GPT runtime with per-layer buckets reduced on the
+ * communicator's stream (owners' reduced slices reach all ranks via copy engines), then the
+ * local clip + AdamW tail. */
+int llmtrain_b200_nvl_backward_overlapped(void* nvl_handle, void* gpt_handle, float* g,
+                                          llm_stream_t stream);
+int llmtrain_b200_nvl_finish_step(void* nvl_handle, float* g, float* p, float* m, float* v,
+                                  void* p16, float* norm_out, float lr, float beta1, float beta2,
+                                  float eps, float weight_decay, int step, float grad_scale,
+                                  float max_norm, llm_stream_t stream);
 
 #ifdef __cplusplus
 }

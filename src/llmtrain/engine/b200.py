@@ -367,8 +367,8 @@ class B200TrainEngine(TrainEngine):
         self.phase_ms: dict[str, float] = {}
 
         if self._world > 1:
-            self._sync_initial_parameters()
             self._comm = self._build_comm(cfg)
+            self._sync_initial_parameters()
 
         # torch's own AdamW object is the checkpoint-format state container; its per-parameter
         # state tensors are views of the flat moment arenas the fused kernel updates.
@@ -394,7 +394,11 @@ class B200TrainEngine(TrainEngine):
         import torch.distributed as dist
 
         assert self._gpt.p32 is not None
-        dist.broadcast(self._gpt.p32, src=0)
+        nvl_comm = getattr(self._comm, "_comm", None)
+        if nvl_comm is not None and hasattr(nvl_comm, "broadcast"):
+            nvl_comm.broadcast(self._gpt.p32, root=0)  # copy engines over mapped peer memory
+        else:
+            dist.broadcast(self._gpt.p32, src=0)
 
     def _build_comm(self, cfg: RunConfig) -> Any:
         from llmtrain.parallel import nvl

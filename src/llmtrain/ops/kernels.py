@@ -202,5 +202,19 @@ def attention_bwd(qkv, out, dout, lse, n_heads, *, key_mask=None, dqkv=None):
     return dqkv
 
 
+def synthetic_tokens(batch: int, seq: int, vocab: int, *, seed: int, first_row: int = 0,
+                     device: torch.device | str = "cuda", with_labels: bool = True):
+    """Device-resident ``(input_ids, labels)`` (next-token targets) from a counter-based hash."""
+    ids = torch.empty(batch, seq, dtype=torch.int64, device=device)
+    labels = torch.empty_like(ids) if with_labels else None
+    check(
+        _lib().llmtrain_b200_synthetic_tokens(
+            ptr(ids), ptr(labels), _c_int(batch), _c_int(seq), _c_int(vocab),
+            ctypes.c_uint64(seed), ctypes.c_uint64(first_row), stream_handle()),
+        "synthetic_tokens",
+    )
+    return ids, labels
+
+
 def softmax_scale(head_dim: int) -> float:
     return 1.0 / math.sqrt(head_dim)

@@ -103,6 +103,24 @@ class NvlComm:
             "nvl_allreduce",
         )
 
+    def allreduce_small(self, src: torch.Tensor, dst: torch.Tensor, scale: float = 1.0) -> None:
+        """One-launch all-reduce for messages up to 262144 elements (every rank reads all peers)."""
+        check(
+            self._lib.llmtrain_b200_nvl_allreduce_oneshot(
+                self._handle, ptr(src), ptr(dst), ctypes.c_size_t(src.numel()),
+                ctypes.c_float(scale), stream_handle()),
+            "nvl_allreduce_oneshot",
+        )
+
+    def broadcast(self, buf: torch.Tensor, root: int = 0) -> None:
+        """Copy-engine broadcast of an fp32 buffer (at most the arena length) from ``root``."""
+        check(
+            self._lib.llmtrain_b200_nvl_broadcast(self._handle, ptr(buf),
+                                                  ctypes.c_size_t(buf.numel()),
+                                                  ctypes.c_int(root), stream_handle()),
+            "nvl_broadcast",
+        )
+
     def step(self, g: torch.Tensor, p: torch.Tensor, m: torch.Tensor, v: torch.Tensor,
              p16: torch.Tensor, norm: torch.Tensor | None, hyper: dict[str, Any]) -> None:
         check(

@@ -31,6 +31,27 @@ def _check_allreduce(comm, rank: int, world: int) -> None:
         assert torch.equal(out, want), f"rank {rank}: allreduce mismatch {(out - want).abs().max()}"
 
 
+def _check_small_and_broadcast(comm, rank: int, world: int) -> None:
+    for n in (8, 1000, 65536):  # twice each: the two send-buffer halves
+        for rep in range(2):
+            torch.manual_seed(50 + rank + rep)
+            src = torch.randn(n, device="cuda")
+            out = torch.empty(n, device="cuda")
+            comm.allreduce_small(src, out, 0.5)
+            torch.cuda.synchronize()
+            rounded = src.to(torch.bfloat16).float()
+            parts = [torch.empty_like(rounded) for _ in range(world)]
+            dist.all_gather(parts, rounded)
+            want = torch.zeros_like(rounded)
+            for part in parts:
+                want += part
+            assert torch.equal(out, want * 0.5), f"one-shot mismatch n={n}"
+    buf = torch.full((12345,), float(rank + 1), device="cuda")
+    comm.broadcast(buf, root=world - 1)
+    torch.cuda.synchronize()
+    assert torch.equal(buf, torch.full_like(buf, float(world)))
+
+
 def _check_step(comm, rank: int, world: int) -> None:
     from llmtrain.ops import kernels as K
 
@@ -110,6 +131,7 @@ def main() -> int:
 
         comm = NvlComm(8 * 1024 * 1024 + 64, rank=rank, world=world, timeout_s=60)
         _check_allreduce(comm, rank, world)
+        _check_small_and_broadcast(comm, rank, world)
         _check_step(comm, rank, world)
         loss_overlapped = _check_trainer(rank, world, overlap=True)
         loss_serial = _check_trainer(rank, world, overlap=False)

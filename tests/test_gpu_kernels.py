@@ -225,3 +225,19 @@ def test_attention_bwd_key_padding() -> None:
     want, _ = _ref_attention(ref_in, h, mask)
     want.backward(dout.float())
     assert _rel(dqkv, ref_in.grad) < 3e-2
+
+
+def test_synthetic_tokens_are_shifted_in_range_and_reproducible() -> None:
+    from llmtrain.ops import kernels as K
+
+    ids, labels = K.synthetic_tokens(4, 257, 50257, seed=7, first_row=10)
+    assert ids.shape == (4, 257) and ids.dtype == torch.int64
+    assert int(ids.min()) >= 0 and int(ids.max()) < 50257
+    assert torch.equal(labels[:, :-1], ids[:, 1:])
+    again, _ = K.synthetic_tokens(4, 257, 50257, seed=7, first_row=10)
+    assert torch.equal(ids, again)
+    shifted, _ = K.synthetic_tokens(2, 257, 50257, seed=7, first_row=12)
+    assert torch.equal(shifted, ids[2:])
+    other, _ = K.synthetic_tokens(4, 257, 50257, seed=8, first_row=10)
+    assert not torch.equal(ids, other)
+    assert ids.float().mean().item() == pytest.approx(50257 / 2, rel=0.1)
