@@ -40,6 +40,8 @@ def main() -> int:
     ap.add_argument("--tokens", type=int, default=16384)
     ap.add_argument("--d", type=int, default=768)
     ap.add_argument("--vocab", type=int, default=50304)
+    ap.add_argument("--square", type=int, default=0,
+                    help="also time an N^3 problem (asymptotic mainloop efficiency)")
     args = ap.parse_args()
     M, d, F, V = args.tokens, args.d, 4 * args.d, args.vocab
     peak = json.loads((ROOT / "MEASURED_PEAKS.json").read_text()).get("bf16_tflops", 1649.3) \
@@ -49,6 +51,17 @@ def main() -> int:
         return (torch.randn(*shape, device="cuda") * 0.05).to(torch.bfloat16)
 
     rows = []
+    if args.square:
+        n = args.square
+        a, b = bf(n, n), bf(n, n)
+        c = torch.empty(n, n, device="cuda", dtype=torch.bfloat16)
+        flops = 2.0 * n * n * n
+        t_ours = _time(lambda: G.gemm(G.NT, G.EPI_BIAS, a, b, c))
+        t_ref = _time(lambda: torch.matmul(a, b.t()))
+        print(json.dumps({"gemm": f"square{n}", "kind": "fwd NT", "ours_ms": round(t_ours, 4),
+                          "cublas_ms": round(t_ref, 4),
+                          "ours_tflops": round(flops / t_ours / 1e9, 1),
+                          "cublas_tflops": round(flops / t_ref / 1e9, 1)}), flush=True)
     fwd = [("qkv", 3 * d, d), ("out", d, d), ("fc", F, d), ("proj", d, F), ("lm_head", V, d)]
     for name, N, K in fwd:
         x, w = bf(M, K), bf(N, K)

@@ -30,19 +30,32 @@ constexpr int BM = 128;
 constexpr int BN = 256;
 constexpr int BK = 64;  // 64 bf16 = 128 B = one swizzle row
 constexpr int UK = 16;
-constexpr int STAGES = 4;
+// smem ring depth: 4 x 48 KB everywhere except the GELU epilogue, which trades one stage for a
+// second 4 KB staging buffer per epilogue warp (its two outputs then leave through two TMA stores
+// in flight instead of one store plus scattered 16-byte global writes).
+template <int EPI> struct Cfg {
+  static constexpr int kStages = 4;
+  static constexpr int kEpiBufs = 1;
+};
+template <> struct Cfg<1 /*kBiasGelu*/> {
+  static constexpr int kStages = 3;
+  static constexpr int kEpiBufs = 2;
+};
 constexpr int A_BYTES = BM * BK * 2;  // 16 KB
 constexpr int B_BYTES = BN * BK * 2;  // 32 KB
 constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
 constexpr int EPI_WARPS = 8;              // two warps per TMEM lane quarter, each owns 128 columns
 constexpr int EPI_BUF_BYTES = 32 * 128;  // 32 rows x 128 B per staging buffer
-constexpr int EPI_BYTES = EPI_WARPS * EPI_BUF_BYTES;
+template <int EPI> __host__ __device__ constexpr int epi_bytes() { return EPI_WARPS * Cfg<EPI>::kEpiBufs * EPI_BUF_BYTES; }
+template <int EPI> __host__ __device__ constexpr int smem_bytes() {
+  return Cfg<EPI>::kStages * STAGE_BYTES + epi_bytes<EPI>() + 256 /*barriers*/;
+}
 constexpr int NUM_THREADS = 32 * (2 + EPI_WARPS);
 constexpr int TMEM_COLS = 512;
 // No alignment slack: the kernel has no static shared memory, so its dynamic window starts at the
 // 1024 B-aligned base of the CTA's allocation.  Staying under 225 KB leaves room for one of the
 // communicator's small, smem-free CTAs to share the SM during the overlapped bucket reduction.
-constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + 256 /*barriers*/;
+// (shared memory per variant: smem_bytes<EPI>())
 
 enum Epi : int {
   kBias = 0,      // C = acc (+ bias)
@@ -108,8 +121,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw;
   if ((smem_u32(smem) & 1023u) != 0) __trap();
+  constexpr int STAGES = Cfg<EPI>::kStages;
+  constexpr int EPI_BUFS = Cfg<EPI>::kEpiBufs;
   uint8_t* epi_smem = smem + STAGES * STAGE_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(epi_smem + EPI_BYTES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(epi_smem + epi_bytes<EPI>());
   uint64_t* full_bar = bars;                  // [STAGES]
   uint64_t* empty_bar = bars + STAGES;        // [STAGES]
   uint64_t* tfull_bar = bars + 2 * STAGES;    // [2]
@@ -229,7 +244,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     const int ew = warp - 2;        // 0..7
     const int quarter = warp & 3;   // TMEM lane quarter this warp may access
     const int half = ew >> 2;       // which 128-column half of the tile
-    uint8_t* stg = epi_smem + ew * EPI_BUF_BYTES;
+    uint8_t* stg = epi_smem + ew * EPI_BUFS * EPI_BUF_BYTES;
+    uint8_t* stg2 = stg + (EPI_BUFS - 1) * EPI_BUF_BYTES;  // == stg unless the variant has two
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -390,24 +406,19 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           }
           }
           if (EPI == kBiasGelu) {
-            // Second output (pre-activation, needed by backward): straight from registers with
-            // 16-byte stores — this thread's row, 128 contiguous bytes.  Pushing it through the
-            // staging buffer as well would serialise two TMA round trips per chunk.
-            if (row_ok) {
-              __nv_bfloat16* dst = p.C2 + size_t(row) * p.ldc2 + col0;
-              if (full_cols) {
+            // Second output, gelu'(x), through its own staging buffer: both TMA stores of this
+            // chunk are in flight together (the wait at the top of the next chunk covers both).
 #pragma unroll
-                for (int j = 0; j < 8; ++j)
-                  reinterpret_cast<uint4*>(dst)[j] =
-                      make_uint4(out2[4 * j], out2[4 * j + 1], out2[4 * j + 2], out2[4 * j + 3]);
-              } else {
-#pragma unroll
-                for (int j = 0; j < 32; ++j) {
-                  const float2 f = unpack_bf16x2(out2[j]);
-                  if (col0 + 2 * j < p.N) dst[2 * j] = __float2bfloat16(f.x);
-                  if (col0 + 2 * j + 1 < p.N) dst[2 * j + 1] = __float2bfloat16(f.y);
-                }
-              }
+            for (int j = 0; j < 8; ++j) {
+              const uint32_t off = swizzle128(lane * 128 + j * 16);
+              *reinterpret_cast<uint4*>(stg2 + off) =
+                  make_uint4(out2[4 * j], out2[4 * j + 1], out2[4 * j + 2], out2[4 * j + 3]);
+            }
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+              tma_store_2d(&tmC2, stg2, col0, m0 + quarter * 32);
+              tma_store_commit();
             }
           }
         }
@@ -436,12 +447,12 @@ int launch(const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tC,
   static bool configured = false;
   if (!configured) {
     B200_CHECK_CUDA(
-        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<EPI>()));
     configured = true;
   }
   const int tiles = ceil_div(p.M, BM) * ceil_div(p.N, BN) * p.k_splits;
   const int grid = tiles < sm_count() ? tiles : sm_count();
-  kern<<<grid, NUM_THREADS, SMEM_BYTES, stream>>>(tA, tB, tC, tC2, p);
+  kern<<<grid, NUM_THREADS, smem_bytes<EPI>(), stream>>>(tA, tB, tC, tC2, p);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   return 0;
@@ -501,9 +512,9 @@ extern "C" int llmtrain_b200_gemm(int layout, int epilogue, int M, int N, int K,
     B200_REQUIRE(!gemm::kDirectStore || (ldc % 8 == 0 && (reinterpret_cast<uintptr_t>(C) & 15) == 0),
                  "gemm: C must be 16-byte aligned with a pitch that is a multiple of 8");
     if (epilogue == kBiasGelu) {
-      B200_REQUIRE(C2 != nullptr, "gemm: GELU epilogue needs the pre-activation output C2");
-      B200_REQUIRE(ldc2 % 8 == 0 && (reinterpret_cast<uintptr_t>(C2) & 15) == 0,
-                   "gemm: C2 must be 16-byte aligned with a pitch that is a multiple of 8");
+      B200_REQUIRE(C2 != nullptr, "gemm: GELU epilogue needs the second output C2");
+      if (make_tmap_2d(&tC2, static_cast<__nv_bfloat16*>(C2), M, N, ldc2, 32, 64, Swz::B128))
+        return 1;
     }
     if (epilogue == kBiasResid || epilogue == kDGelu)
       B200_REQUIRE(R != nullptr, "gemm: this epilogue needs R");
