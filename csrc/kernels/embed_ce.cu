@@ -6,6 +6,8 @@
 // are the autograd of the four nn.Linear biases (K12).  All of these are HBM-bound, so every
 // kernel makes exactly one pass over its large operand with 128-bit accesses.
 
+#include <cstdlib>
+
 #include "../common/host.cuh"
 #include "../common/ptx.cuh"
 #include "../../include/llmtrain_b200.h"
@@ -185,6 +187,160 @@ ce_kernel(__nv_bfloat16* __restrict__ logits, const int64_t* __restrict__ labels
       o[j] = pack_bf16x2(g0, g1);
     }
     rp[c] = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+
+// Row-resident variant (the one the trainer runs when two rows fit in shared memory, i.e.
+// ldv <= CE_ROW_MAX_LDV): a persistent CTA per SM owns rows blockIdx.x, +gridDim.x, ... and keeps
+// each row in shared memory across three sweeps, so HBM sees ONE read and ONE write per logit
+// instead of two reads and a write, and the next row streams in (untiled bulk copy,
+// cp.async.bulk) underneath the math of the current one.
+//   sweep A  exact row max on PACKED bf16 (4 max instructions per 8 logits)
+//   sweep B  sum of exp2((x - max) * log2 e): one FFMA + one MUFU per logit
+//   sweep C  dlogits = exp2(..) / sum * scale - onehot, stored straight to global (in place)
+// ce_kernel's online (max, sum) merge spends ~10 instructions and 1.25 MUFU per logit in its
+// first pass; with 100 K exponentials per row the MUFU pipe, not HBM, was the limiter.
+// Chunk c of a row is touched by thread c % CE_ROW_THREADS in every sweep, so the owner can patch
+// its padding columns to -inf in shared memory without a barrier.
+constexpr int CE_ROW_THREADS = 512;
+constexpr int CE_ROW_CHUNK = 16384;                             // bytes per bulk copy
+constexpr int CE_ROW_MAX_LDV = (220 * 1024 / 2) / 2 / 64 * 64;  // two bf16 rows in <= 220 KB
+
+__device__ __forceinline__ uint32_t bf16x2_max(uint32_t a, uint32_t b) {
+  uint32_t r;
+  asm("max.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+  return r;
+}
+
+template <bool WRITE_GRAD>
+__global__ void __launch_bounds__(CE_ROW_THREADS, 1)
+ce_row_kernel(__nv_bfloat16* __restrict__ logits, const int64_t* __restrict__ labels,
+              const uint8_t* __restrict__ row_valid, float* __restrict__ loss_rows, int rows,
+              int V, int ldv, float grad_scale) {
+  extern __shared__ __align__(128) uint8_t ce_row_smem[];
+  __shared__ uint64_t full[2];
+  __shared__ float red_m[CE_ROW_THREADS / 32], red_s[CE_ROW_THREADS / 32];
+  constexpr int NW = CE_ROW_THREADS / 32;
+  constexpr float LOG2E = 1.4426950408889634f, LN2 = 0.6931471805599453f;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t row_bytes = uint32_t(ldv) * 2u;
+  const uint32_t pitch = (row_bytes + 127u) & ~127u;
+  const int nvec = ldv >> 3;
+  const int first_pad_chunk = V >> 3;  // chunks >= this one contain columns >= V
+
+  if (tid == 0) {
+    mbar_init(&full[0], 1);
+    mbar_init(&full[1], 1);
+    fence_barrier_init();
+  }
+  __syncthreads();
+
+  auto load_row = [&](int r, int b) {
+    mbar_expect_tx(&full[b], row_bytes);
+    const uint8_t* src = reinterpret_cast<const uint8_t*>(logits + size_t(r) * ldv);
+    uint8_t* dst = ce_row_smem + size_t(b) * pitch;
+    for (uint32_t off = 0; off < row_bytes; off += CE_ROW_CHUNK) {
+      const uint32_t n = row_bytes - off < uint32_t(CE_ROW_CHUNK) ? row_bytes - off : CE_ROW_CHUNK;
+      bulk_load_1d(dst + off, src + off, n, &full[b]);
+    }
+  };
+
+  int row = blockIdx.x;
+  if (tid == 0 && row < rows) load_row(row, 0);
+  for (int it = 0; row < rows; row += gridDim.x, ++it) {
+    const int b = it & 1;
+    // Every thread finished reading buffer b^1 before the barrier that ended the last iteration.
+    if (tid == 0 && row + int(gridDim.x) < rows) load_row(row + gridDim.x, b ^ 1);
+    const bool valid = row_valid == nullptr || row_valid[row] != 0;
+    const int label = static_cast<int>(labels[row]);
+    uint4* rp = reinterpret_cast<uint4*>(ce_row_smem + size_t(b) * pitch);
+    mbar_wait(&full[b], (it >> 1) & 1);
+
+    // Padding columns [V, ldv) -> -inf, by the thread that owns the chunk in every sweep.
+    for (int c = tid; c < nvec; c += CE_ROW_THREADS) {
+      if (c >= first_pad_chunk) {
+        __nv_bfloat16* e = reinterpret_cast<__nv_bfloat16*>(rp + c);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (c * 8 + j >= V) e[j] = __ushort_as_bfloat16(0xFF80u);
+        fence_proxy_async_smem();  // ordered before the bulk load that later reuses this buffer
+      }
+    }
+
+    // Sweep A: packed max.
+    uint32_t pm = 0xFF80FF80u;
+#pragma unroll 4
+    for (int c = tid; c < nvec; c += CE_ROW_THREADS) {
+      const uint4 u = rp[c];
+      pm = bf16x2_max(pm, bf16x2_max(bf16x2_max(u.x, u.y), bf16x2_max(u.z, u.w)));
+    }
+    const float2 pmf = unpack_bf16x2(pm);
+    float m = fmaxf(pmf.x, pmf.y);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if (lane == 0) red_m[warp] = m;
+    __syncthreads();
+    m = red_m[0];
+#pragma unroll
+    for (int w = 1; w < NW; ++w) m = fmaxf(m, red_m[w]);
+    const float mxl = m * LOG2E;
+
+    // Sweep B: sum of exponentials.
+    float s0 = 0.f, s1 = 0.f;
+#pragma unroll 2
+    for (int c = tid; c < nvec; c += CE_ROW_THREADS) {
+      const uint4 u = rp[c];
+      const float2 a = unpack_bf16x2(u.x), bb = unpack_bf16x2(u.y), cc = unpack_bf16x2(u.z),
+                   dd = unpack_bf16x2(u.w);
+      s0 += fast_exp2(fmaf(a.x, LOG2E, -mxl)) + fast_exp2(fmaf(bb.x, LOG2E, -mxl)) +
+            fast_exp2(fmaf(cc.x, LOG2E, -mxl)) + fast_exp2(fmaf(dd.x, LOG2E, -mxl));
+      s1 += fast_exp2(fmaf(a.y, LOG2E, -mxl)) + fast_exp2(fmaf(bb.y, LOG2E, -mxl)) +
+            fast_exp2(fmaf(cc.y, LOG2E, -mxl)) + fast_exp2(fmaf(dd.y, LOG2E, -mxl));
+    }
+    float ssum = s0 + s1;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) ssum += __shfl_xor_sync(0xffffffffu, ssum, o);
+    if (lane == 0) red_s[warp] = ssum;
+    __syncthreads();
+    ssum = 0.f;
+#pragma unroll
+    for (int w = 0; w < NW; ++w) ssum += red_s[w];  // fixed order: every thread gets the same bits
+
+    if (tid == 0) {
+      const float picked = (label >= 0 && label < V)
+                               ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(rp)[label])
+                               : 0.f;
+      loss_rows[row] = valid ? (__log2f(ssum) * LN2 + m - picked) : 0.f;
+    }
+
+    if (WRITE_GRAD) {
+      // Sweep C: gradients straight to global memory (the row's own storage).
+      const float inv = valid ? grad_scale / ssum : 0.f;
+      const float hot = valid ? grad_scale : 0.f;
+      const int label_chunk = (label >= 0 && label < V) ? (label >> 3) : -1;
+      uint4* out = reinterpret_cast<uint4*>(logits + size_t(row) * ldv);
+#pragma unroll 2
+      for (int c = tid; c < nvec; c += CE_ROW_THREADS) {
+        const uint4 u = rp[c];
+        const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+        uint32_t o[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float2 f = unpack_bf16x2(w[j]);
+          o[j] = pack_bf16x2(fast_exp2(fmaf(f.x, LOG2E, -mxl)) * inv,
+                             fast_exp2(fmaf(f.y, LOG2E, -mxl)) * inv);
+        }
+        out[c] = make_uint4(o[0], o[1], o[2], o[3]);
+      }
+      // One-hot term: a scalar fix-up by the thread that stored the label's chunk (same thread,
+      // same address, program order => it lands after the vector store).
+      if (label_chunk >= 0 && (label_chunk % CE_ROW_THREADS) == tid) {
+        const float x = __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(rp)[label]);
+        logits[size_t(row) * ldv + label] =
+            __float2bfloat16(fast_exp2(fmaf(x, LOG2E, -mxl)) * inv - hot);
+      }
+    }
+    __syncthreads();  // buffer b and red_* may be reused
   }
 }
 
@@ -378,7 +534,25 @@ extern "C" int llmtrain_b200_cross_entropy(void* logits, const int64_t* labels,
   B200_REQUIRE(ldv % 8 == 0 && ldv >= V, "cross_entropy: row pitch must be >= V and a multiple of 8");
   if (rows == 0) return 0;
   auto* lg = static_cast<__nv_bfloat16*>(logits);
-  if (write_grad) {
+  static const bool row_path_off = std::getenv("LLMTRAIN_CE_TWO_PASS") != nullptr;
+  if (!row_path_off && ldv <= ew::CE_ROW_MAX_LDV && (reinterpret_cast<uintptr_t>(logits) & 15) == 0) {
+    const size_t smem = 2 * ((size_t(ldv) * 2 + 127) & ~size_t(127));
+    static bool configured = false;
+    if (!configured) {
+      B200_CHECK_CUDA(cudaFuncSetAttribute(ew::ce_row_kernel<true>,
+                                           cudaFuncAttributeMaxDynamicSharedMemorySize, 225280));
+      B200_CHECK_CUDA(cudaFuncSetAttribute(ew::ce_row_kernel<false>,
+                                           cudaFuncAttributeMaxDynamicSharedMemorySize, 225280));
+      configured = true;
+    }
+    const int grid = rows < sm_count() ? rows : sm_count();
+    if (write_grad)
+      ew::ce_row_kernel<true><<<grid, ew::CE_ROW_THREADS, smem, stream>>>(
+          lg, labels, row_valid, loss_rows, rows, V, ldv, grad_scale);
+    else
+      ew::ce_row_kernel<false><<<grid, ew::CE_ROW_THREADS, smem, stream>>>(
+          lg, labels, row_valid, loss_rows, rows, V, ldv, grad_scale);
+  } else if (write_grad) {
     ew::ce_kernel<true><<<rows, ew::CE_THREADS, 0, stream>>>(lg, labels, row_valid, loss_rows, V,
                                                              ldv, grad_scale);
   } else {

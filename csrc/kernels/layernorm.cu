@@ -61,19 +61,38 @@ fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
     }
   }
   const float inv_d = 1.0f / d;
-  for (int row = blockIdx.x * WARPS + (threadIdx.x >> 5); row < rows; row += gridDim.x * WARPS) {
-    const uint4* xr = reinterpret_cast<const uint4*>(x + size_t(row) * d);
+  // Two rows are prefetched ahead of the one being normalised (three 1.5 KB rows in flight per
+  // warp at d = 768): the grid is sized to ONE resident wave so the gamma/beta prologue is paid
+  // once per warp, and the prefetch depth supplies the bytes in flight that extra waves did not.
+  const int stride = gridDim.x * WARPS;
+  int row = blockIdx.x * WARPS + (threadIdx.x >> 5);
+  uint4 n0[NV], n1[NV];
+  auto fetch = [&](uint4 (&dst)[NV], int r) {
+    if (r < rows) {
+      const uint4* xr = reinterpret_cast<const uint4*>(x + size_t(r) * d);
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        const int c = lane + i * 32;
+        if (c < nvec) dst[i] = __ldg(xr + c);
+      }
+    }
+  };
+  fetch(n0, row);
+  fetch(n1, row + stride);
+  for (; row < rows; row += stride) {
     float v[NV][8];
     float sum = 0.f;
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
       const int c = lane + i * 32;
       if (c < nvec) {
-        unpack8(__ldg(xr + c), v[i]);
+        unpack8(n0[i], v[i]);
 #pragma unroll
         for (int j = 0; j < 8; ++j) sum += v[i][j];
       }
+      n0[i] = n1[i];
     }
+    fetch(n1, row + 2 * stride);
     const float mean = warp_sum(sum) * inv_d;
     float sq = 0.f;
 #pragma unroll
@@ -140,17 +159,37 @@ bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict
     }
   }
 
-  for (int row = blockIdx.x * WARPS + warp; row < rows; row += gridDim.x * WARPS) {
-    const uint4* dyr = reinterpret_cast<const uint4*>(dy + size_t(row) * d);
-    const uint4* xr = reinterpret_cast<const uint4*>(x + size_t(row) * d);
-    const float mu = mean[row], rs = rstd[row];
-    uint4 pa[NV], pb[NV];
-    float s1 = 0.f, s2 = 0.f;
+  // Software-pipelined over rows: the three 16-byte streams of row r+stride (dy, x, dresid) are
+  // requested before row r is reduced, so ~2x the bytes are in flight per warp.  With ~200
+  // registers per thread only 8 warps fit on an SM, and one row per warp in flight left the
+  // kernel latency-bound at a third of HBM bandwidth.
+  const int stride = gridDim.x * WARPS;
+  int row = blockIdx.x * WARPS + warp;
+  uint4 na[NV], nb[NV], nr[NV];
+  float nmu = 0.f, nrs = 0.f;
+  auto fetch = [&](int r) {
+    const uint4* dyr = reinterpret_cast<const uint4*>(dy + size_t(r) * d);
+    const uint4* xr = reinterpret_cast<const uint4*>(x + size_t(r) * d);
+    const uint4* drr = reinterpret_cast<const uint4*>(dresid + size_t(r) * d);
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
       const int c = lane + i * 32;
-      if (c < nvec) { pa[i] = __ldg(dyr + c); pb[i] = __ldg(xr + c); }
+      if (c < nvec) { na[i] = __ldg(dyr + c); nb[i] = __ldg(xr + c); nr[i] = drr[c]; }
     }
+    nmu = mean[r];
+    nrs = rstd[r];
+  };
+  constexpr bool PIPE = NV <= 4;  // wider rows would spill with two rows held in registers
+  if (PIPE && row < rows) fetch(row);
+  while (row < rows) {
+    if (!PIPE) fetch(row);
+    uint4 pa[NV], pb[NV], pr[NV];
+#pragma unroll
+    for (int i = 0; i < NV; ++i) { pa[i] = na[i]; pb[i] = nb[i]; pr[i] = nr[i]; }
+    const float mu = nmu, rs = nrs;
+    const int next = row + stride;
+    if (PIPE && next < rows) fetch(next);
+    float s1 = 0.f, s2 = 0.f;
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
       const int c = lane + i * 32;
@@ -179,7 +218,7 @@ bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict
         float a[8], b[8], r[8];
         unpack8(pa[i], a);
         unpack8(pb[i], b);
-        unpack8(drr[c], r);
+        unpack8(pr[i], r);
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           const float h = (b[j] - mu) * rs;
@@ -189,6 +228,7 @@ bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict
         drr[c] = pack8(r);
       }
     }
+    row = next;
   }
 
   float* my = sh + size_t(warp) * NS * d;
@@ -259,14 +299,22 @@ extern "C" int llmtrain_b200_layernorm_fwd(const void* x, const float* gamma, co
   if (rows == 0) return 0;
   const auto* x_ = static_cast<const __nv_bfloat16*>(x);
   auto* y_ = static_cast<__nv_bfloat16*>(y);
-  int grid = 8 * sm_count();
+  // One resident wave: as many CTAs per SM as the instantiation's registers allow, at most 2.
   const int need = ceil_div(rows, ln::WARPS);
-  if (grid > need) grid = need;
 #define B200_LN_FWD(NV)                                                                         \
-  case NV:                                                                                      \
+  case NV: {                                                                                    \
+    static int per_sm = 0;                                                                      \
+    if (per_sm == 0) {                                                                          \
+      B200_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(                            \
+          &per_sm, ln::fwd_kernel<NV>, ln::WARPS * 32, 0));                                     \
+      per_sm = per_sm < 1 ? 1 : (per_sm > 2 ? 2 : per_sm);                                      \
+    }                                                                                           \
+    int grid = per_sm * sm_count();                                                             \
+    if (grid > need) grid = need;                                                               \
     ln::fwd_kernel<NV><<<grid, ln::WARPS * 32, 0, stream>>>(x_, gamma, beta, y_, mean, rstd,    \
                                                             rows, d);                           \
-    break;
+    break;                                                                                      \
+  }
   switch (ceil_div(d, 256)) {
     B200_LN_FWD(1) B200_LN_FWD(2) B200_LN_FWD(3) B200_LN_FWD(4)
     B200_LN_FWD(5) B200_LN_FWD(6) B200_LN_FWD(7) B200_LN_FWD(8)

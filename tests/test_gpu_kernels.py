@@ -76,7 +76,10 @@ def test_embedding_fwd_bwd() -> None:
     assert dwpe[t:].abs().max().item() == 0
 
 
-@pytest.mark.parametrize("rows,v,ldv", [(64, 1000, 1024), (33, 50257, 50304), (8, 16, 16)])
+@pytest.mark.parametrize(
+    "rows,v,ldv",
+    [(64, 1000, 1024), (33, 50257, 50304), (8, 16, 16), (1000, 5001, 5056), (5, 60000, 60032)],
+)
 def test_cross_entropy_loss_and_grad(rows: int, v: int, ldv: int) -> None:
     from llmtrain.ops import kernels as K
 
