@@ -14,10 +14,18 @@
 // Fused epilogues: +bias, +bias & exact-erf GELU (writes pre- and post-activation), +bias &
 // residual add, x GELU'(pre) for the MLP dgrad, fp32 accumulate.
 //
-// Tile: 128 x 256 x 64, UMMA 128x256x16 (cta_group::1), 4-stage smem ring (48 KB / stage),
-// 2 x 256 TMEM columns.  10 warps: 0 = TMA producer, 1 = MMA issuer + TMEM owner, 2..9 = epilogue
-// (warp w reads TMEM lanes 32*(w%4)..+31; two warps per lane quarter split the 256 columns).  Grid = #SMs, static round-robin tile schedule with M
-// fastest so concurrently running CTAs share the weight tile through L2.
+// Tile: 128 x 256 x 64 per CTA, 2 x 256 TMEM columns.  10 warps: 0 = TMA producer, 1 = MMA issuer
+// + TMEM owner, 2..9 = epilogue (warp w reads TMEM lanes 32*(w%4)..+31; two warps per lane quarter
+// split the 256 columns).  Static round-robin tile schedule with M fastest so concurrently running
+// CTAs share the weight tile through L2.  Two flavours of the same kernel (template CTAS):
+//   CTAS = 1  UMMA 128x256x16, cta_group::1, 4-stage ring of 48 KB, grid = #SMs.
+//   CTAS = 2  CTA pair (2-CTA cluster on one TPC): UMMA 256x256x16, cta_group::2.  The pair owns a
+//             256 x 256 tile; each CTA stages its own 128 rows of A and HALF of B (128 of the 256
+//             columns), so a stage is 32 KB, the ring is 6 deep, and L2 -> smem traffic per FLOP
+//             drops by a third.  The leader issues the MMAs for both tensor cores; each CTA's
+//             epilogue drains its own TMEM.  This is the default for shapes with >= 2 row tiles.
+
+#include <cstdlib>
 
 #include "../common/host.cuh"
 #include "../common/ptx.cuh"
@@ -33,29 +41,31 @@ constexpr int UK = 16;
 // smem ring depth: 4 x 48 KB everywhere except the GELU epilogue, which trades one stage for a
 // second 4 KB staging buffer per epilogue warp (its two outputs then leave through two TMA stores
 // in flight instead of one store plus scattered 16-byte global writes).
-template <int EPI> struct Cfg {
-  static constexpr int kStages = 4;
+template <int EPI, int CTAS> struct Cfg {
+  static constexpr int kStages = CTAS == 2 ? 6 : 4;
   static constexpr int kEpiBufs = 1;
 };
-template <> struct Cfg<1 /*kBiasGelu*/> {
-  static constexpr int kStages = 3;
+template <int CTAS> struct Cfg<1 /*kBiasGelu*/, CTAS> {
+  static constexpr int kStages = CTAS == 2 ? 5 : 3;
   static constexpr int kEpiBufs = 2;
 };
 constexpr int A_BYTES = BM * BK * 2;  // 16 KB
-constexpr int B_BYTES = BN * BK * 2;  // 32 KB
-constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+template <int CTAS> __host__ __device__ constexpr int b_bytes() { return BN / CTAS * BK * 2; }
+template <int CTAS> __host__ __device__ constexpr int stage_bytes() { return A_BYTES + b_bytes<CTAS>(); }
 constexpr int EPI_WARPS = 8;              // two warps per TMEM lane quarter, each owns 128 columns
 constexpr int EPI_BUF_BYTES = 32 * 128;  // 32 rows x 128 B per staging buffer
-template <int EPI> __host__ __device__ constexpr int epi_bytes() { return EPI_WARPS * Cfg<EPI>::kEpiBufs * EPI_BUF_BYTES; }
-template <int EPI> __host__ __device__ constexpr int smem_bytes() {
-  return Cfg<EPI>::kStages * STAGE_BYTES + epi_bytes<EPI>() + 256 /*barriers*/;
+template <int EPI, int CTAS> __host__ __device__ constexpr int epi_bytes() {
+  return EPI_WARPS * Cfg<EPI, CTAS>::kEpiBufs * EPI_BUF_BYTES;
+}
+template <int EPI, int CTAS> __host__ __device__ constexpr int smem_bytes() {
+  return Cfg<EPI, CTAS>::kStages * stage_bytes<CTAS>() + epi_bytes<EPI, CTAS>() + 256 /*barriers*/;
 }
 constexpr int NUM_THREADS = 32 * (2 + EPI_WARPS);
 constexpr int TMEM_COLS = 512;
 // No alignment slack: the kernel has no static shared memory, so its dynamic window starts at the
 // 1024 B-aligned base of the CTA's allocation.  Staying under 225 KB leaves room for one of the
 // communicator's small, smem-free CTAs to share the SM during the overlapped bucket reduction.
-// (shared memory per variant: smem_bytes<EPI>())
+// (shared memory per variant: smem_bytes<EPI, CTAS>())
 
 enum Epi : int {
   kBias = 0,      // C = acc (+ bias)
@@ -75,7 +85,23 @@ struct Params {
   int ldc2;
   __nv_bfloat16* Cptr;     // bf16 output for the direct-store epilogue, row pitch ldc
   int ldc;
+  int group_m;             // rasterisation: row-tiles per band (>= #row-tiles => M fastest)
 };
+
+// Tile order.  Consecutive tiles walk `group_m` row-tiles for one column-tile, then the next
+// column-tile, ...; after all column-tiles the next band of row-tiles starts.  A wave of resident
+// CTAs therefore touches ~group_m A panels and ~wave/group_m B panels.  With group_m >= num_m this
+// is plain M-fastest order (every CTA of a wave shares one weight tile), which is best while the
+// whole A operand fits in L2; for larger A the band keeps HBM traffic from scaling with #tiles.
+__device__ __forceinline__ void tile_coords(int mn, int num_m, int num_n, int group_m, int& mb,
+                                            int& nb) {
+  const int band = mn / (group_m * num_n);
+  const int first = band * group_m;
+  const int rows = min(group_m, num_m - first);
+  const int idx = mn - band * group_m * num_n;
+  mb = first + idx % rows;
+  nb = idx / rows;
+}
 
 #ifndef B200_GEMM_DIRECT_STORE
 #define B200_GEMM_DIRECT_STORE 0
@@ -113,7 +139,61 @@ __device__ __forceinline__ GeluPair gelu_erf_both(float x) {
   return {x * n.cdf, fmaf(x * 0.7978845608028654f, n.half_e, n.cdf)};  // phi = 2*half_e/sqrt(2pi)
 }
 
-template <bool A_MN, bool B_MN, int EPI>
+// Packed fp32 pairs (Blackwell FFMA2: one instruction, two independent fp32 FMAs).  The GELU
+// epilogue is issue-bound — two epilogue warps per scheduler, ~27 instructions per element — so
+// evaluating two adjacent columns per instruction is worth ~40% of its issue slots.
+struct f32x2 { uint64_t v; };
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
+  f32x2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r.v) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack2(f32x2 a, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(a.v));
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+  f32x2 r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r.v) : "l"(a.v), "l"(b.v), "l"(c.v));
+  return r;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v));
+  return r;
+}
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v));
+  return r;
+}
+__device__ __forceinline__ f32x2 splat2(float c) { return pack2(c, c); }
+
+// Same arithmetic as gelu_erf_both for the pair (x0, x1); y and dy come back packed.
+__device__ __forceinline__ void gelu_erf_both2(float x0, float x1, f32x2& y, f32x2& dy) {
+  constexpr float kP = 0.3275911f * 0.70710678118654752f;
+  constexpr float kC = -0.5f * 1.4426950408889634f;
+  const float t0 = mufu_rcp(fmaf(kP, fabsf(x0), 1.0f));
+  const float t1 = mufu_rcp(fmaf(kP, fabsf(x1), 1.0f));
+  const f32x2 x = pack2(x0, x1), t = pack2(t0, t1);
+  // 0.5 * exp(-x^2/2) = exp2(x^2 * kC - 1)
+  float a0, a1;
+  unpack2(fma2(mul2(x, x), splat2(kC), splat2(-1.0f)), a0, a1);
+  const f32x2 half_e = pack2(fast_exp2(a0), fast_exp2(a1));
+  f32x2 poly = fma2(splat2(1.061405429f), t, splat2(-1.453152027f));
+  poly = fma2(poly, t, splat2(1.421413741f));
+  poly = fma2(poly, t, splat2(-0.284496736f));
+  poly = fma2(poly, t, splat2(0.254829592f));
+  const f32x2 q = mul2(mul2(poly, t), half_e);           // 0.5 * erfc(|x|/sqrt 2)
+  const f32x2 omq = fma2(q, splat2(-1.0f), splat2(1.0f));
+  float q0, q1, r0, r1;
+  unpack2(q, q0, q1);
+  unpack2(omq, r0, r1);
+  const f32x2 cdf = pack2(x0 > 0.f ? r0 : q0, x1 > 0.f ? r1 : q1);
+  y = mul2(x, cdf);
+  dy = fma2(mul2(x, splat2(0.7978845608028654f)), half_e, cdf);
+}
+
+template <bool A_MN, bool B_MN, int EPI, int CTAS>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
             const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmC2,
@@ -121,10 +201,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw;
   if ((smem_u32(smem) & 1023u) != 0) __trap();
-  constexpr int STAGES = Cfg<EPI>::kStages;
-  constexpr int EPI_BUFS = Cfg<EPI>::kEpiBufs;
+  constexpr int STAGES = Cfg<EPI, CTAS>::kStages;
+  constexpr int EPI_BUFS = Cfg<EPI, CTAS>::kEpiBufs;
+  constexpr int STAGE_BYTES = stage_bytes<CTAS>();
+  constexpr int BN_LOCAL = BN / CTAS;  // B columns staged by this CTA
   uint8_t* epi_smem = smem + STAGES * STAGE_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(epi_smem + epi_bytes<EPI>());
+  uint64_t* bars = reinterpret_cast<uint64_t*>(epi_smem + epi_bytes<EPI, CTAS>());
   uint64_t* full_bar = bars;                  // [STAGES]
   uint64_t* empty_bar = bars + STAGES;        // [STAGES]
   uint64_t* tfull_bar = bars + 2 * STAGES;    // [2]
@@ -134,7 +216,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
 
-  const int num_m = (p.M + BM - 1) / BM;
+  // With CTAS = 2 a "tile" is the pair's 256 x 256 block; this CTA owns rows [rank*128, +128).
+  const uint32_t rank = CTAS == 2 ? cluster_ctarank() : 0u;
+  const bool leader = rank == 0;
+  const int first_tile = blockIdx.x / CTAS;
+  const int tile_stride = gridDim.x / CTAS;
+  const int num_m = (p.M + BM * CTAS - 1) / (BM * CTAS);
   const int num_n = (p.N + BN - 1) / BN;
   const int tiles_mn = num_m * num_n;
   const int num_tiles = tiles_mn * p.k_splits;
@@ -151,16 +238,17 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tfull_bar[s], 1);
-      mbar_init(&tempty_bar[s], EPI_WARPS);
+      mbar_init(&tempty_bar[s], EPI_WARPS * CTAS);  // the leader hears from both CTAs' epilogues
     }
     fence_barrier_init();
   }
   if (warp == 1) {
-    tmem_alloc(tmem_slot, TMEM_COLS);
-    tmem_relinquish();
+    if (CTAS == 2) { tmem_alloc_pair(tmem_slot, TMEM_COLS); tmem_relinquish_pair(); }
+    else { tmem_alloc(tmem_slot, TMEM_COLS); tmem_relinquish(); }
   }
   tc_fence_before_sync();
-  __syncthreads();
+  if (CTAS == 2) cluster_sync_all();  // the peer's barriers exist before anything signals them
+  else __syncthreads();
   tc_fence_after_sync();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -169,32 +257,38 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int tile = first_tile; tile < num_tiles; tile += tile_stride) {
         const int split = tile / tiles_mn;
         const int mn = tile - split * tiles_mn;
-        const int m0 = (mn % num_m) * BM;
-        const int n0 = (mn / num_m) * BN;
+        int mb, nb;
+        tile_coords(mn, num_m, num_n, p.group_m, mb, nb);
+        const int m0 = mb * (BM * CTAS) + int(rank) * BM;
+        const int n0 = nb * BN + int(rank) * BN_LOCAL;  // this CTA's share of B
         const int kb_begin = split * kb_per_split;
         const int kb_end = min(kb_total, kb_begin + kb_per_split);
         for (int kb = kb_begin; kb < kb_end; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * STAGE_BYTES;
           uint8_t* sb = sa + A_BYTES;
-          mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
+          // Pair: both CTAs' loads complete on the LEADER's barrier, which expects both shares.
+          if (leader) mbar_expect_tx(&full_bar[stage], STAGE_BYTES * CTAS);
           const int k0 = kb * BK;
+          auto load = [&](void* dst, const CUtensorMap* tm, int c0, int c1) {
+            if (CTAS == 2) tma_load_2d_pair(dst, tm, &full_bar[stage], c0, c1);
+            else tma_load_2d(dst, tm, &full_bar[stage], c0, c1);
+          };
           if (!A_MN) {
-            tma_load_2d(sa, &tmA, &full_bar[stage], k0, m0);
+            load(sa, &tmA, k0, m0);
           } else {
 #pragma unroll
-            for (int i = 0; i < BM / 64; ++i)
-              tma_load_2d(sa + i * (BK * 128), &tmA, &full_bar[stage], m0 + i * 64, k0);
+            for (int i = 0; i < BM / 64; ++i) load(sa + i * (BK * 128), &tmA, m0 + i * 64, k0);
           }
           if (!B_MN) {
-            tma_load_2d(sb, &tmB, &full_bar[stage], k0, n0);
+            load(sb, &tmB, k0, n0);
           } else {
 #pragma unroll
-            for (int i = 0; i < BN / 64; ++i)
-              tma_load_2d(sb + i * (BK * 128), &tmB, &full_bar[stage], n0 + i * 64, k0);
+            for (int i = 0; i < BN_LOCAL / 64; ++i)
+              load(sb + i * (BK * 128), &tmB, n0 + i * 64, k0);
           }
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
@@ -202,13 +296,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
   } else if (warp == 1) {
     // ===================================== MMA issuer =======================================
-    if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(BM, BN, A_MN, B_MN);
+    if (lane == 0 && leader) {
+      constexpr uint32_t idesc = umma_idesc_bf16(BM * CTAS, BN, A_MN, B_MN);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int tile = first_tile; tile < num_tiles; tile += tile_stride) {
         const int split = tile / tiles_mn;
         const int kb_begin = split * kb_per_split;
         const int kb_end = min(kb_total, kb_begin + kb_per_split);
@@ -228,12 +322,17 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                                      : umma_smem_desc(sa + k * (UK * 2), 0, 1024);
             const uint64_t db = B_MN ? umma_smem_desc(sb + k * (UK * 128), BK * 128, 1024)
                                      : umma_smem_desc(sb + k * (UK * 2), 0, 1024);
-            umma_ss(d_tmem, da, db, idesc, (kb > kb_begin) || (k > 0));
+            if (CTAS == 2) umma_ss_pair(d_tmem, da, db, idesc, (kb > kb_begin) || (k > 0));
+            else umma_ss(d_tmem, da, db, idesc, (kb > kb_begin) || (k > 0));
           }
-          umma_commit(&empty_bar[stage]);  // frees this smem stage once the MMAs have read it
+          // frees this smem stage (in both CTAs of a pair) once the MMAs have read it
+          if (CTAS == 2) umma_commit_pair(&empty_bar[stage], 0b11);
+          else umma_commit(&empty_bar[stage]);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
-        umma_commit(&tfull_bar[acc]);  // accumulator complete -> epilogue
+        // accumulator complete -> epilogue (of both CTAs)
+        if (CTAS == 2) umma_commit_pair(&tfull_bar[acc], 0b11);
+        else umma_commit(&tfull_bar[acc]);
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }
@@ -248,11 +347,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     uint8_t* stg2 = stg + (EPI_BUFS - 1) * EPI_BUF_BYTES;  // == stg unless the variant has two
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    for (int tile = first_tile; tile < num_tiles; tile += tile_stride) {
       const int split = tile / tiles_mn;
       const int mn = tile - split * tiles_mn;
-      const int m0 = (mn % num_m) * BM;
-      const int n0 = (mn / num_m) * BN + half * (BN / 2);
+      int mb, nb;
+      tile_coords(mn, num_m, num_n, p.group_m, mb, nb);
+      const int m0 = mb * (BM * CTAS) + int(rank) * BM;
+      const int n0 = nb * BN + half * (BN / 2);
       const int row = m0 + quarter * 32 + lane;  // this thread's output row
       const bool row_ok = row < p.M;
       // Residual / saved pre-activation for this thread's row (2 chunks x 64 bf16): issued BEFORE
@@ -361,9 +462,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                 else { x0 *= f.x; x1 *= f.y; }
               }
               if (EPI == kBiasGelu) {
-                const GeluPair g0 = gelu_erf_both(x0), g1 = gelu_erf_both(x1);
-                out2[h * 16 + j / 2] = pack_bf16x2(g0.dy, g1.dy);
-                x0 = g0.y; x1 = g1.y;
+                f32x2 y2, dy2;
+                gelu_erf_both2(x0, x1, y2, dy2);
+                float d0, d1;
+                unpack2(dy2, d0, d1);
+                out2[h * 16 + j / 2] = pack_bf16x2(d0, d1);
+                unpack2(y2, x0, x1);
               }
               out[h * 16 + j / 2] = pack_bf16x2(x0, x1);
             }
@@ -426,42 +530,79 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       // TMEM reads for this accumulator are complete (wait::ld above): hand it back.
       tc_fence_before_sync();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+      if (lane == 0) {
+        if (CTAS == 2) mbar_arrive_cluster(&tempty_bar[acc], 0);  // the leader's MMA thread waits
+        else mbar_arrive(&tempty_bar[acc]);
+      }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
     tma_store_wait<0>();  // global writes landed before the kernel exits
   }
 
   tc_fence_before_sync();
-  __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem_base, TMEM_COLS);
+  if (CTAS == 2) {
+    // Neither CTA may leave (or free TMEM) while the other can still signal its barriers or the
+    // leader's MMAs can still read its shared memory.
+    cluster_sync_all();
+    if (warp == 1) tmem_dealloc_pair(tmem_base, TMEM_COLS);
+  } else {
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem_base, TMEM_COLS);
+  }
 }
 
 // ------------------------------------------------------------------------------------------------
 // Host launcher
 // ------------------------------------------------------------------------------------------------
-template <bool A_MN, bool B_MN, int EPI>
+template <bool A_MN, bool B_MN, int EPI, int CTAS>
 int launch(const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tC,
            const CUtensorMap& tC2, const Params& p, cudaStream_t stream) {
-  auto kern = gemm_kernel<A_MN, B_MN, EPI>;
+  auto kern = gemm_kernel<A_MN, B_MN, EPI, CTAS>;
+  constexpr int kSmem = smem_bytes<EPI, CTAS>();
+  static_assert(kSmem <= 227 * 1024, "gemm: shared memory budget exceeded");
   static bool configured = false;
   if (!configured) {
-    B200_CHECK_CUDA(
-        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<EPI>()));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
     configured = true;
   }
-  const int tiles = ceil_div(p.M, BM) * ceil_div(p.N, BN) * p.k_splits;
-  const int grid = tiles < sm_count() ? tiles : sm_count();
-  kern<<<grid, NUM_THREADS, smem_bytes<EPI>(), stream>>>(tA, tB, tC, tC2, p);
+  const int tiles = ceil_div(p.M, BM * CTAS) * ceil_div(p.N, BN) * p.k_splits;
+  const int slots = sm_count() / CTAS;  // CTAs, or CTA pairs, that can be resident
+  const int grid = (tiles < slots ? tiles : slots) * CTAS;
+  if (CTAS == 1) {
+    kern<<<grid, NUM_THREADS, kSmem, stream>>>(tA, tB, tC, tC2, p);
+  } else {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(NUM_THREADS);
+    cfg.dynamicSmemBytes = kSmem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr{};
+    attr.id = cudaLaunchAttributeClusterDimension;
+    attr.val.clusterDim.x = CTAS;
+    attr.val.clusterDim.y = 1;
+    attr.val.clusterDim.z = 1;
+    cfg.attrs = &attr;
+    cfg.numAttrs = 1;
+    B200_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, tA, tB, tC, tC2, p));
+  }
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   return 0;
 }
 
-int pick_splits(int M, int N, int K) {
-  const int tiles = ceil_div(M, BM) * ceil_div(N, BN);
+// CTA pairs are the default; LLMTRAIN_GEMM_PAIR=0 selects the single-CTA kernel (A/B runs).
+bool use_pair(int M) {
+  static const int env = [] {
+    const char* e = std::getenv("LLMTRAIN_GEMM_PAIR");
+    return e == nullptr ? 1 : std::atoi(e);
+  }();
+  return env != 0 && M > BM;
+}
+
+int pick_splits(int M, int N, int K, int ctas) {
+  const int tiles = ceil_div(M, BM * ctas) * ceil_div(N, BN);
   const int kb = ceil_div(K, BK);
-  int s = sm_count() / (tiles > 0 ? tiles : 1);
+  int s = (sm_count() / ctas) / (tiles > 0 ? tiles : 1);
   if (s < 1) s = 1;
   if (s > 16) s = 16;
   while (s > 1 && kb / s < 8) --s;  // keep >= 8 k-blocks per split
@@ -497,16 +638,29 @@ extern "C" int llmtrain_b200_gemm(int layout, int epilogue, int M, int N, int K,
   std::memset(&tC2, 0, sizeof(tC2));
   const bool a_mn = (layout == 2);
   const bool b_mn = (layout == 1 || layout == 2);
+  const bool pair = gemm::use_pair(M);
+  {
+    // Band the row-tiles once the A operand (M x K bf16) no longer sits comfortably in the 126 MB
+    // L2 next to the weights and the output stream.
+    const int num_m = ceil_div(M, BM * (pair ? 2 : 1));
+    static const int forced = [] {
+      const char* e = std::getenv("LLMTRAIN_GEMM_GROUP_M");
+      return e == nullptr ? 0 : std::atoi(e);
+    }();
+    const bool big_a = size_t(M) * size_t(K) * 2 > (size_t(40) << 20);
+    int g = forced > 0 ? forced : (big_a ? 8 : num_m);
+    p.group_m = g < num_m ? g : num_m;
+  }
   // K-major operand: memory [rows, K]; box = [tile rows, 64].  MN-major: memory [K, rows];
   // box = [64 k-rows, 64 cols].
   if (!a_mn) { if (make_tmap_2d(&tA, a, M, K, lda, BM, BK, Swz::B128)) return 1; }
   else       { if (make_tmap_2d(&tA, a, K, M, lda, BK, 64, Swz::B128)) return 1; }
-  if (!b_mn) { if (make_tmap_2d(&tB, b, N, K, ldb, BN, BK, Swz::B128)) return 1; }
+  if (!b_mn) { if (make_tmap_2d(&tB, b, N, K, ldb, pair ? BN / 2 : BN, BK, Swz::B128)) return 1; }
   else       { if (make_tmap_2d(&tB, b, K, N, ldb, BK, 64, Swz::B128)) return 1; }
 
   if (epilogue == kAccumF32) {
     if (make_tmap_2d(&tC, static_cast<float*>(C), M, N, ldc, 32, 32, Swz::B128)) return 1;
-    p.k_splits = pick_splits(M, N, K);
+    p.k_splits = pick_splits(M, N, K, pair ? 2 : 1);
   } else {
     if (make_tmap_2d(&tC, static_cast<__nv_bfloat16*>(C), M, N, ldc, 32, 64, Swz::B128)) return 1;
     B200_REQUIRE(!gemm::kDirectStore || (ldc % 8 == 0 && (reinterpret_cast<uintptr_t>(C) & 15) == 0),
@@ -520,8 +674,10 @@ extern "C" int llmtrain_b200_gemm(int layout, int epilogue, int M, int N, int K,
       B200_REQUIRE(R != nullptr, "gemm: this epilogue needs R");
   }
 
-#define B200_GEMM_CASE(L, AMN, BMN, E) \
-  if (layout == L && epilogue == E) return launch<AMN, BMN, E>(tA, tB, tC, tC2, p, stream);
+#define B200_GEMM_CASE(L, AMN, BMN, E)                                                  \
+  if (layout == L && epilogue == E)                                                     \
+    return pair ? launch<AMN, BMN, E, 2>(tA, tB, tC, tC2, p, stream)                    \
+                : launch<AMN, BMN, E, 1>(tA, tB, tC, tC2, p, stream);
   B200_GEMM_CASE(0, false, false, kBias)
   B200_GEMM_CASE(0, false, false, kBiasGelu)
   B200_GEMM_CASE(0, false, false, kBiasResid)
