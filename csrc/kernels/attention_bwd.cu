@@ -52,31 +52,57 @@ struct Params {
   const uint8_t* key_mask;
 };
 
+// Mask modes of one 128x128 (query x key) tile, chosen warp-uniformly (the loops contain
+// .sync.aligned TMEM loads):
+//   kNoMask   strictly below the diagonal, no key padding, no dead rows
+//   kDiag     the diagonal tile (q0 == kv0), no key padding, no dead rows.  A warp owns rows
+//             32*quarter..+31, so 32-column chunk cc of the tile is kept whole for cc < quarter,
+//             dropped whole for cc > quarter (zeros, no TMEM load, no MUFU), and tested per
+//             element (i <= lane) only for cc == quarter.
+//   kGeneral  key padding / rows past T / fully masked rows: per-element test.
+enum MaskMode : int { kNoMask = 0, kDiag = 1, kGeneral = 2 };
+
 // One thread: 64 columns of its row.  P = exp2(S*scale*log2e - lse*log2e), dS = P (dP - D) scale,
 // both written as bf16 into one 64-column swizzled region (row r, 8 x 16 B chunks).
-template <bool MASK>
+template <int MODE>
 __device__ __forceinline__ void softmax_grad(uint32_t t_row, uint8_t* rp, uint8_t* rd, int r,
                                              int col0, int qrow, int T, const uint8_t* kmask,
                                              bool dead_row, float scale_log2, float scale,
-                                             float lse2, float dsum) {
+                                             float lse2, float dsum, int quarter, int half,
+                                             int lane) {
 #pragma unroll 1
   for (int c = 0; c < 2; ++c) {
+    const int cc = half * 2 + c;  // 32-column chunk index inside the 128-column tile
+    if (MODE == kDiag && cc > quarter) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const uint32_t off = swizzle128(r * 128 + (c * 4 + q) * 16);
+        *reinterpret_cast<uint4*>(rp + off) = make_uint4(0u, 0u, 0u, 0u);
+        *reinterpret_cast<uint4*>(rd + off) = make_uint4(0u, 0u, 0u, 0u);
+      }
+      continue;
+    }
     uint32_t sv[32], dv[32];
     tmem_ld_32x32b_x32(t_row + COL_S + c * 32, sv);
     tmem_ld_32x32b_x32(t_row + COL_DP + c * 32, dv);
     tmem_ld_wait();
     uint32_t pk[16], dk[16];
+    const bool plain = MODE == kNoMask || (MODE == kDiag && cc < quarter);
 #pragma unroll
     for (int i = 0; i < 32; i += 2) {
       float pe[2], de[2];
 #pragma unroll
       for (int u = 0; u < 2; ++u) {
         float pv = fast_exp2(fmaf(__uint_as_float(sv[i + u]), scale_log2, -lse2));
-        if (MASK) {
-          const int col = col0 + c * 32 + i + u;
-          bool ok = !dead_row && (col <= qrow);
-          if (kmask != nullptr && col < T) ok = ok && (kmask[col] != 0);
-          if (!ok) pv = 0.f;
+        if (!plain) {
+          if (MODE == kDiag) {
+            if (i + u > lane) pv = 0.f;
+          } else {
+            const int col = col0 + c * 32 + i + u;
+            bool ok = !dead_row && (col <= qrow);
+            if (kmask != nullptr && col < T) ok = ok && (kmask[col] != 0);
+            if (!ok) pv = 0.f;
+          }
         }
         pe[u] = pv;
         de[u] = pv * (__uint_as_float(dv[i + u]) - dsum) * scale;
@@ -229,21 +255,25 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
         dsum = p.dsum[stat_base + qrow];
       }
       const bool dead_row = !row_ok || (lse2 == -INFINITY);
-      // warp-uniform on purpose: the two variants contain .sync.aligned TMEM loads
-      const bool need_mask =
-          (it == 0) || (kmask != nullptr) || (__any_sync(0xffffffffu, dead_row) != 0);
+      // warp-uniform on purpose: the variants contain .sync.aligned TMEM loads
+      const int mode = (kmask != nullptr || __any_sync(0xffffffffu, dead_row) != 0)
+                           ? kGeneral
+                           : (it == 0 ? kDiag : kNoMask);
 
       mbar_wait(s_full, it & 1);
       tc_fence_after_sync();
       uint8_t* rp = smem + OFF_P + half * TILE;
       uint8_t* rd = smem + OFF_DS + half * TILE;
-      if (need_mask) {
-        softmax_grad<true>(tmem + lane_base + half * 64, rp, rd, r, kv0 + half * 64, qrow, p.T,
-                           kmask, dead_row, p.scale_log2, p.scale, lse2, dsum);
-      } else {
-        softmax_grad<false>(tmem + lane_base + half * 64, rp, rd, r, kv0 + half * 64, qrow, p.T,
-                            kmask, dead_row, p.scale_log2, p.scale, lse2, dsum);
-      }
+      const uint32_t t_row = tmem + lane_base + half * 64;
+      if (mode == kNoMask)
+        softmax_grad<kNoMask>(t_row, rp, rd, r, kv0 + half * 64, qrow, p.T, kmask, dead_row,
+                              p.scale_log2, p.scale, lse2, dsum, quarter, half, lane);
+      else if (mode == kDiag)
+        softmax_grad<kDiag>(t_row, rp, rd, r, kv0 + half * 64, qrow, p.T, kmask, dead_row,
+                            p.scale_log2, p.scale, lse2, dsum, quarter, half, lane);
+      else
+        softmax_grad<kGeneral>(t_row, rp, rd, r, kv0 + half * 64, qrow, p.T, kmask, dead_row,
+                               p.scale_log2, p.scale, lse2, dsum, quarter, half, lane);
       fence_proxy_async_smem();
       tc_fence_before_sync();
       __syncwarp();

@@ -50,6 +50,7 @@ def main() -> int:
         "attn::fwd_kernel": ("flop", L * attn),
         "attn_bwd::bwd_kernel": ("flop", L * attn * 2.5),
         "ew::ce_kernel<1>": ("byte", 2.0 * M * Vp * 2),
+        "ew::ce_row_kernel<1>": ("byte", 2.0 * M * Vp * 2),
         "ln::fwd_kernel": ("byte", (2 * L + 1) * 2.0 * M * d * 2),
         "ln::bwd_kernel": ("byte", (2 * L + 1) * 4.0 * M * d * 2),
         "ew::colsum_partial_kernel": ("byte", L * (3 * d + F) * M * 2.0),
@@ -63,8 +64,10 @@ def main() -> int:
     print("| kernel class | launches | ms | share | achieved | of measured peak |")
     print("|---|---:|---:|---:|---:|---:|")
     for name, (n, ms) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
+        norm = name.replace("true", "1").replace("false", "0")
+        # keys name the first template arguments only (gemm_kernel<A_MN, B_MN, EPI[, CTAS]>)
         key = next((k for k in work if name.startswith(k.split("<")[0]) and
-                    (("<" not in k) or name.replace("true", "1").replace("false", "0").startswith(k))), None)
+                    (("<" not in k) or norm.startswith(k.rstrip(">")))), None)
         ach = frac = ""
         if key is not None:
             kind, amount = work[key]
