@@ -17,7 +17,13 @@
 //
 // D_i = rowsum(dO o O) comes from a small pre-kernel.  dK/dV leave through one TMA store each into
 // the fused [B, T, 3d] gradient buffer; dQ contributions from different kv tiles meet in an fp32
-// buffer that a post-kernel converts into the q third of that same gradient buffer.
+// buffer (16-byte vector reductions straight from registers) that a post-kernel converts into the
+// q third of that same gradient buffer.
+//
+// Pipeline.  P/dS live in TWO shared-memory buffers and dQ in two TMEM accumulators, which lets the
+// MMA warp issue S/dP of tile i+1 BEFORE dV/dK/dQ of tile i: the softmax-grad warps wait only for
+// the two score products while the three gradient products of the previous tile run underneath
+// their math, and dQ_i is drained one iteration late, when it has long completed.
 
 #include "../common/host.cuh"
 #include "../common/ptx.cuh"
@@ -32,15 +38,15 @@ constexpr int HD = 64;
 constexpr int TILE = 128 * HD * 2;  // 16 KB
 constexpr int THREADS = 320;  // 8 softmax-grad warps + TMA warp + MMA warp
 constexpr int TMEM_COLS = 512;
-constexpr int COL_S = 0, COL_DP = 128, COL_DV = 256, COL_DK = 320, COL_DQ = 384;
+constexpr int COL_S = 0, COL_DP = 128, COL_DV = 256, COL_DK = 320, COL_DQ = 384;  // dQ: 2 x 64 cols
 constexpr int OFF_K = 0;
 constexpr int OFF_V = OFF_K + TILE;
 constexpr int OFF_Q = OFF_V + TILE;        // [2]
 constexpr int OFF_DO = OFF_Q + 2 * TILE;   // [2]
-constexpr int OFF_P = OFF_DO + 2 * TILE;   // 32 KB
-constexpr int OFF_DS = OFF_P + 2 * TILE;   // 32 KB
-constexpr int OFF_DQ = OFF_DS + 2 * TILE;  // 32 KB fp32 staging
-constexpr int OFF_BAR = OFF_DQ + 2 * TILE;
+constexpr int PDS_BYTES = 2 * TILE;         // one 128x128 bf16 tile = two 64-column regions
+constexpr int OFF_P = OFF_DO + 2 * TILE;    // [2] x 32 KB
+constexpr int OFF_DS = OFF_P + 2 * PDS_BYTES;  // [2] x 32 KB
+constexpr int OFF_BAR = OFF_DS + 2 * PDS_BYTES;
 constexpr int SMEM = OFF_BAR + 256 + 1024;
 
 struct Params {
@@ -50,6 +56,7 @@ struct Params {
   const float* lse;  // [B, H, T]
   const float* dsum; // [B, H, T]   D = rowsum(dO o O)
   const uint8_t* key_mask;
+  float* dq32;       // [B, T, H*64] fp32 accumulator (zeroed by the launcher)
 };
 
 // Mask modes of one 128x128 (query x key) tile, chosen warp-uniformly (the loops contain
@@ -123,8 +130,7 @@ __device__ __forceinline__ void softmax_grad(uint32_t t_row, uint8_t* rp, uint8_
 
 __global__ void __launch_bounds__(THREADS, 1)
 bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
-           const __grid_constant__ CUtensorMap tmDQKV, const __grid_constant__ CUtensorMap tmDQ32,
-           const Params p) {
+           const __grid_constant__ CUtensorMap tmDQKV, const Params p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~uintptr_t(1023));
@@ -134,9 +140,10 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
   uint64_t* q_empty = bars + 3;  // [2]
   uint64_t* s_full = bars + 5;
   uint64_t* pds_full = bars + 6;
-  uint64_t* dq_full = bars + 7;
-  uint64_t* dkv_full = bars + 8;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
+  uint64_t* dq_full = bars + 7;  // [2]: dQ_i accumulates in TMEM buffer i&1 and is drained one
+                                 // iteration later, behind the next tile's softmax-grad
+  uint64_t* dkv_full = bars + 9;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 10);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nq = (p.T + BQ - 1) / BQ;
@@ -146,11 +153,14 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
   const int d = p.H * HD;
   const int n_iter = nq - jt;
 
-  if (threadIdx.x == 0) {
+  // The TMA thread initialises the barriers itself and issues the first loads (K_j, V_j, Q/dO of
+  // the first query tile) BEFORE the CTA-wide sync: TMEM allocation and the barrier round trip
+  // then overlap the ~1 us load latency instead of preceding it (one CTA per SM, so nothing else
+  // would hide it).
+  if (warp == 8 && lane == 0) {
     tma_prefetch_desc(&tmQKV);
     tma_prefetch_desc(&tmDO);
     tma_prefetch_desc(&tmDQKV);
-    tma_prefetch_desc(&tmDQ32);
     mbar_init(kv_full, 1);
     for (int s = 0; s < 2; ++s) {
       mbar_init(&q_full[s], 1);
@@ -158,9 +168,16 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
     }
     mbar_init(s_full, 1);
     mbar_init(pds_full, 8);
-    mbar_init(dq_full, 1);
+    mbar_init(&dq_full[0], 1);
+    mbar_init(&dq_full[1], 1);
     mbar_init(dkv_full, 1);
     fence_barrier_init();
+    mbar_expect_tx(kv_full, 2 * TILE);
+    tma_load_3d(smem + OFF_K, &tmQKV, kv_full, d + h * HD, kv0, b);
+    tma_load_3d(smem + OFF_V, &tmQKV, kv_full, 2 * d + h * HD, kv0, b);
+    mbar_expect_tx(&q_full[0], 2 * TILE);
+    tma_load_3d(smem + OFF_Q, &tmQKV, &q_full[0], h * HD, jt * BQ, b);
+    tma_load_3d(smem + OFF_DO, &tmDO, &q_full[0], h * HD, jt * BQ, b);
   }
   if (warp == 9) {
     tmem_alloc(tmem_slot, TMEM_COLS);
@@ -174,10 +191,7 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
   if (warp == 8) {
     // ------------------------------- TMA producer -------------------------------------------
     if (lane == 0) {
-      mbar_expect_tx(kv_full, 2 * TILE);
-      tma_load_3d(smem + OFF_K, &tmQKV, kv_full, d + h * HD, kv0, b);
-      tma_load_3d(smem + OFF_V, &tmQKV, kv_full, 2 * d + h * HD, kv0, b);
-      for (int it = 0; it < n_iter; ++it) {
+      for (int it = 1; it < n_iter; ++it) {  // tile 0 was requested in the prologue
         const int st = it & 1;
         const uint32_t ph = (it >> 1) & 1;
         const int q0 = (jt + it) * BQ;
@@ -194,14 +208,11 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
       constexpr uint32_t id_t = umma_idesc_bf16(128, 64, true, true);     // P^T dO, dS^T Q
       constexpr uint32_t id_dq = umma_idesc_bf16(128, 64, false, true);   // dS K
       const uint32_t sK = smem_u32(smem + OFF_K), sV = smem_u32(smem + OFF_V);
-      const uint32_t sP = smem_u32(smem + OFF_P), sDS = smem_u32(smem + OFF_DS);
-      mbar_wait(kv_full, 0);
-      for (int it = 0; it < n_iter; ++it) {
+      auto issue_scores = [&](int it) {  // S = Q K^T and dP = dO V^T of query tile `it`
         const int st = it & 1;
-        const uint32_t ph = (it >> 1) & 1;
         const uint32_t sQ = smem_u32(smem + OFF_Q + st * TILE);
         const uint32_t sDO = smem_u32(smem + OFF_DO + st * TILE);
-        mbar_wait(&q_full[st], ph);
+        mbar_wait(&q_full[st], (it >> 1) & 1);
         tc_fence_after_sync();
 #pragma unroll
         for (int k = 0; k < HD / 16; ++k)
@@ -212,9 +223,18 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
           umma_ss(tmem + COL_DP, umma_smem_desc(sDO + k * 32, 0, 1024),
                   umma_smem_desc(sV + k * 32, 0, 1024), id_s, k > 0);
         umma_commit(s_full);
-
-        mbar_wait(pds_full, it & 1);
+      };
+      mbar_wait(kv_full, 0);
+      issue_scores(0);
+      for (int it = 0; it < n_iter; ++it) {
+        const int st = it & 1;
+        const uint32_t sQ = smem_u32(smem + OFF_Q + st * TILE);
+        const uint32_t sDO = smem_u32(smem + OFF_DO + st * TILE);
+        const uint32_t sP = smem_u32(smem + OFF_P + st * PDS_BYTES);
+        const uint32_t sDS = smem_u32(smem + OFF_DS + st * PDS_BYTES);
+        mbar_wait(pds_full, it & 1);  // P_it / dS_it are in smem, S_it / dP_it have left TMEM
         tc_fence_after_sync();
+        if (it + 1 < n_iter) issue_scores(it + 1);  // first: the softmax-grad warps wait on these
         // dV += P^T dO ; dK += dS^T Q   (A, B both MN-major: 16 q-rows = 2048 B per K step)
 #pragma unroll
         for (int k = 0; k < BQ / 16; ++k)
@@ -228,9 +248,10 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
         // dQ_i = dS K  (A K-major over 128 kv = two 64-wide regions; B = K_j MN-major)
 #pragma unroll
         for (int k = 0; k < BKV / 16; ++k)
-          umma_ss(tmem + COL_DQ, umma_smem_desc(sDS + (k >> 2) * TILE + (k & 3) * 32, 0, 1024),
+          umma_ss(tmem + COL_DQ + st * HD,
+                  umma_smem_desc(sDS + (k >> 2) * TILE + (k & 3) * 32, 0, 1024),
                   umma_smem_desc(sK + k * 2048, TILE, 1024), id_dq, k > 0);
-        umma_commit(dq_full);
+        umma_commit(&dq_full[st]);
       }
       umma_commit(dkv_full);
     }
@@ -244,15 +265,48 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
     const uint8_t* kmask = p.key_mask ? p.key_mask + size_t(b) * p.T : nullptr;
     const size_t stat_base = (size_t(b) * p.H + h) * p.T;
 
+    // dQ_i: TMEM -> registers -> eight 16-byte fp32 reductions per thread into dq32 (the thread's
+    // 32 columns of its row are one full 128-byte line).  Called one iteration late, so the MMAs
+    // that precede dq_full(i) are never waited for, and it needs no staging buffer or CTA barrier.
+    auto drain_dq = [&](int i) {
+      mbar_wait(&dq_full[i & 1], (i >> 1) & 1);
+      tc_fence_after_sync();
+      uint32_t v[32];
+      tmem_ld_32x32b_x32(tmem + COL_DQ + (i & 1) * HD + lane_base + half * 32, v);
+      tmem_ld_wait();
+      tc_fence_before_sync();
+      const int qrow_i = (jt + i) * BQ + r;
+      if (qrow_i < p.T) {
+        float* dst = p.dq32 + (size_t(b) * p.T + qrow_i) * d + h * HD + half * 32;
+#pragma unroll
+        for (int q = 0; q < 8; ++q)
+          asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + 4 * q),
+                       "f"(__uint_as_float(v[4 * q])), "f"(__uint_as_float(v[4 * q + 1])),
+                       "f"(__uint_as_float(v[4 * q + 2])), "f"(__uint_as_float(v[4 * q + 3]))
+                       : "memory");
+      }
+    };
+
+    // Row statistics of the NEXT query tile are requested before this tile's math so their
+    // global-memory latency is never exposed.
+    float lse_next = 0.f, dsum_next = 0.f;
+    {
+      const int qrow0 = jt * BQ + r;
+      if (qrow0 < p.T) {
+        lse_next = p.lse[stat_base + qrow0];
+        dsum_next = p.dsum[stat_base + qrow0];
+      }
+    }
     for (int it = 0; it < n_iter; ++it) {
       const int qt = jt + it;
       const int q0 = qt * BQ;
       const int qrow = q0 + r;
       const bool row_ok = qrow < p.T;
-      float lse2 = 0.f, dsum = 0.f;
-      if (row_ok) {
-        lse2 = p.lse[stat_base + qrow] * 1.4426950408889634f;
-        dsum = p.dsum[stat_base + qrow];
+      const float lse2 = row_ok ? lse_next * 1.4426950408889634f : 0.f;
+      const float dsum = row_ok ? dsum_next : 0.f;
+      if (it + 1 < n_iter && qrow + BQ < p.T) {
+        lse_next = p.lse[stat_base + qrow + BQ];
+        dsum_next = p.dsum[stat_base + qrow + BQ];
       }
       const bool dead_row = !row_ok || (lse2 == -INFINITY);
       // warp-uniform on purpose: the variants contain .sync.aligned TMEM loads
@@ -262,8 +316,8 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
 
       mbar_wait(s_full, it & 1);
       tc_fence_after_sync();
-      uint8_t* rp = smem + OFF_P + half * TILE;
-      uint8_t* rd = smem + OFF_DS + half * TILE;
+      uint8_t* rp = smem + OFF_P + (it & 1) * PDS_BYTES + half * TILE;
+      uint8_t* rd = smem + OFF_DS + (it & 1) * PDS_BYTES + half * TILE;
       const uint32_t t_row = tmem + lane_base + half * 64;
       if (mode == kNoMask)
         softmax_grad<kNoMask>(t_row, rp, rd, r, kv0 + half * 64, qrow, p.T, kmask, dead_row,
@@ -279,30 +333,9 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
       __syncwarp();
       if (lane == 0) mbar_arrive(pds_full);
 
-      // dQ_i: TMEM -> fp32 staging (this half's 32 columns = one 128 B-row box) -> TMA reduce-add
-      mbar_wait(dq_full, it & 1);
-      tc_fence_after_sync();
-      if (threadIdx.x == 0) tma_store_wait_read<0>();  // previous iteration's staging drained
-      named_bar_sync(1, 256);
-      {
-        uint32_t v[32];
-        tmem_ld_32x32b_x32(tmem + COL_DQ + lane_base + half * 32, v);
-        tmem_ld_wait();
-        uint8_t* box = smem + OFF_DQ + half * TILE;
-#pragma unroll
-        for (int q = 0; q < 8; ++q)
-          *reinterpret_cast<uint4*>(box + swizzle128(r * 128 + q * 16)) =
-              make_uint4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
-      }
-      tc_fence_before_sync();
-      fence_proxy_async_smem();
-      named_bar_sync(1, 256);
-      if (threadIdx.x == 0) {
-        tma_reduce_add_3d(&tmDQ32, smem + OFF_DQ, h * HD, q0, b);
-        tma_reduce_add_3d(&tmDQ32, smem + OFF_DQ + TILE, h * HD + 32, q0, b);
-        tma_store_commit();
-      }
+      if (it > 0) drain_dq(it - 1);
     }
+    drain_dq(n_iter - 1);
 
     // dV, dK: TMEM -> bf16 -> swizzled staging (P / dS buffers are free now) -> TMA store.
     // Each warp converts its 32-column half of both accumulators.
@@ -332,7 +365,7 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
       tma_store_3d(&tmDQKV, smem + OFF_P, 2 * d + h * HD, kv0, b);   // dV
       tma_store_3d(&tmDQKV, smem + OFF_DS, d + h * HD, kv0, b);      // dK
       tma_store_commit();
-      tma_store_wait<0>();
+      tma_store_wait_read<0>();  // smem may go once it has been read; the writes land on their own
     }
   }
 
@@ -420,14 +453,13 @@ extern "C" int llmtrain_b200_attention_bwd(const void* qkv, const void* out, con
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
 
-  CUtensorMap tQKV, tDO, tDQKV, tDQ32;
+  CUtensorMap tQKV, tDO, tDQKV;
   if (make_tmap_3d(&tQKV, static_cast<const __nv_bfloat16*>(qkv), B, T, 3 * d, 3 * d,
                    uint64_t(T) * 3 * d, 128, ab::HD, Swz::B128)) return 1;
   if (make_tmap_3d(&tDO, static_cast<const __nv_bfloat16*>(dout), B, T, d, d, uint64_t(T) * d, 128,
                    ab::HD, Swz::B128)) return 1;
   if (make_tmap_3d(&tDQKV, static_cast<__nv_bfloat16*>(dqkv), B, T, 3 * d, 3 * d,
                    uint64_t(T) * 3 * d, 128, ab::HD, Swz::B128)) return 1;
-  if (make_tmap_3d(&tDQ32, dq32, B, T, d, d, uint64_t(T) * d, 128, 32, Swz::B128)) return 1;
 
   ab::Params p;
   p.B = B; p.T = T; p.H = H;
@@ -436,6 +468,7 @@ extern "C" int llmtrain_b200_attention_bwd(const void* qkv, const void* out, con
   p.lse = lse;
   p.dsum = dsum;
   p.key_mask = key_mask;
+  p.dq32 = dq32;
   static bool configured = false;
   if (!configured) {
     B200_CHECK_CUDA(cudaFuncSetAttribute(ab::bwd_kernel,
@@ -443,7 +476,7 @@ extern "C" int llmtrain_b200_attention_bwd(const void* qkv, const void* out, con
     configured = true;
   }
   dim3 grid(ceil_div(T, ab::BKV), H, B);
-  ab::bwd_kernel<<<grid, ab::THREADS, ab::SMEM, stream>>>(tQKV, tDO, tDQKV, tDQ32, p);
+  ab::bwd_kernel<<<grid, ab::THREADS, ab::SMEM, stream>>>(tQKV, tDO, tDQKV, p);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
 

@@ -170,7 +170,9 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
   const int d = p.H * HD;
   const int n_kv = qt + 1;
 
-  if (threadIdx.x == 0) {
+  // The TMA thread initialises the barriers itself and requests Q, K_0, V_0 BEFORE the CTA-wide
+  // sync, so TMEM allocation and the barrier round trip overlap the load latency.
+  if (warp == 4 && lane == 0) {
     tma_prefetch_desc(&tmQKV);
     tma_prefetch_desc(&tmO);
     mbar_init(q_full, 1);
@@ -183,6 +185,12 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
     mbar_init(&pv_done[0], 1);
     mbar_init(&pv_done[1], 1);
     fence_barrier_init();
+    mbar_expect_tx(q_full, TILE_BYTES);
+    tma_load_3d(smem + OFF_Q, &tmQKV, q_full, h * HD, q0, b);
+    mbar_expect_tx(k_full, TILE_BYTES);
+    tma_load_3d(smem + OFF_K, &tmQKV, k_full, d + h * HD, 0, b);
+    mbar_expect_tx(v_full, TILE_BYTES);
+    tma_load_3d(smem + OFF_V, &tmQKV, v_full, 2 * d + h * HD, 0, b);
   }
   if (warp == 5) {
     tmem_alloc(tmem_slot, FWD_TMEM_COLS);
@@ -198,13 +206,11 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
   if (warp == 4) {
     // ------------------------------- TMA producer -------------------------------------------
     if (lane == 0) {
-      mbar_expect_tx(q_full, TILE_BYTES);
-      tma_load_3d(smem + OFF_Q, &tmQKV, q_full, h * HD, q0, b);
-      for (int j = 0; j < n_kv; ++j) {
-        if (j > 0) mbar_wait(k_empty, (j - 1) & 1);   // S_{j-1} has consumed K
+      for (int j = 1; j < n_kv; ++j) {  // tile 0 was requested in the prologue
+        mbar_wait(k_empty, (j - 1) & 1);   // S_{j-1} has consumed K
         mbar_expect_tx(k_full, TILE_BYTES);
         tma_load_3d(smem + OFF_K, &tmQKV, k_full, d + h * HD, j * BKV, b);
-        if (j > 0) mbar_wait(v_empty, (j - 1) & 1);   // PV_{j-1} has consumed V
+        mbar_wait(v_empty, (j - 1) & 1);   // PV_{j-1} has consumed V
         mbar_expect_tx(v_full, TILE_BYTES);
         tma_load_3d(smem + OFF_V, &tmQKV, v_full, 2 * d + h * HD, j * BKV, b);
       }
@@ -334,7 +340,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
     if (threadIdx.x == 0) {
       tma_store_3d(&tmO, stage, h * HD, q0, b);
       tma_store_commit();
-      tma_store_wait<0>();
+      tma_store_wait_read<0>();  // smem may go once it has been read; the writes land on their own
     }
   }
 
