@@ -22,6 +22,7 @@
 #include <vector>
 
 #include "../common/host.cuh"
+#include "../common/philox.cuh"
 #include "../../include/llmtrain_b200.h"
 
 namespace b200 {
@@ -51,6 +52,7 @@ struct Gpt {
   std::vector<LayerActs> acts;
   size_t a_x0 = 0, a_lnf = 0, a_lnf_mean = 0, a_lnf_rstd = 0, a_logits = 0, a_loss_rows = 0;
   size_t a_dresid = 0, a_dtmp = 0, a_dqkv = 0, a_dfc = 0, a_attn_scratch = 0, a_red_scratch = 0;
+  size_t a_dmask = 0;  // residual-branch gradient with its dropout mask applied
   size_t attn_scratch_bytes = 0, red_scratch_bytes = 0, act_bytes = 0;
   // bound memory
   float *p32 = nullptr, *g32 = nullptr;
@@ -61,6 +63,11 @@ struct Gpt {
   const int64_t* ids = nullptr;
   const uint8_t* key_mask = nullptr;
   bool have_forward = false;
+  // dropout (`gpt.py:28,30,97,129`): probability and counters for the NEXT mode-2 forward and
+  // its backward; drop_on records whether the last forward actually applied it.
+  float drop_p = 0.f;
+  uint64_t drop_seed = 0, drop_offset = 0;
+  bool drop_on = false;
 };
 
 inline size_t take(size_t& cursor, size_t n) {
@@ -132,6 +139,7 @@ void plan_acts(Gpt& g) {
   g.a_dtmp = take_bytes(c, M * d * 2);
   g.a_dqkv = take_bytes(c, M * 3 * d * 2);
   g.a_dfc = take_bytes(c, M * F * 2);
+  g.a_dmask = take_bytes(c, M * d * 2);
   g.attn_scratch_bytes =
       llmtrain_b200_attention_bwd_scratch_bytes(g.maxB, g.maxT, g.H, g.d / g.H);
   g.a_attn_scratch = take_bytes(c, g.attn_scratch_bytes);
@@ -186,12 +194,24 @@ inline int linear_wgrad(int M, int N, int K, const void* dy, int ld_dy, const vo
                             reinterpret_cast<llm_stream_t>(s));
 }
 
-int forward(Gpt& g, const int64_t* ids, const uint8_t* key_mask, int B, int T, cudaStream_t s) {
+// dropout site ids (philox.cuh): 4 * layer + {0 attention probabilities, 1 attention residual
+// branch, 2 MLP residual branch}; the embedding uses kDropSiteEmbedding.
+inline uint32_t drop_site(int layer, int which) { return uint32_t(4 * layer + which); }
+
+int forward(Gpt& g, const int64_t* ids, const uint8_t* key_mask, int B, int T, bool train,
+            cudaStream_t s) {
   View v(g);
   NvtxRange phase("gpt.forward");
   const int M = B * T, d = g.d, F = g.F, hd = g.d / g.H;
   auto st = reinterpret_cast<llm_stream_t>(s);
+  const bool drop = train && g.drop_p > 0.f;
+  const float dp = g.drop_p;
+  const uint64_t seed = g.drop_seed, off = g.drop_offset;
+  g.drop_on = drop;
   B200_TRY(llmtrain_b200_embed_fwd(ids, v.w(g.wte), v.w(g.wpe), v.bf(g.a_x0), B, T, d, g.V, st));
+  if (drop)
+    B200_TRY(llmtrain_b200_dropout(v.bf(g.a_x0), v.bf(g.a_x0), M, d, d, dp, seed, off,
+                                   kDropSiteEmbedding, st));
   const __nv_bfloat16* x = v.bf(g.a_x0);
   for (int l = 0; l < g.L; ++l) {
     NvtxRange layer_range("layer.fwd");
@@ -201,17 +221,32 @@ int forward(Gpt& g, const int64_t* ids, const uint8_t* key_mask, int B, int T, c
                                          v.f32(a.ln1_mean), v.f32(a.ln1_rstd), M, d, st));
     B200_TRY(linear_fwd(0, M, 3 * d, d, v.bf(a.ln1), v.w(o.qkv_w), v.bf(a.qkv), nullptr,
                         v.p(o.qkv_b), nullptr, s));
-    B200_TRY(llmtrain_b200_attention_fwd(v.bf(a.qkv), v.bf(a.atty), v.f32(a.lse), key_mask, B, T,
-                                         g.H, hd, st));
-    B200_TRY(linear_fwd(2, M, d, d, v.bf(a.atty), v.w(o.out_w), v.bf(a.resid1), nullptr,
-                        v.p(o.out_b), x, s));
+    if (drop) {
+      B200_TRY(llmtrain_b200_attention_fwd_dropout(v.bf(a.qkv), v.bf(a.atty), v.f32(a.lse),
+                                                   key_mask, B, T, g.H, hd, dp, seed, off,
+                                                   drop_site(l, 0), st));
+      B200_TRY(llmtrain_b200_gemm_dropout_resid(M, d, d, v.bf(a.atty), d, v.w(o.out_w), d,
+                                                v.bf(a.resid1), d, v.p(o.out_b), x, d, dp, seed,
+                                                off, drop_site(l, 1), st));
+    } else {
+      B200_TRY(llmtrain_b200_attention_fwd(v.bf(a.qkv), v.bf(a.atty), v.f32(a.lse), key_mask, B,
+                                           T, g.H, hd, st));
+      B200_TRY(linear_fwd(2, M, d, d, v.bf(a.atty), v.w(o.out_w), v.bf(a.resid1), nullptr,
+                          v.p(o.out_b), x, s));
+    }
     B200_TRY(llmtrain_b200_layernorm_fwd(v.bf(a.resid1), v.p(o.ln2_w), v.p(o.ln2_b), v.bf(a.ln2),
                                          v.f32(a.ln2_mean), v.f32(a.ln2_rstd), M, d, st));
     // fch_pre receives gelu'(pre-activation): all that backward needs from this GEMM
     B200_TRY(linear_fwd(1, M, F, d, v.bf(a.ln2), v.w(o.fc_w), v.bf(a.fch_act), v.bf(a.fch_pre),
                         v.p(o.fc_b), nullptr, s));
-    B200_TRY(linear_fwd(2, M, d, F, v.bf(a.fch_act), v.w(o.proj_w), v.bf(a.resid2), nullptr,
-                        v.p(o.proj_b), v.bf(a.resid1), s));
+    if (drop) {
+      B200_TRY(llmtrain_b200_gemm_dropout_resid(M, d, F, v.bf(a.fch_act), F, v.w(o.proj_w), F,
+                                                v.bf(a.resid2), d, v.p(o.proj_b), v.bf(a.resid1),
+                                                d, dp, seed, off, drop_site(l, 2), st));
+    } else {
+      B200_TRY(linear_fwd(2, M, d, F, v.bf(a.fch_act), v.w(o.proj_w), v.bf(a.resid2), nullptr,
+                          v.p(o.proj_b), v.bf(a.resid1), s));
+    }
     x = v.bf(a.resid2);
   }
   B200_TRY(llmtrain_b200_layernorm_fwd(x, v.p(g.lnf_w), v.p(g.lnf_b), v.bf(g.a_lnf),
@@ -241,6 +276,13 @@ int backward(Gpt& g, cudaStream_t s, BucketHook hook = nullptr, void* hook_ctx =
   __nv_bfloat16* dresid = v.bf(g.a_dresid);
   __nv_bfloat16* dqkv = v.bf(g.a_dqkv);
   __nv_bfloat16* dfc = v.bf(g.a_dfc);
+  __nv_bfloat16* dmask = v.bf(g.a_dmask);
+  // With dropout the gradient entering a residual-branch projection is dresid o mask: it is
+  // materialised once (the GEMMs read it through TMA) and the projection's bias gradient is its
+  // column sum, so the LayerNorm backwards stop emitting those sums.
+  const bool drop = g.drop_on;
+  const float dp = g.drop_p;
+  const uint64_t seed = g.drop_seed, off = g.drop_offset;
 
   // LM head: dlnf = dlogits @ head ; dhead += dlogits^T @ lnf   (only the V real rows)
   B200_TRY(llmtrain_b200_gemm(1, 0, M, d, g.Vp, dlogits, g.Vp, v.w(g.head), d, dtmp, d, nullptr, 0,
@@ -254,8 +296,9 @@ int backward(Gpt& g, cudaStream_t s, BucketHook hook = nullptr, void* hook_ctx =
   B200_TRY(llmtrain_b200_layernorm_bwd(dtmp, x_last, v.p(g.lnf_w), v.f32(g.a_lnf_mean),
                                        v.f32(g.a_lnf_rstd), dresid, v.grad(g.lnf_w),
                                        v.grad(g.lnf_b),
-                                       g.L > 0 ? v.grad(g.layer[g.L - 1].proj_b) : nullptr, red,
-                                       red_bytes, M, d, st));
+                                       (g.L > 0 && !drop) ? v.grad(g.layer[g.L - 1].proj_b)
+                                                          : nullptr,
+                                       red, red_bytes, M, d, st));
 
   for (int l = g.L - 1; l >= 0; --l) {
     NvtxRange layer_range("layer.bwd");
@@ -263,29 +306,48 @@ int backward(Gpt& g, cudaStream_t s, BucketHook hook = nullptr, void* hook_ctx =
     const LayerActs& a = g.acts[l];
     const __nv_bfloat16* x_in = l > 0 ? v.bf(g.acts[l - 1].resid2) : v.bf(g.a_x0);
     // ---- MLP: resid2 = gelu(ln2 @ Wfc^T + bfc) @ Wproj^T + bproj + resid1
-    B200_TRY(linear_wgrad(M, d, F, dresid, d, v.bf(a.fch_act), v.grad(o.proj_w), s));
-    B200_TRY(linear_dgrad(3, M, d, F, dresid, v.w(o.proj_w), dfc, v.bf(a.fch_pre), s));
+    const __nv_bfloat16* dproj = dresid;
+    if (drop) {
+      B200_TRY(llmtrain_b200_dropout(dresid, dmask, M, d, d, dp, seed, off, drop_site(l, 2), st));
+      B200_TRY(llmtrain_b200_bias_grad(dmask, d, M, d, v.grad(o.proj_b), red, red_bytes, st));
+      dproj = dmask;
+    }
+    B200_TRY(linear_wgrad(M, d, F, dproj, d, v.bf(a.fch_act), v.grad(o.proj_w), s));
+    B200_TRY(linear_dgrad(3, M, d, F, dproj, v.w(o.proj_w), dfc, v.bf(a.fch_pre), s));
     B200_TRY(llmtrain_b200_bias_grad(dfc, F, M, F, v.grad(o.fc_b), red, red_bytes, st));
     B200_TRY(linear_wgrad(M, F, d, dfc, F, v.bf(a.ln2), v.grad(o.fc_w), s));
     B200_TRY(linear_dgrad(0, M, F, d, dfc, v.w(o.fc_w), dtmp, nullptr, s));
     B200_TRY(llmtrain_b200_layernorm_bwd(dtmp, v.bf(a.resid1), v.p(o.ln2_w), v.f32(a.ln2_mean),
                                          v.f32(a.ln2_rstd), dresid, v.grad(o.ln2_w),
-                                         v.grad(o.ln2_b), v.grad(o.out_b), red, red_bytes, M, d,
-                                         st));
+                                         v.grad(o.ln2_b), drop ? nullptr : v.grad(o.out_b), red,
+                                         red_bytes, M, d, st));
     // ---- attention: resid1 = attn(ln1 @ Wqkv^T + bqkv) @ Wo^T + bo + x_in
-    B200_TRY(linear_wgrad(M, d, d, dresid, d, v.bf(a.atty), v.grad(o.out_w), s));
-    B200_TRY(linear_dgrad(0, M, d, d, dresid, v.w(o.out_w), dtmp, nullptr, s));
-    B200_TRY(llmtrain_b200_attention_bwd(v.bf(a.qkv), v.bf(a.atty), dtmp, v.f32(a.lse), g.key_mask,
-                                         dqkv, g.act + g.a_attn_scratch, g.attn_scratch_bytes, B, T,
-                                         g.H, hd, st));
+    const __nv_bfloat16* dout = dresid;
+    if (drop) {
+      B200_TRY(llmtrain_b200_dropout(dresid, dmask, M, d, d, dp, seed, off, drop_site(l, 1), st));
+      B200_TRY(llmtrain_b200_bias_grad(dmask, d, M, d, v.grad(o.out_b), red, red_bytes, st));
+      dout = dmask;
+    }
+    B200_TRY(linear_wgrad(M, d, d, dout, d, v.bf(a.atty), v.grad(o.out_w), s));
+    B200_TRY(linear_dgrad(0, M, d, d, dout, v.w(o.out_w), dtmp, nullptr, s));
+    if (drop) {
+      B200_TRY(llmtrain_b200_attention_bwd_dropout(
+          v.bf(a.qkv), v.bf(a.atty), dtmp, v.f32(a.lse), g.key_mask, dqkv,
+          g.act + g.a_attn_scratch, g.attn_scratch_bytes, B, T, g.H, hd, dp, seed, off,
+          drop_site(l, 0), st));
+    } else {
+      B200_TRY(llmtrain_b200_attention_bwd(v.bf(a.qkv), v.bf(a.atty), dtmp, v.f32(a.lse),
+                                           g.key_mask, dqkv, g.act + g.a_attn_scratch,
+                                           g.attn_scratch_bytes, B, T, g.H, hd, st));
+    }
     B200_TRY(llmtrain_b200_bias_grad(dqkv, 3 * d, M, 3 * d, v.grad(o.qkv_b), red, red_bytes, st));
     B200_TRY(linear_wgrad(M, 3 * d, d, dqkv, 3 * d, v.bf(a.ln1), v.grad(o.qkv_w), s));
     B200_TRY(linear_dgrad(0, M, 3 * d, d, dqkv, v.w(o.qkv_w), dtmp, nullptr, s));
     B200_TRY(llmtrain_b200_layernorm_bwd(dtmp, x_in, v.p(o.ln1_w), v.f32(a.ln1_mean),
                                          v.f32(a.ln1_rstd), dresid, v.grad(o.ln1_w),
                                          v.grad(o.ln1_b),
-                                         l > 0 ? v.grad(g.layer[l - 1].proj_b) : nullptr, red,
-                                         red_bytes, M, d, st));
+                                         (l > 0 && !drop) ? v.grad(g.layer[l - 1].proj_b) : nullptr,
+                                         red, red_bytes, M, d, st));
     if (hook != nullptr) {
       // layer l's parameters (+ ln_f for the last layer) are contiguous in the arena
       const size_t lo = o.ln1_w;
@@ -293,6 +355,8 @@ int backward(Gpt& g, cudaStream_t s, BucketHook hook = nullptr, void* hook_ctx =
       B200_TRY(hook(hook_ctx, lo, hi - lo));
     }
   }
+  if (drop)
+    B200_TRY(llmtrain_b200_dropout(dresid, dresid, M, d, d, dp, seed, off, kDropSiteEmbedding, st));
   B200_TRY(llmtrain_b200_embed_bwd(g.ids, dresid, v.grad(g.wte), v.grad(g.wpe), B, T, d, g.V, st));
   if (hook != nullptr) {
     const size_t first_layer = g.L > 0 ? g.layer[0].ln1_w : g.lnf_w;
@@ -415,7 +479,7 @@ extern "C" int llmtrain_b200_gpt_forward(void* h, const int64_t* ids, const int6
   B200_REQUIRE(g.act != nullptr, "gpt_forward: arenas not bound");
   B200_REQUIRE(B >= 1 && B <= g.maxB && T >= 1 && T <= g.maxT, "gpt_forward: batch exceeds plan");
   auto s = reinterpret_cast<cudaStream_t>(stream);
-  if (engine::forward(g, ids, key_mask, B, T, s)) return 1;
+  if (engine::forward(g, ids, key_mask, B, T, mode == 2, s)) return 1;
   if (mode >= 1) {
     B200_REQUIRE(labels != nullptr, "gpt_forward: labels required for the loss");
     if (llmtrain_b200_cross_entropy(g.act + g.a_logits, labels, key_mask,
@@ -430,4 +494,15 @@ extern "C" int llmtrain_b200_gpt_forward(void* h, const int64_t* ids, const int6
 
 extern "C" int llmtrain_b200_gpt_backward(void* h, llm_stream_t stream) {
   return engine::backward(*static_cast<Gpt*>(h), reinterpret_cast<cudaStream_t>(stream));
+}
+
+// Dropout for the NEXT mode-2 forward and its backward (p = 0 turns it off; modes 0/1 never drop).
+// `seed` identifies the run and rank, `offset` must change with every micro-batch.
+extern "C" int llmtrain_b200_gpt_set_dropout(void* h, float p, uint64_t seed, uint64_t offset) {
+  B200_REQUIRE(p >= 0.f && p < 1.f, "gpt_set_dropout: p must be in [0, 1)");
+  Gpt& g = *static_cast<Gpt*>(h);
+  g.drop_p = p;
+  g.drop_seed = seed;
+  g.drop_offset = offset;
+  return 0;
 }

@@ -26,6 +26,7 @@
 // their math, and dQ_i is drained one iteration late, when it has long completed.
 
 #include "../common/host.cuh"
+#include "../common/philox.cuh"
 #include "../common/ptx.cuh"
 #include "../../include/llmtrain_b200.h"
 
@@ -57,6 +58,8 @@ struct Params {
   const float* dsum; // [B, H, T]   D = rowsum(dO o O)
   const uint8_t* key_mask;
   float* dq32;       // [B, T, H*64] fp32 accumulator (zeroed by the launcher)
+  DropoutParams drop;  // attention-probability dropout; threshold 0 = off
+  int t_pad;           // T rounded up to 8: row pitch of the mask's element index
 };
 
 // Mask modes of one 128x128 (query x key) tile, chosen warp-uniformly (the loops contain
@@ -71,12 +74,16 @@ enum MaskMode : int { kNoMask = 0, kDiag = 1, kGeneral = 2 };
 
 // One thread: 64 columns of its row.  P = exp2(S*scale*log2e - lse*log2e), dS = P (dP - D) scale,
 // both written as bf16 into one 64-column swizzled region (row r, 8 x 16 B chunks).
-template <int MODE>
+// DROP (attention-probability dropout, keep factor m in {0, 1/(1-p)} regenerated from the
+// forward's counters): the tile handed to dV is P o m, and dS = P o (dP o m - D) * scale; D is
+// still rowsum(dO o O) because O was computed from the dropped probabilities.
+template <int MODE, bool DROP>
 __device__ __forceinline__ void softmax_grad(uint32_t t_row, uint8_t* rp, uint8_t* rd, int r,
                                              int col0, int qrow, int T, const uint8_t* kmask,
                                              bool dead_row, float scale_log2, float scale,
                                              float lse2, float dsum, int quarter, int half,
-                                             int lane) {
+                                             int lane, const DropoutParams& dp,
+                                             uint64_t mask_base) {
 #pragma unroll 1
   for (int c = 0; c < 2; ++c) {
     const int cc = half * 2 + c;  // 32-column chunk index inside the 128-column tile
@@ -95,9 +102,11 @@ __device__ __forceinline__ void softmax_grad(uint32_t t_row, uint8_t* rp, uint8_
     tmem_ld_wait();
     uint32_t pk[16], dk[16];
     const bool plain = MODE == kNoMask || (MODE == kDiag && cc < quarter);
+    Rand8 rnd{};
 #pragma unroll
     for (int i = 0; i < 32; i += 2) {
       float pe[2], de[2];
+      if (DROP && (i & 7) == 0) rnd = philox_group(dp, (mask_base + uint64_t(c * 32 + i)) >> 3);
 #pragma unroll
       for (int u = 0; u < 2; ++u) {
         float pv = fast_exp2(fmaf(__uint_as_float(sv[i + u]), scale_log2, -lse2));
@@ -111,8 +120,14 @@ __device__ __forceinline__ void softmax_grad(uint32_t t_row, uint8_t* rp, uint8_
             if (!ok) pv = 0.f;
           }
         }
-        pe[u] = pv;
-        de[u] = pv * (__uint_as_float(dv[i + u]) - dsum) * scale;
+        if (DROP) {
+          const float m = keep_factor(dp, rnd, (i & 7) + u);
+          pe[u] = pv * m;
+          de[u] = pv * (__uint_as_float(dv[i + u]) * m - dsum) * scale;
+        } else {
+          pe[u] = pv;
+          de[u] = pv * (__uint_as_float(dv[i + u]) - dsum) * scale;
+        }
       }
       pk[i >> 1] = pack_bf16x2(pe[0], pe[1]);
       dk[i >> 1] = pack_bf16x2(de[0], de[1]);
@@ -128,6 +143,7 @@ __device__ __forceinline__ void softmax_grad(uint32_t t_row, uint8_t* rp, uint8_
   }
 }
 
+template <bool DROP>
 __global__ void __launch_bounds__(THREADS, 1)
 bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
            const __grid_constant__ CUtensorMap tmDQKV, const Params p) {
@@ -319,15 +335,22 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
       uint8_t* rp = smem + OFF_P + (it & 1) * PDS_BYTES + half * TILE;
       uint8_t* rd = smem + OFF_DS + (it & 1) * PDS_BYTES + half * TILE;
       const uint32_t t_row = tmem + lane_base + half * 64;
+      const uint64_t mask_base =
+          DROP ? (uint64_t((size_t(b) * p.H + h) * p.T + qrow) * uint64_t(p.t_pad) +
+                  uint64_t(kv0 + half * 64))
+               : 0;
       if (mode == kNoMask)
-        softmax_grad<kNoMask>(t_row, rp, rd, r, kv0 + half * 64, qrow, p.T, kmask, dead_row,
-                              p.scale_log2, p.scale, lse2, dsum, quarter, half, lane);
+        softmax_grad<kNoMask, DROP>(t_row, rp, rd, r, kv0 + half * 64, qrow, p.T, kmask, dead_row,
+                                    p.scale_log2, p.scale, lse2, dsum, quarter, half, lane, p.drop,
+                                    mask_base);
       else if (mode == kDiag)
-        softmax_grad<kDiag>(t_row, rp, rd, r, kv0 + half * 64, qrow, p.T, kmask, dead_row,
-                            p.scale_log2, p.scale, lse2, dsum, quarter, half, lane);
+        softmax_grad<kDiag, DROP>(t_row, rp, rd, r, kv0 + half * 64, qrow, p.T, kmask, dead_row,
+                                  p.scale_log2, p.scale, lse2, dsum, quarter, half, lane, p.drop,
+                                  mask_base);
       else
-        softmax_grad<kGeneral>(t_row, rp, rd, r, kv0 + half * 64, qrow, p.T, kmask, dead_row,
-                               p.scale_log2, p.scale, lse2, dsum, quarter, half, lane);
+        softmax_grad<kGeneral, DROP>(t_row, rp, rd, r, kv0 + half * 64, qrow, p.T, kmask, dead_row,
+                                     p.scale_log2, p.scale, lse2, dsum, quarter, half, lane,
+                                     p.drop, mask_base);
       fence_proxy_async_smem();
       tc_fence_before_sync();
       __syncwarp();
@@ -430,10 +453,10 @@ extern "C" size_t llmtrain_b200_attention_bwd_scratch_bytes(int B, int T, int H,
 }
 
 // qkv [B,T,3d], out/dout [B,T,d] bf16, lse [B,H,T]  ->  dqkv [B,T,3d] bf16.
-extern "C" int llmtrain_b200_attention_bwd(const void* qkv, const void* out, const void* dout,
-                                           const float* lse, const uint8_t* key_mask, void* dqkv,
-                                           void* scratch, size_t scratch_bytes, int B, int T,
-                                           int H, int head_dim, cudaStream_t stream) {
+static int attention_bwd_impl(const void* qkv, const void* out, const void* dout, const float* lse,
+                              const uint8_t* key_mask, void* dqkv, void* scratch,
+                              size_t scratch_bytes, int B, int T, int H, int head_dim,
+                              const DropoutParams& drop, cudaStream_t stream) {
   namespace ab = attn_bwd;
   B200_REQUIRE(head_dim == ab::HD, "attention_bwd: specialised for head_dim 64");
   B200_REQUIRE(B > 0 && T > 0 && H > 0, "attention_bwd: empty problem");
@@ -469,14 +492,21 @@ extern "C" int llmtrain_b200_attention_bwd(const void* qkv, const void* out, con
   p.dsum = dsum;
   p.key_mask = key_mask;
   p.dq32 = dq32;
+  p.drop = drop;
+  p.t_pad = (T + 7) & ~7;
   static bool configured = false;
   if (!configured) {
-    B200_CHECK_CUDA(cudaFuncSetAttribute(ab::bwd_kernel,
+    B200_CHECK_CUDA(cudaFuncSetAttribute(ab::bwd_kernel<false>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, ab::SMEM));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(ab::bwd_kernel<true>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, ab::SMEM));
     configured = true;
   }
   dim3 grid(ceil_div(T, ab::BKV), H, B);
-  ab::bwd_kernel<<<grid, ab::THREADS, ab::SMEM, stream>>>(tQKV, tDO, tDQKV, p);
+  if (drop.threshold != 0)
+    ab::bwd_kernel<true><<<grid, ab::THREADS, ab::SMEM, stream>>>(tQKV, tDO, tDQKV, p);
+  else
+    ab::bwd_kernel<false><<<grid, ab::THREADS, ab::SMEM, stream>>>(tQKV, tDO, tDQKV, p);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
 
@@ -486,4 +516,26 @@ extern "C" int llmtrain_b200_attention_bwd(const void* qkv, const void* out, con
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   return 0;
+}
+
+// qkv [B,T,3d], out/dout [B,T,d] bf16, lse [B,H,T]  ->  dqkv [B,T,3d] bf16.
+extern "C" int llmtrain_b200_attention_bwd(const void* qkv, const void* out, const void* dout,
+                                           const float* lse, const uint8_t* key_mask, void* dqkv,
+                                           void* scratch, size_t scratch_bytes, int B, int T,
+                                           int H, int head_dim, cudaStream_t stream) {
+  return attention_bwd_impl(qkv, out, dout, lse, key_mask, dqkv, scratch, scratch_bytes, B, T, H,
+                            head_dim, make_dropout(0.f, 0, 0, 0), stream);
+}
+
+// Backward of llmtrain_b200_attention_fwd_dropout: pass the same (p, seed, offset, site).
+extern "C" int llmtrain_b200_attention_bwd_dropout(const void* qkv, const void* out,
+                                                   const void* dout, const float* lse,
+                                                   const uint8_t* key_mask, void* dqkv,
+                                                   void* scratch, size_t scratch_bytes, int B,
+                                                   int T, int H, int head_dim, float p,
+                                                   uint64_t seed, uint64_t offset, uint32_t site,
+                                                   cudaStream_t stream) {
+  B200_REQUIRE(p >= 0.f && p < 1.f, "attention_bwd_dropout: p must be in [0, 1)");
+  return attention_bwd_impl(qkv, out, dout, lse, key_mask, dqkv, scratch, scratch_bytes, B, T, H,
+                            head_dim, make_dropout(p, seed, offset, site), stream);
 }

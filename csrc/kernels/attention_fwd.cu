@@ -25,6 +25,7 @@
 // the other's tensor-core work.
 
 #include "../common/host.cuh"
+#include "../common/philox.cuh"
 #include "../common/ptx.cuh"
 #include "../../include/llmtrain_b200.h"
 
@@ -50,6 +51,8 @@ struct FwdParams {
   float scale_log2;              // head_dim^-0.5 * log2(e)
   const uint8_t* key_mask;       // [B, T] (1 = attend) or nullptr
   float* lse;                    // [B, H, T]
+  DropoutParams drop;            // attention-probability dropout (`gpt.py:67`); threshold 0 = off
+  int t_pad;                     // T rounded up to 8: row pitch of the mask's element index
 };
 
 // Mask modes of one 128x128 score tile:
@@ -97,10 +100,14 @@ __device__ __forceinline__ float row_max(uint32_t t_row, int kv0, int qrow, int 
 }
 
 // p = exp2(s*scale - m) -> bf16 into the K-major 128B-swizzled P tile; returns the row sum
-template <int MODE>
+// DROP: the probabilities handed to the PV product are dropped and rescaled; the row sum (the
+// softmax normaliser) is taken BEFORE dropout, as in softmax -> nn.Dropout.  `mask_base` is the
+// mask element index of (this row, column kv0).
+template <int MODE, bool DROP>
 __device__ __forceinline__ float exp_pack(uint32_t t_row, uint8_t* sP, int r, int kv0, int qrow,
                                           int T, const uint8_t* kmask, float scale_log2,
-                                          float m_use, int wchunk, int lane) {
+                                          float m_use, int wchunk, int lane,
+                                          const DropoutParams& dp, uint64_t mask_base) {
   float sum = 0.f;
 #pragma unroll 1
   for (int c = 0; c < BKV / 32; ++c) {
@@ -117,6 +124,7 @@ __device__ __forceinline__ float exp_pack(uint32_t t_row, uint8_t* sP, int r, in
     tmem_ld_wait();
     uint32_t packed[16];
     const bool plain = MODE == kNoMask || (MODE == kDiag && c < wchunk);
+    Rand8 rnd{};
 #pragma unroll
     for (int i = 0; i < 32; i += 2) {
       float e0 = fast_exp2(fmaf(__uint_as_float(v[i]), scale_log2, -m_use));
@@ -131,6 +139,11 @@ __device__ __forceinline__ float exp_pack(uint32_t t_row, uint8_t* sP, int r, in
         }
       }
       sum += e0 + e1;
+      if (DROP) {
+        if ((i & 7) == 0) rnd = philox_group(dp, (mask_base + uint64_t(c * 32 + i)) >> 3);
+        e0 *= keep_factor(dp, rnd, i & 7);
+        e1 *= keep_factor(dp, rnd, (i & 7) + 1);
+      }
       packed[i >> 1] = pack_bf16x2(e0, e1);
     }
 #pragma unroll
@@ -143,6 +156,7 @@ __device__ __forceinline__ float exp_pack(uint32_t t_row, uint8_t* sP, int r, in
   return sum;
 }
 
+template <bool DROP>
 __global__ void __launch_bounds__(FWD_THREADS, 2)
 fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmO,
            const FwdParams p) {
@@ -298,12 +312,18 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
       const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
       const float alpha = fast_exp2(m_run - m_use);  // m_run = -inf -> 0
       float sum;
+      const uint64_t mask_base =
+          DROP ? (uint64_t((size_t(b) * p.H + h) * p.T + qrow) * uint64_t(p.t_pad) + uint64_t(kv0))
+               : 0;
       if (mode == kNoMask)
-        sum = exp_pack<kNoMask>(t_row, sP, r, kv0, qrow, p.T, kmask, p.scale_log2, m_use, warp, lane);
+        sum = exp_pack<kNoMask, DROP>(t_row, sP, r, kv0, qrow, p.T, kmask, p.scale_log2, m_use,
+                                      warp, lane, p.drop, mask_base);
       else if (mode == kDiag)
-        sum = exp_pack<kDiag>(t_row, sP, r, kv0, qrow, p.T, kmask, p.scale_log2, m_use, warp, lane);
+        sum = exp_pack<kDiag, DROP>(t_row, sP, r, kv0, qrow, p.T, kmask, p.scale_log2, m_use, warp,
+                                    lane, p.drop, mask_base);
       else
-        sum = exp_pack<kGeneral>(t_row, sP, r, kv0, qrow, p.T, kmask, p.scale_log2, m_use, warp, lane);
+        sum = exp_pack<kGeneral, DROP>(t_row, sP, r, kv0, qrow, p.T, kmask, p.scale_log2, m_use,
+                                       warp, lane, p.drop, mask_base);
       l_run = l_run * alpha + sum;
       m_run = m_new;
 
@@ -356,9 +376,9 @@ using namespace b200;
 
 // qkv: [B, T, 3*H*64] bf16 (q | k | v, head-major inside each third).  out: [B, T, H*64] bf16.
 // lse: [B, H, T] fp32.  key_mask: [B, T] uint8 or NULL.
-extern "C" int llmtrain_b200_attention_fwd(const void* qkv, void* out, float* lse,
-                                           const uint8_t* key_mask, int B, int T, int H,
-                                           int head_dim, cudaStream_t stream) {
+static int attention_fwd_impl(const void* qkv, void* out, float* lse, const uint8_t* key_mask,
+                              int B, int T, int H, int head_dim, const DropoutParams& drop,
+                              cudaStream_t stream) {
   B200_REQUIRE(head_dim == attn::HD, "attention: the tcgen05 kernel is specialised for head_dim 64");
   B200_REQUIRE(B > 0 && T > 0 && H > 0, "attention: empty problem");
   const int d = H * attn::HD;
@@ -374,16 +394,43 @@ extern "C" int llmtrain_b200_attention_fwd(const void* qkv, void* out, float* ls
   p.scale_log2 = 1.4426950408889634f / std::sqrt(float(head_dim));
   p.key_mask = key_mask;
   p.lse = lse;
+  p.drop = drop;
+  p.t_pad = (T + 7) & ~7;
   static bool configured = false;
   if (!configured) {
-    B200_CHECK_CUDA(cudaFuncSetAttribute(attn::fwd_kernel,
+    B200_CHECK_CUDA(cudaFuncSetAttribute(attn::fwd_kernel<false>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         attn::FWD_SMEM));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(attn::fwd_kernel<true>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          attn::FWD_SMEM));
     configured = true;
   }
   dim3 grid(ceil_div(T, attn::BQ), H, B);
-  attn::fwd_kernel<<<grid, attn::FWD_THREADS, attn::FWD_SMEM, stream>>>(tQKV, tO, p);
+  if (drop.threshold != 0)
+    attn::fwd_kernel<true><<<grid, attn::FWD_THREADS, attn::FWD_SMEM, stream>>>(tQKV, tO, p);
+  else
+    attn::fwd_kernel<false><<<grid, attn::FWD_THREADS, attn::FWD_SMEM, stream>>>(tQKV, tO, p);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   return 0;
+}
+
+extern "C" int llmtrain_b200_attention_fwd(const void* qkv, void* out, float* lse,
+                                           const uint8_t* key_mask, int B, int T, int H,
+                                           int head_dim, cudaStream_t stream) {
+  return attention_fwd_impl(qkv, out, lse, key_mask, B, T, H, head_dim,
+                            make_dropout(0.f, 0, 0, 0), stream);
+}
+
+// As above with dropout on the attention probabilities.  Mask element index:
+// ((b*H + h)*T + q) * roundup(T, 8) + k  (llmtrain_b200_dropout_mask with rows = B*H*T, cols = T).
+extern "C" int llmtrain_b200_attention_fwd_dropout(const void* qkv, void* out, float* lse,
+                                                   const uint8_t* key_mask, int B, int T, int H,
+                                                   int head_dim, float p, uint64_t seed,
+                                                   uint64_t offset, uint32_t site,
+                                                   cudaStream_t stream) {
+  B200_REQUIRE(p >= 0.f && p < 1.f, "attention_fwd_dropout: p must be in [0, 1)");
+  return attention_fwd_impl(qkv, out, lse, key_mask, B, T, H, head_dim,
+                            make_dropout(p, seed, offset, site), stream);
 }

@@ -28,6 +28,7 @@
 #include <cstdlib>
 
 #include "../common/host.cuh"
+#include "../common/philox.cuh"
 #include "../common/ptx.cuh"
 #include "../../include/llmtrain_b200.h"
 
@@ -73,6 +74,7 @@ enum Epi : int {
   kBiasResid = 2, // C = acc (+ bias) + R
   kDGelu = 3,     // C = acc * R                 (R holds gelu'(pre-activation) saved by forward)
   kAccumF32 = 4,  // C(fp32) += acc              (TMA reduce-add)
+  kBiasDropResid = 5,  // C = dropout(acc + bias) + R   (mask regenerated in backward, philox.cuh)
 };
 
 struct Params {
@@ -86,6 +88,7 @@ struct Params {
   __nv_bfloat16* Cptr;     // bf16 output for the direct-store epilogue, row pitch ldc
   int ldc;
   int group_m;             // rasterisation: row-tiles per band (>= #row-tiles => M fastest)
+  DropoutParams drop;      // kBiasDropResid only
 };
 
 // Tile order.  Consecutive tiles walk `group_m` row-tiles for one column-tile, then the next
@@ -359,7 +362,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       // Residual / saved pre-activation for this thread's row (2 chunks x 64 bf16): issued BEFORE
       // waiting for the accumulator so the HBM latency hides behind this tile's mainloop.
       uint4 rv[2][8];
-      if (EPI == kBiasResid || EPI == kDGelu) {
+      if (EPI == kBiasResid || EPI == kDGelu || EPI == kBiasDropResid) {
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
 #pragma unroll
@@ -387,7 +390,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       // no memory latency sits inside the math loop.
       float4 bias4 = make_float4(0.f, 0.f, 0.f, 0.f);
       const bool add_bias =
-          (EPI == kBias || EPI == kBiasGelu || EPI == kBiasResid) && p.bias != nullptr;
+          (EPI == kBias || EPI == kBiasGelu || EPI == kBiasResid || EPI == kBiasDropResid) &&
+          p.bias != nullptr;
       if (add_bias) {
         const int bc = n0 + lane * 4;
         if (bc + 4 <= p.N) {
@@ -442,6 +446,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           const uint32_t* rw = reinterpret_cast<const uint32_t*>(rv[c]);
 #pragma unroll
           for (int h = 0; h < 2; ++h) {
+            Rand8 rnd[4];
+            if (EPI == kBiasDropResid) {
+              // 32 consecutive columns of this thread's row = four 8-element Philox groups
+              const uint64_t g0 = (uint64_t(row) * uint64_t(p.N) + uint64_t(col0 + h * 32)) >> 3;
+#pragma unroll
+              for (int g = 0; g < 4; ++g) rnd[g] = philox_group(p.drop, g0 + g);
+            }
 #pragma unroll
             for (int j = 0; j < 32; j += 2) {
               float x0 = __uint_as_float(v[h][j]);
@@ -456,10 +467,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                 x0 += __shfl_sync(0xffffffffu, lo, cc >> 2);
                 x1 += __shfl_sync(0xffffffffu, hi, cc >> 2);
               }
-              if (EPI == kBiasResid || EPI == kDGelu) {
+              if (EPI == kBiasDropResid) {
+                x0 *= keep_factor(p.drop, rnd[j >> 3], j & 7);
+                x1 *= keep_factor(p.drop, rnd[j >> 3], (j & 7) + 1);
+              }
+              if (EPI == kBiasResid || EPI == kDGelu || EPI == kBiasDropResid) {
                 const float2 f = unpack_bf16x2(rw[h * 16 + (j >> 1)]);
-                if (EPI == kBiasResid) { x0 += f.x; x1 += f.y; }
-                else { x0 *= f.x; x1 *= f.y; }
+                if (EPI == kDGelu) { x0 *= f.x; x1 *= f.y; }
+                else { x0 += f.x; x1 += f.y; }
               }
               if (EPI == kBiasGelu) {
                 f32x2 y2, dy2;
@@ -618,12 +633,13 @@ using namespace b200;
 using namespace b200::gemm;
 
 // layout: 0 = NT, 1 = NN, 2 = TN (see header).  All pointers are device pointers.
-extern "C" int llmtrain_b200_gemm(int layout, int epilogue, int M, int N, int K, const void* A,
-                                  int lda, const void* B, int ldb, void* C, int ldc, void* C2,
-                                  int ldc2, const float* bias, const void* R, int ldr,
-                                  cudaStream_t stream) {
+static int gemm_dispatch(int layout, int epilogue, int M, int N, int K, const void* A, int lda,
+                         const void* B, int ldb, void* C, int ldc, void* C2, int ldc2,
+                         const float* bias, const void* R, int ldr, const DropoutParams& drop,
+                         cudaStream_t stream) {
   B200_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem");
   Params p{};
+  p.drop = drop;
   p.M = M; p.N = N; p.K = K; p.k_splits = 1;
   p.bias = bias;
   p.R = static_cast<const __nv_bfloat16*>(R);
@@ -670,8 +686,10 @@ extern "C" int llmtrain_b200_gemm(int layout, int epilogue, int M, int N, int K,
       if (make_tmap_2d(&tC2, static_cast<__nv_bfloat16*>(C2), M, N, ldc2, 32, 64, Swz::B128))
         return 1;
     }
-    if (epilogue == kBiasResid || epilogue == kDGelu)
+    if (epilogue == kBiasResid || epilogue == kDGelu || epilogue == kBiasDropResid)
       B200_REQUIRE(R != nullptr, "gemm: this epilogue needs R");
+    if (epilogue == kBiasDropResid)
+      B200_REQUIRE(N % 8 == 0, "gemm: the dropout epilogue needs N to be a multiple of 8");
   }
 
 #define B200_GEMM_CASE(L, AMN, BMN, E)                                                  \
@@ -681,9 +699,31 @@ extern "C" int llmtrain_b200_gemm(int layout, int epilogue, int M, int N, int K,
   B200_GEMM_CASE(0, false, false, kBias)
   B200_GEMM_CASE(0, false, false, kBiasGelu)
   B200_GEMM_CASE(0, false, false, kBiasResid)
+  B200_GEMM_CASE(0, false, false, kBiasDropResid)
   B200_GEMM_CASE(1, false, true, kBias)
   B200_GEMM_CASE(1, false, true, kDGelu)
   B200_GEMM_CASE(2, true, true, kAccumF32)
 #undef B200_GEMM_CASE
   return fail("gemm: unsupported layout/epilogue combination");
+}
+
+extern "C" int llmtrain_b200_gemm(int layout, int epilogue, int M, int N, int K, const void* A,
+                                  int lda, const void* B, int ldb, void* C, int ldc, void* C2,
+                                  int ldc2, const float* bias, const void* R, int ldr,
+                                  cudaStream_t stream) {
+  B200_REQUIRE(epilogue != kBiasDropResid, "gemm: use llmtrain_b200_gemm_dropout_resid");
+  return gemm_dispatch(layout, epilogue, M, N, K, A, lda, B, ldb, C, ldc, C2, ldc2, bias, R, ldr,
+                       make_dropout(0.f, 0, 0, 0), stream);
+}
+
+// C[M,N] = dropout(A[M,K] * B[N,K]^T + bias) + R   (NT layout; mask element index row * N + col,
+// regenerated by llmtrain_b200_dropout with the same (p, seed, offset, site) in backward).
+extern "C" int llmtrain_b200_gemm_dropout_resid(int M, int N, int K, const void* A, int lda,
+                                                const void* B, int ldb, void* C, int ldc,
+                                                const float* bias, const void* R, int ldr,
+                                                float p, uint64_t seed, uint64_t offset,
+                                                uint32_t site, cudaStream_t stream) {
+  B200_REQUIRE(p >= 0.f && p < 1.f, "gemm_dropout_resid: p must be in [0, 1)");
+  return gemm_dispatch(0, kBiasDropResid, M, N, K, A, lda, B, ldb, C, ldc, nullptr, 0, bias, R, ldr,
+                       make_dropout(p, seed, offset, site), stream);
 }

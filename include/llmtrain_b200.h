@@ -147,6 +147,35 @@ int llmtrain_b200_attention_bwd(const void* qkv, const void* out, const void* do
                                 int head_dim, llm_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * Dropout (csrc/common/philox.cuh, csrc/kernels/dropout.cu).  Replaces the four nn.Dropout modules
+ * of src/llmtrain/models/gpt.py:28,30,97,129.  A mask is a pure function of (seed, offset, site,
+ * element index = row * roundup(cols, 8) + col): forward and backward regenerate it, nothing is
+ * stored.  keep probability = 1 - round(p * 65536) / 65536; kept values are scaled by its inverse.
+ * ------------------------------------------------------------------------------------------- */
+/* y = x o mask / (1 - p), bf16 [rows, cols] with row pitch ld (x == y allowed) */
+int llmtrain_b200_dropout(const void* x, void* y, long long rows, int cols, int ld, float p,
+                          uint64_t seed, uint64_t offset, uint32_t site, llm_stream_t stream);
+/* out[rows, cols] uint8 = 1 where kept: the mask the fused kernels apply (tests build the
+ * PyTorch reference from it) */
+int llmtrain_b200_dropout_mask(uint8_t* out, long long rows, int cols, float p, uint64_t seed,
+                               uint64_t offset, uint32_t site, llm_stream_t stream);
+/* C[M,N] = dropout(A[M,K] B[N,K]^T + bias) + R ; mask rows = M, cols = N */
+int llmtrain_b200_gemm_dropout_resid(int M, int N, int K, const void* A, int lda, const void* B,
+                                     int ldb, void* C, int ldc, const float* bias, const void* R,
+                                     int ldr, float p, uint64_t seed, uint64_t offset,
+                                     uint32_t site, llm_stream_t stream);
+/* attention with dropout on the probabilities; mask rows = B*H*T (index (b*H+h)*T+q), cols = T */
+int llmtrain_b200_attention_fwd_dropout(const void* qkv, void* out, float* lse,
+                                        const uint8_t* key_mask, int B, int T, int H, int head_dim,
+                                        float p, uint64_t seed, uint64_t offset, uint32_t site,
+                                        llm_stream_t stream);
+int llmtrain_b200_attention_bwd_dropout(const void* qkv, const void* out, const void* dout,
+                                        const float* lse, const uint8_t* key_mask, void* dqkv,
+                                        void* scratch, size_t scratch_bytes, int B, int T, int H,
+                                        int head_dim, float p, uint64_t seed, uint64_t offset,
+                                        uint32_t site, llm_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
  * GPT runtime (csrc/engine/gpt_engine.cu).  Replaces autograd over GPT.forward + compute_loss
  * (src/llmtrain/models/gpt.py:167-184,214-271; src/llmtrain/training/trainer.py:385-387).
  *
@@ -178,6 +207,9 @@ int llmtrain_b200_gpt_refresh_shadow(void* handle, llm_stream_t stream);
 int llmtrain_b200_gpt_forward(void* handle, const int64_t* ids, const int64_t* labels,
                               const uint8_t* key_mask, int B, int T, int mode, float* loss_acc,
                               float loss_scale, float grad_scale, llm_stream_t stream);
+/* Dropout for the NEXT mode-2 forward and its backward (p = 0: off; modes 0/1 never drop).  seed
+ * identifies run and rank, offset must change with every micro-batch. */
+int llmtrain_b200_gpt_set_dropout(void* handle, float p, uint64_t seed, uint64_t offset);
 /* g32 += d loss / d params for the last mode-2 forward. */
 int llmtrain_b200_gpt_backward(void* handle, llm_stream_t stream);
 

@@ -111,6 +111,9 @@ class GPTEngine:
         self.p16: torch.Tensor | None = None
         self.shadow_fresh = False
         self._live: tuple[Any, ...] = ()
+        self._dropout_seed: int | None = None
+        self._dropout_calls = 0
+        self._dropout_armed = False
         self._loss_acc = torch.zeros(1, dtype=torch.float32, device=self.device)
         self._replan(max_batch, max_seq or model.block_size)
         self._adopt_parameters()
@@ -246,6 +249,7 @@ class GPTEngine:
     ) -> None:
         b, t = ids.shape
         self._live = (ids, labels, key_mask)  # pointers are re-read by backward
+        self._arm_dropout(mode)
         check(
             self._lib.llmtrain_b200_gpt_forward(
                 self._handle, ptr(ids), ptr(labels), ptr(key_mask), ctypes.c_int(b),
@@ -254,6 +258,33 @@ class GPTEngine:
             ),
             "gpt_forward",
         )
+
+    def _arm_dropout(self, mode: int) -> None:
+        """Dropout applies to training forwards (mode 2) of a module in ``train()`` mode.
+
+        Reference: four ``nn.Dropout`` modules, ``src/llmtrain/models/gpt.py:28,30,97,129``.  Masks
+        are counter-based (``csrc/common/philox.cuh``): the seed is torch's global seed plus the
+        rank, the offset is a per-engine micro-batch counter, so a run is reproducible and the
+        backward pass regenerates what the forward pass used.
+        """
+        p = float(self.model.dropout_p) if (mode == 2 and self.model.training) else 0.0
+        if p <= 0.0 and not self._dropout_armed:
+            return
+        if self._dropout_seed is None:
+            rank = 0
+            if torch.distributed.is_available() and torch.distributed.is_initialized():
+                rank = torch.distributed.get_rank()
+            self._dropout_seed = (int(torch.initial_seed()) + 0x9E3779B97F4A7C15 * rank) % (1 << 64)
+        if p > 0.0:
+            self._dropout_calls += 1
+        check(
+            self._lib.llmtrain_b200_gpt_set_dropout(
+                self._handle, ctypes.c_float(p), ctypes.c_uint64(self._dropout_seed),
+                ctypes.c_uint64(self._dropout_calls),
+            ),
+            "gpt_set_dropout",
+        )
+        self._dropout_armed = p > 0.0
 
     def run_backward(self) -> None:
         check(self._lib.llmtrain_b200_gpt_backward(self._handle, stream_handle()), "gpt_backward")

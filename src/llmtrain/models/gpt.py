@@ -17,7 +17,7 @@ checkpoints interchange with the reference in both directions.
   A missing native library is an error, never a silent fallback.  The torch-op path remains
   reachable on CUDA on purpose (``prefer_native = False`` / ``trainer.extra.engine: torch``):
   it is the on-device oracle for the equivalence tests and the path taken for shapes the kernels
-  do not cover (head_dim != 64) or training with dropout > 0.
+  do not cover (head_dim != 64).
 
 The causal mask is never materialised on the device (the attention kernel applies it
 implicitly); the ``causal_mask`` tensors exist only inside ``state_dict()`` for format parity,
@@ -201,12 +201,10 @@ class GPT(nn.Module):
     def use_native(self) -> bool:
         """True when calls should run on the sm_100a runtime instead of torch ops.
 
-        Dropout is not implemented in the native kernels yet, so a module that is in training
-        mode with ``dropout > 0`` stays on the torch path (the trainer logs this choice).
+        Dropout is native too (counter-based masks regenerated in backward, see
+        ``csrc/common/philox.cuh``), so training mode with ``dropout > 0`` stays on this path.
         """
         if not (self.on_cuda and self.prefer_native):
-            return False
-        if self.training and self.dropout_p > 0.0:
             return False
         from llmtrain.engine.b200 import supports
 

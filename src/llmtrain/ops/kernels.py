@@ -164,14 +164,84 @@ def adamw(p, m, v, g, p16, *, sumsq, norm_out, lr, beta1, beta2, eps, weight_dec
     )
 
 
-def attention_fwd(qkv, n_heads, *, key_mask=None, out=None, lse=None):
-    """``qkv``: (B, T, 3*d) bf16 → ``(out (B, T, d) bf16, lse (B, H, T) fp32)``."""
+def _c_u64(v: int) -> ctypes.c_uint64:
+    return ctypes.c_uint64(int(v) % (1 << 64))
+
+
+def dropout(x, p, *, seed, offset, site, out=None):
+    """``out = x * mask / (1 - p)`` on a bf16 ``(rows, cols)`` tensor (counter-based mask)."""
+    out = torch.empty_like(x) if out is None else out
+    rows, cols = x.shape
+    check(
+        _lib().llmtrain_b200_dropout(
+            ptr(x), ptr(out), ctypes.c_longlong(rows), _c_int(cols), _c_int(x.stride(0)),
+            _c_float(p), _c_u64(seed), _c_u64(offset), ctypes.c_uint32(site), stream_handle(),
+        ),
+        "dropout",
+    )
+    return out
+
+
+def dropout_mask(rows, cols, p, *, seed, offset, site, device="cuda"):
+    """uint8 ``(rows, cols)`` keep-mask the fused kernels apply for these counters."""
+    out = torch.empty(rows, cols, dtype=torch.uint8, device=device)
+    check(
+        _lib().llmtrain_b200_dropout_mask(
+            ptr(out), ctypes.c_longlong(rows), _c_int(cols), _c_float(p), _c_u64(seed),
+            _c_u64(offset), ctypes.c_uint32(site), stream_handle(),
+        ),
+        "dropout_mask",
+    )
+    return out
+
+
+def dropout_scale(p: float) -> float:
+    """The exact factor kept elements are multiplied by (p is quantised to 1/65536)."""
+    if p <= 0:
+        return 1.0
+    t = min(max(int(p * 65536.0 + 0.5), 1), 65535)
+    return 65536.0 / (65536 - t)
+
+
+def linear_dropout_resid(x, w, bias, resid, p, *, seed, offset, site, out=None):
+    """``dropout(x @ w.T + bias) + resid`` — the residual-branch projections with dropout."""
+    m, k = x.shape
+    n = w.shape[0]
+    out = torch.empty(m, n, dtype=torch.bfloat16, device=x.device) if out is None else out
+    check(
+        _lib().llmtrain_b200_gemm_dropout_resid(
+            _c_int(m), _c_int(n), _c_int(k), ptr(x), _c_int(x.stride(0)), ptr(w),
+            _c_int(w.stride(0)), ptr(out), _c_int(out.stride(0)), ptr(bias), ptr(resid),
+            _c_int(resid.stride(0)), _c_float(p), _c_u64(seed), _c_u64(offset),
+            ctypes.c_uint32(site), stream_handle(),
+        ),
+        "gemm_dropout_resid",
+    )
+    return out
+
+
+def attention_fwd(qkv, n_heads, *, key_mask=None, out=None, lse=None, dropout=None):
+    """``qkv``: (B, T, 3*d) bf16 → ``(out (B, T, d) bf16, lse (B, H, T) fp32)``.
+
+    ``dropout``: optional ``(p, seed, offset, site)`` for dropout on the attention probabilities.
+    """
     b, t, three_d = qkv.shape
     d = three_d // 3
     hd = d // n_heads
     out = torch.empty(b, t, d, dtype=torch.bfloat16, device=qkv.device) if out is None else out
     if lse is None:
         lse = torch.empty(b, n_heads, t, dtype=torch.float32, device=qkv.device)
+    if dropout is not None:
+        p, seed, offset, site = dropout
+        check(
+            _lib().llmtrain_b200_attention_fwd_dropout(
+                ptr(qkv), ptr(out), ptr(lse), ptr(key_mask), _c_int(b), _c_int(t),
+                _c_int(n_heads), _c_int(hd), _c_float(p), _c_u64(seed), _c_u64(offset),
+                ctypes.c_uint32(site), stream_handle(),
+            ),
+            "attention_fwd_dropout",
+        )
+        return out, lse
     check(
         _lib().llmtrain_b200_attention_fwd(
             ptr(qkv), ptr(out), ptr(lse), ptr(key_mask), _c_int(b), _c_int(t), _c_int(n_heads),
@@ -182,7 +252,7 @@ def attention_fwd(qkv, n_heads, *, key_mask=None, out=None, lse=None):
     return out, lse
 
 
-def attention_bwd(qkv, out, dout, lse, n_heads, *, key_mask=None, dqkv=None):
+def attention_bwd(qkv, out, dout, lse, n_heads, *, key_mask=None, dqkv=None, dropout=None):
     """Gradient of :func:`attention_fwd` w.r.t. the fused ``qkv`` buffer."""
     b, t, three_d = qkv.shape
     hd = three_d // 3 // n_heads
@@ -191,6 +261,17 @@ def attention_bwd(qkv, out, dout, lse, n_heads, *, key_mask=None, dqkv=None):
     need = lib.llmtrain_b200_attention_bwd_scratch_bytes(_c_int(b), _c_int(t), _c_int(n_heads),
                                                          _c_int(hd))
     buf = scratch(need, qkv.device)
+    if dropout is not None:
+        p, seed, offset, site = dropout
+        check(
+            lib.llmtrain_b200_attention_bwd_dropout(
+                ptr(qkv), ptr(out), ptr(dout), ptr(lse), ptr(key_mask), ptr(dqkv), ptr(buf),
+                _c_size(buf.numel()), _c_int(b), _c_int(t), _c_int(n_heads), _c_int(hd),
+                _c_float(p), _c_u64(seed), _c_u64(offset), ctypes.c_uint32(site), stream_handle(),
+            ),
+            "attention_bwd_dropout",
+        )
+        return dqkv
     check(
         lib.llmtrain_b200_attention_bwd(
             ptr(qkv), ptr(out), ptr(dout), ptr(lse), ptr(key_mask), ptr(dqkv), ptr(buf),

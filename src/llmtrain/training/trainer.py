@@ -135,8 +135,6 @@ class Trainer:
             blocker = None
             if not supports(model):
                 blocker = f"model {type(model).__name__} is outside the kernels' shape coverage"
-            elif cfg.model.dropout > 0.0:
-                blocker = "model.dropout > 0 (the native kernels do not implement dropout yet)"
             if blocker is None:
                 return B200TrainEngine(
                     model, cfg, device=self._device, ddp_state=self._ddp_state
