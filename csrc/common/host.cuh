@@ -7,6 +7,7 @@
 #include <stdint.h>
 
 #include <atomic>
+#include <cstdlib>
 #include <cstdio>
 #include <cstring>
 #include <mutex>
@@ -127,6 +128,46 @@ inline std::atomic<long long>& launch_counter() {
   return counter;
 }
 #define B200_COUNT_LAUNCH(n) ::b200::launch_counter().fetch_add((n), std::memory_order_relaxed)
+
+// Kernel launch with programmatic dependent launch (see pdl_wait in ptx.cuh) and an optional
+// thread-block cluster.  LLMTRAIN_PDL=0 falls back to plain stream order (A/B measurements).
+// ONLY kernels that call pdl_enter()/pdl_wait() before their first global access may come here.
+inline bool pdl_enabled() {
+  static const bool on = [] {
+    const char* e = std::getenv("LLMTRAIN_PDL");
+    return e == nullptr || std::atoi(e) != 0;
+  }();
+  return on;
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_kernel(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                                 cudaStream_t stream, int cluster_x, Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attrs[2];
+  unsigned n = 0;
+  if (cluster_x > 1) {
+    attrs[n].id = cudaLaunchAttributeClusterDimension;
+    attrs[n].val.clusterDim.x = unsigned(cluster_x);
+    attrs[n].val.clusterDim.y = 1;
+    attrs[n].val.clusterDim.z = 1;
+    ++n;
+  }
+  if (pdl_enabled()) {
+    attrs[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attrs[n].val.programmaticStreamSerializationAllowed = 1;
+    ++n;
+  }
+  cfg.attrs = attrs;
+  cfg.numAttrs = n;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+#define B200_LAUNCH(kernel, grid, block, smem, stream, ...)                                    \
+  B200_CHECK_CUDA(::b200::launch_kernel((kernel), dim3(grid), dim3(block), (smem), (stream), 1, \
+                                        __VA_ARGS__))
 
 inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 

@@ -37,6 +37,24 @@ __device__ __forceinline__ bool elect_one() {
 }
 
 // ----------------------------------------------------------------------------------------------
+// Programmatic dependent launch.  Kernels launched through b200::launch_kernel carry the
+// programmatic-stream-serialization attribute: their CTAs may become resident while the previous
+// kernel of the stream is still draining, and everything they do BEFORE pdl_wait() (barrier init,
+// TMEM allocation, descriptor prefetch) overlaps that tail.  pdl_wait() returns once the
+// previous kernel has completed and its writes are visible; no global memory may be touched
+// before it.  pdl_launch_dependents() lets the NEXT kernel start the same way; it is issued after
+// the wait so that at most one successor is ever parked on the SMs.
+// ----------------------------------------------------------------------------------------------
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+__device__ __forceinline__ void pdl_enter() {
+  pdl_wait();
+  pdl_launch_dependents();
+}
+
+// ----------------------------------------------------------------------------------------------
 // mbarrier
 // ----------------------------------------------------------------------------------------------
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t arrivals) {

@@ -188,6 +188,7 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
     mbar_init(&dq_full[1], 1);
     mbar_init(dkv_full, 1);
     fence_barrier_init();
+    pdl_wait();  // qkv / dO come from the previous kernels of the stream
     mbar_expect_tx(kv_full, 2 * TILE);
     tma_load_3d(smem + OFF_K, &tmQKV, kv_full, d + h * HD, kv0, b);
     tma_load_3d(smem + OFF_V, &tmQKV, kv_full, 2 * d + h * HD, kv0, b);
@@ -202,6 +203,7 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
+  pdl_enter();  // everything above overlapped the previous kernel's tail
   const uint32_t tmem = *tmem_slot;
 
   if (warp == 8) {
@@ -402,6 +404,7 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
 __global__ void dsum_kernel(const __nv_bfloat16* __restrict__ dO,
                             const __nv_bfloat16* __restrict__ O, float* __restrict__ dsum, int B,
                             int T, int H) {
+  pdl_enter();  // previous kernel finished, its writes are visible
   const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const long long pair = gid >> 3;  // (row, head) index
   const int sub = int(gid & 7);
@@ -432,6 +435,7 @@ __global__ void dsum_kernel(const __nv_bfloat16* __restrict__ dO,
 // dqkv[row, 0:d] = bf16(dq32[row, :])   (q third of the fused gradient buffer)
 __global__ void dq_convert_kernel(const float* __restrict__ dq32, __nv_bfloat16* __restrict__ dqkv,
                                   int rows, int d) {
+  pdl_enter();  // previous kernel finished, its writes are visible
   const size_t idx = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
   const int per_row = d >> 3;
   if (idx >= size_t(rows) * per_row) return;
@@ -470,9 +474,9 @@ static int attention_bwd_impl(const void* qkv, const void* out, const void* dout
   B200_CHECK_CUDA(cudaMemsetAsync(dq32, 0, dq_bytes, stream));
 
   const int rows = B * T;
-  ab::dsum_kernel<<<ceil_div(rows * H * 8, 256), 256, 0, stream>>>(
-      static_cast<const __nv_bfloat16*>(dout), static_cast<const __nv_bfloat16*>(out), dsum, B, T,
-      H);
+  B200_LAUNCH((ab::dsum_kernel), ceil_div(rows * H * 8, 256), 256, 0, stream,
+              static_cast<const __nv_bfloat16*>(dout), static_cast<const __nv_bfloat16*>(out), dsum,
+              B, T, H);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
 
@@ -504,15 +508,15 @@ static int attention_bwd_impl(const void* qkv, const void* out, const void* dout
   }
   dim3 grid(ceil_div(T, ab::BKV), H, B);
   if (drop.threshold != 0)
-    ab::bwd_kernel<true><<<grid, ab::THREADS, ab::SMEM, stream>>>(tQKV, tDO, tDQKV, p);
+    B200_LAUNCH((ab::bwd_kernel<true>), grid, ab::THREADS, ab::SMEM, stream, tQKV, tDO, tDQKV, p);
   else
-    ab::bwd_kernel<false><<<grid, ab::THREADS, ab::SMEM, stream>>>(tQKV, tDO, tDQKV, p);
+    B200_LAUNCH((ab::bwd_kernel<false>), grid, ab::THREADS, ab::SMEM, stream, tQKV, tDO, tDQKV, p);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
 
   const size_t n = size_t(rows) * (d / 8);
-  ab::dq_convert_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, stream>>>(
-      dq32, static_cast<__nv_bfloat16*>(dqkv), rows, d);
+  B200_LAUNCH((ab::dq_convert_kernel), static_cast<unsigned>((n + 255) / 256), 256, 0, stream, dq32,
+              static_cast<__nv_bfloat16*>(dqkv), rows, d);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   return 0;

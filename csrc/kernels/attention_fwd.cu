@@ -199,6 +199,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
     mbar_init(&pv_done[0], 1);
     mbar_init(&pv_done[1], 1);
     fence_barrier_init();
+    pdl_wait();  // qkv comes from the previous kernel of the stream
     mbar_expect_tx(q_full, TILE_BYTES);
     tma_load_3d(smem + OFF_Q, &tmQKV, q_full, h * HD, q0, b);
     mbar_expect_tx(k_full, TILE_BYTES);
@@ -213,6 +214,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
+  pdl_enter();  // everything above overlapped the previous kernel's tail
   const uint32_t tmem = *tmem_slot;
   const uint32_t tmem_S = tmem;           // 128 columns
   const uint32_t tmem_PV = tmem + 128;    // 2 x 64 columns
@@ -408,9 +410,10 @@ static int attention_fwd_impl(const void* qkv, void* out, float* lse, const uint
   }
   dim3 grid(ceil_div(T, attn::BQ), H, B);
   if (drop.threshold != 0)
-    attn::fwd_kernel<true><<<grid, attn::FWD_THREADS, attn::FWD_SMEM, stream>>>(tQKV, tO, p);
+    B200_LAUNCH((attn::fwd_kernel<true>), grid, attn::FWD_THREADS, attn::FWD_SMEM, stream, tQKV, tO, p);
   else
-    attn::fwd_kernel<false><<<grid, attn::FWD_THREADS, attn::FWD_SMEM, stream>>>(tQKV, tO, p);
+    B200_LAUNCH((attn::fwd_kernel<false>), grid, attn::FWD_THREADS, attn::FWD_SMEM, stream, tQKV, tO,
+                p);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   return 0;

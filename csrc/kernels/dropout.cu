@@ -20,6 +20,7 @@ namespace drop {
 __global__ void __launch_bounds__(256)
 apply_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, long long rows,
              int cols, int ld, int padded_cols, const DropoutParams dp) {
+  pdl_enter();  // previous kernel finished, its writes are visible
   const int groups_per_row = padded_cols >> 3;
   const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (gid >= rows * groups_per_row) return;
@@ -50,6 +51,7 @@ apply_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y,
 __global__ void __launch_bounds__(256)
 mask_kernel(uint8_t* __restrict__ out, long long rows, int cols, int padded_cols,
             const DropoutParams dp) {
+  pdl_enter();  // previous kernel finished, its writes are visible
   const int groups_per_row = padded_cols >> 3;
   const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (gid >= rows * groups_per_row) return;
@@ -76,9 +78,7 @@ extern "C" int llmtrain_b200_dropout(const void* x, void* y, long long rows, int
   const int padded = (cols + 7) & ~7;
   const long long n = rows * (padded >> 3);
   const DropoutParams dp = make_dropout(p, seed, offset, site);
-  drop::apply_kernel<<<unsigned((n + 255) / 256), 256, 0, stream>>>(
-      static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), rows, cols, ld, padded,
-      dp);
+  B200_LAUNCH((drop::apply_kernel), unsigned((n + 255) / 256), 256, 0, stream, static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), rows, cols, ld, padded, dp);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   return 0;
@@ -95,7 +95,7 @@ extern "C" int llmtrain_b200_dropout_mask(uint8_t* out, long long rows, int cols
   const int padded = (cols + 7) & ~7;
   const long long n = rows * (padded >> 3);
   const DropoutParams dp = make_dropout(p, seed, offset, site);
-  drop::mask_kernel<<<unsigned((n + 255) / 256), 256, 0, stream>>>(out, rows, cols, padded, dp);
+  B200_LAUNCH((drop::mask_kernel), unsigned((n + 255) / 256), 256, 0, stream, out, rows, cols, padded, dp);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   return 0;

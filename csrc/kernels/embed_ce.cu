@@ -33,6 +33,7 @@ __global__ void embed_fwd_kernel(const int64_t* __restrict__ ids,
                                  const __nv_bfloat16* __restrict__ wte,
                                  const __nv_bfloat16* __restrict__ wpe,
                                  __nv_bfloat16* __restrict__ x, int rows, int T, int d, int vocab) {
+  pdl_enter();  // previous kernel finished, its writes are visible
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (row >= rows) return;
   const int lane = threadIdx.x & 31;
@@ -56,6 +57,7 @@ __global__ void embed_fwd_kernel(const int64_t* __restrict__ ids,
 __global__ void embed_bwd_wte_kernel(const int64_t* __restrict__ ids,
                                      const __nv_bfloat16* __restrict__ dx,
                                      float* __restrict__ dwte, int rows, int d, int vocab) {
+  pdl_enter();  // previous kernel finished, its writes are visible
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (row >= rows) return;
   const int lane = threadIdx.x & 31;
@@ -75,6 +77,7 @@ __global__ void embed_bwd_wte_kernel(const int64_t* __restrict__ ids,
 // dwpe[t,:] += sum_b dx[b*T + t,:]   (one thread per (t, 4 columns); fixed order over b)
 __global__ void embed_bwd_wpe_kernel(const __nv_bfloat16* __restrict__ dx,
                                      float* __restrict__ dwpe, int B, int T, int d) {
+  pdl_enter();  // previous kernel finished, its writes are visible
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   const int per_row = d >> 2;
   if (idx >= T * per_row) return;
@@ -113,6 +116,7 @@ __global__ void __launch_bounds__(CE_THREADS)
 ce_kernel(__nv_bfloat16* __restrict__ logits, const int64_t* __restrict__ labels,
           const uint8_t* __restrict__ row_valid, float* __restrict__ loss_rows, int V, int ldv,
           float grad_scale) {
+  pdl_enter();  // previous kernel finished, its writes are visible
   __shared__ float red_m[CE_THREADS / 32], red_s[CE_THREADS / 32];
   __shared__ float bc_m, bc_s;
   const int row = blockIdx.x;
@@ -217,6 +221,7 @@ __global__ void __launch_bounds__(CE_ROW_THREADS, 1)
 ce_row_kernel(__nv_bfloat16* __restrict__ logits, const int64_t* __restrict__ labels,
               const uint8_t* __restrict__ row_valid, float* __restrict__ loss_rows, int rows,
               int V, int ldv, float grad_scale) {
+  pdl_enter();  // previous kernel finished, its writes are visible
   extern __shared__ __align__(128) uint8_t ce_row_smem[];
   __shared__ uint64_t full[2];
   __shared__ float red_m[CE_ROW_THREADS / 32], red_s[CE_ROW_THREADS / 32];
@@ -347,6 +352,7 @@ ce_row_kernel(__nv_bfloat16* __restrict__ logits, const int64_t* __restrict__ la
 // loss_acc[0] += scale * sum(loss_rows)  — single CTA, fixed order => deterministic.
 __global__ void loss_reduce_kernel(const float* __restrict__ loss_rows, int rows, float scale,
                                    float* __restrict__ loss_acc) {
+  pdl_enter();  // previous kernel finished, its writes are visible
   __shared__ float red[32];
   float acc = 0.f;
   for (int i = threadIdx.x; i < rows; i += blockDim.x) acc += loss_rows[i];
@@ -370,6 +376,7 @@ constexpr int CS_COLS = 256;
 __global__ void __launch_bounds__(CS_WARPS * 32)
 colsum_partial_kernel(const __nv_bfloat16* __restrict__ dy, int ld, int M, int N,
                       float* __restrict__ partial /* [splits][N] */) {
+  pdl_enter();  // previous kernel finished, its writes are visible
   __shared__ float sh[CS_WARPS][CS_COLS];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int col = blockIdx.x * CS_COLS + lane * 8;
@@ -413,6 +420,7 @@ colsum_partial_kernel(const __nv_bfloat16* __restrict__ dy, int ld, int M, int N
 __global__ void __launch_bounds__(256)
 colsum_finish_kernel(const float* __restrict__ partial, int splits, int N,
                      float* __restrict__ out) {
+  pdl_enter();  // previous kernel finished, its writes are visible
   __shared__ float sh[8][32];
   const int cx = threadIdx.x & 31, sy = threadIdx.x >> 5;
   const int n = blockIdx.x * 32 + cx;
@@ -443,6 +451,7 @@ inline int colsum_splits(int M, int N) {
 // ------------------------------------------------------------------------------------------------
 __global__ void cast_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst,
                             size_t n) {
+  pdl_enter();  // previous kernel finished, its writes are visible
   const size_t i = (size_t(blockIdx.x) * blockDim.x + threadIdx.x) * 8;
   if (i + 8 <= n) {
     const float4 a = __ldg(reinterpret_cast<const float4*>(src + i));
@@ -467,6 +476,7 @@ __device__ __forceinline__ uint64_t mix64(uint64_t z) {
 }
 __global__ void synth_tokens_kernel(int64_t* __restrict__ ids, int64_t* __restrict__ labels,
                                     int rows, int T, int vocab, uint64_t seed, uint64_t row0) {
+  pdl_enter();  // previous kernel finished, its writes are visible
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= (long long)rows * T) return;
   const int r = int(idx / T), t = int(idx - (long long)r * T);
@@ -488,8 +498,7 @@ extern "C" int llmtrain_b200_synthetic_tokens(int64_t* ids, int64_t* labels, int
   B200_REQUIRE(vocab > 0 && rows >= 0 && T > 0, "synthetic_tokens: bad shape");
   if (rows == 0) return 0;
   const long long n = (long long)rows * T;
-  ew::synth_tokens_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, stream>>>(
-      ids, labels, rows, T, vocab, seed, first_row);
+  B200_LAUNCH((ew::synth_tokens_kernel), static_cast<unsigned>((n + 255) / 256), 256, 0, stream, ids, labels, rows, T, vocab, seed, first_row);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   return 0;
@@ -501,9 +510,7 @@ extern "C" int llmtrain_b200_embed_fwd(const int64_t* ids, const void* wte, cons
   B200_REQUIRE(d % 8 == 0, "embed: d must be a multiple of 8");
   const int rows = B * T;
   if (rows == 0) return 0;
-  ew::embed_fwd_kernel<<<ceil_div(rows, 8), 256, 0, stream>>>(
-      ids, static_cast<const __nv_bfloat16*>(wte), static_cast<const __nv_bfloat16*>(wpe),
-      static_cast<__nv_bfloat16*>(x), rows, T, d, vocab);
+  B200_LAUNCH((ew::embed_fwd_kernel), ceil_div(rows, 8), 256, 0, stream, ids, static_cast<const __nv_bfloat16*>(wte), static_cast<const __nv_bfloat16*>(wpe), static_cast<__nv_bfloat16*>(x), rows, T, d, vocab);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   return 0;
@@ -515,12 +522,10 @@ extern "C" int llmtrain_b200_embed_bwd(const int64_t* ids, const void* dx, float
   B200_REQUIRE(d % 8 == 0, "embed: d must be a multiple of 8");
   const int rows = B * T;
   if (rows == 0) return 0;
-  ew::embed_bwd_wte_kernel<<<ceil_div(rows, 8), 256, 0, stream>>>(
-      ids, static_cast<const __nv_bfloat16*>(dx), dwte, rows, d, vocab);
+  B200_LAUNCH((ew::embed_bwd_wte_kernel), ceil_div(rows, 8), 256, 0, stream, ids, static_cast<const __nv_bfloat16*>(dx), dwte, rows, d, vocab);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
-  ew::embed_bwd_wpe_kernel<<<ceil_div(T * (d / 4), 256), 256, 0, stream>>>(
-      static_cast<const __nv_bfloat16*>(dx), dwpe, B, T, d);
+  B200_LAUNCH((ew::embed_bwd_wpe_kernel), ceil_div(T * (d / 4), 256), 256, 0, stream, static_cast<const __nv_bfloat16*>(dx), dwpe, B, T, d);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   return 0;
@@ -547,22 +552,18 @@ extern "C" int llmtrain_b200_cross_entropy(void* logits, const int64_t* labels,
     }
     const int grid = rows < sm_count() ? rows : sm_count();
     if (write_grad)
-      ew::ce_row_kernel<true><<<grid, ew::CE_ROW_THREADS, smem, stream>>>(
-          lg, labels, row_valid, loss_rows, rows, V, ldv, grad_scale);
+      B200_LAUNCH((ew::ce_row_kernel<true>), grid, ew::CE_ROW_THREADS, smem, stream, lg, labels, row_valid, loss_rows, rows, V, ldv, grad_scale);
     else
-      ew::ce_row_kernel<false><<<grid, ew::CE_ROW_THREADS, smem, stream>>>(
-          lg, labels, row_valid, loss_rows, rows, V, ldv, grad_scale);
+      B200_LAUNCH((ew::ce_row_kernel<false>), grid, ew::CE_ROW_THREADS, smem, stream, lg, labels, row_valid, loss_rows, rows, V, ldv, grad_scale);
   } else if (write_grad) {
-    ew::ce_kernel<true><<<rows, ew::CE_THREADS, 0, stream>>>(lg, labels, row_valid, loss_rows, V,
-                                                             ldv, grad_scale);
+    B200_LAUNCH((ew::ce_kernel<true>), rows, ew::CE_THREADS, 0, stream, lg, labels, row_valid, loss_rows, V, ldv, grad_scale);
   } else {
-    ew::ce_kernel<false><<<rows, ew::CE_THREADS, 0, stream>>>(lg, labels, row_valid, loss_rows, V,
-                                                              ldv, grad_scale);
+    B200_LAUNCH((ew::ce_kernel<false>), rows, ew::CE_THREADS, 0, stream, lg, labels, row_valid, loss_rows, V, ldv, grad_scale);
   }
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   if (loss_acc != nullptr) {
-    ew::loss_reduce_kernel<<<1, 1024, 0, stream>>>(loss_rows, rows, loss_scale, loss_acc);
+    B200_LAUNCH((ew::loss_reduce_kernel), 1, 1024, 0, stream, loss_rows, rows, loss_scale, loss_acc);
     B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   }
@@ -580,12 +581,10 @@ extern "C" int llmtrain_b200_bias_grad(const void* dy, int ld, int M, int N, flo
   const int splits = ew::colsum_splits(M, N);
   B200_REQUIRE(scratch_bytes >= size_t(splits) * N * sizeof(float), "bias_grad: scratch too small");
   dim3 grid(ceil_div(N, ew::CS_COLS), splits);
-  ew::colsum_partial_kernel<<<grid, ew::CS_WARPS * 32, 0, stream>>>(
-      static_cast<const __nv_bfloat16*>(dy), ld, M, N, static_cast<float*>(scratch));
+  B200_LAUNCH((ew::colsum_partial_kernel), grid, ew::CS_WARPS * 32, 0, stream, static_cast<const __nv_bfloat16*>(dy), ld, M, N, static_cast<float*>(scratch));
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
-  ew::colsum_finish_kernel<<<ceil_div(N, 32), 256, 0, stream>>>(static_cast<float*>(scratch),
-                                                                 splits, N, dbias);
+  B200_LAUNCH((ew::colsum_finish_kernel), ceil_div(N, 32), 256, 0, stream, static_cast<float*>(scratch), splits, N, dbias);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   return 0;
@@ -595,8 +594,7 @@ extern "C" int llmtrain_b200_cast_f32_to_bf16(const float* src, void* dst, size_
                                               cudaStream_t stream) {
   if (n == 0) return 0;
   const size_t threads = (n + 7) / 8;
-  ew::cast_kernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, stream>>>(
-      src, static_cast<__nv_bfloat16*>(dst), n);
+  B200_LAUNCH((ew::cast_kernel), static_cast<unsigned>((threads + 255) / 256), 256, 0, stream, src, static_cast<__nv_bfloat16*>(dst), n);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   return 0;
@@ -679,11 +677,10 @@ extern "C" int llmtrain_b200_bias_grad_noalloc(const void* dy, int ld, int M, in
   float* partials = nullptr;
   if (ew::noalloc_scratch(&partials)) return 1;
   dim3 grid(ceil_div(N, ew::CS_COLS), splits);
-  ew::colsum_partial_kernel<<<grid, ew::CS_WARPS * 32, 0, stream>>>(
-      static_cast<const __nv_bfloat16*>(dy), ld, M, N, partials);
+  B200_LAUNCH((ew::colsum_partial_kernel), grid, ew::CS_WARPS * 32, 0, stream, static_cast<const __nv_bfloat16*>(dy), ld, M, N, partials);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
-  ew::colsum_finish_kernel<<<ceil_div(N, 32), 256, 0, stream>>>(partials, splits, N, dbias);
+  B200_LAUNCH((ew::colsum_finish_kernel), ceil_div(N, 32), 256, 0, stream, partials, splits, N, dbias);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   return 0;

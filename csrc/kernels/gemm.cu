@@ -253,6 +253,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   if (CTAS == 2) cluster_sync_all();  // the peer's barriers exist before anything signals them
   else __syncthreads();
   tc_fence_after_sync();
+  pdl_enter();  // barrier init + TMEM allocation above overlapped the previous kernel's tail
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
@@ -583,23 +584,8 @@ int launch(const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tC,
   const int tiles = ceil_div(p.M, BM * CTAS) * ceil_div(p.N, BN) * p.k_splits;
   const int slots = sm_count() / CTAS;  // CTAs, or CTA pairs, that can be resident
   const int grid = (tiles < slots ? tiles : slots) * CTAS;
-  if (CTAS == 1) {
-    kern<<<grid, NUM_THREADS, kSmem, stream>>>(tA, tB, tC, tC2, p);
-  } else {
-    cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3(grid);
-    cfg.blockDim = dim3(NUM_THREADS);
-    cfg.dynamicSmemBytes = kSmem;
-    cfg.stream = stream;
-    cudaLaunchAttribute attr{};
-    attr.id = cudaLaunchAttributeClusterDimension;
-    attr.val.clusterDim.x = CTAS;
-    attr.val.clusterDim.y = 1;
-    attr.val.clusterDim.z = 1;
-    cfg.attrs = &attr;
-    cfg.numAttrs = 1;
-    B200_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, tA, tB, tC, tC2, p));
-  }
+  B200_CHECK_CUDA(launch_kernel(kern, dim3(grid), dim3(NUM_THREADS), kSmem, stream, CTAS, tA, tB, tC,
+                                tC2, p));
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   return 0;

@@ -43,6 +43,7 @@ __global__ void __launch_bounds__(WARPS * 32)
 fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
            const float* __restrict__ beta, __nv_bfloat16* __restrict__ y,
            float* __restrict__ mean_out, float* __restrict__ rstd_out, int rows, int d) {
+  pdl_enter();  // previous kernel finished, its writes are visible
   const int lane = threadIdx.x & 31;
   const int nvec = d >> 3;
   float g[NV][8], bt[NV][8];
@@ -135,6 +136,7 @@ bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict
            const float* __restrict__ rstd, __nv_bfloat16* __restrict__ dresid,
            float* __restrict__ partial /* [gridDim.x][NS][d], NS = COLSUM ? 3 : 2 */, int rows,
            int d) {
+  pdl_enter();  // previous kernel finished, its writes are visible
   constexpr int NS = COLSUM ? 3 : 2;
   extern __shared__ float sh[];  // [WARPS][NS][d]
   float dc[COLSUM ? NV : 1][8];
@@ -262,6 +264,7 @@ __global__ void __launch_bounds__(FIN_COLS * FIN_LANES)
 finish_kernel(const float* __restrict__ partial, int nparts, int d, int ns,
               float* __restrict__ dgamma, float* __restrict__ dbeta,
               float* __restrict__ dcolsum) {
+  pdl_enter();  // previous kernel finished, its writes are visible
   __shared__ float sh[FIN_LANES][FIN_COLS];
   const int cx = threadIdx.x & (FIN_COLS - 1), py = threadIdx.x / FIN_COLS;
   const int idx = blockIdx.x * FIN_COLS + cx;
@@ -311,8 +314,8 @@ extern "C" int llmtrain_b200_layernorm_fwd(const void* x, const float* gamma, co
     }                                                                                           \
     int grid = per_sm * sm_count();                                                             \
     if (grid > need) grid = need;                                                               \
-    ln::fwd_kernel<NV><<<grid, ln::WARPS * 32, 0, stream>>>(x_, gamma, beta, y_, mean, rstd,    \
-                                                            rows, d);                           \
+    B200_LAUNCH((ln::fwd_kernel<NV>), grid, ln::WARPS * 32, 0, stream, x_, gamma, beta, y_,     \
+                mean, rstd, rows, d);                                                           \
     break;                                                                                      \
   }
   switch (ceil_div(d, 256)) {
@@ -359,14 +362,13 @@ extern "C" int llmtrain_b200_layernorm_bwd(const void* dy, const void* x, const 
                                            200 * 1024));                                       \
       configured = true;                                                                       \
     }                                                                                          \
-    if (ns == 3)                                                                               \
-      ln::bwd_kernel<NV, true><<<grid, ln::WARPS * 32, smem, stream>>>(dy_, x_, gamma, mean,   \
-                                                                       rstd, dr_, part_, rows, \
-                                                                       d);                     \
-    else                                                                                       \
-      ln::bwd_kernel<NV, false><<<grid, ln::WARPS * 32, smem, stream>>>(dy_, x_, gamma, mean,  \
-                                                                        rstd, dr_, part_,      \
-                                                                        rows, d);              \
+    if (ns == 3) {                                                                             \
+      B200_LAUNCH((ln::bwd_kernel<NV, true>), grid, ln::WARPS * 32, smem, stream, dy_, x_,     \
+                  gamma, mean, rstd, dr_, part_, rows, d);                                     \
+    } else {                                                                                   \
+      B200_LAUNCH((ln::bwd_kernel<NV, false>), grid, ln::WARPS * 32, smem, stream, dy_, x_,    \
+                  gamma, mean, rstd, dr_, part_, rows, d);                                     \
+    }                                                                                          \
     break;                                                                                     \
   }
   switch (nv) {
@@ -377,8 +379,8 @@ extern "C" int llmtrain_b200_layernorm_bwd(const void* dy, const void* x, const 
 #undef B200_LN_BWD
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
-  ln::finish_kernel<<<ceil_div(ns * d, ln::FIN_COLS), ln::FIN_COLS * ln::FIN_LANES, 0, stream>>>(
-      static_cast<float*>(scratch), grid, d, ns, dgamma, dbeta, dcolsum);
+  B200_LAUNCH((ln::finish_kernel), ceil_div(ns * d, ln::FIN_COLS), ln::FIN_COLS * ln::FIN_LANES, 0,
+              stream, static_cast<float*>(scratch), grid, d, ns, dgamma, dbeta, dcolsum);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   return 0;

@@ -40,6 +40,7 @@ __device__ __forceinline__ float block_sum(float v, float* red) {
 // partial[b] = sum over this CTA's grid-stride slice of g^2  (fixed assignment => deterministic)
 __global__ void __launch_bounds__(THREADS)
 sumsq_partial_kernel(const float* __restrict__ g, size_t n, float* __restrict__ partial) {
+  pdl_enter();  // previous kernel finished, its writes are visible
   __shared__ float red[32];
   float acc = 0.f;
   const size_t n4 = n >> 2;
@@ -61,6 +62,7 @@ sumsq_partial_kernel(const float* __restrict__ g, size_t n, float* __restrict__ 
 __global__ void __launch_bounds__(THREADS)
 sumsq_finish_kernel(const float* __restrict__ partial, int nparts, float* __restrict__ out,
                     int accumulate) {
+  pdl_enter();  // previous kernel finished, its writes are visible
   __shared__ float red[32];
   float acc = 0.f;
   for (int i = threadIdx.x; i < nparts; i += blockDim.x) acc += partial[i];
@@ -80,6 +82,7 @@ adamw_kernel(float* __restrict__ p, float* __restrict__ m, float* __restrict__ v
              float* __restrict__ g, __nv_bfloat16* __restrict__ p16, size_t n,
              const float* __restrict__ sumsq, float* __restrict__ norm_out, AdamArgs a,
              int zero_grad) {
+  pdl_enter();  // previous kernel finished, its writes are visible
   float coef = a.grad_scale;
   if (sumsq != nullptr) {
     const float norm = sqrtf(sumsq[0]) * a.grad_scale;
@@ -152,12 +155,10 @@ extern "C" int llmtrain_b200_grad_sumsq(const float* g, size_t n, float* out, in
   B200_REQUIRE((reinterpret_cast<uintptr_t>(g) & 15) == 0, "grad_sumsq: g must be 16-byte aligned");
   const int grid = optim::sumsq_grid(n);
   B200_REQUIRE(scratch_bytes >= size_t(grid) * sizeof(float), "grad_sumsq: scratch too small");
-  optim::sumsq_partial_kernel<<<grid, optim::THREADS, 0, stream>>>(g, n,
-                                                                   static_cast<float*>(scratch));
+  B200_LAUNCH((optim::sumsq_partial_kernel), grid, optim::THREADS, 0, stream, g, n, static_cast<float*>(scratch));
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
-  optim::sumsq_finish_kernel<<<1, optim::THREADS, 0, stream>>>(static_cast<float*>(scratch), grid,
-                                                               out, accumulate);
+  B200_LAUNCH((optim::sumsq_finish_kernel), 1, optim::THREADS, 0, stream, static_cast<float*>(scratch), grid, out, accumulate);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   return 0;
@@ -182,8 +183,7 @@ extern "C" int llmtrain_b200_adamw(float* p, float* m, float* v, float* g, void*
   const size_t want = (n / 4 + optim::THREADS - 1) / optim::THREADS;
   const size_t cap = size_t(8 * sm_count());
   const int grid = static_cast<int>(want < cap ? (want < 1 ? 1 : want) : cap);
-  optim::adamw_kernel<<<grid, optim::THREADS, 0, stream>>>(
-      p, m, v, g, static_cast<__nv_bfloat16*>(p_bf16), n, sumsq, norm_out, a, zero_grad);
+  B200_LAUNCH((optim::adamw_kernel), grid, optim::THREADS, 0, stream, p, m, v, g, static_cast<__nv_bfloat16*>(p_bf16), n, sumsq, norm_out, a, zero_grad);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   return 0;
