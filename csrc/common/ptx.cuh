@@ -448,6 +448,35 @@ __device__ __forceinline__ float fast_exp2(float x) {
   return y;
 }
 
+// ----------------------------------------------------------------------------------------------
+// Packed fp32 pairs (Blackwell FFMA2: one instruction, two independent fp32 operations).
+// ----------------------------------------------------------------------------------------------
+struct f32x2 { uint64_t v; };
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
+  f32x2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r.v) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack2(f32x2 a, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(a.v));
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+  f32x2 r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r.v) : "l"(a.v), "l"(b.v), "l"(c.v));
+  return r;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v));
+  return r;
+}
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v));
+  return r;
+}
+__device__ __forceinline__ f32x2 splat2(float c) { return pack2(c, c); }
+
 // 128-byte swizzle: byte offset inside a tile whose rows are 128 B and whose base is 1024 B
 // aligned.  The 16-byte chunk index (bits 4..6) is XORed with the row index mod 8 (bits 7..9).
 __device__ __forceinline__ uint32_t swizzle128(uint32_t byte_off) {

@@ -142,35 +142,9 @@ __device__ __forceinline__ GeluPair gelu_erf_both(float x) {
   return {x * n.cdf, fmaf(x * 0.7978845608028654f, n.half_e, n.cdf)};  // phi = 2*half_e/sqrt(2pi)
 }
 
-// Packed fp32 pairs (Blackwell FFMA2: one instruction, two independent fp32 FMAs).  The GELU
-// epilogue is issue-bound — two epilogue warps per scheduler, ~27 instructions per element — so
-// evaluating two adjacent columns per instruction is worth ~40% of its issue slots.
-struct f32x2 { uint64_t v; };
-__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
-  f32x2 r;
-  asm("mov.b64 %0, {%1, %2};" : "=l"(r.v) : "f"(lo), "f"(hi));
-  return r;
-}
-__device__ __forceinline__ void unpack2(f32x2 a, float& lo, float& hi) {
-  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(a.v));
-}
-__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
-  f32x2 r;
-  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r.v) : "l"(a.v), "l"(b.v), "l"(c.v));
-  return r;
-}
-__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
-  f32x2 r;
-  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v));
-  return r;
-}
-__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
-  f32x2 r;
-  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v));
-  return r;
-}
-__device__ __forceinline__ f32x2 splat2(float c) { return pack2(c, c); }
-
+// The pair version below uses packed fp32 (f32x2, ptx.cuh): the GELU epilogue is issue-bound — two
+// epilogue warps per scheduler, ~27 instructions per element — so evaluating two adjacent columns
+// per instruction is worth ~40% of its issue slots.
 // Same arithmetic as gelu_erf_both for the pair (x0, x1); y and dy come back packed.
 __device__ __forceinline__ void gelu_erf_both2(float x0, float x1, f32x2& y, f32x2& dy) {
   constexpr float kP = 0.3275911f * 0.70710678118654752f;
