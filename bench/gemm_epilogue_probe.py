@@ -42,6 +42,9 @@ def main() -> int:
     print("fc gelu    us", round(t(lambda: G.gemm(G.NT, G.EPI_BIAS_GELU, x, wfc, act, c2=pre, bias=bias)), 1))
     print("proj dgrad us", round(t(lambda: G.gemm(G.NN, G.EPI_BIAS, dres, wproj, dfc)), 1))
     print("proj dgelu us", round(t(lambda: G.gemm(G.NN, G.EPI_DGELU, dres, wproj, dfc, r=pre)), 1))
+    cs = torch.zeros(F, device="cuda")
+    print("proj dgelu+colsum us",
+          round(t(lambda: G.gemm_colsum(G.NN, G.EPI_DGELU, dres, wproj, dfc, cs, r=pre)), 1))
     return 0
 
 

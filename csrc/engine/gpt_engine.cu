@@ -313,8 +313,10 @@ int backward(Gpt& g, cudaStream_t s, BucketHook hook = nullptr, void* hook_ctx =
       dproj = dmask;
     }
     B200_TRY(linear_wgrad(M, d, F, dproj, d, v.bf(a.fch_act), v.grad(o.proj_w), s));
-    B200_TRY(linear_dgrad(3, M, d, F, dproj, v.w(o.proj_w), dfc, v.bf(a.fch_pre), s));
-    B200_TRY(llmtrain_b200_bias_grad(dfc, F, M, F, v.grad(o.fc_b), red, red_bytes, st));
+    // dfc = (dproj @ Wproj) o gelu'(pre); its column sums (= fc's bias gradient) come out of the
+    // same epilogue.
+    B200_TRY(llmtrain_b200_gemm_colsum(1, 3, M, F, d, dproj, d, v.w(o.proj_w), F, dfc, F, nullptr,
+                                       v.bf(a.fch_pre), F, v.grad(o.fc_b), st));
     B200_TRY(linear_wgrad(M, F, d, dfc, F, v.bf(a.ln2), v.grad(o.fc_w), s));
     B200_TRY(linear_dgrad(0, M, F, d, dfc, v.w(o.fc_w), dtmp, nullptr, s));
     B200_TRY(llmtrain_b200_layernorm_bwd(dtmp, v.bf(a.resid1), v.p(o.ln2_w), v.f32(a.ln2_mean),
@@ -330,17 +332,11 @@ int backward(Gpt& g, cudaStream_t s, BucketHook hook = nullptr, void* hook_ctx =
     }
     B200_TRY(linear_wgrad(M, d, d, dout, d, v.bf(a.atty), v.grad(o.out_w), s));
     B200_TRY(linear_dgrad(0, M, d, d, dout, v.w(o.out_w), dtmp, nullptr, s));
-    if (drop) {
-      B200_TRY(llmtrain_b200_attention_bwd_dropout(
-          v.bf(a.qkv), v.bf(a.atty), dtmp, v.f32(a.lse), g.key_mask, dqkv,
-          g.act + g.a_attn_scratch, g.attn_scratch_bytes, B, T, g.H, hd, dp, seed, off,
-          drop_site(l, 0), st));
-    } else {
-      B200_TRY(llmtrain_b200_attention_bwd(v.bf(a.qkv), v.bf(a.atty), dtmp, v.f32(a.lse),
-                                           g.key_mask, dqkv, g.act + g.a_attn_scratch,
-                                           g.attn_scratch_bytes, B, T, g.H, hd, st));
-    }
-    B200_TRY(llmtrain_b200_bias_grad(dqkv, 3 * d, M, 3 * d, v.grad(o.qkv_b), red, red_bytes, st));
+    // dqkv and, fused, qkv_proj's bias gradient (column sums of dqkv)
+    B200_TRY(llmtrain_b200_attention_bwd_fused(
+        v.bf(a.qkv), v.bf(a.atty), dtmp, v.f32(a.lse), g.key_mask, dqkv, v.grad(o.qkv_b),
+        g.act + g.a_attn_scratch, g.attn_scratch_bytes, B, T, g.H, hd, drop ? dp : 0.f, seed, off,
+        drop_site(l, 0), st));
     B200_TRY(linear_wgrad(M, 3 * d, d, dqkv, 3 * d, v.bf(a.ln1), v.grad(o.qkv_w), s));
     B200_TRY(linear_dgrad(0, M, 3 * d, d, dqkv, v.w(o.qkv_w), dtmp, nullptr, s));
     B200_TRY(llmtrain_b200_layernorm_bwd(dtmp, x_in, v.p(o.ln1_w), v.f32(a.ln1_mean),

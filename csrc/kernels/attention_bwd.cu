@@ -58,6 +58,7 @@ struct Params {
   const float* dsum; // [B, H, T]   D = rowsum(dO o O)
   const uint8_t* key_mask;
   float* dq32;       // [B, T, H*64] fp32 accumulator (zeroed by the launcher)
+  float* dbias;      // optional [3*H*64]: += column sums of dqkv (bias gradient of qkv_proj)
   DropoutParams drop;  // attention-probability dropout; threshold 0 = off
   int t_pad;           // T rounded up to 8: row pitch of the mask's element index
 };
@@ -386,6 +387,37 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
     tc_fence_before_sync();
     fence_proxy_async_smem();
     named_bar_sync(1, 256);
+    if (p.dbias != nullptr) {
+      // qkv_proj's bias gradient is the column sum of dqkv: take the k and v thirds from the two
+      // bf16 tiles just staged (warp w: rows 16w..16w+15, lane l: columns 2l, 2l+1; conflict-free
+      // in the swizzled layout), combine the eight warps through the idle second P buffer, and
+      // add 128 values per CTA to global memory.  Rows past T hold exact zeros.  The q third comes
+      // from dq_convert_kernel.
+      float* red = reinterpret_cast<float*>(smem + OFF_P + PDS_BYTES);  // [8][2][64]
+#pragma unroll
+      for (int which = 0; which < 2; ++which) {
+        const uint8_t* stage = smem + (which == 0 ? OFF_P : OFF_DS);
+        float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+        for (int rr = 0; rr < 16; ++rr) {
+          const uint32_t row = uint32_t(warp * 16 + rr);
+          const uint32_t off = row * 128u + ((uint32_t(lane >> 2) ^ (row & 7u)) << 4) +
+                               (uint32_t(lane & 3) << 2);
+          const float2 f = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(stage + off));
+          s0 += f.x;
+          s1 += f.y;
+        }
+        *reinterpret_cast<float2*>(red + (warp * 2 + which) * 64 + 2 * lane) = make_float2(s0, s1);
+      }
+      named_bar_sync(1, 256);
+      if (threadIdx.x < 128) {
+        const int which = threadIdx.x >> 6, col = threadIdx.x & 63;
+        float t = 0.f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) t += red[(w * 2 + which) * 64 + col];
+        atomicAdd(p.dbias + (which == 0 ? 2 * d : d) + h * HD + col, t);
+      }
+    }
     if (threadIdx.x == 0) {
       tma_store_3d(&tmDQKV, smem + OFF_P, 2 * d + h * HD, kv0, b);   // dV
       tma_store_3d(&tmDQKV, smem + OFF_DS, d + h * HD, kv0, b);      // dK
@@ -432,18 +464,51 @@ __global__ void dsum_kernel(const __nv_bfloat16* __restrict__ dO,
   }
 }
 
-// dqkv[row, 0:d] = bf16(dq32[row, :])   (q third of the fused gradient buffer)
+// dqkv[row, 0:d] = bf16(dq32[row, :])   (q third of the fused gradient buffer), and optionally
+// dbias[0:d] += column sums of the bf16 result (q third of qkv_proj's bias gradient).
+// blockDim = (d/8) * nsub: thread (g, sub) owns 8 columns and every nsub-th row of the block's slab.
+constexpr int DQ_SLAB_ROWS = 64;
 __global__ void dq_convert_kernel(const float* __restrict__ dq32, __nv_bfloat16* __restrict__ dqkv,
-                                  int rows, int d) {
+                                  float* __restrict__ dbias, int rows, int d, int nsub) {
   pdl_enter();  // previous kernel finished, its writes are visible
-  const size_t idx = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  extern __shared__ float dq_red[];  // [nsub][d] partial column sums (only with dbias)
   const int per_row = d >> 3;
-  if (idx >= size_t(rows) * per_row) return;
-  const int row = int(idx / per_row), c = int(idx - size_t(row) * per_row);
-  const float4 a = __ldg(reinterpret_cast<const float4*>(dq32 + size_t(row) * d) + 2 * c);
-  const float4 b = __ldg(reinterpret_cast<const float4*>(dq32 + size_t(row) * d) + 2 * c + 1);
-  *reinterpret_cast<uint4*>(dqkv + size_t(row) * 3 * d + c * 8) = make_uint4(
-      pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w), pack_bf16x2(b.x, b.y), pack_bf16x2(b.z, b.w));
+  const int g = threadIdx.x % per_row, sub = threadIdx.x / per_row;
+  const int row0 = blockIdx.x * DQ_SLAB_ROWS;
+  const int row_end = min(rows, row0 + DQ_SLAB_ROWS);
+  float acc[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+#pragma unroll 4
+  for (int row = row0 + sub; row < row_end; row += nsub) {
+    const float4 a = __ldg(reinterpret_cast<const float4*>(dq32 + size_t(row) * d) + 2 * g);
+    const float4 b = __ldg(reinterpret_cast<const float4*>(dq32 + size_t(row) * d) + 2 * g + 1);
+    const uint4 o = make_uint4(pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w), pack_bf16x2(b.x, b.y),
+                               pack_bf16x2(b.z, b.w));
+    *reinterpret_cast<uint4*>(dqkv + size_t(row) * 3 * d + g * 8) = o;
+    if (dbias != nullptr) {
+      const uint32_t w[4] = {o.x, o.y, o.z, o.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 f = unpack_bf16x2(w[j]);
+        acc[2 * j] += f.x;
+        acc[2 * j + 1] += f.y;
+      }
+    }
+  }
+  if (dbias == nullptr) return;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) dq_red[sub * d + g * 8 + j] = acc[j];
+  __syncthreads();
+  // blocks finish together: start each one at a different column so they do not all queue on the
+  // same cache lines
+  const int rot = int((blockIdx.x * 67u) % unsigned(d));
+  for (int i = threadIdx.x; i < d; i += blockDim.x) {
+    const int c = (i + rot) % d;
+    float t = 0.f;
+    for (int k = 0; k < nsub; ++k) t += dq_red[k * d + c];
+    atomicAdd(dbias + c, t);
+  }
 }
 
 }  // namespace attn_bwd
@@ -460,7 +525,7 @@ extern "C" size_t llmtrain_b200_attention_bwd_scratch_bytes(int B, int T, int H,
 static int attention_bwd_impl(const void* qkv, const void* out, const void* dout, const float* lse,
                               const uint8_t* key_mask, void* dqkv, void* scratch,
                               size_t scratch_bytes, int B, int T, int H, int head_dim,
-                              const DropoutParams& drop, cudaStream_t stream) {
+                              const DropoutParams& drop, float* dbias, cudaStream_t stream) {
   namespace ab = attn_bwd;
   B200_REQUIRE(head_dim == ab::HD, "attention_bwd: specialised for head_dim 64");
   B200_REQUIRE(B > 0 && T > 0 && H > 0, "attention_bwd: empty problem");
@@ -496,6 +561,7 @@ static int attention_bwd_impl(const void* qkv, const void* out, const void* dout
   p.dsum = dsum;
   p.key_mask = key_mask;
   p.dq32 = dq32;
+  p.dbias = dbias;
   p.drop = drop;
   p.t_pad = (T + 7) & ~7;
   static bool configured = false;
@@ -514,9 +580,13 @@ static int attention_bwd_impl(const void* qkv, const void* out, const void* dout
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
 
-  const size_t n = size_t(rows) * (d / 8);
-  B200_LAUNCH((ab::dq_convert_kernel), static_cast<unsigned>((n + 255) / 256), 256, 0, stream, dq32,
-              static_cast<__nv_bfloat16*>(dqkv), rows, d);
+  {
+    const int per_row = d / 8;
+    const int nsub = per_row >= 256 ? 1 : 256 / per_row;
+    const size_t red_bytes = dbias != nullptr ? size_t(nsub) * d * sizeof(float) : 0;
+    B200_LAUNCH((ab::dq_convert_kernel), ceil_div(rows, ab::DQ_SLAB_ROWS), per_row * nsub, red_bytes,
+                stream, dq32, static_cast<__nv_bfloat16*>(dqkv), dbias, rows, d, nsub);
+  }
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   return 0;
@@ -528,7 +598,7 @@ extern "C" int llmtrain_b200_attention_bwd(const void* qkv, const void* out, con
                                            void* scratch, size_t scratch_bytes, int B, int T,
                                            int H, int head_dim, cudaStream_t stream) {
   return attention_bwd_impl(qkv, out, dout, lse, key_mask, dqkv, scratch, scratch_bytes, B, T, H,
-                            head_dim, make_dropout(0.f, 0, 0, 0), stream);
+                            head_dim, make_dropout(0.f, 0, 0, 0), nullptr, stream);
 }
 
 // Backward of llmtrain_b200_attention_fwd_dropout: pass the same (p, seed, offset, site).
@@ -541,5 +611,20 @@ extern "C" int llmtrain_b200_attention_bwd_dropout(const void* qkv, const void* 
                                                    cudaStream_t stream) {
   B200_REQUIRE(p >= 0.f && p < 1.f, "attention_bwd_dropout: p must be in [0, 1)");
   return attention_bwd_impl(qkv, out, dout, lse, key_mask, dqkv, scratch, scratch_bytes, B, T, H,
-                            head_dim, make_dropout(p, seed, offset, site), stream);
+                            head_dim, make_dropout(p, seed, offset, site), nullptr, stream);
+}
+
+// Everything at once (what the training engine calls): optional dropout (p = 0: none) and, when
+// dbias_qkv is not NULL, dbias_qkv[3d] += column sums of dqkv — qkv_proj's bias gradient
+// (`gpt.py:27`) without a separate pass over dqkv.  fp32 atomics: summation order is not fixed.
+extern "C" int llmtrain_b200_attention_bwd_fused(const void* qkv, const void* out, const void* dout,
+                                                 const float* lse, const uint8_t* key_mask,
+                                                 void* dqkv, float* dbias_qkv, void* scratch,
+                                                 size_t scratch_bytes, int B, int T, int H,
+                                                 int head_dim, float p, uint64_t seed,
+                                                 uint64_t offset, uint32_t site,
+                                                 cudaStream_t stream) {
+  B200_REQUIRE(p >= 0.f && p < 1.f, "attention_bwd_fused: p must be in [0, 1)");
+  return attention_bwd_impl(qkv, out, dout, lse, key_mask, dqkv, scratch, scratch_bytes, B, T, H,
+                            head_dim, make_dropout(p, seed, offset, site), dbias_qkv, stream);
 }

@@ -89,6 +89,8 @@ struct Params {
   int ldc;
   int group_m;             // rasterisation: row-tiles per band (>= #row-tiles => M fastest)
   DropoutParams drop;      // kBiasDropResid only
+  float* colsum;           // optional, kDGelu / kBias: colsum[n] += sum_m C[m, n]  (bias gradient
+                           // of the layer that produced this GEMM's output gradient)
 };
 
 // Tile order.  Consecutive tiles walk `group_m` row-tiles for one column-tile, then the next
@@ -498,6 +500,27 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             tma_store_2d(&tmC, stg, col0, m0 + quarter * 32);
             tma_store_commit();
           }
+          if ((EPI == kDGelu || EPI == kBias) && p.colsum != nullptr) {
+            // Column sums of the bf16 tile just staged (= the bias gradient of the layer whose
+            // output gradient this GEMM produces), read back from shared memory: lane l owns
+            // columns 2l, 2l+1 and walks the warp's 32 rows — conflict-free in the swizzled layout
+            // — then adds its two sums to global memory.  Rows past M hold exact zeros (TMA
+            // zero-fills A), so they contribute nothing.  This replaces a separate pass that
+            // re-read the whole [M, N] tensor from HBM.
+            float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+            for (int rr = 0; rr < 32; ++rr) {
+              const uint32_t off = uint32_t(rr) * 128u +
+                                   ((uint32_t(lane >> 2) ^ uint32_t(rr & 7)) << 4) +
+                                   (uint32_t(lane & 3) << 2);
+              const float2 f = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(stg + off));
+              s0 += f.x;
+              s1 += f.y;
+            }
+            const int cc = col0 + 2 * lane;
+            if (cc < p.N) atomicAdd(p.colsum + cc, s0);
+            if (cc + 1 < p.N) atomicAdd(p.colsum + cc + 1, s1);
+          }
           }
           if (EPI == kBiasGelu) {
             // Second output, gelu'(x), through its own staging buffer: both TMA stores of this
@@ -596,10 +619,13 @@ using namespace b200::gemm;
 static int gemm_dispatch(int layout, int epilogue, int M, int N, int K, const void* A, int lda,
                          const void* B, int ldb, void* C, int ldc, void* C2, int ldc2,
                          const float* bias, const void* R, int ldr, const DropoutParams& drop,
-                         cudaStream_t stream) {
+                         float* colsum, cudaStream_t stream) {
   B200_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem");
   Params p{};
   p.drop = drop;
+  p.colsum = colsum;
+  B200_REQUIRE(colsum == nullptr || ((epilogue == kDGelu || epilogue == kBias) && !kDirectStore),
+               "gemm: column sums are available with the plain and dGELU epilogues only");
   p.M = M; p.N = N; p.K = K; p.k_splits = 1;
   p.bias = bias;
   p.R = static_cast<const __nv_bfloat16*>(R);
@@ -625,6 +651,14 @@ static int gemm_dispatch(int layout, int epilogue, int M, int N, int K, const vo
     }();
     const bool big_a = size_t(M) * size_t(K) * 2 > (size_t(40) << 20);
     int g = forced > 0 ? forced : (big_a ? 8 : num_m);
+    // Fused column sums add into ONE row of N floats: with M-fastest order every resident CTA
+    // would hit the same few cache lines at once (measured: +22 us on the 72 us dGELU GEMM).
+    // Narrow bands put the CTAs of a wave on different column tiles.
+    static const int colsum_band = [] {
+      const char* e = std::getenv("LLMTRAIN_GEMM_COLSUM_BAND");
+      return e == nullptr ? 4 : std::atoi(e);
+    }();
+    if (colsum != nullptr && forced <= 0 && g > colsum_band) g = colsum_band;
     p.group_m = g < num_m ? g : num_m;
   }
   // K-major operand: memory [rows, K]; box = [tile rows, 64].  MN-major: memory [K, rows];
@@ -673,7 +707,19 @@ extern "C" int llmtrain_b200_gemm(int layout, int epilogue, int M, int N, int K,
                                   cudaStream_t stream) {
   B200_REQUIRE(epilogue != kBiasDropResid, "gemm: use llmtrain_b200_gemm_dropout_resid");
   return gemm_dispatch(layout, epilogue, M, N, K, A, lda, B, ldb, C, ldc, C2, ldc2, bias, R, ldr,
-                       make_dropout(0.f, 0, 0, 0), stream);
+                       make_dropout(0.f, 0, 0, 0), nullptr, stream);
+}
+
+// As llmtrain_b200_gemm (epilogue 0 or 3 only) and additionally colsum[n] += sum_m C[m, n] over
+// the bf16-rounded output — the bias gradient of the layer this GEMM back-propagates INTO, fused
+// so that no separate reduction re-reads C.  fp32 atomics: the summation order is not fixed.
+extern "C" int llmtrain_b200_gemm_colsum(int layout, int epilogue, int M, int N, int K,
+                                         const void* A, int lda, const void* B, int ldb, void* C,
+                                         int ldc, const float* bias, const void* R, int ldr,
+                                         float* colsum, cudaStream_t stream) {
+  B200_REQUIRE(colsum != nullptr, "gemm_colsum: colsum must not be null");
+  return gemm_dispatch(layout, epilogue, M, N, K, A, lda, B, ldb, C, ldc, nullptr, 0, bias, R, ldr,
+                       make_dropout(0.f, 0, 0, 0), colsum, stream);
 }
 
 // C[M,N] = dropout(A[M,K] * B[N,K]^T + bias) + R   (NT layout; mask element index row * N + col,
@@ -685,5 +731,5 @@ extern "C" int llmtrain_b200_gemm_dropout_resid(int M, int N, int K, const void*
                                                 uint32_t site, cudaStream_t stream) {
   B200_REQUIRE(p >= 0.f && p < 1.f, "gemm_dropout_resid: p must be in [0, 1)");
   return gemm_dispatch(0, kBiasDropResid, M, N, K, A, lda, B, ldb, C, ldc, nullptr, 0, bias, R, ldr,
-                       make_dropout(p, seed, offset, site), stream);
+                       make_dropout(p, seed, offset, site), nullptr, stream);
 }

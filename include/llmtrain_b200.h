@@ -146,6 +146,14 @@ int llmtrain_b200_attention_bwd(const void* qkv, const void* out, const void* do
                                 void* scratch, size_t scratch_bytes, int B, int T, int H,
                                 int head_dim, llm_stream_t stream);
 
+/* As llmtrain_b200_gemm with epilogue 0 (plain) or 3 (x gelu'), plus colsum[n] += sum_m C[m, n]
+ * over the bf16-rounded output: the bias gradient of the layer this GEMM back-propagates into
+ * (replaces the reduction behind nn.Linear's bias.grad, src/llmtrain/models/gpt.py:27,94), fused
+ * so no separate pass re-reads C.  fp32 atomics: summation order is not fixed. */
+int llmtrain_b200_gemm_colsum(int layout, int epilogue, int M, int N, int K, const void* A, int lda,
+                              const void* B, int ldb, void* C, int ldc, const float* bias,
+                              const void* R, int ldr, float* colsum, llm_stream_t stream);
+
 /* ---------------------------------------------------------------------------------------------
  * Dropout (csrc/common/philox.cuh, csrc/kernels/dropout.cu).  Replaces the four nn.Dropout modules
  * of src/llmtrain/models/gpt.py:28,30,97,129.  A mask is a pure function of (seed, offset, site,
@@ -174,6 +182,15 @@ int llmtrain_b200_attention_bwd_dropout(const void* qkv, const void* out, const 
                                         void* scratch, size_t scratch_bytes, int B, int T, int H,
                                         int head_dim, float p, uint64_t seed, uint64_t offset,
                                         uint32_t site, llm_stream_t stream);
+
+/* attention backward with every option (what the engine calls): dropout as above (p = 0: none)
+ * and, when dbias_qkv != NULL, dbias_qkv[3d] += column sums of dqkv = qkv_proj's bias gradient
+ * (src/llmtrain/models/gpt.py:27) without another pass over dqkv.  fp32 atomics. */
+int llmtrain_b200_attention_bwd_fused(const void* qkv, const void* out, const void* dout,
+                                      const float* lse, const uint8_t* key_mask, void* dqkv,
+                                      float* dbias_qkv, void* scratch, size_t scratch_bytes, int B,
+                                      int T, int H, int head_dim, float p, uint64_t seed,
+                                      uint64_t offset, uint32_t site, llm_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
  * GPT runtime (csrc/engine/gpt_engine.cu).  Replaces autograd over GPT.forward + compute_loss

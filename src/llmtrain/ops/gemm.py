@@ -43,6 +43,30 @@ def gemm(
     return c
 
 
+def gemm_colsum(
+    layout: int,
+    epilogue: int,
+    a: torch.Tensor,
+    b: torch.Tensor,
+    c: torch.Tensor,
+    colsum: torch.Tensor,
+    *,
+    bias: torch.Tensor | None = None,
+    r: torch.Tensor | None = None,
+) -> torch.Tensor:
+    """As :func:`gemm` (plain or dGELU epilogue) and ``colsum += c.sum(0)`` from the same epilogue."""
+    m, n = c.shape
+    k = a.shape[1] if layout != TN else a.shape[0]
+    status = native.lib().llmtrain_b200_gemm_colsum(
+        ctypes.c_int(layout), ctypes.c_int(epilogue), ctypes.c_int(m), ctypes.c_int(n),
+        ctypes.c_int(k), native.ptr(a), ctypes.c_int(_ld(a)), native.ptr(b), ctypes.c_int(_ld(b)),
+        native.ptr(c), ctypes.c_int(_ld(c)), native.ptr(bias), native.ptr(r),
+        ctypes.c_int(_ld(r) if r is not None else 0), native.ptr(colsum), native.stream_handle(),
+    )
+    native.check(status, "gemm_colsum")
+    return c
+
+
 def linear_forward(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None = None) -> torch.Tensor:
     """``x @ w.T + bias`` with bf16 operands, fp32 accumulate, bf16 result."""
     out = torch.empty(x.shape[0], w.shape[0], dtype=torch.bfloat16, device=x.device)

@@ -96,3 +96,20 @@ def test_strided_views() -> None:
     G.gemm(G.NT, G.EPI_BIAS, a, w, out_wide[:, 128:512])
     _close(out_wide[:, 128:512], a.float() @ w.float().t(), 1e-2)
     assert out_wide[:, :128].abs().max().item() == 0 and out_wide[:, 512:].abs().max().item() == 0
+
+
+@pytest.mark.parametrize("m,n,k", [(512, 3072, 768), (1000, 320, 1600), (130, 72, 64)])
+def test_dgrad_with_fused_column_sums(m: int, n: int, k: int) -> None:
+    """dX = (dY @ W) * R with colsum += dX.sum(0) out of the same epilogue (fc bias gradient)."""
+    from llmtrain.ops import gemm as G
+
+    dy, w = _rand((m, k)), _rand((k, n), 0.05)
+    r = _rand((m, n))
+    out = torch.empty(m, n, device="cuda", dtype=torch.bfloat16)
+    colsum = torch.full((n,), 2.0, device="cuda")
+    G.gemm_colsum(G.NN, G.EPI_DGELU, dy, w, out, colsum, r=r)
+    want = (dy.float() @ w.float()) * r.float()
+    _close(out, want, 2e-2)
+    # the sums are taken over the bf16 values that were stored
+    got, ref = colsum - 2.0, out.float().sum(0)
+    assert ((got - ref).abs().max() / (ref.abs().max() + 1e-6)).item() < 1e-3
