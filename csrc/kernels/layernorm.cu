@@ -135,114 +135,161 @@ bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict
            const float* __restrict__ gamma, const float* __restrict__ mean,
            const float* __restrict__ rstd, __nv_bfloat16* __restrict__ dresid,
            float* __restrict__ partial /* [gridDim.x][NS][d], NS = COLSUM ? 3 : 2 */, int rows,
-           int d) {
+           int d, int stages, int warp_bytes) {
   pdl_enter();  // previous kernel finished, its writes are visible
   constexpr int NS = COLSUM ? 3 : 2;
-  extern __shared__ float sh[];  // [WARPS][NS][d]
-  float dc[COLSUM ? NV : 1][8];
+  // Per-warp window of `warp_bytes`: first a ring of `stages` row slots (dy | x | dresid rows,
+  // filled by bulk copies), at the end the warp's NS x d partial column sums.
+  extern __shared__ __align__(128) uint8_t sh_raw[];
+  __shared__ uint64_t full_bar[WARPS][4];
+  // All per-column state is held as packed fp32 pairs (f32x2, ptx.cuh): the kernel is paced by
+  // instruction issue and dependency latency at 8 warps per SM (~200 registers per thread), and
+  // FFMA2 halves the instruction count of both sweeps.
+  f32x2 dc[COLSUM ? NV : 1][4];
 #pragma unroll
   for (int i = 0; i < (COLSUM ? NV : 1); ++i)
 #pragma unroll
-    for (int j = 0; j < 8; ++j) dc[i][j] = 0.f;
+    for (int j = 0; j < 4; ++j) dc[i][j] = splat2(0.f);
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int nvec = d >> 3;
-  float dg[NV][8], db[NV][8], g[NV][8];
+  f32x2 dg[NV][4], db[NV][4], g[NV][4];
 #pragma unroll
   for (int i = 0; i < NV; ++i) {
 #pragma unroll
-    for (int j = 0; j < 8; ++j) { dg[i][j] = 0.f; db[i][j] = 0.f; g[i][j] = 0.f; }
+    for (int j = 0; j < 4; ++j) { dg[i][j] = splat2(0.f); db[i][j] = splat2(0.f); g[i][j] = splat2(0.f); }
     const int c = lane + i * 32;
     if (c < nvec) {
       const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma) + 2 * c);
       const float4 g1 = __ldg(reinterpret_cast<const float4*>(gamma) + 2 * c + 1);
-      g[i][0] = g0.x; g[i][1] = g0.y; g[i][2] = g0.z; g[i][3] = g0.w;
-      g[i][4] = g1.x; g[i][5] = g1.y; g[i][6] = g1.z; g[i][7] = g1.w;
+      g[i][0] = pack2(g0.x, g0.y); g[i][1] = pack2(g0.z, g0.w);
+      g[i][2] = pack2(g1.x, g1.y); g[i][3] = pack2(g1.z, g1.w);
     }
   }
 
-  // Software-pipelined over rows: the three 16-byte streams of row r+stride (dy, x, dresid) are
-  // requested before row r is reduced, so ~2x the bytes are in flight per warp.  With ~200
-  // registers per thread only 8 warps fit on an SM, and one row per warp in flight left the
-  // kernel latency-bound at a third of HBM bandwidth.
+  // Rows reach the warp through a private ring in shared memory: lane 0 issues three untiled bulk
+  // copies (cp.async.bulk; dy, x and dresid rows are contiguous) per slot, `stages` rows ahead,
+  // and refills a slot as soon as its row has been copied to registers.  Holding the prefetched
+  // rows in registers instead (one row ahead was all that fitted) left the loads of the next row
+  // exposed: ncu showed the warps idle on the long scoreboard with the issue slots 40% used.
   const int stride = gridDim.x * WARPS;
-  int row = blockIdx.x * WARPS + warp;
-  uint4 na[NV], nb[NV], nr[NV];
-  float nmu = 0.f, nrs = 0.f;
-  auto fetch = [&](int r) {
-    const uint4* dyr = reinterpret_cast<const uint4*>(dy + size_t(r) * d);
-    const uint4* xr = reinterpret_cast<const uint4*>(x + size_t(r) * d);
-    const uint4* drr = reinterpret_cast<const uint4*>(dresid + size_t(r) * d);
-#pragma unroll
-    for (int i = 0; i < NV; ++i) {
-      const int c = lane + i * 32;
-      if (c < nvec) { na[i] = __ldg(dyr + c); nb[i] = __ldg(xr + c); nr[i] = drr[c]; }
-    }
-    nmu = mean[r];
-    nrs = rstd[r];
+  const uint32_t row_bytes = uint32_t(d) * 2u;
+  const uint32_t slot_bytes = 3u * row_bytes;
+  uint8_t* ring = sh_raw + size_t(warp) * warp_bytes;
+  uint64_t* full = full_bar[warp];
+  if (lane == 0) {
+    for (int s = 0; s < stages; ++s) mbar_init(&full[s], 1);
+    fence_barrier_init();
+  }
+  __syncwarp();
+  auto request = [&](int r, int slot) {  // lane 0 only
+    uint8_t* dst = ring + size_t(slot) * slot_bytes;
+    mbar_expect_tx(&full[slot], slot_bytes);
+    bulk_load_1d(dst, dy + size_t(r) * d, row_bytes, &full[slot]);
+    bulk_load_1d(dst + row_bytes, x + size_t(r) * d, row_bytes, &full[slot]);
+    bulk_load_1d(dst + 2 * row_bytes, dresid + size_t(r) * d, row_bytes, &full[slot]);
   };
-  constexpr bool PIPE = NV <= 4;  // wider rows would spill with two rows held in registers
-  if (PIPE && row < rows) fetch(row);
+  int row = blockIdx.x * WARPS + warp;
+  if (lane == 0) {
+    for (int s = 0; s < stages; ++s)
+      if (row + s * stride < rows) request(row + s * stride, s);
+  }
+  int slot = 0;
+  uint32_t parity = 0;
   while (row < rows) {
-    if (!PIPE) fetch(row);
+    const float mu = mean[row], rs = rstd[row];
+    mbar_wait(&full[slot], parity);
     uint4 pa[NV], pb[NV], pr[NV];
+    {
+      const uint4* sa = reinterpret_cast<const uint4*>(ring + size_t(slot) * slot_bytes);
+      const uint4* sb = reinterpret_cast<const uint4*>(ring + size_t(slot) * slot_bytes + row_bytes);
+      const uint4* sr =
+          reinterpret_cast<const uint4*>(ring + size_t(slot) * slot_bytes + 2 * row_bytes);
 #pragma unroll
-    for (int i = 0; i < NV; ++i) { pa[i] = na[i]; pb[i] = nb[i]; pr[i] = nr[i]; }
-    const float mu = nmu, rs = nrs;
+      for (int i = 0; i < NV; ++i) {
+        const int c = lane + i * 32;
+        if (c < nvec) { pa[i] = sa[c]; pb[i] = sb[c]; pr[i] = sr[c]; }
+      }
+    }
+    __syncwarp();  // every lane has its copy: the slot may be overwritten
+    if (lane == 0 && row + stages * stride < rows) request(row + stages * stride, slot);
+    if (++slot == stages) { slot = 0; parity ^= 1; }
     const int next = row + stride;
-    if (PIPE && next < rows) fetch(next);
-    float s1 = 0.f, s2 = 0.f;
+    // h = (x - mu) * rs = x * rs + (-mu * rs)
+    const f32x2 rs2 = splat2(rs), nmurs2 = splat2(-mu * rs);
+    f32x2 s1p = splat2(0.f), s2p = splat2(0.f);
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
       const int c = lane + i * 32;
       if (c < nvec) {
-        float a[8], b[8];
-        unpack8(pa[i], a);
-        unpack8(pb[i], b);
+        const uint32_t aw[4] = {pa[i].x, pa[i].y, pa[i].z, pa[i].w};
+        const uint32_t bw[4] = {pb[i].x, pb[i].y, pb[i].z, pb[i].w};
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const float h = (b[j] - mu) * rs;
-          dg[i][j] += a[j] * h;
-          db[i][j] += a[j];
-          const float w = a[j] * g[i][j];
-          s1 += w;
-          s2 += w * h;
+        for (int j = 0; j < 4; ++j) {
+          const float2 af = unpack_bf16x2(aw[j]), bf = unpack_bf16x2(bw[j]);
+          const f32x2 a = pack2(af.x, af.y);
+          const f32x2 h = fma2(pack2(bf.x, bf.y), rs2, nmurs2);
+          dg[i][j] = fma2(a, h, dg[i][j]);
+          db[i][j] = add2(db[i][j], a);
+          const f32x2 w = mul2(a, g[i][j]);
+          s1p = add2(s1p, w);
+          s2p = fma2(w, h, s2p);
         }
       }
     }
+    float s1, s2, t0, t1;
+    unpack2(s1p, t0, t1);
+    s1 = t0 + t1;
+    unpack2(s2p, t0, t1);
+    s2 = t0 + t1;
     s1 = warp_sum(s1) / d;
     s2 = warp_sum(s2) / d;
+    const f32x2 ns1 = splat2(-s1), ns2 = splat2(-s2);
     uint4* drr = reinterpret_cast<uint4*>(dresid + size_t(row) * d);
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
       const int c = lane + i * 32;
       if (c < nvec) {
-        float a[8], b[8], r[8];
-        unpack8(pa[i], a);
-        unpack8(pb[i], b);
-        unpack8(pr[i], r);
+        const uint32_t aw[4] = {pa[i].x, pa[i].y, pa[i].z, pa[i].w};
+        const uint32_t bw[4] = {pb[i].x, pb[i].y, pb[i].z, pb[i].w};
+        const uint32_t rw[4] = {pr[i].x, pr[i].y, pr[i].z, pr[i].w};
+        uint32_t ow[4];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const float h = (b[j] - mu) * rs;
-          r[j] += rs * (a[j] * g[i][j] - s1 - h * s2);
-          if (COLSUM) dc[i][j] += r[j];
+        for (int j = 0; j < 4; ++j) {
+          const float2 af = unpack_bf16x2(aw[j]), bf = unpack_bf16x2(bw[j]),
+                       rf = unpack_bf16x2(rw[j]);
+          const f32x2 h = fma2(pack2(bf.x, bf.y), rs2, nmurs2);
+          // r += rs * (a * g - s1 - h * s2)
+          f32x2 t = fma2(pack2(af.x, af.y), g[i][j], ns1);
+          t = fma2(h, ns2, t);
+          const f32x2 r = fma2(t, rs2, pack2(rf.x, rf.y));
+          if (COLSUM) dc[i][j] = add2(dc[i][j], r);
+          float r0, r1;
+          unpack2(r, r0, r1);
+          ow[j] = pack_bf16x2(r0, r1);
         }
-        drr[c] = pack8(r);
+        drr[c] = make_uint4(ow[0], ow[1], ow[2], ow[3]);
       }
     }
     row = next;
   }
 
-  float* my = sh + size_t(warp) * NS * d;
+  float* my = reinterpret_cast<float*>(ring);  // the ring is idle now: reuse it for the sums
 #pragma unroll
   for (int i = 0; i < NV; ++i) {
     const int c = lane + i * 32;
     if (c < nvec) {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        my[c * 8 + j] = dg[i][j];
-        my[d + c * 8 + j] = db[i][j];
-        if (COLSUM) my[2 * d + c * 8 + j] = dc[i][j];
+      for (int j = 0; j < 4; ++j) {
+        float lo, hi;
+        unpack2(dg[i][j], lo, hi);
+        my[c * 8 + 2 * j] = lo; my[c * 8 + 2 * j + 1] = hi;
+        unpack2(db[i][j], lo, hi);
+        my[d + c * 8 + 2 * j] = lo; my[d + c * 8 + 2 * j + 1] = hi;
+        if (COLSUM) {
+          unpack2(dc[i][j], lo, hi);
+          my[2 * d + c * 8 + 2 * j] = lo; my[2 * d + c * 8 + 2 * j + 1] = hi;
+        }
       }
     }
   }
@@ -251,7 +298,8 @@ bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict
   for (int idx = threadIdx.x; idx < NS * d; idx += blockDim.x) {
     float acc = 0.f;
 #pragma unroll
-    for (int w = 0; w < WARPS; ++w) acc += sh[size_t(w) * NS * d + idx];
+    for (int w = 0; w < WARPS; ++w)
+      acc += reinterpret_cast<const float*>(sh_raw + size_t(w) * warp_bytes)[idx];
     out[idx] = acc;
   }
 }
@@ -285,7 +333,7 @@ finish_kernel(const float* __restrict__ partial, int nparts, int d, int ns,
 }
 
 inline int bwd_grid(int rows) {
-  int g = 2 * sm_count();
+  int g = sm_count();  // one resident wave (the register footprint allows one CTA per SM)
   const int need = ceil_div(rows, WARPS);
   return g < need ? g : need;
 }
@@ -344,7 +392,15 @@ extern "C" int llmtrain_b200_layernorm_bwd(const void* dy, const void* x, const 
   const int ns = dcolsum != nullptr ? 3 : 2;
   B200_REQUIRE(scratch_bytes >= size_t(grid) * ns * d * sizeof(float),
                "layernorm_bwd: scratch too small (see llmtrain_b200_layernorm_bwd_scratch_bytes)");
-  const size_t smem = size_t(ln::WARPS) * ns * d * sizeof(float);
+  // per-warp window: ring of row slots (3 rows of d bf16 each), reused for NS x d partial sums
+  const size_t slot_bytes = size_t(3) * d * 2;
+  int stages = int((size_t(200) * 1024 / ln::WARPS) / slot_bytes);
+  stages = stages > 3 ? 3 : (stages < 1 ? 1 : stages);
+  size_t warp_bytes = stages * slot_bytes;
+  if (warp_bytes < size_t(ns) * d * sizeof(float)) warp_bytes = size_t(ns) * d * sizeof(float);
+  warp_bytes = (warp_bytes + 127) & ~size_t(127);
+  const size_t smem = size_t(ln::WARPS) * warp_bytes;
+  B200_REQUIRE(smem <= size_t(200) * 1024, "layernorm_bwd: shared-memory budget exceeded");
   const auto* dy_ = static_cast<const __nv_bfloat16*>(dy);
   const auto* x_ = static_cast<const __nv_bfloat16*>(x);
   auto* dr_ = static_cast<__nv_bfloat16*>(dresid);
@@ -364,10 +420,10 @@ extern "C" int llmtrain_b200_layernorm_bwd(const void* dy, const void* x, const 
     }                                                                                          \
     if (ns == 3) {                                                                             \
       B200_LAUNCH((ln::bwd_kernel<NV, true>), grid, ln::WARPS * 32, smem, stream, dy_, x_,     \
-                  gamma, mean, rstd, dr_, part_, rows, d);                                     \
+                  gamma, mean, rstd, dr_, part_, rows, d, stages, int(warp_bytes));            \
     } else {                                                                                   \
       B200_LAUNCH((ln::bwd_kernel<NV, false>), grid, ln::WARPS * 32, smem, stream, dy_, x_,    \
-                  gamma, mean, rstd, dr_, part_, rows, d);                                     \
+                  gamma, mean, rstd, dr_, part_, rows, d, stages, int(warp_bytes));            \
     }                                                                                          \
     break;                                                                                     \
   }
