@@ -60,7 +60,7 @@ inline EncodeTiledFn encode_tiled_fn() {
   return fn;
 }
 
-enum class Swz { None, B128 };
+enum class Swz { None, B128, B64 };
 
 // 2-D row-major tensor [rows, cols] with `ld` elements between rows; box = [box_rows, box_cols].
 // Out-of-bounds elements are read as zero and never written.
@@ -83,9 +83,13 @@ inline int make_tmap_2d(CUtensorMap* out, const T* base, uint64_t rows, uint64_t
   B200_REQUIRE((ld * sizeof(T)) % 16 == 0, "TMA row pitch must be a multiple of 16 bytes");
   B200_REQUIRE(box_cols * sizeof(T) <= 128 || swz == Swz::None,
                "swizzled TMA box inner extent must be <= 128 bytes");
+  B200_REQUIRE(swz != Swz::B64 || box_cols * sizeof(T) <= 64,
+               "64-byte-swizzled TMA box inner extent must be <= 64 bytes");
   CUresult r = enc(out, dt, 2, const_cast<T*>(base), dims, strides, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE,
-                   swz == Swz::B128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+                   swz == Swz::B128  ? CU_TENSOR_MAP_SWIZZLE_128B
+                   : swz == Swz::B64 ? CU_TENSOR_MAP_SWIZZLE_64B
+                                     : CU_TENSOR_MAP_SWIZZLE_NONE,
                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     return fail("cuTensorMapEncodeTiled failed with CUresult " + std::to_string(int(r)));

@@ -195,6 +195,14 @@ __device__ __forceinline__ void bulk_load_1d(void* smem_dst, const void* gsrc, u
         "r"(smem_u32(bar))
       : "memory");
 }
+// gdst[0 .. bytes/4) += smem_src[...]  (fp32, one L2 reduction transaction per 16 bytes instead of
+// one atomic per element; joins the bulk async-group of the issuing thread)
+__device__ __forceinline__ void bulk_reduce_add_f32(float* gdst, const void* smem_src,
+                                                    uint32_t bytes) {
+  asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], %2;"
+               ::"l"(reinterpret_cast<uint64_t>(gdst)), "r"(smem_u32(smem_src)), "r"(bytes)
+               : "memory");
+}
 __device__ __forceinline__ void bulk_store_1d(void* gdst, const void* smem_src, uint32_t bytes) {
   asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
                ::"l"(reinterpret_cast<uint64_t>(gdst)), "r"(smem_u32(smem_src)), "r"(bytes)
@@ -481,6 +489,11 @@ __device__ __forceinline__ f32x2 splat2(float c) { return pack2(c, c); }
 // aligned.  The 16-byte chunk index (bits 4..6) is XORed with the row index mod 8 (bits 7..9).
 __device__ __forceinline__ uint32_t swizzle128(uint32_t byte_off) {
   return byte_off ^ ((byte_off >> 3) & 0x70u);
+}
+
+// 64-byte swizzle: rows of 64 B, base 512 B aligned; chunk index (bits 4..5) XOR row bits 7..8.
+__device__ __forceinline__ uint32_t swizzle64(uint32_t byte_off) {
+  return byte_off ^ ((byte_off >> 3) & 0x30u);
 }
 
 __device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t nthreads) {

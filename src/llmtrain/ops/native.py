@@ -13,7 +13,14 @@ from typing import Any
 
 import torch  # noqa: F401  (maps libcudart before our library asks for it)
 
-_LIB_PATH = Path(__file__).resolve().parents[1] / "_native" / "libllmtrain_b200.so"
+import os
+
+# LLMTRAIN_NATIVE_LIB points at an alternative build of the library (A/B measurements of two
+# kernel versions inside one process tree / one GPU box); the default is the in-tree build.
+_LIB_PATH = Path(
+    os.environ.get("LLMTRAIN_NATIVE_LIB")
+    or Path(__file__).resolve().parents[1] / "_native" / "libllmtrain_b200.so"
+)
 _lib: ctypes.CDLL | None = None
 
 
