@@ -19,7 +19,9 @@ def _rel(got, want):
     return ((got.float() - want.float()).abs().max() / (want.float().abs().max() + 1e-6)).item()
 
 
-@pytest.mark.parametrize("rows,d", [(64, 768), (1000, 1600), (37, 64), (4096, 1024)])
+@pytest.mark.parametrize(
+    "rows,d", [(64, 768), (1000, 1600), (37, 64), (4096, 1024), (2500, 2048), (3000, 8)]
+)
 def test_layernorm_fwd_bwd(rows: int, d: int) -> None:
     from llmtrain.ops import kernels as K
 
