@@ -113,3 +113,45 @@ def test_dgrad_with_fused_column_sums(m: int, n: int, k: int) -> None:
     # the sums are taken over the bf16 values that were stored
     got, ref = colsum - 2.0, out.float().sum(0)
     assert ((got - ref).abs().max() / (ref.abs().max() + 1e-6)).item() < 1e-3
+
+
+_ALT_PATH_CHECK = r"""
+import torch
+from llmtrain.ops import gemm as G
+torch.manual_seed(0)
+m, n, k = 640, 512, 384
+x = (torch.randn(m, k, device="cuda")).to(torch.bfloat16)
+w = (torch.randn(n, k, device="cuda") * 0.05).to(torch.bfloat16)
+bias = torch.randn(n, device="cuda")
+out = torch.empty(m, n, device="cuda", dtype=torch.bfloat16)
+G.gemm(G.NT, G.EPI_BIAS, x, w, out, bias=bias)
+want = x.float() @ w.float().T + bias
+err = ((out.float() - want).abs().max() / want.abs().max()).item()
+dw = torch.zeros(n, k, device="cuda")
+dy = (torch.randn(m, n, device="cuda") * 0.1).to(torch.bfloat16)
+G.gemm(G.TN, G.EPI_ACCUM_F32, dy, x, dw)
+want_dw = dy.float().T @ x.float()
+err2 = ((dw - want_dw).abs().max() / want_dw.abs().max()).item()
+assert err < 2e-2 and err2 < 2e-2, (err, err2)
+print("ok")
+"""
+
+
+@pytest.mark.parametrize("env", [{"LLMTRAIN_GEMM_PAIR": "0"}, {"LLMTRAIN_PDL": "0"},
+                                 {"LLMTRAIN_GEMM_GROUP_M": "2"}])
+def test_alternative_launch_paths_in_a_fresh_process(env: dict) -> None:
+    """The single-CTA kernel, plain stream order (no PDL) and narrow tile bands are selected by
+    environment variables that the library reads once, so each is exercised in its own process."""
+    import os
+    import subprocess
+    import sys
+    from pathlib import Path
+
+    src = Path(__file__).resolve().parents[1] / "src"
+    proc = subprocess.run(
+        [sys.executable, "-c", _ALT_PATH_CHECK],
+        env={**os.environ, **env, "PYTHONPATH": str(src)},
+        capture_output=True, text=True, timeout=300,
+    )
+    assert proc.returncode == 0, proc.stderr[-2000:]
+    assert "ok" in proc.stdout
