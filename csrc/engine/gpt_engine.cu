@@ -19,6 +19,7 @@
 
 #include <nvtx3/nvToolsExt.h>  // header-only NVTX3: no link dependency, no cost without a tool
 
+#include <cmath>
 #include <vector>
 
 #include "../common/host.cuh"
@@ -38,10 +39,16 @@ struct LayerOffsets {
 struct LayerActs {
   size_t ln1, ln1_mean, ln1_rstd, qkv, atty, lse, resid1, ln2, ln2_mean, ln2_rstd, fch_pre,
       fch_act, resid2;
+  // heads narrower than 64 only: zero-padded per-step copies of qkv_proj.weight (bf16 [3*dq, d]),
+  // qkv_proj.bias (fp32 [3*dq]) and out_proj.weight (bf16 [d, dq]); see csrc/kernels/headpad.cu
+  size_t wq_pad, bq_pad, wo_pad;
 };
 
 struct Gpt {
   int V = 0, Vp = 0, block = 0, d = 0, L = 0, H = 0, F = 0, tied = 1;
+  int hd = 64;        // true head width (d / H)
+  int dq = 0;         // width of the q / k / v / attention-output activations: H * 64
+  bool padded = false;  // hd < 64: heads run zero-padded to 64 lanes
   int maxB = 0, maxT = 0;
   // parameter plan
   size_t wpe = 0, lnf_w = 0, lnf_b = 0, wte = 0, head = 0;
@@ -53,6 +60,8 @@ struct Gpt {
   size_t a_x0 = 0, a_lnf = 0, a_lnf_mean = 0, a_lnf_rstd = 0, a_logits = 0, a_loss_rows = 0;
   size_t a_dresid = 0, a_dtmp = 0, a_dqkv = 0, a_dfc = 0, a_attn_scratch = 0, a_red_scratch = 0;
   size_t a_dmask = 0;  // residual-branch gradient with its dropout mask applied
+  size_t a_datty = 0;  // gradient of the attention output, [M, dq]
+  size_t a_t_dwq = 0, a_t_dbq = 0, a_t_dwo = 0;  // padded fp32 gradient temporaries (hd < 64)
   size_t attn_scratch_bytes = 0, red_scratch_bytes = 0, act_bytes = 0;
   // bound memory
   float *p32 = nullptr, *g32 = nullptr;
@@ -110,7 +119,7 @@ void plan_params(Gpt& g) {
 }
 
 void plan_acts(Gpt& g) {
-  const size_t M = size_t(g.maxB) * g.maxT, d = g.d, F = g.F;
+  const size_t M = size_t(g.maxB) * g.maxT, d = g.d, F = g.F, dq = g.dq;
   size_t c = 0;
   g.a_x0 = take_bytes(c, M * d * 2);
   g.acts.resize(g.L);
@@ -119,8 +128,8 @@ void plan_acts(Gpt& g) {
     a.ln1 = take_bytes(c, M * d * 2);
     a.ln1_mean = take_bytes(c, M * 4);
     a.ln1_rstd = take_bytes(c, M * 4);
-    a.qkv = take_bytes(c, M * 3 * d * 2);
-    a.atty = take_bytes(c, M * d * 2);
+    a.qkv = take_bytes(c, M * 3 * dq * 2);
+    a.atty = take_bytes(c, M * dq * 2);
     a.lse = take_bytes(c, size_t(g.maxB) * g.H * g.maxT * 4);
     a.resid1 = take_bytes(c, M * d * 2);
     a.ln2 = take_bytes(c, M * d * 2);
@@ -129,6 +138,12 @@ void plan_acts(Gpt& g) {
     a.fch_pre = take_bytes(c, M * F * 2);
     a.fch_act = take_bytes(c, M * F * 2);
     a.resid2 = take_bytes(c, M * d * 2);
+    a.wq_pad = a.bq_pad = a.wo_pad = 0;
+    if (g.padded) {
+      a.wq_pad = take_bytes(c, 3 * dq * d * 2);
+      a.bq_pad = take_bytes(c, 3 * dq * 4);
+      a.wo_pad = take_bytes(c, d * dq * 2);
+    }
   }
   g.a_lnf = take_bytes(c, M * d * 2);
   g.a_lnf_mean = take_bytes(c, M * 4);
@@ -137,14 +152,20 @@ void plan_acts(Gpt& g) {
   g.a_loss_rows = take_bytes(c, M * 4);
   g.a_dresid = take_bytes(c, M * d * 2);
   g.a_dtmp = take_bytes(c, M * d * 2);
-  g.a_dqkv = take_bytes(c, M * 3 * d * 2);
+  g.a_dqkv = take_bytes(c, M * 3 * dq * 2);
+  g.a_datty = take_bytes(c, M * dq * 2);
+  if (g.padded) {
+    g.a_t_dwq = take_bytes(c, 3 * dq * d * 4);
+    g.a_t_dbq = take_bytes(c, 3 * dq * 4);
+    g.a_t_dwo = take_bytes(c, d * dq * 4);
+  }
   g.a_dfc = take_bytes(c, M * F * 2);
   g.a_dmask = take_bytes(c, M * d * 2);
   g.attn_scratch_bytes =
-      llmtrain_b200_attention_bwd_scratch_bytes(g.maxB, g.maxT, g.H, g.d / g.H);
+      llmtrain_b200_attention_bwd_scratch_bytes(g.maxB, g.maxT, g.H, 64);
   g.a_attn_scratch = take_bytes(c, g.attn_scratch_bytes);
   size_t red = llmtrain_b200_layernorm_bwd_scratch_bytes(int(M), g.d);
-  const int widths[4] = {g.d, 3 * g.d, g.F, g.d};
+  const int widths[4] = {g.d, 3 * g.dq, g.F, g.d};
   for (int w : widths) {
     const size_t need = llmtrain_b200_bias_grad_scratch_bytes(int(M), w);
     if (need > red) red = need;
@@ -202,7 +223,8 @@ int forward(Gpt& g, const int64_t* ids, const uint8_t* key_mask, int B, int T, b
             cudaStream_t s) {
   View v(g);
   NvtxRange phase("gpt.forward");
-  const int M = B * T, d = g.d, F = g.F, hd = g.d / g.H;
+  const int M = B * T, d = g.d, F = g.F, dq = g.dq;
+  const float sm_scale = 1.0f / std::sqrt(float(g.hd));  // of the TRUE head width
   auto st = reinterpret_cast<llm_stream_t>(s);
   const bool drop = train && g.drop_p > 0.f;
   const float dp = g.drop_p;
@@ -219,20 +241,29 @@ int forward(Gpt& g, const int64_t* ids, const uint8_t* key_mask, int B, int T, b
     const LayerActs& a = g.acts[l];
     B200_TRY(llmtrain_b200_layernorm_fwd(x, v.p(o.ln1_w), v.p(o.ln1_b), v.bf(a.ln1),
                                          v.f32(a.ln1_mean), v.f32(a.ln1_rstd), M, d, st));
-    B200_TRY(linear_fwd(0, M, 3 * d, d, v.bf(a.ln1), v.w(o.qkv_w), v.bf(a.qkv), nullptr,
-                        v.p(o.qkv_b), nullptr, s));
+    // q | k | v with 64-wide heads ([M, 3*dq]); narrower heads use this step's zero-padded weights
+    const __nv_bfloat16* wq = v.w(o.qkv_w);
+    const float* bq = v.p(o.qkv_b);
+    const __nv_bfloat16* wo = v.w(o.out_w);
+    if (g.padded) {
+      B200_TRY(llmtrain_b200_head_pad(v.w(o.qkv_w), v.bf(a.wq_pad), 1, 3 * g.H, g.hd, d, 2, st));
+      B200_TRY(llmtrain_b200_head_pad(v.p(o.qkv_b), v.f32(a.bq_pad), 1, 3 * g.H, g.hd, 1, 4, st));
+      B200_TRY(llmtrain_b200_head_pad(v.w(o.out_w), v.bf(a.wo_pad), d, g.H, g.hd, 1, 2, st));
+      wq = v.bf(a.wq_pad);
+      bq = v.f32(a.bq_pad);
+      wo = v.bf(a.wo_pad);
+    }
+    B200_TRY(linear_fwd(0, M, 3 * dq, d, v.bf(a.ln1), wq, v.bf(a.qkv), nullptr, bq, nullptr, s));
+    B200_TRY(llmtrain_b200_attention_fwd_fused(v.bf(a.qkv), v.bf(a.atty), v.f32(a.lse), key_mask, B,
+                                               T, g.H, 64, sm_scale, drop ? dp : 0.f, seed, off,
+                                               drop_site(l, 0), st));
     if (drop) {
-      B200_TRY(llmtrain_b200_attention_fwd_dropout(v.bf(a.qkv), v.bf(a.atty), v.f32(a.lse),
-                                                   key_mask, B, T, g.H, hd, dp, seed, off,
-                                                   drop_site(l, 0), st));
-      B200_TRY(llmtrain_b200_gemm_dropout_resid(M, d, d, v.bf(a.atty), d, v.w(o.out_w), d,
-                                                v.bf(a.resid1), d, v.p(o.out_b), x, d, dp, seed,
-                                                off, drop_site(l, 1), st));
+      B200_TRY(llmtrain_b200_gemm_dropout_resid(M, d, dq, v.bf(a.atty), dq, wo, dq, v.bf(a.resid1),
+                                                d, v.p(o.out_b), x, d, dp, seed, off,
+                                                drop_site(l, 1), st));
     } else {
-      B200_TRY(llmtrain_b200_attention_fwd(v.bf(a.qkv), v.bf(a.atty), v.f32(a.lse), key_mask, B,
-                                           T, g.H, hd, st));
-      B200_TRY(linear_fwd(2, M, d, d, v.bf(a.atty), v.w(o.out_w), v.bf(a.resid1), nullptr,
-                          v.p(o.out_b), x, s));
+      B200_TRY(llmtrain_b200_gemm(0, 2, M, d, dq, v.bf(a.atty), dq, wo, dq, v.bf(a.resid1), d,
+                                  nullptr, 0, v.p(o.out_b), x, d, st));
     }
     B200_TRY(llmtrain_b200_layernorm_fwd(v.bf(a.resid1), v.p(o.ln2_w), v.p(o.ln2_b), v.bf(a.ln2),
                                          v.f32(a.ln2_mean), v.f32(a.ln2_rstd), M, d, st));
@@ -267,7 +298,8 @@ int backward(Gpt& g, cudaStream_t s, BucketHook hook = nullptr, void* hook_ctx =
   B200_REQUIRE(g.have_forward, "gpt_backward: no forward pass to differentiate");
   View v(g);
   NvtxRange phase("gpt.backward");
-  const int B = g.B, T = g.T, M = B * T, d = g.d, F = g.F, hd = g.d / g.H;
+  const int B = g.B, T = g.T, M = B * T, d = g.d, F = g.F, dq = g.dq;
+  const float sm_scale = 1.0f / std::sqrt(float(g.hd));
   auto st = reinterpret_cast<llm_stream_t>(s);
   void* red = g.act + g.a_red_scratch;
   const size_t red_bytes = g.red_scratch_bytes;
@@ -277,6 +309,7 @@ int backward(Gpt& g, cudaStream_t s, BucketHook hook = nullptr, void* hook_ctx =
   __nv_bfloat16* dqkv = v.bf(g.a_dqkv);
   __nv_bfloat16* dfc = v.bf(g.a_dfc);
   __nv_bfloat16* dmask = v.bf(g.a_dmask);
+  __nv_bfloat16* datty = v.bf(g.a_datty);
   // With dropout the gradient entering a residual-branch projection is dresid o mask: it is
   // materialised once (the GEMMs read it through TMA) and the projection's bias gradient is its
   // column sum, so the LayerNorm backwards stop emitting those sums.
@@ -330,15 +363,32 @@ int backward(Gpt& g, cudaStream_t s, BucketHook hook = nullptr, void* hook_ctx =
       B200_TRY(llmtrain_b200_bias_grad(dmask, d, M, d, v.grad(o.out_b), red, red_bytes, st));
       dout = dmask;
     }
-    B200_TRY(linear_wgrad(M, d, d, dout, d, v.bf(a.atty), v.grad(o.out_w), s));
-    B200_TRY(linear_dgrad(0, M, d, d, dout, v.w(o.out_w), dtmp, nullptr, s));
+    // With heads narrower than 64 the three attention-side parameter gradients are produced in
+    // their padded shapes and folded back into the true-shape gradient arena.
+    float* dwo = g.padded ? v.f32(g.a_t_dwo) : v.grad(o.out_w);
+    float* dwq = g.padded ? v.f32(g.a_t_dwq) : v.grad(o.qkv_w);
+    float* dbq = g.padded ? v.f32(g.a_t_dbq) : v.grad(o.qkv_b);
+    const __nv_bfloat16* wq = g.padded ? v.bf(a.wq_pad) : v.w(o.qkv_w);
+    const __nv_bfloat16* wo = g.padded ? v.bf(a.wo_pad) : v.w(o.out_w);
+    if (g.padded) {
+      B200_CHECK_CUDA(cudaMemsetAsync(dwo, 0, size_t(d) * dq * 4, s));
+      B200_CHECK_CUDA(cudaMemsetAsync(dwq, 0, size_t(3) * dq * d * 4, s));
+      B200_CHECK_CUDA(cudaMemsetAsync(dbq, 0, size_t(3) * dq * 4, s));
+    }
+    B200_TRY(linear_wgrad(M, d, dq, dout, d, v.bf(a.atty), dwo, s));
+    B200_TRY(linear_dgrad(0, M, d, dq, dout, wo, datty, nullptr, s));
     // dqkv and, fused, qkv_proj's bias gradient (column sums of dqkv)
     B200_TRY(llmtrain_b200_attention_bwd_fused(
-        v.bf(a.qkv), v.bf(a.atty), dtmp, v.f32(a.lse), g.key_mask, dqkv, v.grad(o.qkv_b),
-        g.act + g.a_attn_scratch, g.attn_scratch_bytes, B, T, g.H, hd, drop ? dp : 0.f, seed, off,
-        drop_site(l, 0), st));
-    B200_TRY(linear_wgrad(M, 3 * d, d, dqkv, 3 * d, v.bf(a.ln1), v.grad(o.qkv_w), s));
-    B200_TRY(linear_dgrad(0, M, 3 * d, d, dqkv, v.w(o.qkv_w), dtmp, nullptr, s));
+        v.bf(a.qkv), v.bf(a.atty), datty, v.f32(a.lse), g.key_mask, dqkv, dbq,
+        g.act + g.a_attn_scratch, g.attn_scratch_bytes, B, T, g.H, 64, sm_scale, drop ? dp : 0.f,
+        seed, off, drop_site(l, 0), st));
+    B200_TRY(linear_wgrad(M, 3 * dq, d, dqkv, 3 * dq, v.bf(a.ln1), dwq, s));
+    B200_TRY(linear_dgrad(0, M, 3 * dq, d, dqkv, wq, dtmp, nullptr, s));
+    if (g.padded) {
+      B200_TRY(llmtrain_b200_head_unpad_add(dwo, v.grad(o.out_w), d, g.H, g.hd, 1, st));
+      B200_TRY(llmtrain_b200_head_unpad_add(dwq, v.grad(o.qkv_w), 1, 3 * g.H, g.hd, d, st));
+      B200_TRY(llmtrain_b200_head_unpad_add(dbq, v.grad(o.qkv_b), 1, 3 * g.H, g.hd, 1, st));
+    }
     B200_TRY(llmtrain_b200_layernorm_bwd(dtmp, x_in, v.p(o.ln1_w), v.f32(a.ln1_mean),
                                          v.f32(a.ln1_rstd), dresid, v.grad(o.ln1_w),
                                          v.grad(o.ln1_b),
@@ -388,8 +438,9 @@ extern "C" int llmtrain_b200_gpt_create(int vocab, int block_size, int d_model, 
                                         int n_heads, int d_ff, int tied, int max_batch,
                                         int max_seq, void** handle) {
   B200_REQUIRE(handle != nullptr, "gpt_create: null handle");
-  B200_REQUIRE(d_model % n_heads == 0 && d_model / n_heads == 64,
-               "gpt_create: the sm_100a attention kernels need head_dim == 64");
+  B200_REQUIRE(d_model % n_heads == 0 && d_model / n_heads <= 64 && (d_model / n_heads) % 8 == 0,
+               "gpt_create: head_dim must be a multiple of 8 and at most 64 (narrower heads run "
+               "zero-padded on the head_dim-64 attention kernels)");
   B200_REQUIRE(d_model % 8 == 0 && d_ff % 8 == 0 && d_model <= 2048,
                "gpt_create: d_model/d_ff must be multiples of 8 and d_model <= 2048");
   B200_REQUIRE(max_seq <= block_size && max_batch > 0 && max_seq > 0, "gpt_create: bad batch plan");
@@ -398,6 +449,9 @@ extern "C" int llmtrain_b200_gpt_create(int vocab, int block_size, int d_model, 
   g->Vp = int(engine::align_up(size_t(vocab), 128));
   g->block = block_size; g->d = d_model; g->L = n_layers; g->H = n_heads; g->F = d_ff;
   g->tied = tied ? 1 : 0;
+  g->hd = d_model / n_heads;
+  g->dq = n_heads * 64;
+  g->padded = g->hd < 64;
   g->maxB = max_batch; g->maxT = max_seq;
   engine::plan_params(*g);
   engine::plan_acts(*g);

@@ -525,7 +525,8 @@ extern "C" size_t llmtrain_b200_attention_bwd_scratch_bytes(int B, int T, int H,
 static int attention_bwd_impl(const void* qkv, const void* out, const void* dout, const float* lse,
                               const uint8_t* key_mask, void* dqkv, void* scratch,
                               size_t scratch_bytes, int B, int T, int H, int head_dim,
-                              const DropoutParams& drop, float* dbias, cudaStream_t stream) {
+                              const DropoutParams& drop, float* dbias, float softmax_scale,
+                              cudaStream_t stream) {
   namespace ab = attn_bwd;
   B200_REQUIRE(head_dim == ab::HD, "attention_bwd: specialised for head_dim 64");
   B200_REQUIRE(B > 0 && T > 0 && H > 0, "attention_bwd: empty problem");
@@ -555,7 +556,7 @@ static int attention_bwd_impl(const void* qkv, const void* out, const void* dout
 
   ab::Params p;
   p.B = B; p.T = T; p.H = H;
-  p.scale = 1.0f / std::sqrt(float(head_dim));
+  p.scale = softmax_scale > 0.f ? softmax_scale : 1.0f / std::sqrt(float(head_dim));
   p.scale_log2 = p.scale * 1.4426950408889634f;
   p.lse = lse;
   p.dsum = dsum;
@@ -598,7 +599,7 @@ extern "C" int llmtrain_b200_attention_bwd(const void* qkv, const void* out, con
                                            void* scratch, size_t scratch_bytes, int B, int T,
                                            int H, int head_dim, cudaStream_t stream) {
   return attention_bwd_impl(qkv, out, dout, lse, key_mask, dqkv, scratch, scratch_bytes, B, T, H,
-                            head_dim, make_dropout(0.f, 0, 0, 0), nullptr, stream);
+                            head_dim, make_dropout(0.f, 0, 0, 0), nullptr, 0.f, stream);
 }
 
 // Backward of llmtrain_b200_attention_fwd_dropout: pass the same (p, seed, offset, site).
@@ -611,20 +612,21 @@ extern "C" int llmtrain_b200_attention_bwd_dropout(const void* qkv, const void* 
                                                    cudaStream_t stream) {
   B200_REQUIRE(p >= 0.f && p < 1.f, "attention_bwd_dropout: p must be in [0, 1)");
   return attention_bwd_impl(qkv, out, dout, lse, key_mask, dqkv, scratch, scratch_bytes, B, T, H,
-                            head_dim, make_dropout(p, seed, offset, site), nullptr, stream);
+                            head_dim, make_dropout(p, seed, offset, site), nullptr, 0.f, stream);
 }
 
-// Everything at once (what the training engine calls): optional dropout (p = 0: none) and, when
-// dbias_qkv is not NULL, dbias_qkv[3d] += column sums of dqkv — qkv_proj's bias gradient
+// Everything at once (what the training engine calls): optional softmax scale (0 = head_dim^-0.5),
+// optional dropout (p = 0: none) and, when dbias_qkv is not NULL, dbias_qkv[3d] += column sums of dqkv — qkv_proj's bias gradient
 // (`gpt.py:27`) without a separate pass over dqkv.  fp32 atomics: summation order is not fixed.
 extern "C" int llmtrain_b200_attention_bwd_fused(const void* qkv, const void* out, const void* dout,
                                                  const float* lse, const uint8_t* key_mask,
                                                  void* dqkv, float* dbias_qkv, void* scratch,
                                                  size_t scratch_bytes, int B, int T, int H,
-                                                 int head_dim, float p, uint64_t seed,
-                                                 uint64_t offset, uint32_t site,
+                                                 int head_dim, float softmax_scale, float p,
+                                                 uint64_t seed, uint64_t offset, uint32_t site,
                                                  cudaStream_t stream) {
   B200_REQUIRE(p >= 0.f && p < 1.f, "attention_bwd_fused: p must be in [0, 1)");
   return attention_bwd_impl(qkv, out, dout, lse, key_mask, dqkv, scratch, scratch_bytes, B, T, H,
-                            head_dim, make_dropout(p, seed, offset, site), dbias_qkv, stream);
+                            head_dim, make_dropout(p, seed, offset, site), dbias_qkv,
+                            softmax_scale, stream);
 }

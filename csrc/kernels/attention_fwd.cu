@@ -380,7 +380,7 @@ using namespace b200;
 // lse: [B, H, T] fp32.  key_mask: [B, T] uint8 or NULL.
 static int attention_fwd_impl(const void* qkv, void* out, float* lse, const uint8_t* key_mask,
                               int B, int T, int H, int head_dim, const DropoutParams& drop,
-                              cudaStream_t stream) {
+                              float softmax_scale, cudaStream_t stream) {
   B200_REQUIRE(head_dim == attn::HD, "attention: the tcgen05 kernel is specialised for head_dim 64");
   B200_REQUIRE(B > 0 && T > 0 && H > 0, "attention: empty problem");
   const int d = H * attn::HD;
@@ -393,7 +393,10 @@ static int attention_fwd_impl(const void* qkv, void* out, float* lse, const uint
     return 1;
   attn::FwdParams p;
   p.B = B; p.T = T; p.H = H;
-  p.scale_log2 = 1.4426950408889634f / std::sqrt(float(head_dim));
+  // softmax_scale > 0 overrides head_dim^-0.5 (heads narrower than 64 run zero-padded to 64 lanes
+  // and keep the scale of their true width)
+  p.scale_log2 = 1.4426950408889634f *
+                 (softmax_scale > 0.f ? softmax_scale : 1.0f / std::sqrt(float(head_dim)));
   p.key_mask = key_mask;
   p.lse = lse;
   p.drop = drop;
@@ -423,7 +426,7 @@ extern "C" int llmtrain_b200_attention_fwd(const void* qkv, void* out, float* ls
                                            const uint8_t* key_mask, int B, int T, int H,
                                            int head_dim, cudaStream_t stream) {
   return attention_fwd_impl(qkv, out, lse, key_mask, B, T, H, head_dim,
-                            make_dropout(0.f, 0, 0, 0), stream);
+                            make_dropout(0.f, 0, 0, 0), 0.f, stream);
 }
 
 // As above with dropout on the attention probabilities.  Mask element index:
@@ -435,5 +438,17 @@ extern "C" int llmtrain_b200_attention_fwd_dropout(const void* qkv, void* out, f
                                                    cudaStream_t stream) {
   B200_REQUIRE(p >= 0.f && p < 1.f, "attention_fwd_dropout: p must be in [0, 1)");
   return attention_fwd_impl(qkv, out, lse, key_mask, B, T, H, head_dim,
-                            make_dropout(p, seed, offset, site), stream);
+                            make_dropout(p, seed, offset, site), 0.f, stream);
+}
+
+// Everything at once (what the training engine calls): optional dropout (p = 0: none) and an
+// optional softmax scale (0 = head_dim^-0.5).
+extern "C" int llmtrain_b200_attention_fwd_fused(const void* qkv, void* out, float* lse,
+                                                 const uint8_t* key_mask, int B, int T, int H,
+                                                 int head_dim, float softmax_scale, float p,
+                                                 uint64_t seed, uint64_t offset, uint32_t site,
+                                                 cudaStream_t stream) {
+  B200_REQUIRE(p >= 0.f && p < 1.f, "attention_fwd_fused: p must be in [0, 1)");
+  return attention_fwd_impl(qkv, out, lse, key_mask, B, T, H, head_dim,
+                            make_dropout(p, seed, offset, site), softmax_scale, stream);
 }

@@ -184,13 +184,29 @@ int llmtrain_b200_attention_bwd_dropout(const void* qkv, const void* out, const 
                                         uint32_t site, llm_stream_t stream);
 
 /* attention backward with every option (what the engine calls): dropout as above (p = 0: none)
- * and, when dbias_qkv != NULL, dbias_qkv[3d] += column sums of dqkv = qkv_proj's bias gradient
+ * , softmax scale (0 = default) and, when dbias_qkv != NULL, dbias_qkv[3d] += column sums of dqkv = qkv_proj's bias gradient
  * (src/llmtrain/models/gpt.py:27) without another pass over dqkv.  fp32 atomics. */
 int llmtrain_b200_attention_bwd_fused(const void* qkv, const void* out, const void* dout,
                                       const float* lse, const uint8_t* key_mask, void* dqkv,
                                       float* dbias_qkv, void* scratch, size_t scratch_bytes, int B,
-                                      int T, int H, int head_dim, float p, uint64_t seed,
-                                      uint64_t offset, uint32_t site, llm_stream_t stream);
+                                      int T, int H, int head_dim, float softmax_scale, float p,
+                                      uint64_t seed, uint64_t offset, uint32_t site,
+                                      llm_stream_t stream);
+/* forward counterpart: softmax_scale = 0 means head_dim^-0.5; a positive value overrides it (heads
+ * narrower than 64 are run zero-padded to 64 lanes by the engine and keep their true scale). */
+int llmtrain_b200_attention_fwd_fused(const void* qkv, void* out, float* lse,
+                                      const uint8_t* key_mask, int B, int T, int H, int head_dim,
+                                      float softmax_scale, float p, uint64_t seed, uint64_t offset,
+                                      uint32_t site, llm_stream_t stream);
+
+/* Head padding (csrc/kernels/headpad.cu): heads narrower than 64 (any d_model % n_heads == 0 is
+ * legal in the reference, src/llmtrain/models/gpt.py:21-25) run zero-padded to 64 lanes.  A tensor
+ * is seen as [outer][groups][width][inner]; head_pad widens `width` from hd to 64 with zeros
+ * (elem_bytes 2 = bf16, 4 = fp32), head_unpad_add folds an fp32 gradient back (dst += src). */
+int llmtrain_b200_head_pad(const void* src, void* dst, long long outer, int groups, int hd,
+                           long long inner, int elem_bytes, llm_stream_t stream);
+int llmtrain_b200_head_unpad_add(const float* src, float* dst, long long outer, int groups, int hd,
+                                 long long inner, llm_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
  * GPT runtime (csrc/engine/gpt_engine.cu).  Replaces autograd over GPT.forward + compute_loss

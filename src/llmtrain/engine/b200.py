@@ -47,13 +47,19 @@ _LAYER_FIELDS = (
 
 
 def supports(model: nn.Module) -> bool:
-    """Can the native runtime execute this module?  (GPT with head_dim 64 on CUDA.)"""
+    """Can the native runtime execute this module?
+
+    GPT on CUDA with heads of width 8, 16, ..., 64: the attention kernels are written for 64-wide
+    heads and the engine runs narrower ones zero-padded (``csrc/kernels/headpad.cu``), which covers
+    every preset of the reference (16- and 32-wide heads) as well as the GPT-2 family.
+    """
     from llmtrain.models.gpt import GPT
 
     return (
         isinstance(model, GPT)
         and model.d_model % model.n_heads == 0
-        and model.d_model // model.n_heads == 64
+        and model.d_model // model.n_heads <= 64
+        and (model.d_model // model.n_heads) % 8 == 0
         and model.d_model % 8 == 0
         and model.d_ff % 8 == 0
         and model.d_model <= 2048

@@ -17,7 +17,7 @@ checkpoints interchange with the reference in both directions.
   A missing native library is an error, never a silent fallback.  The torch-op path remains
   reachable on CUDA on purpose (``prefer_native = False`` / ``trainer.extra.engine: torch``):
   it is the on-device oracle for the equivalence tests and the path taken for shapes the kernels
-  do not cover (head_dim != 64).
+  do not cover (head_dim > 64).
 
 The causal mask is never materialised on the device (the attention kernel applies it
 implicitly); the ``causal_mask`` tensors exist only inside ``state_dict()`` for format parity,
