@@ -5,6 +5,8 @@ Run under torchrun with 2/4/8 ranks.  For each size: this repo's NVLink peer-mem
 (bf16 on the wire, fp32 accumulate, rank-ordered) vs NCCL ``all_reduce`` on fp32 as torch DDP
 issues it.  Device-timed (CUDA events), max over ranks.  Reported bandwidths:
 
+* ``nvls_*``: the NVLink-SHARP path (``multimem.ld_reduce`` / ``multimem.st``, fp32 on the wire,
+  in place on a registered buffer), when multicast objects are available.
 * ``algbw``  = payload bytes / time                      (payload = n * 4 bytes of fp32 gradient)
 * ``busbw``  = algbw * 2 (W-1) / W                      (the NCCL-tests convention), vs 900 GB/s
   per direction per GPU nominal / 770 GB/s measured peer copy.
@@ -25,13 +27,17 @@ def main() -> int:
     import torch
     import torch.distributed as dist
 
-    from llmtrain.parallel.nvl import NvlComm
+    from llmtrain.parallel.nvl import NvlComm, NvlsTeam
 
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
     dist.init_process_group("cpu:gloo,cuda:nccl")
     sizes = [1 << p for p in range(10, 31, 2)]  # bytes of fp32 payload: 1 KB .. 1 GB
     rows = []
+    # NVLink-SHARP team over one registered buffer big enough for the largest payload (in-switch
+    # reduction, fp32 on the wire); None where multicast objects cannot be created.
+    anchor = NvlComm(1024, rank=rank, world=world, timeout_s=60)
+    team = NvlsTeam.try_create(anchor, max(sizes) // 4)
 
     def timed(fn, iters: int) -> float:
         for _ in range(3):
@@ -59,6 +65,10 @@ def main() -> int:
         buf = src.clone()
         nccl = timed(lambda: dist.all_reduce(buf, op=dist.ReduceOp.SUM), iters)
         comm.close()
+        nvls = None
+        count = n // (4 * world) * (4 * world)
+        if team is not None and count > 0:
+            nvls = timed(lambda: team.allreduce(None, None, count=count, scale=1.0 / world), iters)
         factor = 2.0 * (world - 1) / world
         row = {
             "payload_bytes": n * 4, "world": world,
@@ -67,9 +77,15 @@ def main() -> int:
             "nccl_busbw_GBs": round(n * 4 / nccl / 1e6 * factor, 1),
             "nvl_wire_bytes_in_per_gpu": int(n * 2 * (world - 1) / world + n * 4 * (world - 1) / world),
         }
+        if nvls is not None:
+            row["nvls_us"] = round(nvls * 1e3, 2)
+            row["nvls_busbw_GBs"] = round(count * 4 / nvls / 1e6 * factor, 1)
         rows.append(row)
         if rank == 0:
             print(json.dumps(row), flush=True)
+    if team is not None:
+        team.close()
+    anchor.close()
     dist.barrier()
     dist.destroy_process_group()
     return 0

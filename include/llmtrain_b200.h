@@ -285,6 +285,27 @@ int llmtrain_b200_nvl_finish_step(void* nvl_handle, float* g, float* p, float* m
                                   float eps, float weight_decay, int step, float grad_scale,
                                   float max_norm, llm_stream_t stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * NVLink-SHARP all-reduce (csrc/comm/nvls.cu): the NVSwitch reduces in flight
+ * (multimem.ld_reduce / multimem.st on a multicast mapping).  Large-message alternative to the
+ * peer-to-peer two-shot scheme for what DistributedDataParallel's NCCL all-reduce does in the
+ * reference (src/llmtrain/training/trainer.py:87-91).  Setup, all ranks in lock step:
+ *   create -> (rank 0) export 80 bytes -> caller broadcasts them -> connect -> host barrier ->
+ *   bind -> host barrier.  Cross-GPU ordering inside collectives uses nvl_handle's flag barrier.
+ * ------------------------------------------------------------------------------------------- */
+int llmtrain_b200_nvls_supported(void);
+int llmtrain_b200_nvls_create(void* nvl_handle, int rank, int world, size_t n, int use_fabric,
+                              void** handle);
+int llmtrain_b200_nvls_export(void* handle, void* out_80_bytes);
+int llmtrain_b200_nvls_connect(void* handle, const void* wire_80_bytes);
+int llmtrain_b200_nvls_bind(void* handle);
+void* llmtrain_b200_nvls_buffer(void* handle);
+/* buffer[i] := scale * sum_r buffer_r[i] on every rank (count % (4*world) == 0).  in / out: optional
+ * fp32 [count] copied in before / out after; NULL, NULL runs the collective alone, in place. */
+int llmtrain_b200_nvls_allreduce(void* handle, const float* in, float* out, size_t count,
+                                 float scale, llm_stream_t stream);
+void llmtrain_b200_nvls_destroy(void* handle);
+
 #ifdef __cplusplus
 }
 #endif

@@ -166,6 +166,93 @@ class NvlComm:
             self._handle = ctypes.c_void_p()
 
 
+class NvlsTeam:
+    """NVLink-SHARP all-reduce over a registered fp32 buffer (``csrc/comm/nvls.cu``).
+
+    The NVSwitch adds the ranks' values in flight: every rank pulls its 1/W slice with
+    ``multimem.ld_reduce`` and pushes the result with ``multimem.st``.  Needs a device that reports
+    multicast support; :func:`NvlsTeam.try_create` returns ``None`` (with the reason logged) when
+    the driver or the fabric does not offer it, so callers keep using :class:`NvlComm`.
+    """
+
+    def __init__(self, comm: NvlComm, n: int, *, use_fabric: bool = True) -> None:
+        self._lib = native.lib()
+        self._lib.llmtrain_b200_nvls_buffer.restype = ctypes.c_void_p
+        self._comm = comm
+        self.n = n
+        self._handle = ctypes.c_void_p()
+        world = comm.world
+
+        def stage(what: str, fn: Any) -> None:
+            """Run one setup step everywhere; if ANY rank failed, every rank raises (no hangs)."""
+            err = ""
+            try:
+                fn()
+            except Exception as exc:  # noqa: BLE001  (re-raised collectively below)
+                err = f"{what}: {exc}"
+            seen: list[Any] = [None] * world
+            dist.all_gather_object(seen, err)
+            bad = [e for e in seen if e]
+            if bad:
+                self.close()
+                raise RuntimeError(bad[0])
+
+        handle = ctypes.c_void_p()
+        stage("nvls_create", lambda: check(
+            self._lib.llmtrain_b200_nvls_create(
+                comm._handle, ctypes.c_int(comm.rank), ctypes.c_int(world), ctypes.c_size_t(n),
+                ctypes.c_int(1 if use_fabric else 0), ctypes.byref(handle)),
+            "nvls_create"))
+        self._handle = handle
+        wire = (ctypes.c_ubyte * 80)()
+        if comm.rank == 0:
+            stage("nvls_export",
+                  lambda: check(self._lib.llmtrain_b200_nvls_export(handle, wire), "nvls_export"))
+        else:
+            stage("nvls_export", lambda: None)
+        payload: list[Any] = [bytes(wire) if comm.rank == 0 else None]
+        dist.broadcast_object_list(payload, src=0)
+        shared = (ctypes.c_ubyte * 80).from_buffer_copy(payload[0])
+        # (the all-gather inside stage() doubles as the host barrier the driver API asks for:
+        # every device has joined the multicast object before anyone binds memory to it)
+        stage("nvls_connect",
+              lambda: check(self._lib.llmtrain_b200_nvls_connect(handle, shared), "nvls_connect"))
+        stage("nvls_bind", lambda: check(self._lib.llmtrain_b200_nvls_bind(handle), "nvls_bind"))
+
+    @classmethod
+    def try_create(cls, comm: NvlComm, n: int) -> NvlsTeam | None:
+        lib = native.lib()
+        if not lib.llmtrain_b200_nvls_supported():
+            logger.info("nvls: multicast is not supported on this device/driver")
+            return None
+        # one node: a POSIX file descriptor (picked up with pidfd_getfd) is the natural handle;
+        # fabric handles need the IMEX service and are only tried second
+        for use_fabric in (False, True):
+            try:
+                return cls(comm, n, use_fabric=use_fabric)
+            except RuntimeError as exc:  # raised on every rank together, see stage()
+                logger.info("nvls: %s handles unavailable (%s)",
+                            "fabric" if use_fabric else "posix-fd", exc)
+        return None
+
+    def allreduce(self, src: torch.Tensor | None, dst: torch.Tensor | None, *,
+                  count: int | None = None, scale: float = 1.0) -> None:
+        """``dst = scale * sum_r src_r`` (fp32).  ``src``/``dst`` ``None``: in place on the buffer."""
+        n = count if count is not None else (src.numel() if src is not None else self.n)
+        check(
+            self._lib.llmtrain_b200_nvls_allreduce(
+                self._handle, ptr(src), ptr(dst), ctypes.c_size_t(n), ctypes.c_float(scale),
+                stream_handle(),
+            ),
+            "nvls_allreduce",
+        )
+
+    def close(self) -> None:
+        if self._handle:
+            self._lib.llmtrain_b200_nvls_destroy(self._handle)
+            self._handle = ctypes.c_void_p()
+
+
 class _NvlTrainComm:
     """Adapter with the face the train engine expects.
 

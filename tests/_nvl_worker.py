@@ -122,10 +122,64 @@ def _check_trainer(rank: int, world: int, overlap: bool = True) -> None:
     return result.final_loss
 
 
+def _check_nvls(rank: int, world: int) -> None:
+    """NVLink-SHARP all-reduce (multimem) against an fp32 sum of the gathered inputs."""
+    from llmtrain.parallel.nvl import NvlComm, NvlsTeam, shutdown
+
+    comm = NvlComm(1024 * 1024, rank=rank, world=world, timeout_s=60)
+    n = 4 * 1024 * 1024
+    team = NvlsTeam.try_create(comm, n)
+    if team is None:
+        if rank == 0:
+            print("NVLS_UNAVAILABLE", flush=True)
+        shutdown()
+        return
+    for count, scale in ((n, 1.0), (n // 2, 1.0 / world), (16 * world, 3.0)):
+        torch.manual_seed(17 + rank)
+        src = torch.randn(count, device="cuda") * (rank + 1)
+        out = torch.empty(count, device="cuda")
+        team.allreduce(src, out, scale=scale)
+        torch.cuda.synchronize()
+        parts = [torch.empty_like(src) for _ in range(world)]
+        dist.all_gather(parts, src)
+        want = torch.stack(parts).double().sum(0) * scale
+        err = (out.double() - want).abs().max().item() / (want.abs().max().item() + 1e-12)
+        assert err < 1e-5, f"rank {rank}: nvls allreduce rel err {err:.3e} at count {count}"
+        others = [torch.empty_like(out) for _ in range(world)]
+        dist.all_gather(others, out)
+        assert all(torch.equal(others[0], o) for o in others), "ranks disagree on the result"
+    # in place on the registered buffer, timed
+    team.allreduce(None, None, count=n)
+    torch.cuda.synchronize()
+    start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    start.record()
+    for _ in range(10):
+        team.allreduce(None, None, count=n)
+    stop.record()
+    torch.cuda.synchronize()
+    ms = start.elapsed_time(stop) / 10
+    if rank == 0:
+        print(f"NVLS_OK {n * 4 / 1e6:.0f} MB in {ms * 1e3:.0f} us", flush=True)
+    team.close()
+    shutdown()
+
+
 def main() -> int:
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
     dist.init_process_group("cpu:gloo,cuda:nccl")
+    if len(sys.argv) > 1 and sys.argv[1] == "nvls":
+        import logging
+
+        logging.basicConfig(level=logging.INFO if rank == 0 else logging.WARNING)
+        try:
+            _check_nvls(rank, world)
+            dist.barrier()
+            if rank == 0:
+                print("NVL_WORKER_OK", flush=True)
+        finally:
+            dist.destroy_process_group()
+        return 0
     try:
         from llmtrain.parallel.nvl import NvlComm, shutdown
 
