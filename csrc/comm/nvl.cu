@@ -81,6 +81,10 @@ struct Comm {
   unsigned long long timeout_ns = 1800ull * 1000000000ull;
   bool peers_open = false;
   uint32_t oneshot_calls = 0;
+  // NVLink-SHARP mode of the overlapped path (llmtrain_b200_nvl_attach_nvls): the gradient arena
+  // itself lives in multicast-bound memory; nvls_uc is this rank's view, nvls_mc the team's.
+  float* nvls_uc = nullptr;
+  float* nvls_mc = nullptr;
 };
 
 __device__ __forceinline__ unsigned long long now_ns() {
@@ -292,6 +296,34 @@ scatter_push_kernel(Peers peers, size_t lo, size_t len, float* __restrict__ part
     partial[blockIdx.x * (OVL_THREADS / 32) + (threadIdx.x >> 5)] = sq;
 }
 
+// NVLink-SHARP bucket reduction, in place on the gradient arena: this rank's sub-slice is summed
+// over all ranks INSIDE the switch (multimem.ld_reduce) and the sum is written back to every
+// rank's arena (multimem.st).  No pack, no send buffer, no gather; 1/W of the bucket per rank and
+// two instructions per 16 bytes, so it disturbs the backward GEMMs it runs next to far less than
+// the peer-to-peer pull.  Also leaves the slice's sum of squares (global-norm clipping).
+__global__ void __launch_bounds__(OVL_THREADS, 4)
+nvls_bucket_kernel(float* __restrict__ mc, size_t lo, size_t len, float* __restrict__ partial) {
+  const size_t n4 = len >> 2;
+  float* base = mc + lo;
+  float sq = 0.f;
+  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n4;
+       i += size_t(gridDim.x) * blockDim.x) {
+    float4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                 : "l"(base + 4 * i)
+                 : "memory");
+    sq += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(base + 4 * i),
+                 "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+                 : "memory");
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
+  if ((threadIdx.x & 31) == 0)
+    partial[blockIdx.x * (OVL_THREADS / 32) + (threadIdx.x >> 5)] = sq;
+}
+
 __global__ void __launch_bounds__(OVL_THREADS, 4)
 pack_range_kernel(const float* __restrict__ g, __nv_bfloat16* __restrict__ send, size_t lo,
                   size_t len) {
@@ -308,9 +340,9 @@ pack_range_kernel(const float* __restrict__ g, __nv_bfloat16* __restrict__ send,
 
 // Local AdamW over the complete reduced gradient in `full` (overlapped path).
 __global__ void __launch_bounds__(THREADS)
-adamw_full_kernel(Peers peers, int world, size_t n, const float* __restrict__ full,
-                  float* __restrict__ p, float* __restrict__ m, float* __restrict__ v,
-                  float* __restrict__ g, __nv_bfloat16* __restrict__ p16,
+adamw_full_kernel(Peers peers, int world, size_t n, const float* full /* may alias g */,
+                  float* __restrict__ p, float* __restrict__ m, float* __restrict__ v, float* g,
+                  __nv_bfloat16* __restrict__ p16,
                   float* __restrict__ norm_out, Adam a) {
   float total = 0.f;
   for (int r = 0; r < world; ++r)
@@ -325,7 +357,7 @@ adamw_full_kernel(Peers peers, int world, size_t n, const float* __restrict__ fu
   const size_t n4 = n >> 2;
   for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n4;
        i += size_t(gridDim.x) * blockDim.x) {
-    const float4 gr = __ldg(reinterpret_cast<const float4*>(full) + i);
+    const float4 gr = reinterpret_cast<const float4*>(full)[i];
     float4 pv = reinterpret_cast<float4*>(p)[i];
     float4 mv = reinterpret_cast<float4*>(m)[i];
     float4 vv = reinterpret_cast<float4*>(v)[i];
@@ -611,6 +643,23 @@ int reduce_bucket(void* raw, size_t lo, size_t len) {
   // Ranges touching either end of the arena are the embedding tables: backward is finished.
   const bool tail = (lo == 0) || (lo + len == c.n);
   const int grid = tail ? nvl::TAIL_GRID : c.bucket_grid;
+  if (c.nvls_mc != nullptr && h.g == c.nvls_uc) {
+    // NVLink-SHARP mode: the arena is multicast-bound, the switch does the sum.
+    if (nvl::launch_barrier(c, cs)) return 1;  // every rank's bucket is final
+    size_t nsub = (len + c.world - 1) / c.world;
+    nsub = (nsub + 7) / 8 * 8;
+    const size_t nlo = lo + size_t(c.rank) * nsub;
+    const size_t nhi = nlo + nsub < lo + len ? nlo + nsub : lo + len;
+    const size_t nlen = nhi > nlo ? nhi - nlo : 0;
+    float* npart = c.bucket_partials + size_t(b) * nvl::PARTIAL_STRIDE;
+    B200_CHECK_CUDA(cudaMemsetAsync(npart, 0, nvl::PARTIAL_STRIDE * sizeof(float), cs));
+    if (nlen > 0) {
+      nvl::nvls_bucket_kernel<<<grid, nvl::OVL_THREADS, 0, cs>>>(c.nvls_mc, nlo, nlen, npart);
+      B200_CHECK_CUDA(cudaGetLastError());
+      B200_COUNT_LAUNCH(1);
+    }
+    return 0;
+  }
   nvl::pack_range_kernel<<<grid, nvl::OVL_THREADS, 0, cs>>>(h.g, c.send, lo, len);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
@@ -684,11 +733,26 @@ extern "C" int llmtrain_b200_nvl_finish_step(void* nvl_handle, float* g, float* 
   a.bias_corr1 = static_cast<float>(1.0 - std::pow(double(beta1), double(step)));
   a.bias_corr2_sqrt = static_cast<float>(std::sqrt(1.0 - std::pow(double(beta2), double(step))));
   a.grad_scale = grad_scale; a.max_norm = max_norm;
+  // NVLink-SHARP mode: the reduced gradient is the arena itself
+  const float* reduced = (c.nvls_mc != nullptr && g == c.nvls_uc) ? g : c.full;
   nvl::adamw_full_kernel<<<8 * sm_count(), nvl::THREADS, 0, s>>>(
-      c.peers, c.world, c.n, c.full, p, m, v, g, static_cast<__nv_bfloat16*>(p16), norm_out, a);
+      c.peers, c.world, c.n, reduced, p, m, v, g, static_cast<__nv_bfloat16*>(p16), norm_out, a);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   c.buckets_this_step = 0;
+  return 0;
+}
+
+// Switch the overlapped path to NVLink-SHARP: `uc` / `mc` are this rank's and the team's view of a
+// multicast-bound fp32 buffer of at least n elements (llmtrain_b200_nvls_buffer / _mc_buffer).
+// From now on llmtrain_b200_nvl_backward_overlapped(.., g == uc, ..) reduces each bucket in the
+// switch, in place on g, and llmtrain_b200_nvl_finish_step reads the reduced gradient from g.
+// NULL, NULL detaches.
+extern "C" int llmtrain_b200_nvl_attach_nvls(void* handle, float* uc, float* mc) {
+  Comm& c = *static_cast<Comm*>(handle);
+  B200_REQUIRE((uc == nullptr) == (mc == nullptr), "nvl_attach_nvls: pass both views or neither");
+  c.nvls_uc = uc;
+  c.nvls_mc = mc;
   return 0;
 }
 

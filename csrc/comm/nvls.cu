@@ -305,6 +305,11 @@ extern "C" void* llmtrain_b200_nvls_buffer(void* handle) {
   return reinterpret_cast<void*>(static_cast<Team*>(handle)->ucast);
 }
 
+// The team's multicast view of the same buffer (only multimem.* instructions may touch it).
+extern "C" void* llmtrain_b200_nvls_mc_buffer(void* handle) {
+  return reinterpret_cast<void*>(static_cast<Team*>(handle)->mcast);
+}
+
 // buffer_r[i] := scale * sum_r buffer_r[i] on every rank, for i < count (count % (4*world) == 0).
 // If `in` is not NULL it is first copied into the buffer, if `out` is not NULL the result is
 // copied out (both fp32 [count]); pass NULL / NULL to time the collective alone.

@@ -299,7 +299,11 @@ int llmtrain_b200_nvls_create(void* nvl_handle, int rank, int world, size_t n, i
 int llmtrain_b200_nvls_export(void* handle, void* out_80_bytes);
 int llmtrain_b200_nvls_connect(void* handle, const void* wire_80_bytes);
 int llmtrain_b200_nvls_bind(void* handle);
-void* llmtrain_b200_nvls_buffer(void* handle);
+void* llmtrain_b200_nvls_buffer(void* handle);     /* this rank's view (ordinary memory) */
+void* llmtrain_b200_nvls_mc_buffer(void* handle);  /* the team's view (multimem.* only) */
+/* overlapped training path in NVLink-SHARP mode: the gradient arena passed to
+ * nvl_backward_overlapped / nvl_finish_step must then be `uc` itself (NULL, NULL detaches) */
+int llmtrain_b200_nvl_attach_nvls(void* nvl_handle, float* uc, float* mc);
 /* buffer[i] := scale * sum_r buffer_r[i] on every rank (count % (4*world) == 0).  in / out: optional
  * fp32 [count] copied in before / out after; NULL, NULL runs the collective alone, in place. */
 int llmtrain_b200_nvls_allreduce(void* handle, const float* in, float* out, size_t count,

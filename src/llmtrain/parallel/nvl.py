@@ -247,6 +247,32 @@ class NvlsTeam:
             "nvls_allreduce",
         )
 
+    def buffer_tensor(self, n: int | None = None) -> torch.Tensor:
+        """fp32 tensor aliasing this rank's view of the registered buffer (no copy)."""
+        n = self.n if n is None else n
+        assert 0 < n <= self.n
+        self._lib.llmtrain_b200_nvls_buffer.restype = ctypes.c_void_p
+        address = int(self._lib.llmtrain_b200_nvls_buffer(self._handle))
+
+        class _Raw:  # torch aliases device memory described by the CUDA array interface
+            __cuda_array_interface__ = {
+                "shape": (n,), "typestr": "<f4", "data": (address, False), "version": 3,
+                "strides": None,
+            }
+
+        raw = _Raw()
+        tensor = torch.as_tensor(raw, device=torch.device("cuda", torch.cuda.current_device()))
+        tensor._nvls_owner = (self, raw)  # type: ignore[attr-defined]  # keep the mapping alive
+        return tensor
+
+    def attach_to(self, comm: NvlComm) -> None:
+        """Put ``comm``'s overlapped bucket path into in-switch mode on this buffer."""
+        self._lib.llmtrain_b200_nvls_buffer.restype = ctypes.c_void_p
+        self._lib.llmtrain_b200_nvls_mc_buffer.restype = ctypes.c_void_p
+        uc = ctypes.c_void_p(self._lib.llmtrain_b200_nvls_buffer(self._handle))
+        mc = ctypes.c_void_p(self._lib.llmtrain_b200_nvls_mc_buffer(self._handle))
+        check(self._lib.llmtrain_b200_nvl_attach_nvls(comm._handle, uc, mc), "nvl_attach_nvls")
+
     def close(self) -> None:
         if self._handle:
             self._lib.llmtrain_b200_nvls_destroy(self._handle)
@@ -263,12 +289,23 @@ class _NvlTrainComm:
     after backward.
     """
 
-    def __init__(self, gpt: Any, comm: NvlComm, *, overlap: bool = True) -> None:
+    def __init__(self, gpt: Any, comm: NvlComm, *, overlap: bool = True,
+                 team: NvlsTeam | None = None) -> None:
         self._gpt, self._comm = gpt, comm
         self.overlap = overlap
         self._reduced = False
+        self._team = team
         self.name = ("nvl-p2p(per-layer buckets overlapped with backward: pack-bf16 -> "
                      "reduce+push -> local adamw)") if overlap else comm.name
+        if team is not None:
+            # NVLink-SHARP mode: the gradient arena IS the multicast-bound buffer, each bucket is
+            # summed inside the switch, in place (multimem.ld_reduce / multimem.st).
+            gpt.g32 = team.buffer_tensor(gpt.n_params)
+            gpt.g32.zero_()
+            gpt._bind()
+            team.attach_to(comm)
+            self.name = ("nvls(per-layer buckets overlapped with backward: in-switch "
+                         "multimem.ld_reduce/st in place on the fp32 gradient arena -> local adamw)")
 
     def backward_last(self) -> None:
         g = self._gpt
@@ -289,7 +326,24 @@ class _NvlTrainComm:
             self._comm.step(g.g32, g.p32, m, v, g.p16, norm, hyper)
 
     def close(self) -> None:
+        if self._team is not None:
+            check(self._comm._lib.llmtrain_b200_nvl_attach_nvls(self._comm._handle, None, None),
+                  "nvl_attach_nvls")
+            self._gpt.g32 = None  # the arena lived in the team's buffer
+            self._team.close()
+            self._team = None
         self._comm.close()
+
+
+def _want_nvls(world: int, overlap: bool) -> bool:
+    """In-switch reduction pays from 4 GPUs up (at 2 the bf16 peer-to-peer wire format is cheaper);
+    LLMTRAIN_NVLS=0/1 forces the choice."""
+    import os
+
+    forced = os.environ.get("LLMTRAIN_NVLS")
+    if forced is not None:
+        return overlap and forced != "0"
+    return overlap and world >= 4
 
 
 def try_create(gpt: Any, m: torch.Tensor, v: torch.Tensor, *, rank: int, world: int,
@@ -314,7 +368,10 @@ def try_create(gpt: Any, m: torch.Tensor, v: torch.Tensor, *, rank: int, world: 
     if int(failed.item()):
         comm.close()
         return None
-    return _NvlTrainComm(gpt, comm, overlap=overlap)
+    team = None
+    if _want_nvls(world, overlap) and gpt.n_params % (4 * world) == 0:
+        team = NvlsTeam.try_create(comm, gpt.n_params)
+    return _NvlTrainComm(gpt, comm, overlap=overlap, team=team)
 
 
 def shutdown() -> None:

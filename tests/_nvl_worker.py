@@ -92,7 +92,7 @@ def _check_step(comm, rank: int, world: int) -> None:
     assert all(torch.equal(others[0], o) for o in others), "replicas diverged"
 
 
-def _check_trainer(rank: int, world: int, overlap: bool = True) -> None:
+def _check_trainer(rank: int, world: int, overlap: bool = True, nvls: bool = False) -> None:
     from llmtrain.config.schemas import RunConfig
     from llmtrain.distributed import DDPState
     from llmtrain.training import Trainer
@@ -108,11 +108,14 @@ def _check_trainer(rank: int, world: int, overlap: bool = True) -> None:
         "ddp": {"enabled": True, "backend": "nvl"},
         "mlflow": {"enabled": False}, "logging": {"log_to_file": False}, "output": {},
     })
+    os.environ["LLMTRAIN_NVLS"] = "1" if nvls else "0"
     state = DDPState(rank=rank, world_size=world, local_rank=rank, is_main=rank == 0)
     trainer = Trainer(cfg, ddp_state=state)
     comm = trainer._engine._comm
     assert comm is not None and comm.name.startswith("nvl"), getattr(comm, "name", None)
     assert comm.overlap is overlap
+    if nvls and rank == 0:
+        print("TRAINER_COMM", comm.name.split("(")[0], flush=True)
     result = trainer.fit()
     assert result.final_loss < result.first_step_loss - 0.3, (result.first_step_loss, result.final_loss)
     flat = trainer._engine._gpt.p32.clone()
@@ -189,6 +192,9 @@ def main() -> int:
         _check_step(comm, rank, world)
         loss_overlapped = _check_trainer(rank, world, overlap=True)
         loss_serial = _check_trainer(rank, world, overlap=False)
+        # in-switch bucket reduction (falls back to the peer-to-peer path where multicast is absent)
+        loss_nvls = _check_trainer(rank, world, overlap=True, nvls=True)
+        assert abs(loss_nvls - loss_serial) < 2.0
         # same data, same init seed path? (fresh random init per trainer) -> only sanity-compare
         assert abs(loss_overlapped - loss_serial) < 2.0
         shutdown()
