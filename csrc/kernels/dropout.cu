@@ -78,7 +78,9 @@ extern "C" int llmtrain_b200_dropout(const void* x, void* y, long long rows, int
   const int padded = (cols + 7) & ~7;
   const long long n = rows * (padded >> 3);
   const DropoutParams dp = make_dropout(p, seed, offset, site);
-  B200_LAUNCH((drop::apply_kernel), unsigned((n + 255) / 256), 256, 0, stream, static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), rows, cols, ld, padded, dp);
+  B200_LAUNCH((drop::apply_kernel), unsigned((n + 255) / 256), 256, 0, stream,
+              static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), rows, cols, ld,
+              padded, dp);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   return 0;
@@ -95,7 +97,8 @@ extern "C" int llmtrain_b200_dropout_mask(uint8_t* out, long long rows, int cols
   const int padded = (cols + 7) & ~7;
   const long long n = rows * (padded >> 3);
   const DropoutParams dp = make_dropout(p, seed, offset, site);
-  B200_LAUNCH((drop::mask_kernel), unsigned((n + 255) / 256), 256, 0, stream, out, rows, cols, padded, dp);
+  B200_LAUNCH((drop::mask_kernel), unsigned((n + 255) / 256), 256, 0, stream, out, rows, cols,
+              padded, dp);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   return 0;

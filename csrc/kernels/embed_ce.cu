@@ -498,7 +498,8 @@ extern "C" int llmtrain_b200_synthetic_tokens(int64_t* ids, int64_t* labels, int
   B200_REQUIRE(vocab > 0 && rows >= 0 && T > 0, "synthetic_tokens: bad shape");
   if (rows == 0) return 0;
   const long long n = (long long)rows * T;
-  B200_LAUNCH((ew::synth_tokens_kernel), static_cast<unsigned>((n + 255) / 256), 256, 0, stream, ids, labels, rows, T, vocab, seed, first_row);
+  B200_LAUNCH((ew::synth_tokens_kernel), static_cast<unsigned>((n + 255) / 256), 256, 0, stream,
+              ids, labels, rows, T, vocab, seed, first_row);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   return 0;
@@ -510,7 +511,9 @@ extern "C" int llmtrain_b200_embed_fwd(const int64_t* ids, const void* wte, cons
   B200_REQUIRE(d % 8 == 0, "embed: d must be a multiple of 8");
   const int rows = B * T;
   if (rows == 0) return 0;
-  B200_LAUNCH((ew::embed_fwd_kernel), ceil_div(rows, 8), 256, 0, stream, ids, static_cast<const __nv_bfloat16*>(wte), static_cast<const __nv_bfloat16*>(wpe), static_cast<__nv_bfloat16*>(x), rows, T, d, vocab);
+  B200_LAUNCH((ew::embed_fwd_kernel), ceil_div(rows, 8), 256, 0, stream, ids,
+              static_cast<const __nv_bfloat16*>(wte), static_cast<const __nv_bfloat16*>(wpe),
+              static_cast<__nv_bfloat16*>(x), rows, T, d, vocab);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   return 0;
@@ -522,10 +525,12 @@ extern "C" int llmtrain_b200_embed_bwd(const int64_t* ids, const void* dx, float
   B200_REQUIRE(d % 8 == 0, "embed: d must be a multiple of 8");
   const int rows = B * T;
   if (rows == 0) return 0;
-  B200_LAUNCH((ew::embed_bwd_wte_kernel), ceil_div(rows, 8), 256, 0, stream, ids, static_cast<const __nv_bfloat16*>(dx), dwte, rows, d, vocab);
+  B200_LAUNCH((ew::embed_bwd_wte_kernel), ceil_div(rows, 8), 256, 0, stream, ids,
+              static_cast<const __nv_bfloat16*>(dx), dwte, rows, d, vocab);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
-  B200_LAUNCH((ew::embed_bwd_wpe_kernel), ceil_div(T * (d / 4), 256), 256, 0, stream, static_cast<const __nv_bfloat16*>(dx), dwpe, B, T, d);
+  B200_LAUNCH((ew::embed_bwd_wpe_kernel), ceil_div(T * (d / 4), 256), 256, 0, stream,
+              static_cast<const __nv_bfloat16*>(dx), dwpe, B, T, d);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   return 0;
@@ -552,18 +557,23 @@ extern "C" int llmtrain_b200_cross_entropy(void* logits, const int64_t* labels,
     }
     const int grid = rows < sm_count() ? rows : sm_count();
     if (write_grad)
-      B200_LAUNCH((ew::ce_row_kernel<true>), grid, ew::CE_ROW_THREADS, smem, stream, lg, labels, row_valid, loss_rows, rows, V, ldv, grad_scale);
+      B200_LAUNCH((ew::ce_row_kernel<true>), grid, ew::CE_ROW_THREADS, smem, stream, lg, labels,
+                  row_valid, loss_rows, rows, V, ldv, grad_scale);
     else
-      B200_LAUNCH((ew::ce_row_kernel<false>), grid, ew::CE_ROW_THREADS, smem, stream, lg, labels, row_valid, loss_rows, rows, V, ldv, grad_scale);
+      B200_LAUNCH((ew::ce_row_kernel<false>), grid, ew::CE_ROW_THREADS, smem, stream, lg, labels,
+                  row_valid, loss_rows, rows, V, ldv, grad_scale);
   } else if (write_grad) {
-    B200_LAUNCH((ew::ce_kernel<true>), rows, ew::CE_THREADS, 0, stream, lg, labels, row_valid, loss_rows, V, ldv, grad_scale);
+    B200_LAUNCH((ew::ce_kernel<true>), rows, ew::CE_THREADS, 0, stream, lg, labels, row_valid,
+                loss_rows, V, ldv, grad_scale);
   } else {
-    B200_LAUNCH((ew::ce_kernel<false>), rows, ew::CE_THREADS, 0, stream, lg, labels, row_valid, loss_rows, V, ldv, grad_scale);
+    B200_LAUNCH((ew::ce_kernel<false>), rows, ew::CE_THREADS, 0, stream, lg, labels, row_valid,
+                loss_rows, V, ldv, grad_scale);
   }
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   if (loss_acc != nullptr) {
-    B200_LAUNCH((ew::loss_reduce_kernel), 1, 1024, 0, stream, loss_rows, rows, loss_scale, loss_acc);
+    B200_LAUNCH((ew::loss_reduce_kernel), 1, 1024, 0, stream, loss_rows, rows, loss_scale,
+                loss_acc);
     B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   }
@@ -581,10 +591,12 @@ extern "C" int llmtrain_b200_bias_grad(const void* dy, int ld, int M, int N, flo
   const int splits = ew::colsum_splits(M, N);
   B200_REQUIRE(scratch_bytes >= size_t(splits) * N * sizeof(float), "bias_grad: scratch too small");
   dim3 grid(ceil_div(N, ew::CS_COLS), splits);
-  B200_LAUNCH((ew::colsum_partial_kernel), grid, ew::CS_WARPS * 32, 0, stream, static_cast<const __nv_bfloat16*>(dy), ld, M, N, static_cast<float*>(scratch));
+  B200_LAUNCH((ew::colsum_partial_kernel), grid, ew::CS_WARPS * 32, 0, stream,
+              static_cast<const __nv_bfloat16*>(dy), ld, M, N, static_cast<float*>(scratch));
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
-  B200_LAUNCH((ew::colsum_finish_kernel), ceil_div(N, 32), 256, 0, stream, static_cast<float*>(scratch), splits, N, dbias);
+  B200_LAUNCH((ew::colsum_finish_kernel), ceil_div(N, 32), 256, 0, stream,
+              static_cast<float*>(scratch), splits, N, dbias);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   return 0;
@@ -594,7 +606,8 @@ extern "C" int llmtrain_b200_cast_f32_to_bf16(const float* src, void* dst, size_
                                               cudaStream_t stream) {
   if (n == 0) return 0;
   const size_t threads = (n + 7) / 8;
-  B200_LAUNCH((ew::cast_kernel), static_cast<unsigned>((threads + 255) / 256), 256, 0, stream, src, static_cast<__nv_bfloat16*>(dst), n);
+  B200_LAUNCH((ew::cast_kernel), static_cast<unsigned>((threads + 255) / 256), 256, 0, stream, src,
+              static_cast<__nv_bfloat16*>(dst), n);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   return 0;
@@ -677,10 +690,12 @@ extern "C" int llmtrain_b200_bias_grad_noalloc(const void* dy, int ld, int M, in
   float* partials = nullptr;
   if (ew::noalloc_scratch(&partials)) return 1;
   dim3 grid(ceil_div(N, ew::CS_COLS), splits);
-  B200_LAUNCH((ew::colsum_partial_kernel), grid, ew::CS_WARPS * 32, 0, stream, static_cast<const __nv_bfloat16*>(dy), ld, M, N, partials);
+  B200_LAUNCH((ew::colsum_partial_kernel), grid, ew::CS_WARPS * 32, 0, stream,
+              static_cast<const __nv_bfloat16*>(dy), ld, M, N, partials);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
-  B200_LAUNCH((ew::colsum_finish_kernel), ceil_div(N, 32), 256, 0, stream, partials, splits, N, dbias);
+  B200_LAUNCH((ew::colsum_finish_kernel), ceil_div(N, 32), 256, 0, stream, partials, splits, N,
+              dbias);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   return 0;

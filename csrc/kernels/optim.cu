@@ -155,10 +155,12 @@ extern "C" int llmtrain_b200_grad_sumsq(const float* g, size_t n, float* out, in
   B200_REQUIRE((reinterpret_cast<uintptr_t>(g) & 15) == 0, "grad_sumsq: g must be 16-byte aligned");
   const int grid = optim::sumsq_grid(n);
   B200_REQUIRE(scratch_bytes >= size_t(grid) * sizeof(float), "grad_sumsq: scratch too small");
-  B200_LAUNCH((optim::sumsq_partial_kernel), grid, optim::THREADS, 0, stream, g, n, static_cast<float*>(scratch));
+  B200_LAUNCH((optim::sumsq_partial_kernel), grid, optim::THREADS, 0, stream, g, n,
+              static_cast<float*>(scratch));
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
-  B200_LAUNCH((optim::sumsq_finish_kernel), 1, optim::THREADS, 0, stream, static_cast<float*>(scratch), grid, out, accumulate);
+  B200_LAUNCH((optim::sumsq_finish_kernel), 1, optim::THREADS, 0, stream,
+              static_cast<float*>(scratch), grid, out, accumulate);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   return 0;
@@ -183,7 +185,8 @@ extern "C" int llmtrain_b200_adamw(float* p, float* m, float* v, float* g, void*
   const size_t want = (n / 4 + optim::THREADS - 1) / optim::THREADS;
   const size_t cap = size_t(8 * sm_count());
   const int grid = static_cast<int>(want < cap ? (want < 1 ? 1 : want) : cap);
-  B200_LAUNCH((optim::adamw_kernel), grid, optim::THREADS, 0, stream, p, m, v, g, static_cast<__nv_bfloat16*>(p_bf16), n, sumsq, norm_out, a, zero_grad);
+  B200_LAUNCH((optim::adamw_kernel), grid, optim::THREADS, 0, stream, p, m, v, g,
+              static_cast<__nv_bfloat16*>(p_bf16), n, sumsq, norm_out, a, zero_grad);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   return 0;
