@@ -20,6 +20,12 @@ test: ## CPU test-suite
 test-gpu: ## GPU test-suite (needs a B200)
 	$(PY) -m pytest tests -q -m gpu
 
+sanitize: ## compute-sanitizer memcheck + racecheck + synccheck over every native kernel (needs a B200)
+	$(PY) bench/sanitize_probe.py
+	scripts/sanitize.sh memcheck
+	scripts/sanitize.sh racecheck
+	scripts/sanitize.sh synccheck
+
 conformance: ## run the reference's own tests against this package
 	scripts/run_conformance.sh
 

@@ -246,3 +246,17 @@ def test_synthetic_tokens_are_shifted_in_range_and_reproducible() -> None:
     other, _ = K.synthetic_tokens(4, 257, 50257, seed=8, first_row=10)
     assert not torch.equal(ids, other)
     assert ids.float().mean().item() == pytest.approx(50257 / 2, rel=0.1)
+
+
+def test_every_kernel_probe_runs_clean() -> None:
+    """bench/sanitize_probe.py (the compute-sanitizer target) launches every native kernel once on
+    tiny shapes and checks results; running it here keeps the target itself from rotting."""
+    import importlib.util
+    from pathlib import Path
+
+    path = Path(__file__).resolve().parents[1] / "bench" / "sanitize_probe.py"
+    spec = importlib.util.spec_from_file_location("sanitize_probe", path)
+    assert spec is not None and spec.loader is not None
+    module = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(module)
+    assert module.main() == 0
