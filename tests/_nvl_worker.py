@@ -52,6 +52,43 @@ def _check_small_and_broadcast(comm, rank: int, world: int) -> None:
     assert torch.equal(buf, torch.full_like(buf, float(world)))
 
 
+def _stress_flags(comm, rank: int, world: int) -> None:
+    """Back-to-back collectives with ranks arriving in a different order every time (random device
+    sleeps): epoch flags must never be confused with an earlier round's (ABA), buffers never
+    overwritten while a slow peer still reads them."""
+    import random
+
+    rng = random.Random(1234)  # same sequence on every rank
+    n_small = 4096
+    big_src = torch.empty(comm._n, device="cuda")
+    big_out = torch.empty(comm._n, device="cuda")
+    for it in range(40):
+        late = rng.randrange(world)
+        cycles = rng.choice((0, 200_000, 2_000_000))
+        kind = rng.choice(("small", "big", "bcast"))
+        if rank == late and cycles:
+            torch.cuda._sleep(cycles)
+        if kind == "small":
+            src = torch.full((n_small,), float(rank + 1 + it), device="cuda")
+            out = torch.empty_like(src)
+            comm.allreduce_small(src, out, 1.0)
+            want = float(sum(r + 1 + it for r in range(world)))
+            torch.cuda.synchronize()
+            assert torch.equal(out, torch.full_like(out, want)), f"stress small it={it}"
+        elif kind == "big":
+            big_src.fill_(float(rank + it % 7))
+            comm.allreduce(big_src, big_out, 1.0)
+            want = float(sum(r + it % 7 for r in range(world)))
+            torch.cuda.synchronize()
+            assert torch.equal(big_out, torch.full_like(big_out, want)), f"stress big it={it}"
+        else:
+            root = rng.randrange(world)
+            buf = torch.full((777,), float(rank * 10 + it), device="cuda")
+            comm.broadcast(buf, root=root)
+            torch.cuda.synchronize()
+            assert torch.equal(buf, torch.full_like(buf, float(root * 10 + it))), f"bcast it={it}"
+
+
 def _check_step(comm, rank: int, world: int) -> None:
     from llmtrain.ops import kernels as K
 
@@ -189,6 +226,7 @@ def main() -> int:
         comm = NvlComm(8 * 1024 * 1024 + 64, rank=rank, world=world, timeout_s=60)
         _check_allreduce(comm, rank, world)
         _check_small_and_broadcast(comm, rank, world)
+        _stress_flags(comm, rank, world)
         _check_step(comm, rank, world)
         loss_overlapped = _check_trainer(rank, world, overlap=True)
         loss_serial = _check_trainer(rank, world, overlap=False)
