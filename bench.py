@@ -237,6 +237,20 @@ def run_ours(args: argparse.Namespace) -> dict[str, Any]:
         d2h = 4 + 4                       # loss + grad-norm scalars read at the per-step log
 
         comm = getattr(engine, "_comm", None)
+        # ---- exposed communication: the same steps with the gradient reduction switched off ----
+        # (every rank then applies its local gradient; the replicas diverge, nothing is timed after
+        # this).  exposed = step time with the bucket engine - step time without it, both
+        # device-timed, max over ranks, same process, same clocks.
+        exposed = None
+        if world > 1 and comm is not None:
+            engine._comm = None
+            try:
+                steps_device(2)
+                ms_local = _max_over_ranks(_timed(lambda: steps_device(args.steps), world), world)
+            finally:
+                engine._comm = comm
+            exposed = {"compute_only_ms_per_step": ms_local / args.steps,
+                       "exposed_comm_ms_per_step": (ms - ms_local) / args.steps}
         result = {
             "metric": METRIC,
             "value": value,
@@ -276,6 +290,8 @@ def run_ours(args: argparse.Namespace) -> dict[str, Any]:
             "gpu_launches": launches,
             "peak_memory_gb": torch.cuda.max_memory_allocated() / 2**30,
         }
+        if exposed is not None:
+            result["comm_exposed"] = exposed
         if phases:
             result["phase_ms_rank0"] = phases
         return result if rank == 0 else {}

@@ -395,6 +395,7 @@ class B200TrainEngine(TrainEngine):
         self._comm: Any | None = None
         self._prefetch = bool(cfg.trainer.extra.get("prefetch", True))
         self._prefetched: tuple[Any, ...] | None = None
+        self._last_seq_len = 0
         # Optional CUDA-event phase timeline (LLMTRAIN_PHASE_TIMING=1): forward / backward(+bucket
         # reductions) / reduce+optimiser, averaged per step in ``phase_ms``.
         import os
@@ -485,6 +486,7 @@ class B200TrainEngine(TrainEngine):
             if ids.shape[0] > g._plan[0] or ids.shape[1] > g._plan[1]:
                 g._replan(max(ids.shape[0], g._plan[0]), max(ids.shape[1], g._plan[1]))
             tokens += ids.numel()
+            self._last_seq_len = int(ids.shape[1])
             scale = 1.0 / (n_valid * accum_steps)
             marks = self._mark()
             g.run_forward(ids, labels, key_mask, mode=2, loss_acc=self._loss_acc,
@@ -571,5 +573,36 @@ class B200TrainEngine(TrainEngine):
     def peak_memory_bytes(self) -> float:
         return float(torch.cuda.max_memory_allocated(self._device))
 
-    def extra_metrics(self) -> dict[str, float]:
-        return {"train/grad_norm": float(self._norm.item())}
+    def model_flops_per_token(self, seq_len: int) -> float:
+        """Training FLOPs per token: 6 per matmul parameter (the tied table counts once, as the LM
+        head; the position table does no matmul) plus 12 * L * d * T for attention, the usual MFU
+        accounting (non-causal count)."""
+        m = self.model
+        n_matmul = sum(p.numel() for p in m.parameters()) - m.position_embedding.weight.numel()
+        if not m.tie_embeddings:
+            n_matmul -= m.token_embedding.weight.numel()
+        return 6.0 * n_matmul + 12.0 * m.n_layers * m.d_model * seq_len
+
+    @staticmethod
+    def _peak_tflops() -> float:
+        """Measured bf16 GEMM burst peak when the pod's MEASURED_PEAKS.json is present, else the
+        nominal dense B200 figure."""
+        import json
+        from pathlib import Path
+
+        for parent in Path(__file__).resolve().parents:
+            candidate = parent / "MEASURED_PEAKS.json"
+            if candidate.exists():
+                try:
+                    return float(json.loads(candidate.read_text())["bf16_tflops"])
+                except (OSError, ValueError, KeyError):
+                    break
+        return 2250.0
+
+    def extra_metrics(self, tokens_per_sec: float | None = None) -> dict[str, float]:
+        out = {"train/grad_norm": float(self._norm.item())}
+        if tokens_per_sec and self._last_seq_len:
+            tflops = tokens_per_sec * self.model_flops_per_token(self._last_seq_len) / 1e12
+            out["train/model_tflops_per_gpu"] = tflops
+            out["train/mfu"] = tflops / self._peak_tflops()
+        return out

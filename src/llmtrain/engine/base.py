@@ -57,6 +57,11 @@ class TrainEngine(abc.ABC):
     def peak_memory_bytes(self) -> float:
         return 0.0
 
-    def extra_metrics(self) -> dict[str, float]:
-        """Engine-specific metrics appended (never renaming the reference's keys)."""
+    def extra_metrics(self, tokens_per_sec: float | None = None) -> dict[str, float]:
+        """Engine-specific metrics appended (never renaming the reference's keys).
+
+        ``tokens_per_sec`` is this rank's rate over the interval being logged, for engines that
+        report utilisation.
+        """
+        del tokens_per_sec
         return {}

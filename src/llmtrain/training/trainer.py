@@ -319,7 +319,7 @@ class Trainer:
                         "train/tokens_per_sec": pooled["tokens"] / elapsed if elapsed > 0 else 0.0,
                         "train/tokens_total": float(tokens_global_total),
                         "train/step_time_sec": step_time,
-                        **self._engine.extra_metrics(),
+                        **self._engine.extra_metrics(rate),
                     },
                     step=step,
                 )
@@ -331,7 +331,7 @@ class Trainer:
                     "train/tokens_per_sec": rate,
                     "train/step_time_sec": step_time,
                     "train/tokens_total": float(tokens_local_total),
-                    **self._engine.extra_metrics(),
+                    **self._engine.extra_metrics(rate),
                 },
                 step=step,
             )
