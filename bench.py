@@ -18,6 +18,10 @@ with CUDA events on the launching stream, max over ranks:
 * ``e2e``    — the public API (``Trainer.fit``): every step copies its inputs from pinned host
   memory and reads the step's loss back to the host.
 
+For N > 1 a third, separate segment measures the exposed communication (the second half of the
+BASELINE metric): the same steps with the gradient reduction switched off, in the same process;
+``comm_exposed.exposed_comm_ms_per_step`` = step time with the bucket engine - step time without.
+
 Rank 0 prints ONE JSON line.  Clocks / throttle reasons are sampled (NVML) during the timed
 regions.  Inputs are far larger than L2 (weights + optimiser state alone are ~2 GB/step of
 traffic), which is recorded in ``config``.
