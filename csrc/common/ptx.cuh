@@ -108,10 +108,17 @@ __device__ __forceinline__ unsigned long long global_timer_ns() {
   asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
   return t;
 }
+// A kernel that redistributes registers with setmaxnreg must not contain a real function call:
+// ptxas then gives every region the smallest budget.  Such kernels define B200_MBAR_TRAP_INLINE
+// before including this header and get a bare trap (the CUDA error still names the kernel).
+#ifdef B200_MBAR_TRAP_INLINE
+__device__ __forceinline__ void mbar_timeout_trap() { __trap(); }
+#else
 static __device__ __noinline__ void mbar_timeout_trap() {
   printf("b200: mbarrier wait timed out (block %d thread %d)\n", blockIdx.x, threadIdx.x);
   __trap();
 }
+#endif
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
   const unsigned long long t0 = global_timer_ns();

@@ -20,10 +20,17 @@
 // buffer (16-byte vector reductions straight from registers) that a post-kernel converts into the
 // q third of that same gradient buffer.
 //
-// Pipeline.  P/dS live in TWO shared-memory buffers and dQ in two TMEM accumulators, which lets the
-// MMA warp issue S/dP of tile i+1 BEFORE dV/dK/dQ of tile i: the softmax-grad warps wait only for
-// the two score products while the three gradient products of the previous tile run underneath
-// their math, and dQ_i is drained one iteration late, when it has long completed.
+// Pipeline.  The tensor core executes its queue in order, so the issue order IS the schedule.  After
+// the softmax-grad warps hand over P_i / dS_i the MMA warp issues
+//     dV += P_i^T dO_i   ->   S_{i+1}, dP_{i+1}   ->   dK += dS_i^T Q_i   ->   dQ_i = dS_i K
+// P has ONE shared-memory buffer (its only reader, the dV product, is first in the queue and has
+// retired by the time S_{i+1}/dP_{i+1} complete, which is what the warps wait for before they write
+// P_{i+1}); dS has two, so dK/dQ of tile i run underneath the math of tile i+1; dQ has two TMEM
+// accumulators and is drained one iteration late.  The 32 KB saved on P buy a THIRD Q/dO stage:
+// the loads of tile i+2 are in flight while tile i is computed (with two stages the load of the
+// next tile could only start when dK of the previous one had retired, and its ~1 us latency sat
+// on the critical path of every iteration: tensor pipe 20% busy, softmax warps 45% of their time
+// waiting for S — profiles/attention_bwd_ncu_r1.md).
 
 #include "../common/host.cuh"
 #include "../common/philox.cuh"
@@ -42,11 +49,12 @@ constexpr int TMEM_COLS = 512;
 constexpr int COL_S = 0, COL_DP = 128, COL_DV = 256, COL_DK = 320, COL_DQ = 384;  // dQ: 2 x 64 cols
 constexpr int OFF_K = 0;
 constexpr int OFF_V = OFF_K + TILE;
-constexpr int OFF_Q = OFF_V + TILE;        // [2]
-constexpr int OFF_DO = OFF_Q + 2 * TILE;   // [2]
-constexpr int PDS_BYTES = 2 * TILE;         // one 128x128 bf16 tile = two 64-column regions
-constexpr int OFF_P = OFF_DO + 2 * TILE;    // [2] x 32 KB
-constexpr int OFF_DS = OFF_P + 2 * PDS_BYTES;  // [2] x 32 KB
+constexpr int NQ = 3;                        // Q / dO ring depth
+constexpr int OFF_Q = OFF_V + TILE;          // [NQ]
+constexpr int OFF_DO = OFF_Q + NQ * TILE;    // [NQ]
+constexpr int PDS_BYTES = 2 * TILE;          // one 128x128 bf16 tile = two 64-column regions
+constexpr int OFF_P = OFF_DO + NQ * TILE;    // 32 KB, single buffer
+constexpr int OFF_DS = OFF_P + PDS_BYTES;    // [2] x 32 KB
 constexpr int OFF_BAR = OFF_DS + 2 * PDS_BYTES;
 constexpr int SMEM = OFF_BAR + 256 + 1024;
 
@@ -61,7 +69,14 @@ struct Params {
   float* dbias;      // optional [3*H*64]: += column sums of dqkv (bias gradient of qkv_proj)
   DropoutParams drop;  // attention-probability dropout; threshold 0 = off
   int t_pad;           // T rounded up to 8: row pitch of the mask's element index
+  long long* trace;    // debug (LLMTRAIN_ATTN_TRACE): clock64 stamps of CTA 0, else nullptr
 };
+
+// trace layout: [role 0 = softmax-grad warp 0, 1 = MMA, 2 = TMA][iteration < 16][4 stamps]
+__device__ __forceinline__ void stamp(const Params& p, int role, int it, int k) {
+  if (p.trace != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && it < 16)
+    p.trace[(role * 16 + it) * 4 + k] = clock64();
+}
 
 // Mask modes of one 128x128 (query x key) tile, chosen warp-uniformly (the loops contain
 // .sync.aligned TMEM loads):
@@ -153,14 +168,14 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
                                              ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
   uint64_t* kv_full = bars + 0;
-  uint64_t* q_full = bars + 1;   // [2]
-  uint64_t* q_empty = bars + 3;  // [2]
-  uint64_t* s_full = bars + 5;
-  uint64_t* pds_full = bars + 6;
-  uint64_t* dq_full = bars + 7;  // [2]: dQ_i accumulates in TMEM buffer i&1 and is drained one
-                                 // iteration later, behind the next tile's softmax-grad
-  uint64_t* dkv_full = bars + 9;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 10);
+  uint64_t* q_full = bars + 1;         // [NQ]
+  uint64_t* q_empty = q_full + NQ;     // [NQ]
+  uint64_t* s_full = q_empty + NQ;
+  uint64_t* pds_full = s_full + 1;
+  uint64_t* dq_full = pds_full + 1;    // [2]: dQ_i accumulates in TMEM buffer i&1 and is drained
+                                       // one iteration later, behind the next tile's softmax-grad
+  uint64_t* dkv_full = dq_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(dkv_full + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nq = (p.T + BQ - 1) / BQ;
@@ -179,7 +194,7 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
     tma_prefetch_desc(&tmDO);
     tma_prefetch_desc(&tmDQKV);
     mbar_init(kv_full, 1);
-    for (int s = 0; s < 2; ++s) {
+    for (int s = 0; s < NQ; ++s) {
       mbar_init(&q_full[s], 1);
       mbar_init(&q_empty[s], 1);
     }
@@ -211,10 +226,12 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
     // ------------------------------- TMA producer -------------------------------------------
     if (lane == 0) {
       for (int it = 1; it < n_iter; ++it) {  // tile 0 was requested in the prologue
-        const int st = it & 1;
-        const uint32_t ph = (it >> 1) & 1;
+        const int st = it % NQ;
+        const uint32_t ph = uint32_t(it / NQ) & 1u;
         const int q0 = (jt + it) * BQ;
-        mbar_wait(&q_empty[st], ph ^ 1);
+        stamp(p, 2, it, 0);
+        mbar_wait(&q_empty[st], ph ^ 1u);
+        stamp(p, 2, it, 1);
         mbar_expect_tx(&q_full[st], 2 * TILE);
         tma_load_3d(smem + OFF_Q + st * TILE, &tmQKV, &q_full[st], h * HD, q0, b);
         tma_load_3d(smem + OFF_DO + st * TILE, &tmDO, &q_full[st], h * HD, q0, b);
@@ -228,10 +245,11 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
       constexpr uint32_t id_dq = umma_idesc_bf16(128, 64, false, true);   // dS K
       const uint32_t sK = smem_u32(smem + OFF_K), sV = smem_u32(smem + OFF_V);
       auto issue_scores = [&](int it) {  // S = Q K^T and dP = dO V^T of query tile `it`
-        const int st = it & 1;
+        const int st = it % NQ;
         const uint32_t sQ = smem_u32(smem + OFF_Q + st * TILE);
         const uint32_t sDO = smem_u32(smem + OFF_DO + st * TILE);
-        mbar_wait(&q_full[st], (it >> 1) & 1);
+        mbar_wait(&q_full[st], uint32_t(it / NQ) & 1u);
+        stamp(p, 1, it, 0);
         tc_fence_after_sync();
 #pragma unroll
         for (int k = 0; k < HD / 16; ++k)
@@ -246,19 +264,23 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
       mbar_wait(kv_full, 0);
       issue_scores(0);
       for (int it = 0; it < n_iter; ++it) {
-        const int st = it & 1;
+        const int st = it % NQ;
         const uint32_t sQ = smem_u32(smem + OFF_Q + st * TILE);
         const uint32_t sDO = smem_u32(smem + OFF_DO + st * TILE);
-        const uint32_t sP = smem_u32(smem + OFF_P + st * PDS_BYTES);
-        const uint32_t sDS = smem_u32(smem + OFF_DS + st * PDS_BYTES);
+        const uint32_t sP = smem_u32(smem + OFF_P);
+        const uint32_t sDS = smem_u32(smem + OFF_DS + (it & 1) * PDS_BYTES);
+        stamp(p, 1, it, 1);
         mbar_wait(pds_full, it & 1);  // P_it / dS_it are in smem, S_it / dP_it have left TMEM
+        stamp(p, 1, it, 2);
         tc_fence_after_sync();
-        if (it + 1 < n_iter) issue_scores(it + 1);  // first: the softmax-grad warps wait on these
-        // dV += P^T dO ; dK += dS^T Q   (A, B both MN-major: 16 q-rows = 2048 B per K step)
+        // dV += P^T dO   (A, B both MN-major: 16 q-rows = 2048 B per K step).  First in the queue:
+        // it is the only reader of the single P buffer.
 #pragma unroll
         for (int k = 0; k < BQ / 16; ++k)
           umma_ss(tmem + COL_DV, umma_smem_desc(sP + k * 2048, TILE, 1024),
                   umma_smem_desc(sDO + k * 2048, TILE, 1024), id_t, (it > 0) || (k > 0));
+        if (it + 1 < n_iter) issue_scores(it + 1);  // the softmax-grad warps wait on these
+        // dK += dS^T Q
 #pragma unroll
         for (int k = 0; k < BQ / 16; ++k)
           umma_ss(tmem + COL_DK, umma_smem_desc(sDS + k * 2048, TILE, 1024),
@@ -267,10 +289,11 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
         // dQ_i = dS K  (A K-major over 128 kv = two 64-wide regions; B = K_j MN-major)
 #pragma unroll
         for (int k = 0; k < BKV / 16; ++k)
-          umma_ss(tmem + COL_DQ + st * HD,
+          umma_ss(tmem + COL_DQ + (it & 1) * HD,
                   umma_smem_desc(sDS + (k >> 2) * TILE + (k & 3) * 32, 0, 1024),
                   umma_smem_desc(sK + k * 2048, TILE, 1024), id_dq, k > 0);
-        umma_commit(&dq_full[st]);
+        umma_commit(&dq_full[it & 1]);
+        stamp(p, 1, it, 3);
       }
       umma_commit(dkv_full);
     }
@@ -333,9 +356,11 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
                            ? kGeneral
                            : (it == 0 ? kDiag : kNoMask);
 
+      if (threadIdx.x == 0) stamp(p, 0, it, 0);
       mbar_wait(s_full, it & 1);
       tc_fence_after_sync();
-      uint8_t* rp = smem + OFF_P + (it & 1) * PDS_BYTES + half * TILE;
+      if (threadIdx.x == 0) stamp(p, 0, it, 1);
+      uint8_t* rp = smem + OFF_P + half * TILE;
       uint8_t* rd = smem + OFF_DS + (it & 1) * PDS_BYTES + half * TILE;
       const uint32_t t_row = tmem + lane_base + half * 64;
       const uint64_t mask_base =
@@ -358,8 +383,10 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
       tc_fence_before_sync();
       __syncwarp();
       if (lane == 0) mbar_arrive(pds_full);
+      if (threadIdx.x == 0) stamp(p, 0, it, 2);
 
       if (it > 0) drain_dq(it - 1);
+      if (threadIdx.x == 0) stamp(p, 0, it, 3);
     }
     drain_dq(n_iter - 1);
 
@@ -390,10 +417,10 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
     if (p.dbias != nullptr) {
       // qkv_proj's bias gradient is the column sum of dqkv: take the k and v thirds from the two
       // bf16 tiles just staged (warp w: rows 16w..16w+15, lane l: columns 2l, 2l+1; conflict-free
-      // in the swizzled layout), combine the eight warps through the idle second P buffer, and
+      // in the swizzled layout), combine the eight warps through the idle second dS buffer, and
       // add 128 values per CTA to global memory.  Rows past T hold exact zeros.  The q third comes
       // from dq_convert_kernel.
-      float* red = reinterpret_cast<float*>(smem + OFF_P + PDS_BYTES);  // [8][2][64]
+      float* red = reinterpret_cast<float*>(smem + OFF_DS + PDS_BYTES);  // [8][2][64]
 #pragma unroll
       for (int which = 0; which < 2; ++which) {
         const uint8_t* stage = smem + (which == 0 ? OFF_P : OFF_DS);
@@ -565,6 +592,12 @@ static int attention_bwd_impl(const void* qkv, const void* out, const void* dout
   p.dbias = dbias;
   p.drop = drop;
   p.t_pad = (T + 7) & ~7;
+  p.trace = nullptr;
+  static const bool want_trace = std::getenv("LLMTRAIN_ATTN_TRACE") != nullptr;
+  if (want_trace) {
+    B200_CHECK_CUDA(cudaMalloc(&p.trace, 3 * 16 * 4 * sizeof(long long)));
+    B200_CHECK_CUDA(cudaMemsetAsync(p.trace, 0, 3 * 16 * 4 * sizeof(long long), stream));
+  }
   static bool configured = false;
   if (!configured) {
     B200_CHECK_CUDA(cudaFuncSetAttribute(ab::bwd_kernel<false>,
@@ -580,6 +613,21 @@ static int attention_bwd_impl(const void* qkv, const void* out, const void* dout
     B200_LAUNCH((ab::bwd_kernel<false>), grid, ab::THREADS, ab::SMEM, stream, tQKV, tDO, tDQKV, p);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
+  if (p.trace != nullptr) {  // debug: timeline of the CTA with the most query tiles
+    static long long host[3 * 16 * 4];
+    B200_CHECK_CUDA(cudaMemcpyAsync(host, p.trace, sizeof(host), cudaMemcpyDeviceToHost, stream));
+    B200_CHECK_CUDA(cudaStreamSynchronize(stream));
+    const long long t0 = host[1];
+    for (int it = 0; it < 16 && host[it * 4] != 0; ++it) {
+      std::fprintf(stderr, "attn bwd trace it=%2d", it);
+      for (int role = 0; role < 3; ++role)
+        for (int k = 0; k < 4; ++k)
+          std::fprintf(stderr, "%s%7lld", k == 0 ? " |" : "",
+                       host[(role * 16 + it) * 4 + k] == 0 ? -1LL : host[(role * 16 + it) * 4 + k] - t0);
+      std::fprintf(stderr, "\n");
+    }
+    cudaFree(p.trace);
+  }
 
   {
     const int per_row = d / 8;

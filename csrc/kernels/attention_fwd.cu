@@ -2,28 +2,39 @@
 //
 // Replaces the reference's materialised attention (`src/llmtrain/models/gpt.py:56-70`: scores
 // (B,H,T,T) fp32, masked_fill, softmax, P@V — SURVEY §2.5 K4, work item W2).  Nothing of size T^2
-// ever reaches HBM: per (batch, head, 128-query tile) one CTA walks the key/value tiles up to the
-// diagonal.
+// ever reaches HBM.  One CTA per SM owns TWO
+// 128-row query tiles of one (batch, head) and everything the tensor core touches besides Q/K/V
+// lives in tensor memory:
 //
-//   TMA warp   : Q once, then K_j / V_j (3-D tensor maps over the fused [B, T, 3d] QKV buffer, so
-//                no permute/copy is ever made and rows past T read 0); K is reloaded as soon as
-//                S_j has consumed it, V as soon as PV_j has.
-//   MMA warp   : S = Q K_j^T   (SS, 128x128x64, accumulator in TMEM cols [0,128))
-//                PV = P_j V_j  (SS, 128x64x128, two TMEM accumulators of 64 cols), P_j read from a
-//                double-buffered bf16 smem tile, V_j consumed as an MN-major operand straight from
-//                its [kv, hd] layout.  Issue order: p_full(j) -> S_{j+1} -> PV_j.
-//   4 softmax warps: thread i owns query row i (= TMEM lane i): two passes over S (max, then
-//                exp2 + row-sum + bf16 pack into the swizzled P tile); PV_{j-1} is folded into the
-//                register-resident output AFTER P_j has been handed over, so the tensor-core
-//                latency of PV hides behind the next tile's softmax.
+//   TMEM  [  0,128) S_0   [128,256) S_1   [256,320) O_0   [320,384) O_1
+//         [384,448) P_0   [448,512) P_1      (P_t: bf16, two probabilities per 32-bit column)
+//
+//   warp 8  (TMA)  : Q_0, Q_1 once; K_j / V_j through a 3-deep ring shared by both query tiles.
+//   warp 9  (MMA)  : S_t = Q_t K_j^T (SS, 128x128x64) and O_t += P_t V_j (TS: the A operand is read
+//                    straight from TMEM, V_j MN-major from its TMA tile).  S_t(j+1) is issued as
+//                    soon as the softmax group has pulled S_t(j) into registers (~130 cycles after
+//                    it appeared), PV_t(j) when P_t(j) has been written: the score product of the
+//                    next tile runs underneath the exponentials of the current one and neither
+//                    product is on a softmax group's critical path.  The whole warp walks the loop
+//                    (uniform control flow keeps descriptors in uniform registers); one elected
+//                    lane issues.
+//   warps 0-3 / 4-7: softmax group of tile 0 / 1, one query row per thread.  ONE pass over S: the
+//                    whole 128-column row is pulled into registers, max, exp2, bf16 pack,
+//                    tcgen05.st back into TMEM.  O is never read in the steady state: the running
+//                    maximum is only raised (and O_t / l rescaled in place) when it grew by more
+//                    than 2^8, which keeps exp2(s - m_ref) <= 256 — exact in fp32 accumulation and
+//                    harmless in bf16 — and happens on the first tiles of a row only.
+//
+// setmaxnreg moves registers from the TMA/MMA warpgroup to the two softmax warpgroups (one row of
+// S is 128 live registers).  Work is scheduled heaviest first (most key tiles).
 //
 // Masking follows the reference's semantics: causal (col > row) and optional key padding are
-// excluded from the softmax; a query whose keys are ALL excluded yields zeros (the reference
-// zeroes such rows after out_proj, `gpt.py:73-74`).  LSE (natural log) is saved for backward.
-//
-// ~113 KB smem and 256 TMEM columns per CTA => two CTAs per SM, so one CTA's softmax overlaps
-// the other's tensor-core work.
+// excluded from the softmax; a query whose keys are ALL excluded yields zeros and LSE = -inf (the
+// reference zeroes such rows after out_proj, `gpt.py:73-74`).  LSE (natural log) is saved for
+// backward.  Rows past T read zeros through the 3-D tensor maps over the fused [B, T, 3d] QKV
+// buffer (no permute/copy is ever made) and are clipped on store.
 
+#define B200_MBAR_TRAP_INLINE  // see ptx.cuh: required by the setmaxnreg register split
 #include "../common/host.cuh"
 #include "../common/philox.cuh"
 #include "../common/ptx.cuh"
@@ -36,342 +47,525 @@ constexpr int BQ = 128;
 constexpr int BKV = 128;
 constexpr int HD = 64;
 constexpr int TILE_BYTES = 128 * HD * 2;  // 16 KB: 128 rows x 128 B
-constexpr int FWD_THREADS = 192;
-constexpr int FWD_TMEM_COLS = 256;
-constexpr int OFF_Q = 0;
-constexpr int OFF_K = OFF_Q + TILE_BYTES;          // single stage (reloaded once S_j has read it)
-constexpr int OFF_V = OFF_K + TILE_BYTES;          // single stage (reloaded once PV_j has read it)
-constexpr int OFF_P = OFF_V + TILE_BYTES;          // 2 x 32 KB: P_j is written while PV_{j-1} runs
-constexpr int P_BYTES = 2 * TILE_BYTES;
-constexpr int OFF_BAR = OFF_P + 2 * P_BYTES;
-constexpr int FWD_SMEM = OFF_BAR + 256;
+constexpr int THREADS = 384;              // 2 softmax warpgroups + {TMA, MMA, 2 idle} warpgroup
+constexpr int NST = 3;                    // K/V ring depth
+constexpr int TMEM_COLS = 512;
+constexpr int COL_S = 0;    // + 128 * t
+constexpr int COL_O = 256;  // + 64 * t
+constexpr int COL_P = 384;  // + 64 * t
+constexpr int OFF_Q = 0;                          // [2]
+constexpr int OFF_K = OFF_Q + 2 * TILE_BYTES;     // [NST]
+constexpr int OFF_V = OFF_K + NST * TILE_BYTES;   // [NST]
+constexpr int OFF_BAR = OFF_V + NST * TILE_BYTES;
+constexpr int SMEM = OFF_BAR + 512;
+constexpr float kRescaleThreshold = 8.0f;  // log2 units
+// Of every 4 consecutive column pairs, this many take their exponential on the FMA pipe (the rest
+// use MUFU.EX2, 16 per clock per SM — the scarce unit of this kernel: one 128x128 tile needs 1024
+// MUFU cycles against 512 tensor-core cycles).
+#ifndef B200_ATTN_POLY_OF4
+#define B200_ATTN_POLY_OF4 1
+#endif
+constexpr int kPolyOf4 = B200_ATTN_POLY_OF4;
 
-struct FwdParams {
-  int B, T, H;
-  float scale_log2;              // head_dim^-0.5 * log2(e)
-  const uint8_t* key_mask;       // [B, T] (1 = attend) or nullptr
-  float* lse;                    // [B, H, T]
-  DropoutParams drop;            // attention-probability dropout (`gpt.py:67`); threshold 0 = off
-  int t_pad;                     // T rounded up to 8: row pitch of the mask's element index
-};
+// 2^x for a pair, no MUFU: round-to-nearest split x = n + f (magic-number add), cubic minimax of
+// 2^f on [-0.5, 0.5] (relative error 7.7e-5, far inside bf16), exponent patched in by integer add.
+// Inputs below -126 (masked scores are -inf) are clamped: the result is ~1e-38, i.e. zero against
+// a row whose largest term is >= 2^-8.
+__device__ __forceinline__ void exp2_poly_pair(f32x2 x, float& e0, float& e1) {
+  float x0, x1;
+  unpack2(x, x0, x1);
+  x = pack2(fmaxf(x0, -126.f), fmaxf(x1, -126.f));
+  const f32x2 t = add2(x, splat2(12582912.f));           // low mantissa bits = round(x)
+  const f32x2 n = add2(t, splat2(-12582912.f));
+  const f32x2 f = fma2(n, splat2(-1.f), x);
+  f32x2 q = fma2(f, splat2(0.05508868396282196f), splat2(0.24260404706001282f));
+  q = fma2(q, f, splat2(0.6932762265205383f));
+  q = fma2(q, f, splat2(0.9999289512634277f));
+  float t0, t1, q0, q1;
+  unpack2(t, t0, t1);
+  unpack2(q, q0, q1);
+  e0 = __int_as_float(__float_as_int(q0) + (__float_as_int(t0) << 23));
+  e1 = __int_as_float(__float_as_int(q1) + (__float_as_int(t1) << 23));
+}
 
-// Mask modes of one 128x128 score tile:
-//   kNoMask   tile strictly below the diagonal, no key padding: no per-element work at all
-//   kDiag     the diagonal tile, no key padding.  Rows of warp w are 32w..32w+31 and kv0 == q0, so
-//             32-column chunk c is entirely kept for c < w, entirely dropped for c > w, and only
-//             chunk c == w needs the per-element test (column i of the chunk kept iff i <= lane).
-//             The decision is warp-uniform, dropped chunks cost four zero stores and no MUFU.
-//   kGeneral  key padding present: per-element causal + padding test.
-// (A first version ran the general test on every diagonal tile: 22% of the tiles took 40% of the
-// softmax warps' time.)
 enum MaskMode : int { kNoMask = 0, kDiag = 1, kGeneral = 2 };
 
-__device__ __forceinline__ bool keep_general(int col, int qrow, int T, const uint8_t* kmask) {
-  bool ok = col <= qrow;
-  if (kmask != nullptr && col < T) ok = ok && (kmask[col] != 0);
-  return ok;
+__device__ __forceinline__ void tmem_st_32x32b_x32(uint32_t taddr, const uint32_t* r) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+      "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]),
+      "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]),
+      "r"(r[16]), "r"(r[17]), "r"(r[18]), "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]),
+      "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]), "r"(r[28]), "r"(r[29]),
+      "r"(r[30]), "r"(r[31])
+      : "memory");
 }
 
-// max over this thread's row of the 128-column S tile
-template <int MODE>
-__device__ __forceinline__ float row_max(uint32_t t_row, int kv0, int qrow, int T,
-                                         const uint8_t* kmask, int wchunk, int lane) {
-  float mx = -INFINITY;
-#pragma unroll 1
-  for (int c = 0; c < BKV / 32; ++c) {
-    if (MODE == kDiag && c > wchunk) break;
-    uint32_t v[32];
-    tmem_ld_32x32b_x32(t_row + c * 32, v);
-    tmem_ld_wait();
-    if (MODE == kNoMask || (MODE == kDiag && c < wchunk)) {
-#pragma unroll
-      for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(v[i]));
-    } else if (MODE == kDiag) {
-#pragma unroll
-      for (int i = 0; i < 32; ++i)
-        if (i <= lane) mx = fmaxf(mx, __uint_as_float(v[i]));
-    } else {
-#pragma unroll
-      for (int i = 0; i < 32; ++i)
-        if (keep_general(kv0 + c * 32 + i, qrow, T, kmask)) mx = fmaxf(mx, __uint_as_float(v[i]));
-    }
-  }
-  return mx;
+template <int N>
+__device__ __forceinline__ void reg_alloc() {
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N));
+}
+template <int N>
+__device__ __forceinline__ void reg_dealloc() {
+  asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N));
 }
 
-// p = exp2(s*scale - m) -> bf16 into the K-major 128B-swizzled P tile; returns the row sum
-// DROP: the probabilities handed to the PV product are dropped and rescaled; the row sum (the
-// softmax normaliser) is taken BEFORE dropout, as in softmax -> nn.Dropout.  `mask_base` is the
-// mask element index of (this row, column kv0).
+struct Params {
+  int B, T, H;
+  int nqb;                  // query blocks (256 rows) per sequence
+  float scale_log2;         // softmax scale * log2(e)
+  const uint8_t* key_mask;  // [B, T] (1 = attend) or nullptr
+  float* lse;               // [B, H, T]
+  DropoutParams drop;
+  int t_pad;
+  long long* trace;  // debug (LLMTRAIN_ATTN_TRACE): clock64 stamps of CTA 0, else nullptr
+};
+
+// trace layout: [role 0/1 = softmax group, 2 = MMA, 3 = inside softmax group 0][tile j < 32][4]
+__device__ __forceinline__ void stamp(const Params& p, int role, int j, int k) {
+  if (p.trace != nullptr && blockIdx.x == 0 && j < 32) p.trace[(role * 32 + j) * 4 + k] = clock64();
+}
+
+// One softmax step of one query row: S row (TMEM) -> P row (bf16, TMEM), running (m_ref, l).
 template <int MODE, bool DROP>
-__device__ __forceinline__ float exp_pack(uint32_t t_row, uint8_t* sP, int r, int kv0, int qrow,
-                                          int T, const uint8_t* kmask, float scale_log2,
-                                          float m_use, int wchunk, int lane,
-                                          const DropoutParams& dp, uint64_t mask_base) {
-  float sum = 0.f;
-#pragma unroll 1
+__device__ __forceinline__ void softmax_tile(uint32_t t_s, uint32_t t_p, uint32_t t_o,
+                                             uint64_t* s_read, uint64_t* pv_done, bool first,
+                                             uint32_t pv_parity, int kv0,
+                                             int qrow, int T, const uint8_t* kmask,
+                                             float scale_log2, float& m_ref, float& l_run, int wq,
+                                             int lane, const DropoutParams& dp,
+                                             uint64_t mask_base, const Params& prm, int tj,
+                                             bool tracer) {
+  uint32_t v[BKV / 32][32];
+  // chunks wholly above the diagonal (kDiag, c > wq) are never loaded
+#pragma unroll
   for (int c = 0; c < BKV / 32; ++c) {
-    uint8_t* region = sP + (c >> 1) * TILE_BYTES;
-    if (MODE == kDiag && c > wchunk) {  // whole chunk above the diagonal for every row of the warp
+    if (MODE == kDiag && c > wq) continue;
+    tmem_ld_32x32b_x32(t_s + c * 32, v[c]);
+    tmem_ld_wait();  // one load in flight: four back to back were measured 3x slower in total
+  }
+  // S_t is in registers: the tensor core may overwrite it with the next tile's scores
+  tc_fence_before_sync();
+  if (lane == 0) mbar_arrive(s_read);
+  if (tracer) stamp(prm, 3, tj, 0);
+
+  // masked scores become -inf: they drop out of the max and exp2 turns them into exact zeros
+  if (MODE == kDiag) {
 #pragma unroll
-      for (int q = 0; q < 4; ++q)
-        *reinterpret_cast<uint4*>(region + swizzle128(r * 128 + ((c & 1) * 4 + q) * 16)) =
-            make_uint4(0u, 0u, 0u, 0u);
-      continue;
-    }
-    uint32_t v[32];
-    tmem_ld_32x32b_x32(t_row + c * 32, v);
-    tmem_ld_wait();
-    uint32_t packed[16];
-    const bool plain = MODE == kNoMask || (MODE == kDiag && c < wchunk);
-    Rand8 rnd{};
+    for (int c = 0; c < BKV / 32; ++c) {
+      if (c == wq) {
 #pragma unroll
-    for (int i = 0; i < 32; i += 2) {
-      float e0 = fast_exp2(fmaf(__uint_as_float(v[i]), scale_log2, -m_use));
-      float e1 = fast_exp2(fmaf(__uint_as_float(v[i + 1]), scale_log2, -m_use));
-      if (!plain) {
-        if (MODE == kDiag) {
-          if (i > lane) e0 = 0.f;
-          if (i + 1 > lane) e1 = 0.f;
-        } else {
-          if (!keep_general(kv0 + c * 32 + i, qrow, T, kmask)) e0 = 0.f;
-          if (!keep_general(kv0 + c * 32 + i + 1, qrow, T, kmask)) e1 = 0.f;
-        }
+        for (int i = 0; i < 32; ++i)
+          if (i > lane) v[c][i] = 0xff800000u;
       }
-      sum += e0 + e1;
-      if (DROP) {
-        if ((i & 7) == 0) rnd = philox_group(dp, (mask_base + uint64_t(c * 32 + i)) >> 3);
-        e0 *= keep_factor(dp, rnd, i & 7);
-        e1 *= keep_factor(dp, rnd, (i & 7) + 1);
-      }
-      packed[i >> 1] = pack_bf16x2(e0, e1);
     }
+  } else if (MODE == kGeneral) {
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      const uint32_t off = swizzle128(r * 128 + ((c & 1) * 4 + q) * 16);
-      *reinterpret_cast<uint4*>(region + off) =
-          make_uint4(packed[4 * q], packed[4 * q + 1], packed[4 * q + 2], packed[4 * q + 3]);
+    for (int c = 0; c < BKV / 32; ++c) {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        const int col = kv0 + c * 32 + i;
+        bool ok = col <= qrow;
+        if (kmask != nullptr && col < T) ok = ok && (kmask[col] != 0);
+        if (!ok) v[c][i] = 0xff800000u;
+      }
     }
   }
-  return sum;
+
+  float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+  for (int c = 0; c < BKV / 32; ++c) {
+    if (MODE == kDiag && c > wq) continue;
+#pragma unroll
+    for (int i = 0; i < 32; i += 4) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) mx[u] = fmaxf(mx[u], __uint_as_float(v[c][i + u]));
+    }
+  }
+  const float m_tile = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])) * scale_log2;
+
+  // Raise the reference maximum only when it is far behind; the decision is warp-uniform because
+  // the rescale of O contains .sync.aligned TMEM accesses.
+  const bool grow = m_tile > m_ref + kRescaleThreshold;  // also true for the first finite maximum
+  // PV_t(j-1) must have retired before O_t is rescaled or P_t is overwritten.  It has, long ago;
+  // the check is deferred to the first P store so that its latency hides under the exponentials.
+  bool pv_checked = first;
+  if (__any_sync(0xffffffffu, grow)) {
+    const float m_new = fmaxf(m_ref, m_tile);
+    const float alpha = (m_new == -INFINITY) ? 1.f : fast_exp2(m_ref - m_new);  // -inf -> 0
+    l_run *= alpha;
+    if (!first) {
+      mbar_wait(pv_done, pv_parity);
+      tc_fence_after_sync();
+      pv_checked = true;
+#pragma unroll
+      for (int c = 0; c < HD / 32; ++c) {
+        uint32_t o[32];
+        tmem_ld_32x32b_x32(t_o + c * 32, o);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+        tmem_st_32x32b_x32(t_o + c * 32, o);
+      }
+    }
+    m_ref = m_new;
+  }
+  const float m_use = (m_ref == -INFINITY) ? 0.f : m_ref;
+  if (tracer) stamp(prm, 3, tj, 1);
+
+  const f32x2 sc2 = splat2(scale_log2), nm2 = splat2(-m_use);
+  f32x2 sum2 = splat2(0.f);
+#pragma unroll
+  for (int c = 0; c < BKV / 32; ++c) {
+    uint32_t pk[16];
+    if (MODE == kDiag && c > wq) {
+#pragma unroll
+      for (int i = 0; i < 16; ++i) pk[i] = 0u;
+    } else {
+      Rand8 rnd{};
+#pragma unroll
+      for (int i = 0; i < 32; i += 2) {
+        const f32x2 x2 =
+            fma2(pack2(__uint_as_float(v[c][i]), __uint_as_float(v[c][i + 1])), sc2, nm2);
+        float e0, e1;
+        if (MODE != kGeneral && ((i >> 1) & 3) < kPolyOf4) {
+          exp2_poly_pair(x2, e0, e1);
+        } else {
+          float x0, x1;
+          unpack2(x2, x0, x1);
+          e0 = fast_exp2(x0);
+          e1 = fast_exp2(x1);
+        }
+        sum2 = add2(sum2, pack2(e0, e1));
+        if (DROP) {
+          if ((i & 7) == 0) rnd = philox_group(dp, (mask_base + uint64_t(c * 32 + i)) >> 3);
+          e0 *= keep_factor(dp, rnd, i & 7);
+          e1 *= keep_factor(dp, rnd, (i & 7) + 1);
+        }
+        pk[i >> 1] = pack_bf16x2(e0, e1);
+      }
+    }
+    if (c == 0 && !pv_checked) {
+      mbar_wait(pv_done, pv_parity);
+      tc_fence_after_sync();
+    }
+    tmem_st_32x32b_x16(t_p + c * 16, pk);
+  }
+  float s0, s1;
+  unpack2(sum2, s0, s1);
+  l_run += s0 + s1;
+  if (tracer) stamp(prm, 3, tj, 2);
+  tmem_st_wait();
+  if (tracer) stamp(prm, 3, tj, 3);
 }
 
 template <bool DROP>
-__global__ void __launch_bounds__(FWD_THREADS, 2)
+__global__ void __launch_bounds__(THREADS, 1)
 fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmO,
-           const FwdParams p) {
-  // No static smem in this kernel, so the dynamic window starts at the (1024 B aligned) base of
-  // the CTA's shared memory; relying on that instead of padding keeps two CTAs resident per SM.
+           const Params p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
-  uint8_t* smem = smem_raw;
-  if ((smem_u32(smem) & 1023u) != 0) __trap();
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
-  uint64_t* q_full = bars + 0;
-  uint64_t* k_full = bars + 1;
-  uint64_t* k_empty = bars + 2;
-  uint64_t* v_full = bars + 3;
-  uint64_t* v_empty = bars + 4;
-  uint64_t* s_full = bars + 5;
-  uint64_t* p_full = bars + 6;
-  uint64_t* pv_done = bars + 7;   // [2], one per PV accumulator
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
+  uint64_t* q_full = bars + 0;                 // [2]
+  uint64_t* k_full = bars + 2;                 // [NST]
+  uint64_t* k_empty = k_full + NST;            // [NST]
+  uint64_t* v_full = k_empty + NST;            // [NST]
+  uint64_t* v_empty = v_full + NST;            // [NST]
+  uint64_t* s_full = v_empty + NST;            // [2]
+  uint64_t* p_full = s_full + 2;               // [2]
+  uint64_t* pv_done = p_full + 2;              // [2]
+  uint64_t* s_read = pv_done + 2;              // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(s_read + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int nq = (p.T + BQ - 1) / BQ;
-  const int qt = nq - 1 - int(blockIdx.x);  // heaviest (most kv tiles) first
-  const int h = blockIdx.y, b = blockIdx.z;
-  const int q0 = qt * BQ;
+  const int bh_count = p.B * p.H;
+  const int qb = p.nqb - 1 - int(blockIdx.x) / bh_count;  // heaviest query blocks first
+  const int bh = int(blockIdx.x) % bh_count;
+  const int b = bh / p.H, h = bh % p.H;
   const int d = p.H * HD;
-  const int n_kv = qt + 1;
+  const int q0 = qb * 2 * BQ;
+  // key tiles of query tile t: 0 .. (2 qb + t); a tile that starts past T is inactive
+  const int n0 = 2 * qb + 1;
+  const int n1 = (q0 + BQ < p.T) ? 2 * qb + 2 : 0;
+  const int n_max = n1 > n0 ? n1 : n0;
 
-  // The TMA thread initialises the barriers itself and requests Q, K_0, V_0 BEFORE the CTA-wide
-  // sync, so TMEM allocation and the barrier round trip overlap the load latency.
-  if (warp == 4 && lane == 0) {
+  if (warp == 8 && lane == 0) {
     tma_prefetch_desc(&tmQKV);
     tma_prefetch_desc(&tmO);
-    mbar_init(q_full, 1);
-    mbar_init(k_full, 1);
-    mbar_init(k_empty, 1);
-    mbar_init(v_full, 1);
-    mbar_init(v_empty, 1);
-    mbar_init(s_full, 1);
-    mbar_init(p_full, 4);
-    mbar_init(&pv_done[0], 1);
-    mbar_init(&pv_done[1], 1);
+    for (int t = 0; t < 2; ++t) {
+      mbar_init(&q_full[t], 1);
+      mbar_init(&s_full[t], 1);
+      mbar_init(&p_full[t], 4);
+      mbar_init(&pv_done[t], 1);
+      mbar_init(&s_read[t], 4);
+    }
+    for (int s = 0; s < NST; ++s) {
+      mbar_init(&k_full[s], 1);
+      mbar_init(&k_empty[s], 1);
+      mbar_init(&v_full[s], 1);
+      mbar_init(&v_empty[s], 1);
+    }
     fence_barrier_init();
     pdl_wait();  // qkv comes from the previous kernel of the stream
-    mbar_expect_tx(q_full, TILE_BYTES);
-    tma_load_3d(smem + OFF_Q, &tmQKV, q_full, h * HD, q0, b);
-    mbar_expect_tx(k_full, TILE_BYTES);
-    tma_load_3d(smem + OFF_K, &tmQKV, k_full, d + h * HD, 0, b);
-    mbar_expect_tx(v_full, TILE_BYTES);
-    tma_load_3d(smem + OFF_V, &tmQKV, v_full, 2 * d + h * HD, 0, b);
+    mbar_expect_tx(&q_full[0], TILE_BYTES);
+    tma_load_3d(smem + OFF_Q, &tmQKV, &q_full[0], h * HD, q0, b);
+    mbar_expect_tx(&k_full[0], TILE_BYTES);
+    tma_load_3d(smem + OFF_K, &tmQKV, &k_full[0], d + h * HD, 0, b, kEvictLast);
+    if (n1 > 0) {
+      mbar_expect_tx(&q_full[1], TILE_BYTES);
+      tma_load_3d(smem + OFF_Q + TILE_BYTES, &tmQKV, &q_full[1], h * HD, q0 + BQ, b);
+    }
+    mbar_expect_tx(&v_full[0], TILE_BYTES);
+    tma_load_3d(smem + OFF_V, &tmQKV, &v_full[0], 2 * d + h * HD, 0, b, kEvictLast);
   }
-  if (warp == 5) {
-    tmem_alloc(tmem_slot, FWD_TMEM_COLS);
+  if (warp == 9) {
+    tmem_alloc(tmem_slot, TMEM_COLS);
     tmem_relinquish();
   }
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
-  pdl_enter();  // everything above overlapped the previous kernel's tail
+  pdl_enter();
   const uint32_t tmem = *tmem_slot;
-  const uint32_t tmem_S = tmem;           // 128 columns
-  const uint32_t tmem_PV = tmem + 128;    // 2 x 64 columns
 
-  if (warp == 4) {
-    // ------------------------------- TMA producer -------------------------------------------
-    if (lane == 0) {
-      for (int j = 1; j < n_kv; ++j) {  // tile 0 was requested in the prologue
-        mbar_wait(k_empty, (j - 1) & 1);   // S_{j-1} has consumed K
-        mbar_expect_tx(k_full, TILE_BYTES);
-        tma_load_3d(smem + OFF_K, &tmQKV, k_full, d + h * HD, j * BKV, b);
-        mbar_wait(v_empty, (j - 1) & 1);   // PV_{j-1} has consumed V
-        mbar_expect_tx(v_full, TILE_BYTES);
-        tma_load_3d(smem + OFF_V, &tmQKV, v_full, 2 * d + h * HD, j * BKV, b);
+  if (warp >= 8) {
+    reg_dealloc<64>();
+    if (warp == 8 && lane == 0) {
+      // ------------------------------- TMA producer -------------------------------------------
+      for (int j = 1; j < n_max; ++j) {  // tile 0 was requested in the prologue
+        const int s = j % NST;
+        const uint32_t ph = uint32_t(j / NST) & 1u;
+        mbar_wait(&k_empty[s], ph ^ 1u);
+        mbar_expect_tx(&k_full[s], TILE_BYTES);
+        tma_load_3d(smem + OFF_K + s * TILE_BYTES, &tmQKV, &k_full[s], d + h * HD, j * BKV, b,
+                    kEvictLast);
+        mbar_wait(&v_empty[s], ph ^ 1u);
+        mbar_expect_tx(&v_full[s], TILE_BYTES);
+        tma_load_3d(smem + OFF_V + s * TILE_BYTES, &tmQKV, &v_full[s], 2 * d + h * HD, j * BKV, b,
+                    kEvictLast);
       }
-    }
-  } else if (warp == 5) {
-    // ------------------------------- MMA issuer ---------------------------------------------
-    // Issue order per tile: ... p_full(j) -> S_{j+1} -> PV_j.  S_{j+1} goes first because the
-    // softmax warps need it next; PV_j is only folded one iteration later.
-    if (lane == 0) {
+    } else if (warp == 9) {
+      // ------------------------------- MMA issuer ---------------------------------------------
       constexpr uint32_t idesc_s = umma_idesc_bf16(BQ, BKV, false, false);
       constexpr uint32_t idesc_pv = umma_idesc_bf16(BQ, HD, false, true);
-      const uint32_t sQ = smem_u32(smem + OFF_Q);
-      const uint32_t sK = smem_u32(smem + OFF_K);
-      const uint32_t sV = smem_u32(smem + OFF_V);
-      auto issue_s = [&](int j) {
-        mbar_wait(k_full, j & 1);
-        tc_fence_after_sync();
+      const int nt[2] = {n0, n1};
+      const bool leader = elect_one();
+      const uint32_t sQ0 = smem_u32(smem + OFF_Q), sK0 = smem_u32(smem + OFF_K),
+                     sV0 = smem_u32(smem + OFF_V);
+      auto issue_s = [&](int t, int j) {  // S_t = Q_t K_j^T
+        const uint64_t dq = umma_smem_desc(sQ0 + t * TILE_BYTES, 0, 1024);
+        const uint64_t dk = umma_smem_desc(sK0 + (j % NST) * TILE_BYTES, 0, 1024);
+        if (leader) {
 #pragma unroll
-        for (int k = 0; k < HD / 16; ++k)
-          umma_ss(tmem_S, umma_smem_desc(sQ + k * 32, 0, 1024), umma_smem_desc(sK + k * 32, 0, 1024),
-                  idesc_s, k > 0);
-        umma_commit(k_empty);
-        umma_commit(s_full);
+          for (int k = 0; k < HD / 16; ++k)  // +32 B per K step = +2 in the address field
+            umma_ss(tmem + COL_S + t * BKV, dq + 2 * k, dk + 2 * k, idesc_s, k > 0);
+          umma_commit(&s_full[t]);
+        }
       };
-      mbar_wait(q_full, 0);
-      issue_s(0);
-      for (int j = 0; j < n_kv; ++j) {
-        mbar_wait(p_full, j & 1);  // P_j is in smem and S_j has been read out of TMEM
-        if (j + 1 < n_kv) issue_s(j + 1);
-        mbar_wait(v_full, j & 1);
-        tc_fence_after_sync();
-        const uint32_t sP = smem_u32(smem + OFF_P + (j & 1) * P_BYTES);
-        const uint32_t acc = tmem_PV + (j & 1) * HD;
+      auto issue_pv = [&](int t, int j) {  // O_t (+)= P_t V_j, P_t read from TMEM
+        const uint64_t dv = umma_smem_desc(sV0 + (j % NST) * TILE_BYTES, TILE_BYTES, 1024);
+        if (leader) {
 #pragma unroll
-        for (int k = 0; k < BKV / 16; ++k)
-          umma_ss(acc, umma_smem_desc(sP + (k >> 2) * TILE_BYTES + (k & 3) * 32, 0, 1024),
-                  umma_smem_desc(sV + k * 2048, TILE_BYTES, 1024), idesc_pv, k > 0);
-        umma_commit(v_empty);
-        umma_commit(&pv_done[j & 1]);
+          for (int k = 0; k < BKV / 16; ++k)  // +2048 B per K step = +128 in the address field
+            umma_ts(tmem + COL_O + t * HD, tmem + COL_P + t * HD + k * 8, dv + 128 * k, idesc_pv,
+                    (j > 0) || (k > 0));
+          umma_commit(&pv_done[t]);
+        }
+      };
+      mbar_wait(&q_full[0], 0);
+      if (n1 > 0) mbar_wait(&q_full[1], 0);
+      mbar_wait(&k_full[0], 0);
+      tc_fence_after_sync();
+      issue_s(0, 0);
+      if (n1 > 0) issue_s(1, 0);
+      if (leader) umma_commit(&k_empty[0]);
+      // Round j, per query tile t: once S_t(j) has been pulled into registers (s_read), issue
+      // PV_t(j-1) and S_t(j+1).  PV is deliberately NOT issued the moment P_t(j-1) is complete: a
+      // tcgen05.ld is not served while the tensor core streams accumulators through TMEM, so a PV
+      // issued right at p_full would sit on the load of the next score tile (measured: 130 -> 930
+      // cycles).  Nothing needs O_t before the next rescale, and that waits on pv_done itself.
+      for (int j = 0; j < n_max; ++j) {
+        const int sv = j % NST, sn = (j + 1) % NST;
+        const uint32_t phv = uint32_t(j / NST) & 1u, phn = uint32_t((j + 1) / NST) & 1u;
+        bool k_ready = false, v_ready = false;
+        // scores of the next key tile, as soon as the current ones have left TMEM
+#pragma unroll
+        for (int t = 0; t < 2; ++t) {
+          if (j + 1 >= nt[t]) continue;
+          mbar_wait(&s_read[t], uint32_t(j) & 1u);
+          if (!k_ready) {
+            mbar_wait(&k_full[sn], phn);
+            k_ready = true;
+          }
+          tc_fence_after_sync();
+          issue_s(t, j + 1);
+          if ((t == 1 || j + 1 >= nt[1]) && leader) umma_commit(&k_empty[sn]);  // last reader of K
+        }
+#pragma unroll
+        for (int t = 0; t < 2; ++t) {
+          if (j >= nt[t]) continue;
+          stamp(p, 2, j, 2 * t);
+          mbar_wait(&p_full[t], uint32_t(j) & 1u);  // P_t(j) has been written
+          stamp(p, 2, j, 2 * t + 1);
+          if (!v_ready) {
+            mbar_wait(&v_full[sv], phv);
+            v_ready = true;
+          }
+          tc_fence_after_sync();
+          issue_pv(t, j);
+          if ((t == 1 || j >= nt[1]) && leader) umma_commit(&v_empty[sv]);  // last reader of V_j
+        }
       }
     }
   } else {
-    // ------------------------------- softmax / output ---------------------------------------
-    const int r = threadIdx.x;  // 0..127: query row inside the tile == TMEM lane
-    const int qrow = q0 + r;
-    const uint32_t lane_base = uint32_t(warp * 32) << 16;
-    float m_run = -INFINITY, l_run = 0.f, alpha_prev = 0.f;
-    float o[HD];
-#pragma unroll
-    for (int i = 0; i < HD; ++i) o[i] = 0.f;
+    // ------------------------------- softmax groups ------------------------------------------
+    reg_alloc<216>();
+    const int t = warp >> 2;         // query tile of this group
+    const int wq = warp & 3;         // warp inside the group = 32-row quarter of the tile
+    const int r = wq * 32 + lane;    // row inside the tile == TMEM lane
+    const int n_t = t == 0 ? n0 : n1;
+    const int qi = 2 * qb + t;       // query tile index == index of its diagonal key tile
+    const int qrow = q0 + t * BQ + r;
+    const uint32_t lane_base = uint32_t(wq * 32) << 16;
+    const uint32_t t_s = tmem + lane_base + COL_S + t * BKV;
+    const uint32_t t_o = tmem + lane_base + COL_O + t * HD;
+    const uint32_t t_p = tmem + lane_base + COL_P + t * HD;
     const uint8_t* kmask = p.key_mask ? p.key_mask + size_t(b) * p.T : nullptr;
+    float m_ref = -INFINITY, l_run = 0.f;
 
-    // o = o * alpha + PV_j, PV_j read from its TMEM accumulator
-    auto fold = [&](int j, float alpha) {
-      mbar_wait(&pv_done[j & 1], (j >> 1) & 1);
-      tc_fence_after_sync();
-#pragma unroll
-      for (int c = 0; c < HD / 32; ++c) {
-        uint32_t v[32];
-        tmem_ld_32x32b_x32(tmem_PV + (j & 1) * HD + lane_base + c * 32, v);
-        tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < 32; ++i) o[c * 32 + i] = o[c * 32 + i] * alpha + __uint_as_float(v[i]);
-      }
-      tc_fence_before_sync();
-    };
-
-    for (int j = 0; j < n_kv; ++j) {
+    for (int j = 0; j < n_t; ++j) {
       const int kv0 = j * BKV;
-      uint8_t* sP = smem + OFF_P + (j & 1) * P_BYTES;
-      mbar_wait(s_full, j & 1);
+      if (r == 0) stamp(p, t, j, 0);
+      mbar_wait(&s_full[t], uint32_t(j) & 1u);
       tc_fence_after_sync();
-
-      // Two passes over S in TMEM (max, then exp2 + pack).  The masked variant is only
-      // instantiated for the diagonal tile / key-padding case, so off-diagonal tiles execute no
-      // per-element integer or predicate instructions at all.
-      // warp-uniform mode: general when key padding is present, diagonal for the last tile
-      const int mode = kmask != nullptr ? kGeneral : (j == qt ? kDiag : kNoMask);
-      const uint32_t t_row = tmem_S + lane_base;
-      float mx;
-      if (mode == kNoMask) mx = row_max<kNoMask>(t_row, kv0, qrow, p.T, kmask, warp, lane);
-      else if (mode == kDiag) mx = row_max<kDiag>(t_row, kv0, qrow, p.T, kmask, warp, lane);
-      else mx = row_max<kGeneral>(t_row, kv0, qrow, p.T, kmask, warp, lane);
-      const float m_new = fmaxf(m_run, mx * p.scale_log2);
-      const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
-      const float alpha = fast_exp2(m_run - m_use);  // m_run = -inf -> 0
-      float sum;
+      if (r == 0) stamp(p, t, j, 1);
+      const int mode = kmask != nullptr ? kGeneral : (j == qi ? kDiag : kNoMask);
       const uint64_t mask_base =
           DROP ? (uint64_t((size_t(b) * p.H + h) * p.T + qrow) * uint64_t(p.t_pad) + uint64_t(kv0))
                : 0;
       if (mode == kNoMask)
-        sum = exp_pack<kNoMask, DROP>(t_row, sP, r, kv0, qrow, p.T, kmask, p.scale_log2, m_use,
-                                      warp, lane, p.drop, mask_base);
+        softmax_tile<kNoMask, DROP>(t_s, t_p, t_o, &s_read[t], &pv_done[t], j == 0,
+                                    uint32_t(j - 1) & 1u, kv0, qrow, p.T, kmask, p.scale_log2, m_ref,
+                                    l_run, wq, lane, p.drop, mask_base, p, j, threadIdx.x == 0);
       else if (mode == kDiag)
-        sum = exp_pack<kDiag, DROP>(t_row, sP, r, kv0, qrow, p.T, kmask, p.scale_log2, m_use, warp,
-                                    lane, p.drop, mask_base);
+        softmax_tile<kDiag, DROP>(t_s, t_p, t_o, &s_read[t], &pv_done[t], j == 0,
+                                    uint32_t(j - 1) & 1u, kv0, qrow, p.T, kmask, p.scale_log2, m_ref,
+                                  l_run, wq, lane, p.drop, mask_base, p, j, threadIdx.x == 0);
       else
-        sum = exp_pack<kGeneral, DROP>(t_row, sP, r, kv0, qrow, p.T, kmask, p.scale_log2, m_use,
-                                       warp, lane, p.drop, mask_base);
-      l_run = l_run * alpha + sum;
-      m_run = m_new;
-
-      fence_proxy_async_smem();
+        softmax_tile<kGeneral, DROP>(t_s, t_p, t_o, &s_read[t], &pv_done[t], j == 0,
+                                    uint32_t(j - 1) & 1u, kv0, qrow, p.T, kmask, p.scale_log2, m_ref,
+                                     l_run, wq, lane, p.drop, mask_base, p, j, threadIdx.x == 0);
       tc_fence_before_sync();
       __syncwarp();
-      if (lane == 0) mbar_arrive(p_full);
+      if (lane == 0) mbar_arrive(&p_full[t]);
+      if (r == 0) stamp(p, t, j, 2);
+    }
 
-      // Fold the PREVIOUS tile's PV while the tensor core works on S_{j+1} / PV_j: the PV latency
-      // never sits between two softmax passes.
-      if (j > 0) fold(j - 1, alpha_prev);
-      alpha_prev = alpha;
-    }
-    fold(n_kv - 1, alpha_prev);
-
-    // normalise, stage as bf16 (swizzled 128 B rows) in a P buffer, one TMA store per CTA
-    const float inv_l = l_run > 0.f ? 1.0f / l_run : 0.f;
-    uint8_t* stage = smem + OFF_P + (n_kv & 1) * P_BYTES;  // the buffer the last PV did NOT use
+    if (n_t > 0) {
+      // O_t / l -> bf16 -> the (now idle) Q_t tile as staging -> one TMA store per query tile
+      mbar_wait(&pv_done[t], uint32_t(n_t - 1) & 1u);
+      tc_fence_after_sync();
+      const float inv_l = l_run > 0.f ? 1.0f / l_run : 0.f;
+      uint8_t* stage = smem + OFF_Q + t * TILE_BYTES;
 #pragma unroll
-    for (int q = 0; q < 8; ++q) {
-      uint32_t w[4];
+      for (int c = 0; c < HD / 32; ++c) {
+        uint32_t o[32];
+        tmem_ld_32x32b_x32(t_o + c * 32, o);
+        tmem_ld_wait();
 #pragma unroll
-      for (int u = 0; u < 4; ++u)
-        w[u] = pack_bf16x2(o[q * 8 + 2 * u] * inv_l, o[q * 8 + 2 * u + 1] * inv_l);
-      *reinterpret_cast<uint4*>(stage + swizzle128(r * 128 + q * 16)) =
-          make_uint4(w[0], w[1], w[2], w[3]);
-    }
-    if (qrow < p.T) {
-      p.lse[(size_t(b) * p.H + h) * p.T + qrow] =
-          l_run > 0.f ? (m_run + log2f(l_run)) * 0.6931471805599453f : -INFINITY;
-    }
-    fence_proxy_async_smem();
-    named_bar_sync(1, 128);
-    if (threadIdx.x == 0) {
-      tma_store_3d(&tmO, stage, h * HD, q0, b);
-      tma_store_commit();
-      tma_store_wait_read<0>();  // smem may go once it has been read; the writes land on their own
+        for (int q = 0; q < 4; ++q) {
+          uint32_t w[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u)
+            w[u] = pack_bf16x2(__uint_as_float(o[q * 8 + 2 * u]) * inv_l,
+                               __uint_as_float(o[q * 8 + 2 * u + 1]) * inv_l);
+          *reinterpret_cast<uint4*>(stage + swizzle128(r * 128 + (c * 4 + q) * 16)) =
+              make_uint4(w[0], w[1], w[2], w[3]);
+        }
+      }
+      if (qrow < p.T) {
+        p.lse[(size_t(b) * p.H + h) * p.T + qrow] =
+            l_run > 0.f ? (m_ref + log2f(l_run)) * 0.6931471805599453f : -INFINITY;
+      }
+      tc_fence_before_sync();
+      fence_proxy_async_smem();
+      named_bar_sync(1 + t, 128);
+      if (r == 0) {
+        tma_store_3d(&tmO, stage, h * HD, q0 + t * BQ, b);
+        tma_store_commit();
+        tma_store_wait_read<0>();
+      }
     }
   }
 
   tc_fence_before_sync();
   __syncthreads();
-  if (warp == 5) tmem_dealloc(tmem, FWD_TMEM_COLS);
+  if (warp == 9) tmem_dealloc(tmem, TMEM_COLS);
 }
 
 }  // namespace attn
+
+static int attention_fwd_launch(const void* qkv, void* out, float* lse, const uint8_t* key_mask, int B, int T,
+                     int H, const DropoutParams& drop, float scale_log2, cudaStream_t stream) {
+  namespace a2 = attn;
+  const int d = H * a2::HD;
+  CUtensorMap tQKV, tO;
+  if (make_tmap_3d(&tQKV, static_cast<const __nv_bfloat16*>(qkv), B, T, 3 * d, 3 * d,
+                   uint64_t(T) * 3 * d, 128, a2::HD, Swz::B128))
+    return 1;
+  if (make_tmap_3d(&tO, static_cast<__nv_bfloat16*>(out), B, T, d, d, uint64_t(T) * d, 128, a2::HD,
+                   Swz::B128))
+    return 1;
+  a2::Params p;
+  p.B = B; p.T = T; p.H = H;
+  p.nqb = ceil_div(T, 2 * a2::BQ);
+  p.scale_log2 = scale_log2;
+  p.key_mask = key_mask;
+  p.lse = lse;
+  p.drop = drop;
+  p.t_pad = (T + 7) & ~7;
+  p.trace = nullptr;
+  static const bool want_trace = std::getenv("LLMTRAIN_ATTN_TRACE") != nullptr;
+  if (want_trace) {
+    B200_CHECK_CUDA(cudaMalloc(&p.trace, 4 * 32 * 4 * sizeof(long long)));
+    B200_CHECK_CUDA(cudaMemsetAsync(p.trace, 0, 4 * 32 * 4 * sizeof(long long), stream));
+  }
+  static bool configured = false;
+  if (!configured) {
+    B200_CHECK_CUDA(cudaFuncSetAttribute(a2::fwd_kernel<false>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, a2::SMEM + 1024));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(a2::fwd_kernel<true>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, a2::SMEM + 1024));
+    configured = true;
+  }
+  const int grid = p.nqb * B * H;
+  if (drop.threshold != 0)
+    B200_LAUNCH((a2::fwd_kernel<true>), grid, a2::THREADS, a2::SMEM + 1024, stream, tQKV, tO, p);
+  else
+    B200_LAUNCH((a2::fwd_kernel<false>), grid, a2::THREADS, a2::SMEM + 1024, stream, tQKV, tO, p);
+  B200_CHECK_CUDA(cudaGetLastError());
+  B200_COUNT_LAUNCH(1);
+  if (p.trace != nullptr) {  // debug: per-tile timeline of the heaviest CTA, cycles since its first stamp
+    static long long host[4 * 32 * 4];
+    B200_CHECK_CUDA(cudaMemcpyAsync(host, p.trace, sizeof(host), cudaMemcpyDeviceToHost, stream));
+    B200_CHECK_CUDA(cudaStreamSynchronize(stream));
+    const long long t0 = host[1];
+    for (int j = 0; j < 32 && host[(1 * 32 + j) * 4] != 0; ++j) {
+      std::fprintf(stderr, "attn trace j=%2d", j);
+      for (int role = 0; role < 4; ++role)
+        for (int k = 0; k < 4; ++k)
+          std::fprintf(stderr, "%s%7lld", k == 0 ? " |" : "",
+                       host[(role * 32 + j) * 4 + k] == 0 ? -1LL : host[(role * 32 + j) * 4 + k] - t0);
+      std::fprintf(stderr, "\n");
+    }
+    cudaFree(p.trace);
+  }
+  return 0;
+}
+
 }  // namespace b200
 
 using namespace b200;
@@ -383,43 +577,11 @@ static int attention_fwd_impl(const void* qkv, void* out, float* lse, const uint
                               float softmax_scale, cudaStream_t stream) {
   B200_REQUIRE(head_dim == attn::HD, "attention: the tcgen05 kernel is specialised for head_dim 64");
   B200_REQUIRE(B > 0 && T > 0 && H > 0, "attention: empty problem");
-  const int d = H * attn::HD;
-  CUtensorMap tQKV, tO;
-  if (make_tmap_3d(&tQKV, static_cast<const __nv_bfloat16*>(qkv), B, T, 3 * d, 3 * d,
-                   uint64_t(T) * 3 * d, 128, attn::HD, Swz::B128))
-    return 1;
-  if (make_tmap_3d(&tO, static_cast<__nv_bfloat16*>(out), B, T, d, d, uint64_t(T) * d, 128,
-                   attn::HD, Swz::B128))
-    return 1;
-  attn::FwdParams p;
-  p.B = B; p.T = T; p.H = H;
   // softmax_scale > 0 overrides head_dim^-0.5 (heads narrower than 64 run zero-padded to 64 lanes
   // and keep the scale of their true width)
-  p.scale_log2 = 1.4426950408889634f *
-                 (softmax_scale > 0.f ? softmax_scale : 1.0f / std::sqrt(float(head_dim)));
-  p.key_mask = key_mask;
-  p.lse = lse;
-  p.drop = drop;
-  p.t_pad = (T + 7) & ~7;
-  static bool configured = false;
-  if (!configured) {
-    B200_CHECK_CUDA(cudaFuncSetAttribute(attn::fwd_kernel<false>,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         attn::FWD_SMEM));
-    B200_CHECK_CUDA(cudaFuncSetAttribute(attn::fwd_kernel<true>,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         attn::FWD_SMEM));
-    configured = true;
-  }
-  dim3 grid(ceil_div(T, attn::BQ), H, B);
-  if (drop.threshold != 0)
-    B200_LAUNCH((attn::fwd_kernel<true>), grid, attn::FWD_THREADS, attn::FWD_SMEM, stream, tQKV, tO, p);
-  else
-    B200_LAUNCH((attn::fwd_kernel<false>), grid, attn::FWD_THREADS, attn::FWD_SMEM, stream, tQKV, tO,
-                p);
-  B200_CHECK_CUDA(cudaGetLastError());
-  B200_COUNT_LAUNCH(1);
-  return 0;
+  const float scale_log2 = 1.4426950408889634f *
+                           (softmax_scale > 0.f ? softmax_scale : 1.0f / std::sqrt(float(head_dim)));
+  return attention_fwd_launch(qkv, out, lse, key_mask, B, T, H, drop, scale_log2, stream);
 }
 
 extern "C" int llmtrain_b200_attention_fwd(const void* qkv, void* out, float* lse,

@@ -123,8 +123,11 @@ ce_kernel(__nv_bfloat16* __restrict__ logits, const int64_t* __restrict__ labels
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   uint4* rp = reinterpret_cast<uint4*>(logits + size_t(row) * ldv);
   const int nvec = ldv >> 3;
-  const bool valid = row_valid == nullptr || row_valid[row] != 0;
   const int label = static_cast<int>(labels[row]);
+  // label == -100 is torch's ignore_index (`F.cross_entropy` in the reference's loss,
+  // `src/llmtrain/models/gpt.py:256-260`): zero loss, zero gradient, still counted by the caller's
+  // denominator.
+  const bool valid = (row_valid == nullptr || row_valid[row] != 0) && label != -100;
 
   float m = -INFINITY, ssum = 0.f;
   for (int c = tid; c < nvec; c += CE_THREADS) {
@@ -256,8 +259,8 @@ ce_row_kernel(__nv_bfloat16* __restrict__ logits, const int64_t* __restrict__ la
     const int b = it & 1;
     // Every thread finished reading buffer b^1 before the barrier that ended the last iteration.
     if (tid == 0 && row + int(gridDim.x) < rows) load_row(row + gridDim.x, b ^ 1);
-    const bool valid = row_valid == nullptr || row_valid[row] != 0;
     const int label = static_cast<int>(labels[row]);
+    const bool valid = (row_valid == nullptr || row_valid[row] != 0) && label != -100;  // ignore_index
     uint4* rp = reinterpret_cast<uint4*>(ce_row_smem + size_t(b) * pitch);
     mbar_wait(&full[b], (it >> 1) & 1);
 
@@ -623,8 +626,10 @@ extern "C" int llmtrain_b200_cast_f32_to_bf16(const float* src, void* dst, size_
 // pass pointers it was given but has no allocator to ask.  llmtrain_b200_bias_grad needs a few
 // hundred KB of temporary global memory for its deterministic two-stage column sum, so those
 // callers could not use it.  This variant carries that temporary storage inside the library image
-// instead: a fixed array in device global memory that exists on every GPU that loads the library,
-// from load until process exit, whether or not the function is ever called.
+// instead: a fixed array in device global memory that belongs to the library's module on every GPU
+// that has loaded it, until process exit.  With CUDA's default lazy module loading the module —
+// and with it this 1 MiB — is only materialised on a GPU when something in it is first used
+// there, which can be this function's first call: the driver may allocate at that moment.
 //
 // Consequences the caller has to know about:
 //   * The array has a fixed capacity (kNoAllocFloats floats = 1 MiB per GPU).  A problem whose
@@ -635,8 +640,10 @@ extern "C" int llmtrain_b200_cast_f32_to_bf16(const float* src, void* dst, size_
 //     (different streams, or different host threads on different streams) would overwrite each
 //     other's partial sums.  Issue calls for one GPU on one stream, or order them with events.
 //   * The device address of the array is looked up once per GPU, on the first call made while
-//     that GPU is current.  That first call does a little host-side set-up work; make it during
-//     initialisation, before starting any stream capture.
+//     that GPU is current.  That first call does host-side set-up work and may be the moment the
+//     driver loads the module (see above): make it during initialisation — BEFORE the host's own
+//     pool claims the rest of the device and before starting any stream capture — or run the
+//     process with CUDA_MODULE_LOADING=EAGER so the memory is taken at library load.
 // ------------------------------------------------------------------------------------------------
 namespace b200 {
 namespace ew {

@@ -93,13 +93,16 @@ int llmtrain_b200_bias_grad(const void* dy, int ld, int M, int N, float* dbias, 
  * memory themselves (a process whose pool already owns all of HBM, a latency-critical loop that
  * cannot take cudaMalloc's device-wide stall, a binding with no allocator).  This entry point has
  * no counterpart in the reference; it exists only for such hosts.  The partial sums go to a 1 MiB
- * array built into the library image (resident on every GPU that loads the library, until exit).
+ * array built into the library's device module (held by every GPU that has loaded the module,
+ * until exit; with CUDA's lazy module loading that may only happen at the first call on a GPU).
  *   - refused with an error when colsum splits * N exceeds capacity_bytes()/4 partial sums;
  *   - every call on a GPU shares that array and nothing is cleared between calls (none of it needs
  *     to start at zero); calls whose kernels overlap on the GPU corrupt each other: keep them on
  *     one stream or order them with events;
- *   - the first call made on each GPU looks the array's address up; make that call during
- *     start-up, before beginning any stream capture.
+ *   - the first call made on each GPU looks the array's address up and may make the driver load
+ *     the module (taking the 1 MiB then): make that call during start-up, before the host's pool
+ *     claims the device and before beginning any stream capture, or set
+ *     CUDA_MODULE_LOADING=EAGER.
  * Performs no cudaMalloc/cudaFree and calls no allocating library routine. */
 size_t llmtrain_b200_bias_grad_noalloc_capacity_bytes(void);
 int llmtrain_b200_bias_grad_noalloc(const void* dy, int ld, int M, int N, float* dbias,

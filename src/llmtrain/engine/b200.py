@@ -100,7 +100,7 @@ class GPTEngine:
     def __init__(self, model: nn.Module, *, max_batch: int = 1, max_seq: int | None = None) -> None:
         if not supports(model):
             raise RuntimeError(
-                "The sm_100a runtime needs a GPT with head_dim == 64 (d_model / n_heads), "
+                "The sm_100a runtime needs a GPT with head_dim (d_model / n_heads) in 8, 16, ..., 64, "
                 "d_model <= 2048 and dims divisible by 8; "
                 f"got d_model={getattr(model, 'd_model', '?')} n_heads={getattr(model, 'n_heads', '?')}. "
                 "Use trainer.extra.engine: torch for other shapes."
@@ -154,6 +154,7 @@ class GPTEngine:
             "gpt_create",
         )
         self._handle = handle
+        self._dropout_armed = False  # a fresh runtime handle starts with dropout off
         self._plan = (max_batch, max_seq)
         self.n_params = int(self._lib.llmtrain_b200_gpt_param_elems(handle))
         self.n_shadow = int(self._lib.llmtrain_b200_gpt_shadow_elems(handle))
@@ -226,10 +227,15 @@ class GPTEngine:
         self.shadow_fresh = True
 
     # ------------------------------------------------------------------ execution
+    def fit_plan(self, batch: int, seq: int) -> None:
+        """Grow the activation plan when a batch exceeds it (the reference accepts any batch the
+        model accepts; the arena is re-laid-out, which is rare and outside the steady state)."""
+        if batch > self._plan[0] or seq > self._plan[1]:
+            self._replan(max(batch, self._plan[0]), max(seq, self._plan[1]))
+
     def _prepare(self, ids: torch.Tensor, mask: torch.Tensor | None):
         b, t = ids.shape
-        if b > self._plan[0] or t > self._plan[1]:
-            self._replan(max(b, self._plan[0]), max(t, self._plan[1]))
+        self.fit_plan(b, t)
         if not self.shadow_fresh:
             self.refresh_shadow()
         ids = ids.to(self.device, non_blocking=True).contiguous()
@@ -270,8 +276,11 @@ class GPTEngine:
 
         Reference: four ``nn.Dropout`` modules, ``src/llmtrain/models/gpt.py:28,30,97,129``.  Masks
         are counter-based (``csrc/common/philox.cuh``): the seed is torch's global seed plus the
-        rank, the offset is a per-engine micro-batch counter, so a run is reproducible and the
-        backward pass regenerates what the forward pass used.
+        rank, the offset is a micro-batch counter, so a run is reproducible and the backward pass
+        regenerates what the forward pass used.  The train engine derives the counter from the
+        optimiser step (``B200TrainEngine.train_step``), which is in every checkpoint, and the
+        seed from torch's generator state, which ``Trainer.restore`` puts back: a resumed run
+        continues the mask stream of the interrupted one instead of replaying it from the start.
         """
         p = float(self.model.dropout_p) if (mode == 2 and self.model.training) else 0.0
         if p <= 0.0 and not self._dropout_armed:
@@ -391,6 +400,7 @@ class B200TrainEngine(TrainEngine):
         self._sumsq = torch.zeros(1, dtype=torch.float32, device=device)
         self._norm = torch.zeros(1, dtype=torch.float32, device=device)
         self._loss_acc = torch.zeros(1, dtype=torch.float32, device=device)
+        self._eval_acc = torch.zeros(1, dtype=torch.float32, device=device)
         self._step = 0
         self._comm: Any | None = None
         self._prefetch = bool(cfg.trainer.extra.get("prefetch", True))
@@ -468,6 +478,15 @@ class B200TrainEngine(TrainEngine):
                 raise ValueError("attention_mask has no valid target tokens.")
             if n_valid != b * t:
                 key_mask = (mask_h != 0).to(torch.uint8).to(self._device, non_blocking=True)
+        # torch raises for a target outside [0, V) other than ignore_index (-100); the native loss
+        # kernel cannot raise, so the (host-resident) labels are checked here
+        if labels_h.numel():
+            lo, hi = int(labels_h.min()), int(labels_h.max())
+            if hi >= self.model.vocab_size or (lo < 0 and lo != -100):
+                raise ValueError(
+                    f"labels must lie in [0, {self.model.vocab_size}) or equal -100 (ignored); "
+                    f"got min={lo} max={hi}"
+                )
         ids = ids_h.to(self._device, non_blocking=True)
         labels = labels_h.to(self._device, non_blocking=True)
         return ids, labels, key_mask, n_valid
@@ -483,8 +502,10 @@ class B200TrainEngine(TrainEngine):
             staged = self._prefetched if self._prefetched is not None else self._stage(next_batch())
             self._prefetched = None
             ids, labels, key_mask, n_valid = staged
-            if ids.shape[0] > g._plan[0] or ids.shape[1] > g._plan[1]:
-                g._replan(max(ids.shape[0], g._plan[0]), max(ids.shape[1], g._plan[1]))
+            g.fit_plan(int(ids.shape[0]), int(ids.shape[1]))
+            # dropout offset = number of training micro-batches before this one: a pure function
+            # of (optimiser step, position in the accumulation window), both durable
+            g._dropout_calls = self._step * accum_steps + micro
             tokens += ids.numel()
             self._last_seq_len = int(ids.shape[1])
             scale = 1.0 / (n_valid * accum_steps)
@@ -498,6 +519,9 @@ class B200TrainEngine(TrainEngine):
                 g.run_backward()
             self._mark(marks)
         self._step += 1
+        # the fused kernel is this optimiser's step(): tell torch's LR scheduler so, or it warns
+        # about scheduler.step() preceding optimizer.step() on every run
+        self.optimizer._opt_called = True  # type: ignore[attr-defined]
         lr = float(self.optimizer.param_groups[0]["lr"])
         group = self.optimizer.param_groups[0]
         hyper = dict(
@@ -545,7 +569,9 @@ class B200TrainEngine(TrainEngine):
 
     def eval_loss(self, batch: Batch) -> float:
         ids, labels, key_mask, n_valid = self._stage(batch)
-        acc = torch.zeros(1, dtype=torch.float32, device=self._device)
+        self._gpt.fit_plan(int(ids.shape[0]), int(ids.shape[1]))  # val batches may be larger
+        acc = self._eval_acc
+        acc.zero_()
         self._gpt.run_forward(ids, labels, key_mask, mode=1, loss_acc=acc, loss_scale=1.0 / n_valid)
         return float(acc.item())
 
@@ -567,6 +593,7 @@ class B200TrainEngine(TrainEngine):
                 self._v[off : off + n].view(param.shape).copy_(state["exp_avg_sq"])
                 steps.append(int(float(state["step"])))
         self._step = max(steps) if steps else 0
+        self._gpt._dropout_seed = None  # re-derive from the restored torch generator state
         self._install_state_views()
         self._gpt.refresh_shadow()
 

@@ -273,7 +273,8 @@ class GPTAdapter(ModelAdapter):
         ids, labels, mask = validate_lm_batch(batch, min_seq_len=2)
         inner = getattr(model, "module", model)  # tolerate a DDP wrapper
         if isinstance(inner, GPT) and inner.use_native():
-            # Fused path: logits are never materialised; loss keeps an autograd edge to params.
+            # Fused native path: bf16 logits live only in the engine's activation arena (consumed in
+            # place by the loss kernel); loss keeps an autograd edge to params.
             loss = inner.native_engine().loss(ids, labels, mask)
             return loss, {"loss": float(loss.item())}
 

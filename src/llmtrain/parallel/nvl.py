@@ -31,6 +31,28 @@ _HANDLES_PER_RANK = 4  # send, red, sync, full
 _live: list[Any] = []
 
 
+def _collective_stage(what: str, fn: Any, world: int, on_fail: Any = None) -> None:
+    """Run one set-up step on every rank; if ANY rank failed, every rank raises together.
+
+    Set-up steps can fail on one rank only (an allocation, an IPC export, a handle import).  A
+    rank that raised on its own would leave the others inside the next collective until
+    ``ddp.timeout_sec`` expires; gathering the error strings after every step keeps the ranks in
+    lock-step, so a failure becomes a clean fallback to NCCL instead of a hang.
+    """
+    err = ""
+    try:
+        fn()
+    except Exception as exc:  # noqa: BLE001  (re-raised collectively below)
+        err = f"{what}: {exc}"
+    seen: list[Any] = [None] * world
+    dist.all_gather_object(seen, err)
+    bad = [e for e in seen if e]
+    if bad:
+        if on_fail is not None:
+            on_fail()
+        raise RuntimeError(bad[0])
+
+
 class NcclFallback:
     """torch.distributed (NCCL) all-reduce, then the fused optimiser kernel."""
 
@@ -70,25 +92,38 @@ class NvlComm:
         self._lib = native.lib()
         self._n = n
         self.rank, self.world = rank, world
+        self._handle = ctypes.c_void_p()
         handle = ctypes.c_void_p()
-        check(
-            self._lib.llmtrain_b200_nvl_create(
-                ctypes.c_int(rank), ctypes.c_int(world), ctypes.c_size_t(n),
-                ctypes.c_double(float(timeout_s)), ctypes.byref(handle),
-            ),
-            "nvl_create",
-        )
-        self._handle = handle
+
+        def create() -> None:
+            check(
+                self._lib.llmtrain_b200_nvl_create(
+                    ctypes.c_int(rank), ctypes.c_int(world), ctypes.c_size_t(n),
+                    ctypes.c_double(float(timeout_s)), ctypes.byref(handle),
+                ),
+                "nvl_create",
+            )
+            self._handle = handle
+
+        _collective_stage("nvl_create", create, world, self.close)
         mine = (ctypes.c_ubyte * (_HANDLES_PER_RANK * _IPC_HANDLE_BYTES))()
-        check(self._lib.llmtrain_b200_nvl_export(handle, mine), "nvl_export")
+        _collective_stage(
+            "nvl_export",
+            lambda: check(self._lib.llmtrain_b200_nvl_export(handle, mine), "nvl_export"),
+            world, self.close)
         gathered: list[bytes | None] = [None] * world
         dist.all_gather_object(gathered, bytes(mine))
         blob = b"".join(g for g in gathered if g is not None)
-        if len(blob) != world * _HANDLES_PER_RANK * _IPC_HANDLE_BYTES:
-            raise RuntimeError("nvl: IPC handle exchange returned an unexpected payload size")
-        everyone = (ctypes.c_ubyte * len(blob)).from_buffer_copy(blob)
-        check(self._lib.llmtrain_b200_nvl_connect(handle, everyone), "nvl_connect")
-        dist.barrier()  # every rank has mapped every peer before the first kernel runs
+
+        def connect() -> None:
+            if len(blob) != world * _HANDLES_PER_RANK * _IPC_HANDLE_BYTES:
+                raise RuntimeError("nvl: IPC handle exchange returned an unexpected payload size")
+            everyone = (ctypes.c_ubyte * len(blob)).from_buffer_copy(blob)
+            check(self._lib.llmtrain_b200_nvl_connect(handle, everyone), "nvl_connect")
+
+        # (the gather inside the stage doubles as the barrier "every rank has mapped every peer
+        # before the first kernel runs")
+        _collective_stage("nvl_connect", connect, world, self.close)
         _live.append(self)
 
     def barrier(self) -> None:
@@ -184,18 +219,7 @@ class NvlsTeam:
         world = comm.world
 
         def stage(what: str, fn: Any) -> None:
-            """Run one setup step everywhere; if ANY rank failed, every rank raises (no hangs)."""
-            err = ""
-            try:
-                fn()
-            except Exception as exc:  # noqa: BLE001  (re-raised collectively below)
-                err = f"{what}: {exc}"
-            seen: list[Any] = [None] * world
-            dist.all_gather_object(seen, err)
-            bad = [e for e in seen if e]
-            if bad:
-                self.close()
-                raise RuntimeError(bad[0])
+            _collective_stage(what, fn, world, self.close)
 
         handle = ctypes.c_void_p()
         stage("nvls_create", lambda: check(
@@ -292,6 +316,11 @@ class _NvlTrainComm:
     def __init__(self, gpt: Any, comm: NvlComm, *, overlap: bool = True,
                  team: NvlsTeam | None = None) -> None:
         self._gpt, self._comm = gpt, comm
+        # shutdown() must release the multicast team (object, fd, mappings) as well as the peer
+        # mappings: this adapter takes the inner communicator's place in the live list
+        if comm in _live:
+            _live.remove(comm)
+        _live.append(self)
         self.overlap = overlap
         self._reduced = False
         self._team = team
@@ -326,6 +355,8 @@ class _NvlTrainComm:
             self._comm.step(g.g32, g.p32, m, v, g.p16, norm, hyper)
 
     def close(self) -> None:
+        if self in _live:
+            _live.remove(self)
         if self._team is not None:
             check(self._comm._lib.llmtrain_b200_nvl_attach_nvls(self._comm._handle, None, None),
                   "nvl_attach_nvls")
@@ -358,15 +389,8 @@ def try_create(gpt: Any, m: torch.Tensor, v: torch.Tensor, *, rank: int, world: 
         return None
     try:
         comm = NvlComm(gpt.n_params, rank=rank, world=world, timeout_s=timeout_s)
-    except Exception as exc:
+    except RuntimeError as exc:  # raised on every rank together (see _collective_stage)
         logger.warning("nvl communicator could not be created: %s", exc)
-        failed = torch.tensor([1], device="cuda")
-        dist.all_reduce(failed, op=dist.ReduceOp.MAX)
-        return None
-    failed = torch.tensor([0], device="cuda")
-    dist.all_reduce(failed, op=dist.ReduceOp.MAX)
-    if int(failed.item()):
-        comm.close()
         return None
     team = None
     if _want_nvls(world, overlap) and gpt.n_params % (4 * world) == 0:

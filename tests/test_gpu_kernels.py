@@ -110,6 +110,28 @@ def test_cross_entropy_loss_and_grad(rows: int, v: int, ldv: int) -> None:
     assert torch.equal(untouched, logits)
 
 
+@pytest.mark.parametrize("v,ldv", [(1000, 1024), (50257, 50304)])
+def test_cross_entropy_ignore_index_rows_have_no_loss_and_no_gradient(v: int, ldv: int) -> None:
+    """label == -100 follows ``F.cross_entropy``: zero loss, zero gradient, row still counted by
+    the caller's mean (both kernels: the streaming one and the row-resident one)."""
+    from llmtrain.ops import kernels as K
+
+    rows = 48
+    logits = torch.zeros(rows, ldv, device="cuda", dtype=torch.bfloat16)
+    logits[:, :v] = _bf((rows, v), 2.0)
+    labels = torch.randint(0, v, (rows,), device="cuda")
+    labels[::3] = -100
+    ref_in = logits[:, :v].float().requires_grad_(True)
+    per_tok = F.cross_entropy(ref_in, labels, reduction="none")  # ignore_index=-100 -> 0
+    (per_tok.sum() / rows).backward()
+    work = logits.clone()
+    rows_loss = K.cross_entropy(work, labels, vocab=v, grad_scale=1.0 / rows)
+    assert _rel(rows_loss, per_tok) < 1e-3
+    assert rows_loss[::3].abs().max().item() == 0
+    assert work[::3].abs().max().item() == 0
+    assert _rel(work[:, :v], ref_in.grad) < 2e-2
+
+
 @pytest.mark.parametrize("m,n", [(4096, 768), (1000, 2304), (130, 50)])
 def test_bias_grad(m: int, n: int) -> None:
     from llmtrain.ops import kernels as K

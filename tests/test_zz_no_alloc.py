@@ -61,10 +61,14 @@ def test_noalloc_bias_grad_matches_regular_entry_point_twice_in_a_row() -> None:
         assert rc == 0, lib.llmtrain_b200_last_error()
 
         got = start.clone()
+        torch.cuda.synchronize()
+        free_before = torch.cuda.mem_get_info()[0]
         rc = lib.llmtrain_b200_bias_grad_noalloc(dy.data_ptr(), dy.stride(0), m, n,
                                                  got.data_ptr(), _stream())
         assert rc == 0, lib.llmtrain_b200_last_error()
         torch.cuda.synchronize()
+        if seed == 1:  # the module is loaded by now: a call must not take device memory at all
+            assert torch.cuda.mem_get_info()[0] == free_before
 
         ref = start + dy.float().sum(0)
         scale = ref.abs().max().item() + 1e-6
