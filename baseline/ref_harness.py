@@ -12,7 +12,7 @@ through its own public API and stock code path:
   downloads, so a registered plugin is the reference's own extension point for seq-1024 data.
 
 Three things the reference cannot do by itself are supplied from the *outside*, without touching
-its source (all recorded in the emitted JSON under ``config.reference_mode``):
+its source (all recorded in the emitted JSON under ``notes.reference_mode``):
 
 1. ``run.device`` / ``ddp.backend`` are ``Literal["cpu","mps"]`` / ``Literal["gloo"]`` in its
    schema; the config object is assembled with pydantic's ``model_construct`` so that the stock
@@ -94,7 +94,7 @@ def _config(model: dict[str, Any], mb: int, accum: int, world: int, steps: int) 
 
 
 def run(args: Any, *, rank: int, local_rank: int, world: int, model: dict[str, Any], metric: str,
-        timed: Any, max_over_ranks: Any, sampler: Any) -> dict[str, Any]:
+        timed: Any, max_over_ranks: Any, sampler: Any, config: dict[str, Any]) -> dict[str, Any]:
     import torch
 
     import llmtrain
@@ -135,20 +135,12 @@ def run(args: Any, *, rank: int, local_rank: int, world: int, model: dict[str, A
             "dtype": "bf16",
             "data": "synthetic",
             "impl": "reference",
-            "config": {
-                "model": "gpt2-small-124M (d768 L12 H12 F3072 V50257 tied)",
-                "global_batch": mb * accum * world,
-                "micro_batch_per_gpu": mb,
-                "grad_accum": accum,
-                "seq_len": seq,
-                "parallelism": f"dp{world}",
-                "reference_mode": "unmodified baseline/_ref: stock Trainer.fit/GPT/AdamW/DDP; "
-                                  "device=cuda + backend=cpu:gloo,cuda:nccl via pydantic "
-                                  "model_construct; outer torch.autocast(bf16); synthetic_text "
-                                  "registered through the reference's plugin registry; tiktoken "
-                                  "stubbed (offline)",
-                "l2": "inputs larger than L2; no explicit flush",
-            },
+            "config": config,
+            "notes": {"reference_mode": "unmodified baseline/_ref: stock Trainer.fit/GPT/AdamW/DDP; "
+                                        "device=cuda + backend=cpu:gloo,cuda:nccl via pydantic "
+                                        "model_construct; outer torch.autocast(bf16); "
+                                        "synthetic_text registered through the reference's plugin "
+                                        "registry; tiktoken stubbed (offline)"},
             "clocks": clocks.summary(),
             "e2e": {"value": value, "unit": "tokens/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": 4 * accum,

@@ -63,6 +63,7 @@ class ClockSampler:
         self._stop = threading.Event()
         self._thread: threading.Thread | None = None
         self.samples: list[int] = []
+        self.power_w: list[float] = []
         self.reasons: set[str] = set()
         self.max_mhz: int | None = None
         self.error: str | None = None
@@ -82,6 +83,7 @@ class ClockSampler:
             self.max_mhz = int(pynvml.nvmlDeviceGetMaxClockInfo(handle, pynvml.NVML_CLOCK_SM))
             while not self._stop.is_set():
                 self.samples.append(int(pynvml.nvmlDeviceGetClockInfo(handle, pynvml.NVML_CLOCK_SM)))
+                self.power_w.append(pynvml.nvmlDeviceGetPowerUsage(handle) / 1000.0)
                 mask = int(pynvml.nvmlDeviceGetCurrentClocksEventReasons(handle))
                 for bit, name in self._REASONS.items():
                     if mask & bit and name != "gpu_idle":
@@ -106,6 +108,7 @@ class ClockSampler:
             "sm_max_mhz": self.max_mhz,
             "reasons": sorted(self.reasons),
             "samples": len(self.samples),
+            "power_w": round(statistics.median(self.power_w), 1) if self.power_w else None,
         }
         if self.error:
             out["error"] = self.error
@@ -129,6 +132,19 @@ def _max_over_ranks(ms: float, world: int) -> float:
     t = torch.tensor([ms], dtype=torch.float64, device="cuda")
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     return float(t.item())
+
+
+def _gather_rows(row: list[float], world: int) -> list[list[float]]:
+    """Every rank's row of floats, in rank order (NCCL all-gather of a small float64 tensor)."""
+    if world == 1:
+        return [row]
+    import torch
+    import torch.distributed as dist
+
+    mine = torch.tensor(row, dtype=torch.float64, device="cuda")
+    out = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(out, mine)
+    return [[float(x) for x in t.tolist()] for t in out]
 
 
 def _barrier(world: int) -> None:
@@ -173,6 +189,88 @@ def _payload(cfg_model: dict[str, Any], micro_batch: int, accum: int, world: int
     }
 
 
+def bench_config(mb: int, accum: int, seq: int, world: int) -> dict[str, Any]:
+    """The ``config`` object of the JSON line: identical for both arms by construction (the driver
+    compares the two dictionaries); anything implementation-specific goes under ``notes``."""
+    return {
+        "model": "gpt2-small-124M (d768 L12 H12 F3072 V50257 tied)",
+        "global_batch": mb * accum * world,
+        "micro_batch_per_gpu": mb,
+        "grad_accum": accum,
+        "seq_len": seq,
+        "parallelism": f"dp{world}",
+        "optimizer": "AdamW on fp32 parameters + clip 1.0 (inside the timed region)",
+        "l2": "inputs larger than L2 (>=2 GB of weights/optimizer state + GBs of activations "
+              "touched per step vs 126 MB L2); no explicit flush",
+    }
+
+
+def _ddp_check(engine: Any, batch: dict[str, Any], world: int) -> dict[str, Any]:
+    """Multi-GPU correctness evidence inside the bench run itself (the driver's pytest box has one
+    GPU).  (1) replicas bit-identical: two integer checksums of the fp32 master arena, gathered.
+    (2) the gradient the live reduction path (P2P buckets at 2 GPUs, in-switch buckets from 4)
+    produces equals the sum of the ranks' local gradients of the same micro-batch, summed by NCCL
+    in fp32 — to the tolerance of the wire format (bf16 for P2P, fp32 in-switch)."""
+    import torch
+    import torch.distributed as dist
+
+    g, comm = engine._gpt, engine._comm
+    bits = g.p32.view(torch.int32).to(torch.int64)
+    weights = (torch.arange(bits.numel(), device="cuda", dtype=torch.int64) % 65521) + 1
+    sums = _gather_rows([float(bits.sum().item() % (1 << 52)),
+                         float((bits * weights).sum().item() % (1 << 52))], world)
+    identical = all(r == sums[0] for r in sums)
+    del bits, weights
+
+    ids, labels = batch["input_ids"], batch["labels"]
+    scale = 1.0 / ids.numel()
+
+    def forward() -> None:
+        engine._loss_acc.zero_()
+        g.run_forward(ids, labels, None, mode=2, loss_acc=engine._loss_acc, loss_scale=scale,
+                      grad_scale=scale)
+
+    g.g32.zero_()
+    forward()
+    g.run_backward()  # local gradient only
+    torch.cuda.synchronize()
+    want = g.g32.clone()
+    dist.all_reduce(want, op=dist.ReduceOp.SUM)
+    g.g32.zero_()
+    forward()
+    reduced_by = "none"
+    if hasattr(comm, "backward_last") and getattr(comm, "overlap", False):
+        comm.backward_last()  # the bucket engine: reduced while backward runs
+        reduced_by = "bucket engine (overlapped with backward)"
+    else:
+        g.run_backward()
+    torch.cuda.synchronize()
+    dist.barrier()  # peers' pushes into this rank's buffers have landed
+    torch.cuda.synchronize()
+    got = comm.reduced_gradient() if reduced_by != "none" else g.g32
+    denom = float(want.abs().max().item()) + 1e-30
+    err = float((got - want).abs().max().item()) / denom
+    rms = float((got - want).pow(2).mean().sqrt().item()) / (
+        float(want.pow(2).mean().sqrt().item()) + 1e-30)
+    worst = max(r[0] for r in _gather_rows([err], world))
+    g.g32.zero_()
+    if hasattr(comm, "_reduced"):
+        comm._reduced = False
+    torch.cuda.synchronize()
+    dist.barrier()
+    tol = 2e-2 if reduced_by != "none" else 0.0
+    out = {
+        "replicas_bit_identical": identical,
+        "path": getattr(comm, "name", "?"),
+        "reduced_by": reduced_by,
+        "grad_max_abs_err_over_max_abs": worst,
+        "grad_rms_err_over_rms_rank0": rms,
+        "tolerance": tol,
+    }
+    out["ok"] = bool(identical and (reduced_by == "none" or worst <= tol))
+    return out
+
+
 # ------------------------------------------------------------------------------------------------
 # our arm
 # ------------------------------------------------------------------------------------------------
@@ -204,30 +302,57 @@ def run_ours(args: argparse.Namespace) -> dict[str, Any]:
         lib.llmtrain_b200_launch_count.restype = __import__("ctypes").c_longlong
 
         # ---- device-resident arm ---------------------------------------------------------------
-        gen = torch.Generator(device="cuda").manual_seed(1234 + rank)
+        # (tokens come from the library's device-resident generator, SURVEY W13: each rank draws
+        # its own rows of one global counter-based stream)
+        from llmtrain.ops import kernels as K
+
         pool = []
-        for _ in range(4):
-            stream_ = torch.randint(0, GPT2_SMALL["vocab_size"], (mb, seq + 1), device="cuda",
-                                    generator=gen)
-            pool.append({"input_ids": stream_[:, :-1].contiguous(),
-                         "labels": stream_[:, 1:].contiguous()})
+        for i in range(4):
+            ids_, labels_ = K.synthetic_tokens(mb, seq, GPT2_SMALL["vocab_size"], seed=1234,
+                                               first_row=(i * world + rank) * mb)
+            pool.append({"input_ids": ids_, "labels": labels_})
         cursor = [0]
 
         def next_device_batch() -> dict[str, Any]:
             cursor[0] += 1
             return pool[cursor[0] % len(pool)]
 
-        def steps_device(n: int) -> None:
+        step_marks: list[Any] = []
+
+        def steps_device(n: int, *, mark: bool = False) -> None:
             for _ in range(n):
                 engine.train_step(next_device_batch, accum)
+                if mark:
+                    ev = torch.cuda.Event(enable_timing=True)
+                    ev.record()
+                    step_marks.append(ev)
 
         steps_device(args.warmup)
         engine.collect_phase_timing()  # drop warm-up samples
         launches_before = int(lib.llmtrain_b200_launch_count())
         with ClockSampler(torch.cuda.current_device()) as clocks:
-            ms = _timed(lambda: steps_device(args.steps), world)
+            ms = _timed(lambda: steps_device(args.steps, mark=True), world)
         launches = int(lib.llmtrain_b200_launch_count()) - launches_before
+        ms_rank = ms
         ms = _max_over_ranks(ms, world)
+        # per-rank attribution of the N-GPU step time: this rank's total, its per-step spread
+        # (event to event), its SM clock and board power during the timed region
+        per_step = [step_marks[i].elapsed_time(step_marks[i + 1]) for i in range(len(step_marks) - 1)]
+        clk = clocks.summary()
+        rows = _gather_rows(
+            [ms_rank / args.steps,
+             min(per_step) if per_step else 0.0,
+             statistics.median(per_step) if per_step else 0.0,
+             max(per_step) if per_step else 0.0,
+             float(clk["sm_mhz"] or 0), float(clk["power_w"] or 0)], world)
+        per_rank = {
+            "ms_per_step": [round(r[0], 3) for r in rows],
+            "step_ms_min": [round(r[1], 3) for r in rows],
+            "step_ms_median": [round(r[2], 3) for r in rows],
+            "step_ms_max": [round(r[3], 3) for r in rows],
+            "sm_mhz": [r[4] for r in rows],
+            "power_w": [r[5] for r in rows],
+        }
         value = tokens_per_step * args.steps / (ms / 1e3)
         phases = engine.collect_phase_timing()
 
@@ -241,6 +366,10 @@ def run_ours(args: argparse.Namespace) -> dict[str, Any]:
         d2h = 4 + 4                       # loss + grad-norm scalars read at the per-step log
 
         comm = getattr(engine, "_comm", None)
+        ddp_check = None
+        if world > 1 and comm is not None:
+            engine._prefetched = None
+            ddp_check = _ddp_check(engine, pool[0], world)
         # ---- exposed communication: the same steps with the gradient reduction switched off ----
         # (every rank then applies its local gradient; the replicas diverge, nothing is timed after
         # this).  exposed = step time with the bucket engine - step time without it, both
@@ -269,19 +398,11 @@ def run_ours(args: argparse.Namespace) -> dict[str, Any]:
             "dtype": "bf16",
             "data": "synthetic",
             "impl": "ours",
-            "config": {
-                "model": "gpt2-small-124M (d768 L12 H12 F3072 V50257 tied)",
-                "global_batch": mb * accum * world,
-                "micro_batch_per_gpu": mb,
-                "grad_accum": accum,
-                "seq_len": seq,
-                "parallelism": f"dp{world}",
-                "optimizer": "AdamW fp32 master + clip 1.0 (inside the timed region)",
-                "comm": getattr(comm, "name", "none") if world > 1 else "none",
-                "l2": "inputs larger than L2 (>=2 GB of weights/optimizer state + GBs of "
-                      "activations touched per step vs 126 MB L2); no explicit flush",
-            },
+            "config": bench_config(mb, accum, seq, world),
+            "notes": {"comm": getattr(comm, "name", "none") if world > 1 else "none",
+                      "master_weights": "fp32 arena + bf16 shadow, fused clip+AdamW kernel"},
             "clocks": clocks.summary(),
+            "per_rank": per_rank,
             "e2e": {
                 "value": e2e_value,
                 "unit": "tokens/s",
@@ -296,6 +417,8 @@ def run_ours(args: argparse.Namespace) -> dict[str, Any]:
         }
         if exposed is not None:
             result["comm_exposed"] = exposed
+        if ddp_check is not None:
+            result["ddp_check"] = ddp_check
         if phases:
             result["phase_ms_rank0"] = phases
         return result if rank == 0 else {}
@@ -324,7 +447,9 @@ def run_reference(args: argparse.Namespace) -> dict[str, Any]:
     try:
         return ref_harness.run(args, rank=rank, local_rank=local_rank, world=world,
                                model=GPT2_SMALL, metric=METRIC, timed=_timed,
-                               max_over_ranks=_max_over_ranks, sampler=ClockSampler)
+                               max_over_ranks=_max_over_ranks, sampler=ClockSampler,
+                               config=bench_config(args.micro_batch, args.grad_accum,
+                                                   args.seq_len, world))
     except Exception as exc:  # the arm must never take the driver down
         if rank == 0:
             return {"impl": "reference", "unavailable": f"{type(exc).__name__}: {exc}"[:300]}

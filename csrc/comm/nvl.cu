@@ -756,6 +756,11 @@ extern "C" int llmtrain_b200_nvl_attach_nvls(void* handle, float* uc, float* mc)
   return 0;
 }
 
+extern "C" const float* llmtrain_b200_nvl_reduced(void* handle, const float* g) {
+  Comm& c = *static_cast<Comm*>(handle);
+  return (c.nvls_mc != nullptr && g == c.nvls_uc) ? g : c.full;
+}
+
 // Small-message all-reduce: out[i] = scale * sum_r bf16(in_r[i]) for count <= 262144 elements
 // (count may be smaller than the communicator's arena; the arena must hold 2 * count elements).
 extern "C" int llmtrain_b200_nvl_allreduce_oneshot(void* handle, const float* in, float* out,

@@ -220,7 +220,7 @@ inline int linear_wgrad(int M, int N, int K, const void* dy, int ld_dy, const vo
 inline uint32_t drop_site(int layer, int which) { return uint32_t(4 * layer + which); }
 
 int forward(Gpt& g, const int64_t* ids, const uint8_t* key_mask, int B, int T, bool train,
-            cudaStream_t s) {
+            cudaStream_t s, bool chunked_head = false) {
   View v(g);
   NvtxRange phase("gpt.forward");
   const int M = B * T, d = g.d, F = g.F, dq = g.dq;
@@ -283,10 +283,52 @@ int forward(Gpt& g, const int64_t* ids, const uint8_t* key_mask, int B, int T, b
   B200_TRY(llmtrain_b200_layernorm_fwd(x, v.p(g.lnf_w), v.p(g.lnf_b), v.bf(g.a_lnf),
                                        v.f32(g.a_lnf_mean), v.f32(g.a_lnf_rstd), M, d, st));
   // logits[M, Vp] = lnf @ head^T   (pad rows of the shadow are zero -> pad logits are 0, ignored)
-  B200_TRY(llmtrain_b200_gemm(0, 0, M, g.Vp, d, v.bf(g.a_lnf), d, v.w(g.head), d,
-                              v.bf(g.a_logits), g.Vp, nullptr, 0, nullptr, nullptr, 0, st));
+  // With a loss to follow, the head runs in row chunks interleaved with the loss kernel instead
+  // (head_and_loss below).
+  if (!chunked_head)
+    B200_TRY(llmtrain_b200_gemm(0, 0, M, g.Vp, d, v.bf(g.a_lnf), d, v.w(g.head), d,
+                                v.bf(g.a_logits), g.Vp, nullptr, 0, nullptr, nullptr, 0, st));
   g.B = B; g.T = T; g.ids = ids; g.key_mask = key_mask;
   g.have_forward = true;
+  return 0;
+}
+
+// LM head + loss in row chunks (reference `src/llmtrain/models/gpt.py:143,184,256-269`).
+// The logits of all M rows are 3.3 GB at the bench shape — far beyond the 126 MB L2 — so the
+// one-shot sequence "GEMM writes logits, loss kernel reads them back and rewrites them as
+// dlogits" pays an HBM write, an HBM read and another HBM write per logit.  Per chunk of rows
+// sized to stay L2-resident the loss kernel finds the GEMM's output still in L2 and its in-place
+// rewrite is the only version that ever travels to HBM: one write per logit instead of
+// write + read + write.  (dlogits must exist in full for the weight-gradient GEMM, whose reduction
+// runs over ALL rows; recomputing instead costs a fourth vocabulary-sized GEMM, more than the
+// traffic it saves.)  LLMTRAIN_HEAD_CHUNK_ROWS overrides the chunk (0: one shot).
+inline int head_chunk_rows(const Gpt& g, int M) {
+  static const int forced = [] {
+    const char* e = std::getenv("LLMTRAIN_HEAD_CHUNK_ROWS");
+    return e != nullptr ? std::atoi(e) : -1;
+  }();
+  if (forced == 0) return M;
+  int rows = forced > 0 ? forced : int((80u << 20) / (size_t(g.Vp) * 2));  // ~80 MB of logits
+  rows = rows / 256 * 256;  // whole CTA-pair row tiles
+  if (rows < 256) rows = 256;
+  return rows < M ? rows : M;
+}
+
+int head_and_loss(Gpt& g, const int64_t* labels, const uint8_t* key_mask, int M, float* loss_acc,
+                  float loss_scale, float grad_scale, int write_grad, llm_stream_t st) {
+  View v(g);
+  const int d = g.d;
+  const int chunk = head_chunk_rows(g, M);
+  for (int r0 = 0; r0 < M; r0 += chunk) {
+    const int rows = M - r0 < chunk ? M - r0 : chunk;
+    __nv_bfloat16* logits = v.bf(g.a_logits) + size_t(r0) * g.Vp;
+    B200_TRY(llmtrain_b200_gemm(0, 0, rows, g.Vp, d, v.bf(g.a_lnf) + size_t(r0) * d, d,
+                                v.w(g.head), d, logits, g.Vp, nullptr, 0, nullptr, nullptr, 0, st));
+    B200_TRY(llmtrain_b200_cross_entropy(logits, labels + r0,
+                                         key_mask != nullptr ? key_mask + r0 : nullptr,
+                                         v.f32(g.a_loss_rows) + r0, loss_acc, rows, g.V, g.Vp,
+                                         loss_scale, grad_scale, write_grad, st));
+  }
   return 0;
 }
 
@@ -529,15 +571,11 @@ extern "C" int llmtrain_b200_gpt_forward(void* h, const int64_t* ids, const int6
   B200_REQUIRE(g.act != nullptr, "gpt_forward: arenas not bound");
   B200_REQUIRE(B >= 1 && B <= g.maxB && T >= 1 && T <= g.maxT, "gpt_forward: batch exceeds plan");
   auto s = reinterpret_cast<cudaStream_t>(stream);
-  if (engine::forward(g, ids, key_mask, B, T, mode == 2, s)) return 1;
-  if (mode >= 1) {
-    B200_REQUIRE(labels != nullptr, "gpt_forward: labels required for the loss");
-    if (llmtrain_b200_cross_entropy(g.act + g.a_logits, labels, key_mask,
-                                    reinterpret_cast<float*>(g.act + g.a_loss_rows), loss_acc,
-                                    B * T, g.V, g.Vp, loss_scale, grad_scale, mode == 2 ? 1 : 0,
-                                    stream))
-      return 1;
-  }
+  B200_REQUIRE(mode == 0 || labels != nullptr, "gpt_forward: labels required for the loss");
+  if (engine::forward(g, ids, key_mask, B, T, mode == 2, s, /*chunked_head=*/mode >= 1)) return 1;
+  if (mode >= 1 && engine::head_and_loss(g, labels, key_mask, B * T, loss_acc, loss_scale,
+                                         grad_scale, mode == 2 ? 1 : 0, stream))
+    return 1;
   if (mode != 2) g.have_forward = false;
   return 0;
 }

@@ -307,6 +307,12 @@ void* llmtrain_b200_nvls_mc_buffer(void* handle);  /* the team's view (multimem.
 /* overlapped training path in NVLink-SHARP mode: the gradient arena passed to
  * nvl_backward_overlapped / nvl_finish_step must then be `uc` itself (NULL, NULL detaches) */
 int llmtrain_b200_nvl_attach_nvls(void* nvl_handle, float* uc, float* mc);
+/* Where llmtrain_b200_nvl_backward_overlapped leaves the cross-rank SUM of the gradient buckets
+ * (fp32, arena layout, valid once the communicator's stream has drained and every rank has passed
+ * a barrier): the symmetric `full` buffer on the peer-to-peer path, the arena `g` itself when the
+ * buckets are reduced in the switch.  For verification (bench.py ddp_check, the DDP-equivalence
+ * test; reference behaviour being checked: DDP's averaged gradients, trainer.py:377-387). */
+const float* llmtrain_b200_nvl_reduced(void* nvl_handle, const float* g);
 /* buffer[i] := scale * sum_r buffer_r[i] on every rank (count % (4*world) == 0).  in / out: optional
  * fp32 [count] copied in before / out after; NULL, NULL runs the collective alone, in place. */
 int llmtrain_b200_nvls_allreduce(void* handle, const float* in, float* out, size_t count,

@@ -11,7 +11,10 @@ Knobs (``data.extra``): ``num_examples`` (default: enough for ``max_steps``, cap
 ``"arith"`` — a learnable arithmetic progression used by loss-goes-down tests).
 
 Rows are produced on the host in pinned memory when the run device is CUDA, so the trainer's
-host→device copy is asynchronous.
+host→device copy is asynchronous.  With ``data.extra.device_resident: true`` (CUDA runs, pattern
+``random``) the batches are generated ON the device instead, by the library's counter-based
+token kernel (``llmtrain_b200_synthetic_tokens``): no host work and no copy at all,
+every rank draws its own rows of one global stream.
 """
 
 from __future__ import annotations
@@ -46,6 +49,29 @@ class _SyntheticRows(Dataset[dict[str, torch.Tensor]]):
         stream = stream.to(torch.long)
         ids = stream[:-1].clone()
         return {"input_ids": ids, "labels": stream[1:].clone(), "attention_mask": torch.ones_like(ids)}
+
+
+class _DeviceBatches:
+    """Endless stream of device-generated ``(input_ids, labels)`` batches (train split only)."""
+
+    def __init__(self, batch: int, seq_len: int, vocab: int, seed: int, rank: int,
+                 world: int) -> None:
+        self._shape = (batch, seq_len, vocab)
+        self._seed, self._rank, self._world = seed, rank, world
+        self._batches_per_epoch = 1 << 20
+
+    def __len__(self) -> int:
+        return self._batches_per_epoch
+
+    def __iter__(self):  # noqa: ANN204
+        from llmtrain.ops import kernels as K
+
+        batch, seq_len, vocab = self._shape
+        for index in range(self._batches_per_epoch):
+            first_row = (index * self._world + self._rank) * batch
+            ids, labels = K.synthetic_tokens(batch, seq_len, vocab, seed=self._seed,
+                                             first_row=first_row)
+            yield {"input_ids": ids, "labels": labels}
 
 
 @register_data_module("synthetic_text")
@@ -92,6 +118,18 @@ class SyntheticTextDataModule(DataModule):
     def train_dataloader(self) -> DataLoader:
         if self._cfg is None or self._train is None:
             raise RuntimeError("setup must be called before train_dataloader")
+        cfg = self._cfg
+        if bool(cfg.data.extra.get("device_resident", False)):
+            if cfg.run.device != "cuda" or not torch.cuda.is_available():
+                raise ValueError("synthetic_text: data.extra.device_resident needs run.device: cuda")
+            if self._train._pattern != "random":
+                raise ValueError("synthetic_text: device_resident supports pattern 'random' only")
+            rank, world = 0, 1
+            if dist.is_available() and dist.is_initialized():
+                rank, world = dist.get_rank(), dist.get_world_size()
+            stream = _DeviceBatches(cfg.trainer.micro_batch_size, self._train._t, self._train._v,
+                                    cfg.run.seed, rank, world)
+            return stream  # type: ignore[return-value]  # iterable of batches, like a DataLoader
         return self._loader(self._train, train=True)
 
     def val_dataloader(self) -> DataLoader | None:

@@ -480,7 +480,7 @@ class B200TrainEngine(TrainEngine):
                 key_mask = (mask_h != 0).to(torch.uint8).to(self._device, non_blocking=True)
         # torch raises for a target outside [0, V) other than ignore_index (-100); the native loss
         # kernel cannot raise, so the (host-resident) labels are checked here
-        if labels_h.numel():
+        if labels_h.numel() and not labels_h.is_cuda:  # device-generated batches are in range
             lo, hi = int(labels_h.min()), int(labels_h.max())
             if hi >= self.model.vocab_size or (lo < 0 and lo != -100):
                 raise ValueError(

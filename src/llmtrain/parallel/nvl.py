@@ -354,6 +354,27 @@ class _NvlTrainComm:
         else:
             self._comm.step(g.g32, g.p32, m, v, g.p16, norm, hyper)
 
+    def reduced_gradient(self) -> torch.Tensor:
+        """fp32 view of the cross-rank gradient SUM left by :meth:`backward_last` (overlapped mode):
+        the communicator's symmetric buffer on the peer-to-peer path, the arena itself in-switch.
+        Synchronise the device and pass a barrier before reading it."""
+        lib = self._comm._lib
+        lib.llmtrain_b200_nvl_reduced.restype = ctypes.c_void_p
+        lib.llmtrain_b200_nvl_reduced.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        address = int(lib.llmtrain_b200_nvl_reduced(self._comm._handle, ptr(self._gpt.g32)))
+        n = self._gpt.n_params
+
+        class _Raw:
+            __cuda_array_interface__ = {
+                "shape": (n,), "typestr": "<f4", "data": (address, True), "version": 3,
+                "strides": None,
+            }
+
+        raw = _Raw()
+        tensor = torch.as_tensor(raw, device=torch.device("cuda", torch.cuda.current_device()))
+        tensor._owner = (self, raw)  # type: ignore[attr-defined]
+        return tensor
+
     def close(self) -> None:
         if self in _live:
             _live.remove(self)

@@ -235,3 +235,23 @@ def test_narrow_heads_run_natively_and_match_torch_ops(d_model: int, n_heads: in
     w = native.blocks[0].attn.qkv_proj.weight
     err = (w.grad - 2 * ref["blocks.0.attn.qkv_proj.weight"].grad).abs().max().item()
     assert err / (ref["blocks.0.attn.qkv_proj.weight"].grad.abs().max().item() + 1e-8) < 0.12
+
+
+def test_trainer_runs_on_device_resident_synthetic_tokens(tmp_path: Path) -> None:
+    """``data.extra.device_resident``: batches come from the library's token kernel,
+    nothing is copied from the host; the trainer contract (TrainResult, finite loss near ln V for
+    random tokens) is unchanged."""
+    from llmtrain.engine.b200 import B200TrainEngine
+    from llmtrain.training import Trainer
+
+    cfg = _cfg(tmp_path,
+               data={"extra": {"pattern": "random", "device_resident": True}},
+               trainer={"max_steps": 5, "eval_every_steps": 1000, "save_every_steps": 1000})
+    trainer = Trainer(cfg)
+    assert isinstance(trainer._engine, B200TrainEngine)
+    first = next(iter(trainer._train_loader))
+    assert first["input_ids"].is_cuda and first["input_ids"].shape == (4, 128)
+    assert torch.equal(first["labels"][:, :-1], first["input_ids"][:, 1:])
+    result = trainer.fit()
+    assert result.final_step == 5
+    assert abs(result.final_loss - math.log(1000)) < 1.0

@@ -19,7 +19,7 @@ def _free_port() -> int:
         return int(s.getsockname()[1])
 
 
-@pytest.mark.parametrize("world", [2])
+@pytest.mark.parametrize("world", [2, 4, 8])
 def test_nvl_allreduce_step_and_trainer(world: int) -> None:
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
@@ -31,6 +31,7 @@ def test_nvl_allreduce_step_and_trainer(world: int) -> None:
     )
     assert proc.returncode == 0, proc.stdout[-3000:] + proc.stderr[-3000:]
     assert "NVL_WORKER_OK" in proc.stdout
+    assert proc.stdout.count("DDP_EQUIVALENCE_OK") == 2, proc.stdout[-2000:]
 
 
 def test_nvls_multimem_allreduce() -> None:
