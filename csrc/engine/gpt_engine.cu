@@ -293,23 +293,26 @@ int forward(Gpt& g, const int64_t* ids, const uint8_t* key_mask, int B, int T, b
   return 0;
 }
 
-// LM head + loss in row chunks (reference `src/llmtrain/models/gpt.py:143,184,256-269`).
-// The logits of all M rows are 3.3 GB at the bench shape — far beyond the 126 MB L2 — so the
-// one-shot sequence "GEMM writes logits, loss kernel reads them back and rewrites them as
-// dlogits" pays an HBM write, an HBM read and another HBM write per logit.  Per chunk of rows
-// sized to stay L2-resident the loss kernel finds the GEMM's output still in L2 and its in-place
-// rewrite is the only version that ever travels to HBM: one write per logit instead of
-// write + read + write.  (dlogits must exist in full for the weight-gradient GEMM, whose reduction
-// runs over ALL rows; recomputing instead costs a fourth vocabulary-sized GEMM, more than the
-// traffic it saves.)  LLMTRAIN_HEAD_CHUNK_ROWS overrides the chunk (0: one shot).
+// LM head + loss, optionally in row chunks (reference
+// `src/llmtrain/models/gpt.py:143,184,256-269`).  The logits of all M rows are 3.3 GB at the
+// bench shape, so "GEMM writes logits, loss kernel reads them back and rewrites them as dlogits"
+// pays an HBM write, a read and another write per logit; per chunk of rows small enough to stay in
+// the 126 MB L2 the loss kernel could find the GEMM's output still on chip.  MEASURED on B200
+// (GPT-2 124M, mb 32, whole step): one shot 33.40 ms, chunks of 2048 / 1024 / 768 / 512 rows
+// 33.47 / 33.51 / 33.84 / 34.12 ms — the wave quantisation of the small GEMMs (a 512-row chunk is
+// 394 pair tiles on 74 pairs) and of the 148-CTA loss kernel costs more than the saved traffic, so
+// one shot stays the default and LLMTRAIN_HEAD_CHUNK_ROWS=<rows> is the experiment knob.
+// (dlogits must exist in full for the weight-gradient GEMM, whose reduction runs over ALL rows;
+// recomputing them instead costs a fourth vocabulary-sized GEMM — 2.6 TFLOP, ~2 ms — against
+// ~1.3 ms of loss-kernel traffic: profiles/README.md, "LM head".)
 inline int head_chunk_rows(const Gpt& g, int M) {
   static const int forced = [] {
     const char* e = std::getenv("LLMTRAIN_HEAD_CHUNK_ROWS");
-    return e != nullptr ? std::atoi(e) : -1;
+    return e != nullptr ? std::atoi(e) : 0;
   }();
-  if (forced == 0) return M;
-  int rows = forced > 0 ? forced : int((80u << 20) / (size_t(g.Vp) * 2));  // ~80 MB of logits
-  rows = rows / 256 * 256;  // whole CTA-pair row tiles
+  (void)g;
+  if (forced <= 0) return M;
+  int rows = forced / 256 * 256;  // whole CTA-pair row tiles
   if (rows < 256) rows = 256;
   return rows < M ? rows : M;
 }
