@@ -369,7 +369,10 @@ def run_ours(args: argparse.Namespace) -> dict[str, Any]:
         ddp_check = None
         if world > 1 and comm is not None:
             engine._prefetched = None
-            ddp_check = _ddp_check(engine, pool[0], world)
+            try:
+                ddp_check = _ddp_check(engine, pool[0], world)
+            except Exception as exc:  # evidence only: must never take the measurement down
+                ddp_check = {"ok": False, "error": f"{type(exc).__name__}: {exc}"[:300]}
         # ---- exposed communication: the same steps with the gradient reduction switched off ----
         # (every rank then applies its local gradient; the replicas diverge, nothing is timed after
         # this).  exposed = step time with the bucket engine - step time without it, both

@@ -366,7 +366,7 @@ class _NvlTrainComm:
 
         class _Raw:
             __cuda_array_interface__ = {
-                "shape": (n,), "typestr": "<f4", "data": (address, True), "version": 3,
+                "shape": (n,), "typestr": "<f4", "data": (address, False), "version": 3,
                 "strides": None,
             }
 

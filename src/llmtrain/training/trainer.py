@@ -119,7 +119,10 @@ class Trainer:
             return torch.device(kind)
         if not torch.cuda.is_available():
             raise RuntimeError("run.device is 'cuda' but torch sees no CUDA device")
-        local = self._ddp_state.local_rank if self._ddp_state is not None else 0
+        # without a DDP state: the device the caller made current (0 in a fresh process), so a
+        # trainer built inside a multi-GPU program stays on that process's GPU
+        local = (self._ddp_state.local_rank if self._ddp_state is not None
+                 else torch.cuda.current_device())
         index = local % torch.cuda.device_count()
         torch.cuda.set_device(index)
         return torch.device("cuda", index)

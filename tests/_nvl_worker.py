@@ -183,16 +183,22 @@ def _check_ddp_equivalence(rank: int, world: int, nvls: bool) -> None:
             "trainer": {"max_steps": steps, "micro_batch_size": batch, "grad_accum_steps": 1,
                         "warmup_steps": 0, "lr": 1e-3, "weight_decay": 0.0,
                         "extra": {"overlap_comm": True, "prefetch": False}},
-            "ddp": {"enabled": ddp, "backend": "nvl"},
+            "ddp": {"enabled": ddp, "backend": "nvl", "timeout_sec": 60},
             "mlflow": {"enabled": False}, "logging": {"log_to_file": False}, "output": {},
         })
+
+    def say(what: str) -> None:
+        if os.environ.get("NVL_WORKER_VERBOSE"):
+            print(f"[ddp-eq rank {rank}] {what}", flush=True)
 
     os.environ["LLMTRAIN_NVLS"] = "1" if nvls else "0"
     state = DDPState(rank=rank, world_size=world, local_rank=rank, is_main=rank == 0)
     torch.manual_seed(4321)
     many = Trainer(cfg_for(mb, True), ddp_state=state)._engine
+    say("W-rank trainer built")
     torch.manual_seed(4321)
     one = Trainer(cfg_for(mb * world, False))._engine
+    say("1-rank trainer built")
     one._gpt.p32.copy_(many._gpt.p32)
     one._gpt.refresh_shadow()
     start = many._gpt.p32.clone()
@@ -202,7 +208,10 @@ def _check_ddp_equivalence(rank: int, world: int, nvls: bool) -> None:
         whole = {"input_ids": tokens[:, :-1].contiguous(), "labels": tokens[:, 1:].contiguous()}
         shard = {k: v[rank * mb:(rank + 1) * mb].contiguous() for k, v in whole.items()}
         loss_many, _ = many.train_step(lambda shard=shard: shard, 1)
+        say(f"step {step}: W-rank step enqueued")
         loss_one, _ = one.train_step(lambda whole=whole: whole, 1)
+        torch.cuda.synchronize()
+        say(f"step {step}: both steps done")
         mean = loss_many.detach().clone()
         dist.all_reduce(mean)
         mean /= world
@@ -266,6 +275,19 @@ def main() -> int:
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
     dist.init_process_group("cpu:gloo,cuda:nccl")
+    if len(sys.argv) > 1 and sys.argv[1] == "ddp-eq":
+        try:
+            from llmtrain.parallel.nvl import shutdown
+
+            _check_ddp_equivalence(rank, world, nvls=False)
+            _check_ddp_equivalence(rank, world, nvls=True)
+            shutdown()
+            dist.barrier()
+            if rank == 0:
+                print("NVL_WORKER_OK", flush=True)
+        finally:
+            dist.destroy_process_group()
+        return 0
     if len(sys.argv) > 1 and sys.argv[1] == "nvls":
         import logging
 
