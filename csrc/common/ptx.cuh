@@ -175,6 +175,15 @@ __device__ __forceinline__ void tma_store_3d(const void* tmap, const void* smem_
       ::"l"(reinterpret_cast<uint64_t>(tmap)), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2)
       : "memory");
 }
+__device__ __forceinline__ void tma_reduce_add_3d(const void* tmap, const void* smem_src,
+                                                  int32_t c0, int32_t c1, int32_t c2) {
+  asm volatile(
+      "cp.reduce.async.bulk.tensor.3d.global.shared::cta.add.tile.bulk_group"
+      " [%0, {%2, %3, %4}], [%1];"
+      ::"l"(reinterpret_cast<uint64_t>(tmap)), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+
 // out[...] += smem tile (element-wise add done by the TMA unit in L2; fp32 / bf16 supported).
 __device__ __forceinline__ void tma_reduce_add_2d(const void* tmap, const void* smem_src,
                                                   int32_t c0, int32_t c1) {

@@ -17,8 +17,8 @@
 //
 // D_i = rowsum(dO o O) comes from a small pre-kernel.  dK/dV leave through one TMA store each into
 // the fused [B, T, 3d] gradient buffer; dQ contributions from different kv tiles meet in an fp32
-// buffer (16-byte vector reductions straight from registers) that a post-kernel converts into the
-// q third of that same gradient buffer.
+// buffer (TMA reduce-add of 32x32 slices) that a post-kernel converts into the q third of that
+// same gradient buffer.
 //
 // Pipeline.  The tensor core executes its queue in order, so the issue order IS the schedule.  After
 // the softmax-grad warps hand over P_i / dS_i the MMA warp issues
@@ -26,11 +26,13 @@
 // P has ONE shared-memory buffer (its only reader, the dV product, is first in the queue and has
 // retired by the time S_{i+1}/dP_{i+1} complete, which is what the warps wait for before they write
 // P_{i+1}); dS has two, so dK/dQ of tile i run underneath the math of tile i+1; dQ has two TMEM
-// accumulators and is drained one iteration late.  The 32 KB saved on P buy a THIRD Q/dO stage:
-// the loads of tile i+2 are in flight while tile i is computed (with two stages the load of the
-// next tile could only start when dK of the previous one had retired, and its ~1 us latency sat
-// on the critical path of every iteration: tensor pipe 20% busy, softmax warps 45% of their time
-// waiting for S — profiles/attention_bwd_ncu_r1.md).
+// accumulators and is drained one iteration late.  The 32 KB saved on P hold the fp32 dQ tile on
+// its way out: each warp stages its 32x32 slice and hands it to the TMA unit as one reduce-add
+// into the fp32 dQ buffer (a post-kernel converts that buffer into the q third of dqkv).
+// What limits the kernel (B = 32, T = 1024, H = 12, 425 us per layer before this change; each
+// variant measured with that work removed): per-thread dQ atomics 76 us, the softmax-grad math
+// 55 us, all five MMAs together ~45 us; the remaining skeleton (barrier hops MMA <-> warps, TMA
+// latency) is ~230 us, and the dsum / memset / convert passes around the kernel ~60 us.
 
 #include "../common/host.cuh"
 #include "../common/philox.cuh"
@@ -49,13 +51,14 @@ constexpr int TMEM_COLS = 512;
 constexpr int COL_S = 0, COL_DP = 128, COL_DV = 256, COL_DK = 320, COL_DQ = 384;  // dQ: 2 x 64 cols
 constexpr int OFF_K = 0;
 constexpr int OFF_V = OFF_K + TILE;
-constexpr int NQ = 3;                        // Q / dO ring depth
+constexpr int NQ = 2;                        // Q / dO ring depth
 constexpr int OFF_Q = OFF_V + TILE;          // [NQ]
 constexpr int OFF_DO = OFF_Q + NQ * TILE;    // [NQ]
 constexpr int PDS_BYTES = 2 * TILE;          // one 128x128 bf16 tile = two 64-column regions
 constexpr int OFF_P = OFF_DO + NQ * TILE;    // 32 KB, single buffer
 constexpr int OFF_DS = OFF_P + PDS_BYTES;    // [2] x 32 KB
-constexpr int OFF_BAR = OFF_DS + 2 * PDS_BYTES;
+constexpr int OFF_DQS = OFF_DS + 2 * PDS_BYTES;  // 32 KB: fp32 dQ tile on its way out (8 warp slices)
+constexpr int OFF_BAR = OFF_DQS + 2 * TILE;
 constexpr int SMEM = OFF_BAR + 256 + 1024;
 
 struct Params {
@@ -162,7 +165,8 @@ __device__ __forceinline__ void softmax_grad(uint32_t t_row, uint8_t* rp, uint8_
 template <bool DROP>
 __global__ void __launch_bounds__(THREADS, 1)
 bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
-           const __grid_constant__ CUtensorMap tmDQKV, const Params p) {
+           const __grid_constant__ CUtensorMap tmDQKV, const __grid_constant__ CUtensorMap tmDQ,
+           const Params p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~uintptr_t(1023));
@@ -193,6 +197,7 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
     tma_prefetch_desc(&tmQKV);
     tma_prefetch_desc(&tmDO);
     tma_prefetch_desc(&tmDQKV);
+    tma_prefetch_desc(&tmDQ);
     mbar_init(kv_full, 1);
     for (int s = 0; s < NQ; ++s) {
       mbar_init(&q_full[s], 1);
@@ -307,9 +312,13 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
     const uint8_t* kmask = p.key_mask ? p.key_mask + size_t(b) * p.T : nullptr;
     const size_t stat_base = (size_t(b) * p.H + h) * p.T;
 
-    // dQ_i: TMEM -> registers -> eight 16-byte fp32 reductions per thread into dq32 (the thread's
-    // 32 columns of its row are one full 128-byte line).  Called one iteration late, so the MMAs
-    // that precede dq_full(i) are never waited for, and it needs no staging buffer or CTA barrier.
+    // dQ_i: TMEM -> registers -> this warp's 32-row x 32-column fp32 slice of a swizzled staging
+    // tile -> ONE TMA reduce-add per warp into dq32.  (Per-thread red.global.add.v4 of the same
+    // data was the single largest cost of this kernel: 453 MB of 16-byte L2 reductions per layer,
+    // 76 us of 425 at B = 32; the TMA unit hands L2 whole 128-byte lines.)  Called one iteration
+    // late, so the MMAs that precede dq_full(i) are never waited for; each warp owns its slice and
+    // its own bulk group, so no CTA-wide barrier is involved.  Rows past T are clipped by the map.
+    uint8_t* dq_stage = smem + OFF_DQS + half * TILE + quarter * 4096;
     auto drain_dq = [&](int i) {
       mbar_wait(&dq_full[i & 1], (i >> 1) & 1);
       tc_fence_after_sync();
@@ -317,15 +326,17 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
       tmem_ld_32x32b_x32(tmem + COL_DQ + (i & 1) * HD + lane_base + half * 32, v);
       tmem_ld_wait();
       tc_fence_before_sync();
-      const int qrow_i = (jt + i) * BQ + r;
-      if (qrow_i < p.T) {
-        float* dst = p.dq32 + (size_t(b) * p.T + qrow_i) * d + h * HD + half * 32;
+      if (lane == 0) tma_store_wait_read<0>();  // the previous slice has left shared memory
+      __syncwarp();
 #pragma unroll
-        for (int q = 0; q < 8; ++q)
-          asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + 4 * q),
-                       "f"(__uint_as_float(v[4 * q])), "f"(__uint_as_float(v[4 * q + 1])),
-                       "f"(__uint_as_float(v[4 * q + 2])), "f"(__uint_as_float(v[4 * q + 3]))
-                       : "memory");
+      for (int q = 0; q < 8; ++q)
+        *reinterpret_cast<uint4*>(dq_stage + swizzle128(lane * 128 + q * 16)) =
+            make_uint4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        tma_reduce_add_3d(&tmDQ, dq_stage, h * HD + half * 32, (jt + i) * BQ + quarter * 32, b);
+        tma_store_commit();
       }
     };
 
@@ -389,6 +400,7 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
       if (threadIdx.x == 0) stamp(p, 0, it, 3);
     }
     drain_dq(n_iter - 1);
+    if (lane == 0) tma_store_wait_read<0>();  // staging must outlive the last reduction's read
 
     // dV, dK: TMEM -> bf16 -> swizzled staging (P / dS buffers are free now) -> TMA store.
     // Each warp converts its 32-column half of both accumulators.
@@ -581,6 +593,9 @@ static int attention_bwd_impl(const void* qkv, const void* out, const void* dout
   if (make_tmap_3d(&tDQKV, static_cast<__nv_bfloat16*>(dqkv), B, T, 3 * d, 3 * d,
                    uint64_t(T) * 3 * d, 128, ab::HD, Swz::B128)) return 1;
 
+  CUtensorMap tDQ;  // fp32 accumulator [B, T, d], boxes of 32 rows x 32 columns (128-byte rows)
+  if (make_tmap_3d(&tDQ, dq32, B, T, d, d, uint64_t(T) * d, 32, 32, Swz::B128)) return 1;
+
   ab::Params p;
   p.B = B; p.T = T; p.H = H;
   p.scale = softmax_scale > 0.f ? softmax_scale : 1.0f / std::sqrt(float(head_dim));
@@ -608,9 +623,9 @@ static int attention_bwd_impl(const void* qkv, const void* out, const void* dout
   }
   dim3 grid(ceil_div(T, ab::BKV), H, B);
   if (drop.threshold != 0)
-    B200_LAUNCH((ab::bwd_kernel<true>), grid, ab::THREADS, ab::SMEM, stream, tQKV, tDO, tDQKV, p);
+    B200_LAUNCH((ab::bwd_kernel<true>), grid, ab::THREADS, ab::SMEM, stream, tQKV, tDO, tDQKV, tDQ, p);
   else
-    B200_LAUNCH((ab::bwd_kernel<false>), grid, ab::THREADS, ab::SMEM, stream, tQKV, tDO, tDQKV, p);
+    B200_LAUNCH((ab::bwd_kernel<false>), grid, ab::THREADS, ab::SMEM, stream, tQKV, tDO, tDQKV, tDQ, p);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   if (p.trace != nullptr) {  // debug: timeline of the CTA with the most query tiles
