@@ -7,3 +7,7 @@ extern "C" int llmtrain_b200_abi_version(void) { return 1000; }
 extern "C" long long llmtrain_b200_launch_count(void) {
   return b200::launch_counter().load(std::memory_order_relaxed);
 }
+extern "C" void llmtrain_b200_set_deterministic(int on) {
+  b200::deterministic_flag().store(on != 0 ? 1 : 0, std::memory_order_relaxed);
+}
+extern "C" int llmtrain_b200_get_deterministic(void) { return b200::deterministic() ? 1 : 0; }

@@ -133,6 +133,15 @@ inline std::atomic<long long>& launch_counter() {
 }
 #define B200_COUNT_LAUNCH(n) ::b200::launch_counter().fetch_add((n), std::memory_order_relaxed)
 
+// Deterministic mode (llmtrain_b200_set_deterministic): kernels whose fast path sums floats in a
+// hardware-chosen order switch to a fixed order — split-K weight gradients run unsplit, attention
+// backward takes turns on dQ, the embedding scatter and the bias gradients use ordered kernels.
+inline std::atomic<int>& deterministic_flag() {
+  static std::atomic<int> flag{0};
+  return flag;
+}
+inline bool deterministic() { return deterministic_flag().load(std::memory_order_relaxed) != 0; }
+
 // Kernel launch with programmatic dependent launch (see pdl_wait in ptx.cuh) and an optional
 // thread-block cluster.  LLMTRAIN_PDL=0 falls back to plain stream order (A/B measurements).
 // ONLY kernels that call pdl_enter()/pdl_wait() before their first global access may come here.

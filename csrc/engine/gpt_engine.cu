@@ -170,6 +170,10 @@ void plan_acts(Gpt& g) {
     const size_t need = llmtrain_b200_bias_grad_scratch_bytes(int(M), w);
     if (need > red) red = need;
   }
+  {
+    const size_t need = llmtrain_b200_embed_bwd_ordered_scratch_bytes(g.V);
+    if (need > red) red = need;
+  }
   g.red_scratch_bytes = red;
   g.a_red_scratch = take_bytes(c, red);
   g.act_bytes = c;
@@ -359,6 +363,7 @@ int backward(Gpt& g, cudaStream_t s, BucketHook hook = nullptr, void* hook_ctx =
   // materialised once (the GEMMs read it through TMA) and the projection's bias gradient is its
   // column sum, so the LayerNorm backwards stop emitting those sums.
   const bool drop = g.drop_on;
+  const bool det = deterministic();  // fixed summation orders (llmtrain_b200_set_deterministic)
   const float dp = g.drop_p;
   const uint64_t seed = g.drop_seed, off = g.drop_offset;
 
@@ -393,8 +398,14 @@ int backward(Gpt& g, cudaStream_t s, BucketHook hook = nullptr, void* hook_ctx =
     B200_TRY(linear_wgrad(M, d, F, dproj, d, v.bf(a.fch_act), v.grad(o.proj_w), s));
     // dfc = (dproj @ Wproj) o gelu'(pre); its column sums (= fc's bias gradient) come out of the
     // same epilogue.
-    B200_TRY(llmtrain_b200_gemm_colsum(1, 3, M, F, d, dproj, d, v.w(o.proj_w), F, dfc, F, nullptr,
-                                       v.bf(a.fch_pre), F, v.grad(o.fc_b), st));
+    if (det) {  // fixed-order bias gradient instead of the epilogue's atomics
+      B200_TRY(llmtrain_b200_gemm(1, 3, M, F, d, dproj, d, v.w(o.proj_w), F, dfc, F, nullptr, 0,
+                                  nullptr, v.bf(a.fch_pre), F, st));
+      B200_TRY(llmtrain_b200_bias_grad(dfc, F, M, F, v.grad(o.fc_b), red, red_bytes, st));
+    } else {
+      B200_TRY(llmtrain_b200_gemm_colsum(1, 3, M, F, d, dproj, d, v.w(o.proj_w), F, dfc, F,
+                                         nullptr, v.bf(a.fch_pre), F, v.grad(o.fc_b), st));
+    }
     B200_TRY(linear_wgrad(M, F, d, dfc, F, v.bf(a.ln2), v.grad(o.fc_w), s));
     B200_TRY(linear_dgrad(0, M, F, d, dfc, v.w(o.fc_w), dtmp, nullptr, s));
     B200_TRY(llmtrain_b200_layernorm_bwd(dtmp, v.bf(a.resid1), v.p(o.ln2_w), v.f32(a.ln2_mean),
@@ -424,9 +435,10 @@ int backward(Gpt& g, cudaStream_t s, BucketHook hook = nullptr, void* hook_ctx =
     B200_TRY(linear_dgrad(0, M, d, dq, dout, wo, datty, nullptr, s));
     // dqkv and, fused, qkv_proj's bias gradient (column sums of dqkv)
     B200_TRY(llmtrain_b200_attention_bwd_fused(
-        v.bf(a.qkv), v.bf(a.atty), datty, v.f32(a.lse), g.key_mask, dqkv, dbq,
+        v.bf(a.qkv), v.bf(a.atty), datty, v.f32(a.lse), g.key_mask, dqkv, det ? nullptr : dbq,
         g.act + g.a_attn_scratch, g.attn_scratch_bytes, B, T, g.H, 64, sm_scale, drop ? dp : 0.f,
         seed, off, drop_site(l, 0), st));
+    if (det) B200_TRY(llmtrain_b200_bias_grad(dqkv, 3 * dq, M, 3 * dq, dbq, red, red_bytes, st));
     B200_TRY(linear_wgrad(M, 3 * dq, d, dqkv, 3 * dq, v.bf(a.ln1), dwq, s));
     B200_TRY(linear_dgrad(0, M, 3 * dq, d, dqkv, wq, dtmp, nullptr, s));
     if (g.padded) {
@@ -448,7 +460,11 @@ int backward(Gpt& g, cudaStream_t s, BucketHook hook = nullptr, void* hook_ctx =
   }
   if (drop)
     B200_TRY(llmtrain_b200_dropout(dresid, dresid, M, d, d, dp, seed, off, kDropSiteEmbedding, st));
-  B200_TRY(llmtrain_b200_embed_bwd(g.ids, dresid, v.grad(g.wte), v.grad(g.wpe), B, T, d, g.V, st));
+  if (det)
+    B200_TRY(llmtrain_b200_embed_bwd_ordered(g.ids, dresid, v.grad(g.wte), v.grad(g.wpe), B, T, d,
+                                             g.V, red, red_bytes, st));
+  else
+    B200_TRY(llmtrain_b200_embed_bwd(g.ids, dresid, v.grad(g.wte), v.grad(g.wpe), B, T, d, g.V, st));
   if (hook != nullptr) {
     const size_t first_layer = g.L > 0 ? g.layer[0].ln1_w : g.lnf_w;
     B200_TRY(hook(hook_ctx, 0, first_layer));              // position embedding (small, first)

@@ -73,6 +73,7 @@ struct Params {
   DropoutParams drop;  // attention-probability dropout; threshold 0 = off
   int t_pad;           // T rounded up to 8: row pitch of the mask's element index
   long long* trace;    // debug (LLMTRAIN_ATTN_TRACE): clock64 stamps of CTA 0, else nullptr
+  int* turn;           // deterministic mode: [B, H, nq, 8] contribution counters (zeroed), else nullptr
 };
 
 // trace layout: [role 0 = softmax-grad warp 0, 1 = MMA, 2 = TMA][iteration < 16][4 stamps]
@@ -335,8 +336,27 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
       fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) {
+        // Deterministic mode: the key tiles add into a query tile in ascending order.  This CTA
+        // (key tile jt) waits until jt earlier contributions to this 32x32 slice have landed and
+        // publishes its own once the reduction has completed.  CTAs with a smaller key tile have
+        // a smaller block index, so they are resident or done: the wait cannot deadlock.
+        int* turn = nullptr;
+        if (p.turn != nullptr) {
+          turn = p.turn + ((size_t(b) * p.H + h) * nq + (jt + i)) * 8 + (warp & 7);
+          const unsigned long long t0 = global_timer_ns();
+          int seen;
+          do {
+            asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(seen) : "l"(turn) : "memory");
+            if (seen != jt && global_timer_ns() - t0 > B200_MBAR_TIMEOUT_NS) mbar_timeout_trap();
+          } while (seen != jt);
+        }
         tma_reduce_add_3d(&tmDQ, dq_stage, h * HD + half * 32, (jt + i) * BQ + quarter * 32, b);
         tma_store_commit();
+        if (turn != nullptr) {
+          tma_store_wait<0>();  // the reduction has been performed, not merely read from smem
+          __threadfence();
+          asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(turn), "r"(jt + 1) : "memory");
+        }
       }
     };
 
@@ -556,8 +576,10 @@ __global__ void dq_convert_kernel(const float* __restrict__ dq32, __nv_bfloat16*
 using namespace b200;
 
 extern "C" size_t llmtrain_b200_attention_bwd_scratch_bytes(int B, int T, int H, int head_dim) {
-  // fp32 dQ accumulator [B,T,d] followed by D [B,H,T]
-  return size_t(B) * T * H * head_dim * sizeof(float) + size_t(B) * H * T * sizeof(float);
+  // fp32 dQ accumulator [B,T,d], D [B,H,T], and the deterministic mode's turn counters [B,H,nq,8]
+  const size_t nq = size_t((T + 127) / 128);
+  return size_t(B) * T * H * head_dim * sizeof(float) + size_t(B) * H * T * sizeof(float) +
+         size_t(B) * H * nq * 8 * sizeof(int);
 }
 
 // qkv [B,T,3d], out/dout [B,T,d] bf16, lse [B,H,T]  ->  dqkv [B,T,3d] bf16.
@@ -607,6 +629,13 @@ static int attention_bwd_impl(const void* qkv, const void* out, const void* dout
   p.dbias = dbias;
   p.drop = drop;
   p.t_pad = (T + 7) & ~7;
+  p.turn = nullptr;
+  if (deterministic()) {
+    const size_t turn_bytes = size_t(B) * H * ceil_div(T, ab::BQ) * 8 * sizeof(int);
+    p.turn = reinterpret_cast<int*>(static_cast<uint8_t*>(scratch) + dq_bytes +
+                                    size_t(B) * H * T * sizeof(float));
+    B200_CHECK_CUDA(cudaMemsetAsync(p.turn, 0, turn_bytes, stream));
+  }
   p.trace = nullptr;
   static const bool want_trace = std::getenv("LLMTRAIN_ATTN_TRACE") != nullptr;
   if (want_trace) {

@@ -74,6 +74,68 @@ __global__ void embed_bwd_wte_kernel(const int64_t* __restrict__ ids,
   }
 }
 
+// Deterministic variant of the scatter (llmtrain_b200_set_deterministic): every vocabulary row gets
+// ONE writer — the warp of the first position that holds the token — which walks the later
+// positions in ascending order and adds their rows in registers before a single plain update of
+// dwte[token].  first[] is found with atomicMin (an order-independent result).
+__global__ void embed_first_kernel(const int64_t* __restrict__ ids, int* __restrict__ first,
+                                   int rows, int vocab) {
+  pdl_enter();
+  const int row = blockIdx.x * blockDim.x + threadIdx.x;
+  if (row >= rows) return;
+  const int64_t tok = ids[row];
+  if (tok >= 0 && tok < vocab) atomicMin(first + tok, row);
+}
+
+constexpr int EMB_MAX_V4 = 16;  // float4 chunks per lane: d <= 2048
+__global__ void embed_bwd_wte_ordered_kernel(const int64_t* __restrict__ ids,
+                                             const __nv_bfloat16* __restrict__ dx,
+                                             const int* __restrict__ first,
+                                             float* __restrict__ dwte, int rows, int d, int vocab) {
+  pdl_enter();
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int lane = threadIdx.x & 31;
+  const int64_t tok = ids[row];
+  if (tok < 0 || tok >= vocab || first[tok] != row) return;  // warp-uniform
+  const int nv = d >> 2;
+  float4 acc[EMB_MAX_V4];
+  auto add_row = [&](int r, bool init) {
+    const uint2* src = reinterpret_cast<const uint2*>(dx + size_t(r) * d);
+#pragma unroll
+    for (int i = 0; i < EMB_MAX_V4; ++i) {
+      const int c = lane + i * 32;
+      if (c < nv) {
+        const uint2 u = __ldg(src + c);
+        const float2 f0 = unpack_bf16x2(u.x), f1 = unpack_bf16x2(u.y);
+        if (init) acc[i] = make_float4(f0.x, f0.y, f1.x, f1.y);
+        else { acc[i].x += f0.x; acc[i].y += f0.y; acc[i].z += f1.x; acc[i].w += f1.y; }
+      }
+    }
+  };
+  add_row(row, true);
+  for (int base = row + 1; base < rows; base += 32) {
+    const int r = base + lane;
+    const bool hit = r < rows && ids[r] == tok;
+    unsigned m = __ballot_sync(0xffffffffu, hit);
+    while (m != 0) {  // ascending positions
+      const int bit = __ffs(m) - 1;
+      m &= m - 1;
+      add_row(base + bit, false);
+    }
+  }
+  float4* dst = reinterpret_cast<float4*>(dwte + size_t(tok) * d);
+#pragma unroll
+  for (int i = 0; i < EMB_MAX_V4; ++i) {
+    const int c = lane + i * 32;
+    if (c < nv) {
+      float4 cur = dst[c];
+      cur.x += acc[i].x; cur.y += acc[i].y; cur.z += acc[i].z; cur.w += acc[i].w;
+      dst[c] = cur;
+    }
+  }
+}
+
 // dwpe[t,:] += sum_b dx[b*T + t,:]   (one thread per (t, 4 columns); fixed order over b)
 __global__ void embed_bwd_wpe_kernel(const __nv_bfloat16* __restrict__ dx,
                                      float* __restrict__ dwpe, int B, int T, int d) {
@@ -536,6 +598,33 @@ extern "C" int llmtrain_b200_embed_bwd(const int64_t* ids, const void* dx, float
               static_cast<const __nv_bfloat16*>(dx), dwpe, B, T, d);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
+  return 0;
+}
+
+// Deterministic-order variant (see embed_bwd_wte_ordered_kernel): scratch holds vocab ints.
+extern "C" size_t llmtrain_b200_embed_bwd_ordered_scratch_bytes(int vocab) {
+  return size_t(vocab) * sizeof(int);
+}
+extern "C" int llmtrain_b200_embed_bwd_ordered(const int64_t* ids, const void* dx, float* dwte,
+                                               float* dwpe, int B, int T, int d, int vocab,
+                                               void* scratch, size_t scratch_bytes,
+                                               cudaStream_t stream) {
+  B200_REQUIRE(d % 8 == 0 && d <= ew::EMB_MAX_V4 * 128, "embed: d must be a multiple of 8, <= 2048");
+  B200_REQUIRE(scratch_bytes >= size_t(vocab) * sizeof(int), "embed_bwd_ordered: scratch too small");
+  const int rows = B * T;
+  if (rows == 0) return 0;
+  int* first = static_cast<int*>(scratch);
+  B200_CHECK_CUDA(cudaMemsetAsync(first, 0x7f, size_t(vocab) * sizeof(int), stream));
+  B200_LAUNCH((ew::embed_first_kernel), ceil_div(rows, 256), 256, 0, stream, ids, first, rows, vocab);
+  B200_CHECK_CUDA(cudaGetLastError());
+  B200_LAUNCH((ew::embed_bwd_wte_ordered_kernel), ceil_div(rows, 8), 256, 0, stream, ids,
+              static_cast<const __nv_bfloat16*>(dx), static_cast<const int*>(first), dwte, rows, d,
+              vocab);
+  B200_CHECK_CUDA(cudaGetLastError());
+  B200_LAUNCH((ew::embed_bwd_wpe_kernel), ceil_div(T * (d / 4), 256), 256, 0, stream,
+              static_cast<const __nv_bfloat16*>(dx), dwpe, B, T, d);
+  B200_CHECK_CUDA(cudaGetLastError());
+  B200_COUNT_LAUNCH(3);
   return 0;
 }
 

@@ -627,7 +627,8 @@ static int gemm_dispatch(int layout, int epilogue, int M, int N, int K, const vo
 
   if (epilogue == kAccumF32) {
     if (make_tmap_2d(&tC, static_cast<float*>(C), M, N, ldc, 32, 16, Swz::B64)) return 1;
-    p.k_splits = pick_splits(M, N, K, pair ? 2 : 1);
+    // split-K partials meet in L2 in arrival order; deterministic mode keeps one writer per element
+    p.k_splits = deterministic() ? 1 : pick_splits(M, N, K, pair ? 2 : 1);
   } else {
     if (make_tmap_2d(&tC, static_cast<__nv_bfloat16*>(C), M, N, ldc, 32, 32, Swz::B64)) return 1;
     if (epilogue == kBiasGelu) {

@@ -29,6 +29,17 @@ int llmtrain_b200_abi_version(void);
 /* Kernels launched by this library so far in this process (monotonic). */
 long long llmtrain_b200_launch_count(void);
 
+/* Deterministic mode (process-wide, off by default).  The reference gets run-to-run equality of a
+ * resumed and an uninterrupted run from torch.use_deterministic_algorithms on the CPU
+ * (tests/test_checkpoint.py:58-62,301-320).  Here the fast kernels add floats in a
+ * hardware-chosen order in five places; with the mode on they use a fixed order instead:
+ * weight-gradient GEMMs run without split-K, attention backward adds the dQ contributions of the
+ * key tiles in ascending order (turn counters), the fused bias-gradient column sums are replaced
+ * by the two-stage reduction, and the embedding gradient is accumulated in position order.
+ * Gradients are then bit-reproducible for a fixed (weights, batch, world size). */
+void llmtrain_b200_set_deterministic(int on);
+int llmtrain_b200_get_deterministic(void);
+
 /* ---------------------------------------------------------------------------------------------
  * GEMM (tcgen05 + TMEM + TMA).  Replaces nn.Linear forward and its autograd dgrad/wgrad:
  * src/llmtrain/models/gpt.py:27,29,94,96,143.
@@ -71,6 +82,12 @@ int llmtrain_b200_embed_fwd(const int64_t* ids, const void* wte, const void* wpe
                             int T, int d, int vocab, llm_stream_t stream);
 int llmtrain_b200_embed_bwd(const int64_t* ids, const void* dx, float* dwte, float* dwpe, int B,
                             int T, int d, int vocab, llm_stream_t stream);
+/* Same gradients with a fixed summation order (positions ascending, one writer per vocabulary row);
+ * used when llmtrain_b200_set_deterministic is on.  scratch: vocab ints. */
+size_t llmtrain_b200_embed_bwd_ordered_scratch_bytes(int vocab);
+int llmtrain_b200_embed_bwd_ordered(const int64_t* ids, const void* dx, float* dwte, float* dwpe,
+                                    int B, int T, int d, int vocab, void* scratch,
+                                    size_t scratch_bytes, llm_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Fused softmax cross-entropy.  Replaces F.cross_entropy(reduction="none") + (masked) mean at

@@ -387,6 +387,14 @@ class B200TrainEngine(TrainEngine):
         self._cfg = cfg
         self._device = device
         self.model = model
+        # trainer.extra.deterministic_kernels: fixed summation orders in the native kernels (see
+        # llmtrain_b200_set_deterministic) so that a resumed run reproduces the uninterrupted one
+        # bit for bit, as the reference's CPU path does under use_deterministic_algorithms
+        # (`tests/test_checkpoint.py:301-320`).  Off by default: it costs throughput (weight
+        # gradients lose their split-K parallelism).  `run.deterministic` keeps the reference's
+        # meaning (fixed data order).
+        self.deterministic = bool(cfg.trainer.extra.get("deterministic_kernels", False))
+        native.lib().llmtrain_b200_set_deterministic(ctypes.c_int(1 if self.deterministic else 0))
         self._world = ddp_state.world_size if ddp_state is not None else 1
         self._rank = ddp_state.rank if ddp_state is not None else 0
         t = int(cfg.data.extra.get("seq_len", cfg.model.block_size))
@@ -456,7 +464,8 @@ class B200TrainEngine(TrainEngine):
         if want == "nvl" or (want == "nccl" and algo == "nvl"):
             comm = nvl.try_create(self._gpt, self._m, self._v, rank=self._rank, world=self._world,
                                   device=self._device, timeout_s=cfg.ddp.timeout_sec,
-                                  overlap=bool(cfg.trainer.extra.get("overlap_comm", True)))
+                                  overlap=bool(cfg.trainer.extra.get("overlap_comm", True)),
+                                  allow_nvls=not self.deterministic)
             if comm is not None:
                 return comm
             logger.warning("NVLink peer access unavailable; falling back to NCCL all-reduce")

@@ -399,7 +399,8 @@ def _want_nvls(world: int, overlap: bool) -> bool:
 
 
 def try_create(gpt: Any, m: torch.Tensor, v: torch.Tensor, *, rank: int, world: int,
-               device: torch.device, timeout_s: int, overlap: bool = True) -> Any | None:
+               device: torch.device, timeout_s: int, overlap: bool = True,
+               allow_nvls: bool = True) -> Any | None:
     """Build the peer-memory communicator, or ``None`` when the ranks cannot map each other."""
     del m, v, device
     if not 2 <= world <= 8:
@@ -414,7 +415,9 @@ def try_create(gpt: Any, m: torch.Tensor, v: torch.Tensor, *, rank: int, world: 
         logger.warning("nvl communicator could not be created: %s", exc)
         return None
     team = None
-    if _want_nvls(world, overlap) and gpt.n_params % (4 * world) == 0:
+    # (deterministic runs keep the peer-to-peer path: its sums are rank-ordered by construction,
+    # the order of additions inside the switch is not specified)
+    if allow_nvls and _want_nvls(world, overlap) and gpt.n_params % (4 * world) == 0:
         team = NvlsTeam.try_create(comm, gpt.n_params)
     return _NvlTrainComm(gpt, comm, overlap=overlap, team=team)
 

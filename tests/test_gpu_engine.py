@@ -255,3 +255,35 @@ def test_trainer_runs_on_device_resident_synthetic_tokens(tmp_path: Path) -> Non
     result = trainer.fit()
     assert result.final_step == 5
     assert abs(result.final_loss - math.log(1000)) < 1.0
+
+
+def test_deterministic_kernels_make_resume_reproduce_the_uninterrupted_run(tmp_path: Path) -> None:
+    """``trainer.extra.deterministic_kernels`` + dropout: a run resumed from step 4 ends on the loss
+    of the uninterrupted run to the reference's own tolerance (its CPU test demands 1e-5,
+    `tests/test_checkpoint.py:301-320`), and two identical runs agree bit for bit."""
+    from llmtrain.ops import native
+    from llmtrain.training import Trainer
+
+    over = dict(model={"dropout": 0.1},
+                trainer={"max_steps": 8, "save_every_steps": 4, "eval_every_steps": 1000,
+                         "grad_accum_steps": 2, "extra": {"deterministic_kernels": True}})
+    try:
+        torch.manual_seed(7)
+        first = Trainer(_cfg(tmp_path, **over), run_dir=tmp_path / "a")
+        whole = first.fit()
+        weights = first._engine._gpt.p32.clone()
+
+        torch.manual_seed(7)
+        second = Trainer(_cfg(tmp_path, **over), run_dir=tmp_path / "b")
+        again = second.fit()
+        assert again.final_loss == whole.final_loss
+        assert torch.equal(second._engine._gpt.p32, weights)
+
+        torch.manual_seed(99)  # a different process state: everything must come from the checkpoint
+        third = Trainer(_cfg(tmp_path, **over), run_dir=tmp_path / "c")
+        resumed = third.fit(resume_from=tmp_path / "a" / "checkpoints" / "step_000004.pt")
+        assert resumed.resumed_from_step == 4
+        assert abs(resumed.final_loss - whole.final_loss) <= 1e-5
+        assert torch.equal(third._engine._gpt.p32, weights)
+    finally:
+        native.lib().llmtrain_b200_set_deterministic(0)
