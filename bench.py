@@ -45,6 +45,15 @@ METRIC = "GPT-2 124M DDP tok/s (max over ranks)"
 GPT2_SMALL = dict(block_size=1024, d_model=768, n_layers=12, n_heads=12, d_ff=3072, dropout=0.0,
                   tie_embeddings=True, vocab_size=50257)
 
+GPT2_MEDIUM = dict(GPT2_SMALL, d_model=1024, n_layers=24, n_heads=16, d_ff=4096)
+GPT2_XL = dict(GPT2_SMALL, block_size=2048, d_model=1600, n_layers=48, n_heads=25, d_ff=6400)
+MODELS = {"small": GPT2_SMALL, "medium": GPT2_MEDIUM, "xl": GPT2_XL}
+MODEL_NAMES = {
+    "small": "gpt2-small-124M (d768 L12 H12 F3072 V50257 tied)",
+    "medium": "gpt2-medium-350M (d1024 L24 H16 F4096 V50257 tied)",
+    "xl": "gpt2-xl-1.5B (d1600 L48 H25 F6400 V50257 tied)",
+}
+
 
 # ------------------------------------------------------------------------------------------------
 # clocks
@@ -176,24 +185,28 @@ def _payload(cfg_model: dict[str, Any], micro_batch: int, accum: int, world: int
         "run": {"name": "bench-gpt2-124m", "device": "cuda", "seed": 1234},
         "model": {"name": "gpt", **cfg_model},
         "data": {"name": "synthetic_text", "num_workers": 0,
-                 "extra": {"num_examples": max(256, 2 * micro_batch * accum)}},
+                 "extra": {"num_examples": max(256, 2 * micro_batch * accum), "seq_len": seq}},
         "trainer": {"max_steps": max(steps, 1), "micro_batch_size": micro_batch,
                     "grad_accum_steps": accum, "lr": 3e-4, "weight_decay": 0.1, "warmup_steps": 0,
                     "max_grad_norm": 1.0, "log_every_steps": 1, "eval_every_steps": 10**9,
                     "save_every_steps": 10**9,
-                    "extra": {"overlap_comm": os.environ.get("LLMTRAIN_OVERLAP", "1") != "0"}},
-        "ddp": {"enabled": world > 1, "backend": "nvl"},
+                    "extra": {"overlap_comm": os.environ.get("LLMTRAIN_OVERLAP", "1") != "0",
+                              # cost measurement of the fixed-order kernels, not the headline
+                              "deterministic_kernels":
+                                  os.environ.get("LLMTRAIN_DETERMINISTIC", "0") == "1"}},
+        # LLMTRAIN_BENCH_BACKEND=nccl measures the fallback transport (pods without shared IPC)
+        "ddp": {"enabled": world > 1, "backend": os.environ.get("LLMTRAIN_BENCH_BACKEND", "nvl")},
         "mlflow": {"enabled": False},
         "logging": {"level": "WARNING", "log_to_file": False},
         "output": {"root_dir": "runs"},
     }
 
 
-def bench_config(mb: int, accum: int, seq: int, world: int) -> dict[str, Any]:
+def bench_config(mb: int, accum: int, seq: int, world: int, model: str = "small") -> dict[str, Any]:
     """The ``config`` object of the JSON line: identical for both arms by construction (the driver
     compares the two dictionaries); anything implementation-specific goes under ``notes``."""
     return {
-        "model": "gpt2-small-124M (d768 L12 H12 F3072 V50257 tied)",
+        "model": MODEL_NAMES[model],
         "global_batch": mb * accum * world,
         "micro_batch_per_gpu": mb,
         "grad_accum": accum,
@@ -256,6 +269,8 @@ def _ddp_check(engine: Any, batch: dict[str, Any], world: int) -> dict[str, Any]
     g.g32.zero_()
     if hasattr(comm, "_reduced"):
         comm._reduced = False
+    if hasattr(comm, "_works"):
+        comm._works.clear()
     torch.cuda.synchronize()
     dist.barrier()
     tol = 2e-2 if reduced_by != "none" else 0.0
@@ -288,8 +303,8 @@ def run_ours(args: argparse.Namespace) -> dict[str, Any]:
     if world != args.gpus:
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torchrun for N>1")
     seq, mb, accum = args.seq_len, args.micro_batch, args.grad_accum
-    cfg = RunConfig.model_validate(_payload(GPT2_SMALL, mb, accum, world, seq,
-                                            args.steps + args.warmup))
+    spec = MODELS[args.model]
+    cfg = RunConfig.model_validate(_payload(spec, mb, accum, world, seq, args.steps + args.warmup))
     ddp_state = setup_ddp(cfg) if world > 1 else None
     torch.cuda.set_device(local_rank % torch.cuda.device_count())
     try:
@@ -308,7 +323,7 @@ def run_ours(args: argparse.Namespace) -> dict[str, Any]:
 
         pool = []
         for i in range(4):
-            ids_, labels_ = K.synthetic_tokens(mb, seq, GPT2_SMALL["vocab_size"], seed=1234,
+            ids_, labels_ = K.synthetic_tokens(mb, seq, spec["vocab_size"], seed=1234,
                                                first_row=(i * world + rank) * mb)
             pool.append({"input_ids": ids_, "labels": labels_})
         cursor = [0]
@@ -388,7 +403,8 @@ def run_ours(args: argparse.Namespace) -> dict[str, Any]:
             exposed = {"compute_only_ms_per_step": ms_local / args.steps,
                        "exposed_comm_ms_per_step": (ms - ms_local) / args.steps}
         result = {
-            "metric": METRIC,
+            "metric": METRIC if args.model == "small" else METRIC.replace(
+                "GPT-2 124M", MODEL_NAMES[args.model].split(" ")[0]),
             "value": value,
             "unit": "tokens/s",
             "n_gpus": world,
@@ -401,7 +417,7 @@ def run_ours(args: argparse.Namespace) -> dict[str, Any]:
             "dtype": "bf16",
             "data": "synthetic",
             "impl": "ours",
-            "config": bench_config(mb, accum, seq, world),
+            "config": bench_config(mb, accum, seq, world, args.model),
             "notes": {"comm": getattr(comm, "name", "none") if world > 1 else "none",
                       "master_weights": "fp32 arena + bf16 shadow, fused clip+AdamW kernel"},
             "clocks": clocks.summary(),
@@ -449,10 +465,10 @@ def run_reference(args: argparse.Namespace) -> dict[str, Any]:
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torchrun for N>1")
     try:
         return ref_harness.run(args, rank=rank, local_rank=local_rank, world=world,
-                               model=GPT2_SMALL, metric=METRIC, timed=_timed,
+                               model=MODELS[args.model], metric=METRIC, timed=_timed,
                                max_over_ranks=_max_over_ranks, sampler=ClockSampler,
                                config=bench_config(args.micro_batch, args.grad_accum,
-                                                   args.seq_len, world))
+                                                   args.seq_len, world, args.model))
     except Exception as exc:  # the arm must never take the driver down
         if rank == 0:
             return {"impl": "reference", "unavailable": f"{type(exc).__name__}: {exc}"[:300]}
@@ -468,7 +484,11 @@ def main() -> int:
     ap.add_argument("--micro-batch", type=int, default=32, help="sequences per GPU per micro-step")
     ap.add_argument("--grad-accum", type=int, default=1)
     ap.add_argument("--seq-len", type=int, default=1024)
+    ap.add_argument("--model", choices=sorted(MODELS), default="small",
+                    help="small = the headline config; medium / xl = BASELINE configs #3 / #4")
     args = ap.parse_args()
+    if args.seq_len > MODELS[args.model]["block_size"]:
+        raise SystemExit("--seq-len exceeds the model's block_size")
     args.warmup = max(args.warmup, 3)  # timing rule: at least 3 warm-up steps
     result = run_reference(args) if args.impl == "reference" else run_ours(args)
     if result:

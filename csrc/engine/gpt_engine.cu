@@ -477,6 +477,17 @@ int backward(Gpt& g, cudaStream_t s, BucketHook hook = nullptr, void* hook_ctx =
 }  // namespace engine
 }  // namespace b200
 
+// Backward with a host callback after each gradient bucket has been enqueued: hook(ctx, lo, len)
+// is called once the kernels that finalise arena range [lo, lo+len) are on `stream` (ranges arrive
+// back to front, the embedding tables last).  The NCCL fallback uses it to start one all-reduce
+// per bucket on a side stream while backward continues (what the c10d Reducer does for the
+// reference, `src/llmtrain/training/trainer.py:88-91,377-387`).
+extern "C" int llmtrain_b200_gpt_backward_hooked(void* h, int (*hook)(void*, size_t, size_t),
+                                                 void* ctx, llm_stream_t stream) {
+  return b200::engine::backward(*static_cast<b200::engine::Gpt*>(h),
+                                reinterpret_cast<cudaStream_t>(stream), hook, ctx);
+}
+
 // Internal (non-ABI) entry used by the communicator to interleave bucket reductions.
 int b200_gpt_backward_with_hook(void* handle, cudaStream_t stream, b200::engine::BucketHook hook,
                                 void* ctx) {

@@ -265,6 +265,12 @@ int llmtrain_b200_gpt_forward(void* handle, const int64_t* ids, const int64_t* l
 int llmtrain_b200_gpt_set_dropout(void* handle, float p, uint64_t seed, uint64_t offset);
 /* g32 += d loss / d params for the last mode-2 forward. */
 int llmtrain_b200_gpt_backward(void* handle, llm_stream_t stream);
+/* As llmtrain_b200_gpt_backward; hook(ctx, lo, len) is called on the host each time the kernels
+ * that finalise gradient-arena range [lo, lo+len) have been enqueued (back to front), so a
+ * transport of the caller's choice can reduce that bucket while backward continues (c10d Reducer
+ * behaviour, reference trainer.py:88-91).  A non-zero return aborts backward. */
+int llmtrain_b200_gpt_backward_hooked(void* gpt, int (*hook)(void*, size_t, size_t), void* ctx,
+                                      llm_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
  * NVLink peer-memory communicator (csrc/comm/nvl.cu).  Replaces DistributedDataParallel's bucketed

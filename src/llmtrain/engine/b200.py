@@ -469,7 +469,7 @@ class B200TrainEngine(TrainEngine):
             if comm is not None:
                 return comm
             logger.warning("NVLink peer access unavailable; falling back to NCCL all-reduce")
-        return nvl.NcclFallback(self._gpt)
+        return nvl.NcclFallback(self._gpt, overlap=bool(cfg.trainer.extra.get("overlap_comm", True)))
 
     # ------------------------------------------------------------------ TrainEngine API
     @property

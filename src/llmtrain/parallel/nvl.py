@@ -53,22 +53,78 @@ def _collective_stage(what: str, fn: Any, world: int, on_fail: Any = None) -> No
         raise RuntimeError(bad[0])
 
 
+_BUCKET_HOOK = ctypes.CFUNCTYPE(ctypes.c_int, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_size_t)
+
+
 class NcclFallback:
-    """torch.distributed (NCCL) all-reduce, then the fused optimiser kernel."""
+    """torch.distributed (NCCL) transport: the path across nodes and between pods that cannot map
+    each other's memory.
 
-    name = "nccl"
+    ``overlap=True`` (default): the last micro-batch's backward reports every gradient bucket as
+    soon as its kernels are enqueued (``llmtrain_b200_gpt_backward_hooked``) and one asynchronous
+    fp32 all-reduce per bucket starts on a side stream while backward continues — the job the
+    c10d Reducer does for the reference (`src/llmtrain/training/trainer.py:88-91,377-387`), with
+    this engine's per-layer buckets instead of 25 MiB ones.  The fused clip + AdamW kernel follows
+    once the last bucket has landed.  ``overlap=False``: one all-reduce of the whole arena after
+    backward.
+    """
 
-    def __init__(self, gpt: Any) -> None:
+    def __init__(self, gpt: Any, *, overlap: bool = True) -> None:
         self._gpt = gpt
         self._world = dist.get_world_size()
+        self.overlap = overlap
+        self.name = ("nccl(per-layer fp32 buckets overlapped with backward -> local adamw)"
+                     if overlap else "nccl(one fp32 all-reduce after backward -> local adamw)")
+        self._side = torch.cuda.Stream() if overlap else None
+        self._works: list[Any] = []
+        self._reduced = False
+
+    def backward_last(self) -> None:
+        g = self._gpt
+        if not self.overlap:
+            g.run_backward()
+            return
+        arena = g.g32
+        compute = torch.cuda.current_stream()
+        side = self._side
+        works = self._works
+        works.clear()
+
+        def on_bucket(_ctx: Any, lo: int, length: int) -> int:
+            if length == 0:
+                return 0
+            ready = torch.cuda.Event()
+            ready.record(compute)
+            side.wait_event(ready)
+            with torch.cuda.stream(side):
+                works.append(dist.all_reduce(arena[lo:lo + length], op=dist.ReduceOp.SUM,
+                                             async_op=True))
+            return 0
+
+        hook = _BUCKET_HOOK(on_bucket)
+        lib = native.lib()
+        lib.llmtrain_b200_gpt_backward_hooked.argtypes = [ctypes.c_void_p, _BUCKET_HOOK,
+                                                          ctypes.c_void_p, ctypes.c_void_p]
+        check(lib.llmtrain_b200_gpt_backward_hooked(g._handle, hook, None, stream_handle()),
+              "gpt_backward_hooked")
+        self._reduced = True
 
     def reduce_and_step(self, m: torch.Tensor, v: torch.Tensor, sumsq: torch.Tensor,
                         norm: torch.Tensor, hyper: dict[str, Any]) -> None:
         g = self._gpt
-        dist.all_reduce(g.g32, op=dist.ReduceOp.SUM)
+        if self._reduced:
+            for work in self._works:
+                work.wait()  # the compute stream waits for that bucket's reduction
+            self._works.clear()
+            self._reduced = False
+        else:
+            dist.all_reduce(g.g32, op=dist.ReduceOp.SUM)
         K.grad_sumsq(g.g32, sumsq)
         K.adamw(g.p32, m, v, g.g32, g.p16, sumsq=sumsq, norm_out=norm,
                 grad_scale=1.0 / self._world, **hyper)
+
+    def reduced_gradient(self) -> torch.Tensor:
+        return self._gpt.g32
 
     def close(self) -> None:
         return None

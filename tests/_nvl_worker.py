@@ -163,7 +163,7 @@ def _check_trainer(rank: int, world: int, overlap: bool = True, nvls: bool = Fal
     return result.final_loss
 
 
-def _check_ddp_equivalence(rank: int, world: int, nvls: bool) -> None:
+def _check_ddp_equivalence(rank: int, world: int, nvls: bool, backend: str = "nvl") -> None:
     """W ranks on their shards == one rank on the concatenated batch, from the same weights
     (the reference has no such test, `tests/test_distributed.py` only fakes the
     collectives).  Three optimiser steps; compared per step: the global mean loss and the
@@ -183,7 +183,7 @@ def _check_ddp_equivalence(rank: int, world: int, nvls: bool) -> None:
             "trainer": {"max_steps": steps, "micro_batch_size": batch, "grad_accum_steps": 1,
                         "warmup_steps": 0, "lr": 1e-3, "weight_decay": 0.0,
                         "extra": {"overlap_comm": True, "prefetch": False}},
-            "ddp": {"enabled": ddp, "backend": "nvl", "timeout_sec": 60},
+            "ddp": {"enabled": ddp, "backend": backend, "timeout_sec": 60},
             "mlflow": {"enabled": False}, "logging": {"log_to_file": False}, "output": {},
         })
 
@@ -223,7 +223,8 @@ def _check_ddp_equivalence(rank: int, world: int, nvls: bool) -> None:
     apart = (many._gpt.p32 - one._gpt.p32).pow(2).mean().sqrt().item()
     assert apart < 0.1 * travelled, (apart, travelled)
     if rank == 0:
-        path = "nvls" if many._comm._team is not None else "p2p"
+        path = ("nccl" if backend == "nccl"
+                else "nvls" if many._comm._team is not None else "p2p")
         print(f"DDP_EQUIVALENCE_OK world={world} path={path} rms_apart/rms_travelled="
               f"{apart / travelled:.4f}", flush=True)
     many._comm.close()
@@ -281,6 +282,7 @@ def main() -> int:
 
             _check_ddp_equivalence(rank, world, nvls=False)
             _check_ddp_equivalence(rank, world, nvls=True)
+            _check_ddp_equivalence(rank, world, nvls=False, backend="nccl")
             shutdown()
             dist.barrier()
             if rank == 0:
@@ -328,6 +330,7 @@ def main() -> int:
         assert abs(loss_overlapped - loss_serial) < 0.05, (loss_overlapped, loss_serial)
         _check_ddp_equivalence(rank, world, nvls=False)
         _check_ddp_equivalence(rank, world, nvls=True)
+        _check_ddp_equivalence(rank, world, nvls=False, backend="nccl")
         shutdown()
         dist.barrier()
         if rank == 0:

@@ -31,7 +31,7 @@ def test_nvl_allreduce_step_and_trainer(world: int) -> None:
     )
     assert proc.returncode == 0, proc.stdout[-3000:] + proc.stderr[-3000:]
     assert "NVL_WORKER_OK" in proc.stdout
-    assert proc.stdout.count("DDP_EQUIVALENCE_OK") == 2, proc.stdout[-2000:]
+    assert proc.stdout.count("DDP_EQUIVALENCE_OK") == 3, proc.stdout[-2000:]
 
 
 def test_nvls_multimem_allreduce() -> None:
