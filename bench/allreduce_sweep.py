@@ -64,6 +64,13 @@ def main() -> int:
         ours = timed(lambda: comm.allreduce(src, dst, 1.0 / world), iters)
         buf = src.clone()
         nccl = timed(lambda: dist.all_reduce(buf, op=dist.ReduceOp.SUM), iters)
+        # one-shot kernel (every rank reads all peers in ONE launch): the small-message algorithm,
+        # available up to 262144 elements; the communicator's arena must hold 2 * n elements
+        oneshot = None
+        if n <= 262144:
+            small = NvlComm(max(2 * n, 1024), rank=rank, world=world, timeout_s=60)
+            oneshot = timed(lambda: small.allreduce_small(src, dst, 1.0 / world), iters)
+            small.close()
         comm.close()
         nvls = None
         count = n // (4 * world) * (4 * world)
@@ -77,6 +84,9 @@ def main() -> int:
             "nccl_busbw_GBs": round(n * 4 / nccl / 1e6 * factor, 1),
             "nvl_wire_bytes_in_per_gpu": int(n * 2 * (world - 1) / world + n * 4 * (world - 1) / world),
         }
+        if oneshot is not None:
+            row["oneshot_us"] = round(oneshot * 1e3, 2)
+            row["oneshot_busbw_GBs"] = round(n * 4 / oneshot / 1e6 * factor, 1)
         if nvls is not None:
             row["nvls_us"] = round(nvls * 1e3, 2)
             row["nvls_busbw_GBs"] = round(count * 4 / nvls / 1e6 * factor, 1)
