@@ -202,6 +202,13 @@ def _payload(cfg_model: dict[str, Any], micro_batch: int, accum: int, world: int
     }
 
 
+def metric_name(model: str) -> str:
+    """BASELINE.json's headline string for the default model; the same sentence with the model's
+    name for configs #3 / #4."""
+    return METRIC if model == "small" else METRIC.replace(
+        "GPT-2 124M", MODEL_NAMES[model].split(" ")[0])
+
+
 def bench_config(mb: int, accum: int, seq: int, world: int, model: str = "small") -> dict[str, Any]:
     """The ``config`` object of the JSON line: identical for both arms by construction (the driver
     compares the two dictionaries); anything implementation-specific goes under ``notes``."""
@@ -403,8 +410,7 @@ def run_ours(args: argparse.Namespace) -> dict[str, Any]:
             exposed = {"compute_only_ms_per_step": ms_local / args.steps,
                        "exposed_comm_ms_per_step": (ms - ms_local) / args.steps}
         result = {
-            "metric": METRIC if args.model == "small" else METRIC.replace(
-                "GPT-2 124M", MODEL_NAMES[args.model].split(" ")[0]),
+            "metric": metric_name(args.model),
             "value": value,
             "unit": "tokens/s",
             "n_gpus": world,
@@ -465,7 +471,8 @@ def run_reference(args: argparse.Namespace) -> dict[str, Any]:
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torchrun for N>1")
     try:
         return ref_harness.run(args, rank=rank, local_rank=local_rank, world=world,
-                               model=MODELS[args.model], metric=METRIC, timed=_timed,
+                               model=MODELS[args.model], metric=metric_name(args.model),
+                               timed=_timed,
                                max_over_ranks=_max_over_ranks, sampler=ClockSampler,
                                config=bench_config(args.micro_batch, args.grad_accum,
                                                    args.seq_len, world, args.model))

@@ -261,7 +261,12 @@ int forward(Gpt& g, const int64_t* ids, const uint8_t* key_mask, int B, int T, b
     B200_TRY(llmtrain_b200_attention_fwd_fused(v.bf(a.qkv), v.bf(a.atty), v.f32(a.lse), key_mask, B,
                                                T, g.H, 64, sm_scale, drop ? dp : 0.f, seed, off,
                                                drop_site(l, 0), st));
-    if (drop) {
+    if (key_mask != nullptr) {
+      // padded query rows take no attention update (`gpt.py:73-74`); dropout (if any) fused too
+      B200_TRY(llmtrain_b200_gemm_resid_rowmask(M, d, dq, v.bf(a.atty), dq, wo, dq, v.bf(a.resid1),
+                                                d, v.p(o.out_b), x, d, key_mask, drop ? dp : 0.f,
+                                                seed, off, drop_site(l, 1), st));
+    } else if (drop) {
       B200_TRY(llmtrain_b200_gemm_dropout_resid(M, d, dq, v.bf(a.atty), dq, wo, dq, v.bf(a.resid1),
                                                 d, v.p(o.out_b), x, d, dp, seed, off,
                                                 drop_site(l, 1), st));
@@ -410,11 +415,17 @@ int backward(Gpt& g, cudaStream_t s, BucketHook hook = nullptr, void* hook_ctx =
     B200_TRY(linear_dgrad(0, M, F, d, dfc, v.w(o.fc_w), dtmp, nullptr, s));
     B200_TRY(llmtrain_b200_layernorm_bwd(dtmp, v.bf(a.resid1), v.p(o.ln2_w), v.f32(a.ln2_mean),
                                          v.f32(a.ln2_rstd), dresid, v.grad(o.ln2_w),
-                                         v.grad(o.ln2_b), drop ? nullptr : v.grad(o.out_b), red,
+                                         v.grad(o.ln2_b),
+                                         (drop || g.key_mask != nullptr) ? nullptr : v.grad(o.out_b), red,
                                          red_bytes, M, d, st));
     // ---- attention: resid1 = attn(ln1 @ Wqkv^T + bqkv) @ Wo^T + bo + x_in
     const __nv_bfloat16* dout = dresid;
-    if (drop) {
+    if (g.key_mask != nullptr) {  // no gradient enters the branch from padded query rows
+      B200_TRY(llmtrain_b200_dropout_rowmask(dresid, dmask, M, d, d, g.key_mask, drop ? dp : 0.f,
+                                             seed, off, drop_site(l, 1), st));
+      B200_TRY(llmtrain_b200_bias_grad(dmask, d, M, d, v.grad(o.out_b), red, red_bytes, st));
+      dout = dmask;
+    } else if (drop) {
       B200_TRY(llmtrain_b200_dropout(dresid, dmask, M, d, d, dp, seed, off, drop_site(l, 1), st));
       B200_TRY(llmtrain_b200_bias_grad(dmask, d, M, d, v.grad(o.out_b), red, red_bytes, st));
       dout = dmask;

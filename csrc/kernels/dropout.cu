@@ -19,7 +19,8 @@ namespace drop {
 // One thread per 8 consecutive columns (one Philox call, one 16-byte load, one 16-byte store).
 __global__ void __launch_bounds__(256)
 apply_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, long long rows,
-             int cols, int ld, int padded_cols, const DropoutParams dp) {
+             int cols, int ld, int padded_cols, const DropoutParams dp,
+             const uint8_t* __restrict__ row_keep) {
   pdl_enter();  // previous kernel finished, its writes are visible
   const int groups_per_row = padded_cols >> 3;
   const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -30,6 +31,12 @@ apply_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y,
   const Rand8 r = philox_group(dp, uint64_t(row) * uint64_t(groups_per_row) + uint64_t(g));
   const __nv_bfloat16* src = x + size_t(row) * ld + col;
   __nv_bfloat16* dst = y + size_t(row) * ld + col;
+  if (row_keep != nullptr && row_keep[row] == 0) {  // the whole row is dropped (padded position)
+#pragma unroll
+    for (int k = 0; k < 8; ++k)
+      if (col + k < cols) dst[k] = __float2bfloat16(0.f);
+    return;
+  }
   if (col + 8 <= cols && (ld & 7) == 0) {
     const uint4 u = *reinterpret_cast<const uint4*>(src);
     const uint32_t w[4] = {u.x, u.y, u.z, u.w};
@@ -80,7 +87,29 @@ extern "C" int llmtrain_b200_dropout(const void* x, void* y, long long rows, int
   const DropoutParams dp = make_dropout(p, seed, offset, site);
   B200_LAUNCH((drop::apply_kernel), unsigned((n + 255) / 256), 256, 0, stream,
               static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), rows, cols, ld,
-              padded, dp);
+              padded, dp, static_cast<const uint8_t*>(nullptr));
+  B200_CHECK_CUDA(cudaGetLastError());
+  B200_COUNT_LAUNCH(1);
+  return 0;
+}
+
+// y = x o dropout_mask(p, ...) o row_keep[:, None]   (p = 0: only the row mask).  Backward of the
+// attention branch when a padding mask is present: the reference multiplies that branch by the
+// mask (`gpt.py:73-74`), so no gradient flows into it from padded positions.
+extern "C" int llmtrain_b200_dropout_rowmask(const void* x, void* y, long long rows, int cols,
+                                             int ld, const uint8_t* row_keep, float p,
+                                             uint64_t seed, uint64_t offset, uint32_t site,
+                                             cudaStream_t stream) {
+  B200_REQUIRE(rows >= 0 && cols > 0 && ld >= cols, "dropout_rowmask: bad shape");
+  B200_REQUIRE(p >= 0.f && p < 1.f, "dropout_rowmask: p must be in [0, 1)");
+  B200_REQUIRE(row_keep != nullptr, "dropout_rowmask: row_keep must not be null");
+  if (rows == 0) return 0;
+  const int padded = (cols + 7) & ~7;
+  const long long n = rows * (padded >> 3);
+  const DropoutParams dp = make_dropout(p, seed, offset, site);
+  B200_LAUNCH((drop::apply_kernel), unsigned((n + 255) / 256), 256, 0, stream,
+              static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), rows, cols, ld,
+              padded, dp, row_keep);
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   return 0;

@@ -92,6 +92,8 @@ struct Params {
   DropoutParams drop;      // kBiasDropResid only
   float* colsum;           // optional, kDGelu / kBias: colsum[n] += sum_m C[m, n]  (bias gradient
                            // of the layer that produced this GEMM's output gradient)
+  const uint8_t* row_keep; // optional, kBiasResid / kBiasDropResid: rows with row_keep[m] == 0 get
+                           // C = R (the branch is dropped, `gpt.py:73-74`: padded query rows)
 };
 
 // Tile order.  Consecutive tiles walk `group_m` row-tiles for one column-tile, then the next
@@ -112,63 +114,34 @@ __device__ __forceinline__ void tile_coords(int mn, int num_m, int num_n, int gr
 // (An epilogue that stored 16-byte vectors straight to global memory instead of staging + TMA
 // store was measured slower — fc forward 70 -> 87 us — and removed; see profiles/README.md.)
 
-// Phi(x) (standard normal CDF) via Abramowitz & Stegun 7.1.26 for erf (|abs err| < 1.5e-7 — two
-// orders of magnitude below bf16 resolution), arranged for the fewest issue slots: constants are
-// pre-folded, the exponential and reciprocal are the bare MUFU approximations, and one exponential
-// serves both Phi(x) and phi(x).  libm's erff made the GELU epilogues the pacing stage of their
-// GEMMs (the epilogue must keep up with a 128x256x768 mainloop: ~6K cycles per tile).
-__device__ __forceinline__ float mufu_rcp(float x) {
-  float y;
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
-struct PhiPair { float cdf, half_e; };  // Phi(x) and 0.5*exp(-x^2/2)
-__device__ __forceinline__ PhiPair normal_cdf(float x) {
-  constexpr float kP = 0.3275911f * 0.70710678118654752f;   // p / sqrt(2)
-  constexpr float kC = -0.5f * 1.4426950408889634f;         // -log2(e)/2
-  const float t = mufu_rcp(fmaf(kP, fabsf(x), 1.0f));
-  const float half_e = 0.5f * fast_exp2(x * x * kC);        // 0.5 * exp(-x^2/2)
-  float poly = fmaf(1.061405429f, t, -1.453152027f);
-  poly = fmaf(poly, t, 1.421413741f);
-  poly = fmaf(poly, t, -0.284496736f);
-  poly = fmaf(poly, t, 0.254829592f);
-  const float q = poly * t * half_e;                         // 0.5 * erfc(|x|/sqrt 2)
-  return {x > 0.f ? 1.0f - q : q, half_e};
-}
 // gelu(x) = x Phi(x) and gelu'(x) = Phi(x) + x phi(x) from ONE evaluation: forward stores the
 // derivative (bf16) instead of the pre-activation, so the MLP dgrad epilogue is a single multiply.
-struct GeluPair { float y, dy; };
-__device__ __forceinline__ GeluPair gelu_erf_both(float x) {
-  const PhiPair n = normal_cdf(x);
-  return {x * n.cdf, fmaf(x * 0.7978845608028654f, n.half_e, n.cdf)};  // phi = 2*half_e/sqrt(2pi)
-}
-
-// The pair version below uses packed fp32 (f32x2, ptx.cuh): the GELU epilogue is issue-bound — two
-// epilogue warps per scheduler, ~27 instructions per element — so evaluating two adjacent columns
-// per instruction is worth ~40% of its issue slots.
-// Same arithmetic as gelu_erf_both for the pair (x0, x1); y and dy come back packed.
+// The GELU epilogue must keep up with a 128x256x768 mainloop (~6K cycles per tile) and is
+// issue-bound, so everything is evaluated on packed fp32 pairs (f32x2, ptx.cuh).  libm's erff, and
+// then an Abramowitz & Stegun 7.1.26 form (reciprocal + exponential + select per element), were
+// the pacing stage of these GEMMs before.
+// Phi(x) - 1/2 here is an odd degree-15 polynomial in x on [-4, 4] (least-squares fit on Chebyshev
+// nodes, max abs error 5e-5 including the clamp — 40x below bf16 resolution), evaluated as
+// x * Q(x^2) with packed FMAs: against the A&S form above it needs no reciprocal (one MUFU per
+// element instead of two — the exponential for phi(x) remains) and no sign select.
 __device__ __forceinline__ void gelu_erf_both2(float x0, float x1, f32x2& y, f32x2& dy) {
-  constexpr float kP = 0.3275911f * 0.70710678118654752f;
-  constexpr float kC = -0.5f * 1.4426950408889634f;
-  const float t0 = mufu_rcp(fmaf(kP, fabsf(x0), 1.0f));
-  const float t1 = mufu_rcp(fmaf(kP, fabsf(x1), 1.0f));
-  const f32x2 x = pack2(x0, x1), t = pack2(t0, t1);
-  // 0.5 * exp(-x^2/2) = exp2(x^2 * kC - 1)
+  constexpr float kC = -0.5f * 1.4426950408889634f;  // exp(-x^2/2) = exp2(x^2 * kC)
+  const f32x2 x = pack2(x0, x1);
+  const f32x2 xc = pack2(fminf(fmaxf(x0, -4.0f), 4.0f), fminf(fmaxf(x1, -4.0f), 4.0f));
+  const f32x2 u = mul2(xc, xc);
+  f32x2 q = fma2(splat2(-1.5807526398958771e-09f), u, splat2(1.2182773900804023e-07f));
+  q = fma2(q, u, splat2(-4.10726079280721e-06f));
+  q = fma2(q, u, splat2(8.080291445367038e-05f));
+  q = fma2(q, u, splat2(-0.0010496044997125864f));
+  q = fma2(q, u, splat2(0.009672095067799091f));
+  q = fma2(q, u, splat2(-0.066192127764225f));
+  q = fma2(q, u, splat2(0.3988598585128784f));
+  const f32x2 cdf = fma2(q, xc, splat2(0.5f));
   float a0, a1;
-  unpack2(fma2(mul2(x, x), splat2(kC), splat2(-1.0f)), a0, a1);
-  const f32x2 half_e = pack2(fast_exp2(a0), fast_exp2(a1));
-  f32x2 poly = fma2(splat2(1.061405429f), t, splat2(-1.453152027f));
-  poly = fma2(poly, t, splat2(1.421413741f));
-  poly = fma2(poly, t, splat2(-0.284496736f));
-  poly = fma2(poly, t, splat2(0.254829592f));
-  const f32x2 q = mul2(mul2(poly, t), half_e);           // 0.5 * erfc(|x|/sqrt 2)
-  const f32x2 omq = fma2(q, splat2(-1.0f), splat2(1.0f));
-  float q0, q1, r0, r1;
-  unpack2(q, q0, q1);
-  unpack2(omq, r0, r1);
-  const f32x2 cdf = pack2(x0 > 0.f ? r0 : q0, x1 > 0.f ? r1 : q1);
+  unpack2(mul2(mul2(x, x), splat2(kC)), a0, a1);
+  const f32x2 e = pack2(fast_exp2(a0), fast_exp2(a1));  // exp(-x^2/2)
   y = mul2(x, cdf);
-  dy = fma2(mul2(x, splat2(0.7978845608028654f)), half_e, cdf);
+  dy = fma2(mul2(x, splat2(0.3989422804014327f)), e, cdf);  // Phi + x phi,  phi = e / sqrt(2 pi)
 }
 
 template <bool A_MN, bool B_MN, int EPI, int CTAS>
@@ -372,6 +345,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           bias2.x = __ldg(p.bias + bc);
         }
       }
+      bool keep_row = true;
+      if ((EPI == kBiasResid || EPI == kBiasDropResid) && p.row_keep != nullptr && row_ok)
+        keep_row = p.row_keep[row] != 0;
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after_sync();
       const uint32_t t_row = tmem_base + (uint32_t(quarter * 32) << 16) + acc * BN + colgrp * 64;
@@ -433,7 +409,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             if (EPI == kBiasResid || EPI == kDGelu || EPI == kBiasDropResid) {
               const float2 f = unpack_bf16x2(rw[h * 16 + (j >> 1)]);
               if (EPI == kDGelu) { x0 *= f.x; x1 *= f.y; }
-              else { x0 += f.x; x1 += f.y; }
+              else if (keep_row) { x0 += f.x; x1 += f.y; }
+              else { x0 = f.x; x1 = f.y; }
             }
             if (EPI == kBiasGelu) {
               f32x2 y2, dy2;
@@ -578,11 +555,14 @@ using namespace b200::gemm;
 static int gemm_dispatch(int layout, int epilogue, int M, int N, int K, const void* A, int lda,
                          const void* B, int ldb, void* C, int ldc, void* C2, int ldc2,
                          const float* bias, const void* R, int ldr, const DropoutParams& drop,
-                         float* colsum, cudaStream_t stream) {
+                         float* colsum, cudaStream_t stream, const uint8_t* row_keep = nullptr) {
   B200_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem");
   Params p{};
   p.drop = drop;
   p.colsum = colsum;
+  p.row_keep = row_keep;
+  B200_REQUIRE(row_keep == nullptr || epilogue == kBiasResid || epilogue == kBiasDropResid,
+               "gemm: a row mask is available with the residual epilogues only");
   B200_REQUIRE(colsum == nullptr || epilogue == kDGelu || epilogue == kBias,
                "gemm: column sums are available with the plain and dGELU epilogues only");
   p.M = M; p.N = N; p.K = K; p.k_splits = 1;
@@ -688,4 +668,20 @@ extern "C" int llmtrain_b200_gemm_dropout_resid(int M, int N, int K, const void*
   B200_REQUIRE(p >= 0.f && p < 1.f, "gemm_dropout_resid: p must be in [0, 1)");
   return gemm_dispatch(0, kBiasDropResid, M, N, K, A, lda, B, ldb, C, ldc, nullptr, 0, bias, R, ldr,
                        make_dropout(p, seed, offset, site), nullptr, stream);
+}
+
+// C = (row_keep[m] ? dropout(A B^T + bias) : 0) + R   (NT layout; p = 0: no dropout).  The attention
+// branch of the reference multiplies its output by the padding mask before the residual add
+// (`src/llmtrain/models/gpt.py:71-74`); this is that branch's out_proj with the multiply fused.
+extern "C" int llmtrain_b200_gemm_resid_rowmask(int M, int N, int K, const void* A, int lda,
+                                                const void* B, int ldb, void* C, int ldc,
+                                                const float* bias, const void* R, int ldr,
+                                                const uint8_t* row_keep, float p, uint64_t seed,
+                                                uint64_t offset, uint32_t site,
+                                                cudaStream_t stream) {
+  B200_REQUIRE(p >= 0.f && p < 1.f, "gemm_resid_rowmask: p must be in [0, 1)");
+  const bool drop = p > 0.f;
+  return gemm_dispatch(0, drop ? kBiasDropResid : kBiasResid, M, N, K, A, lda, B, ldb, C, ldc,
+                       nullptr, 0, bias, R, ldr, make_dropout(p, seed, offset, site), nullptr,
+                       stream, row_keep);
 }

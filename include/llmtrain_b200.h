@@ -192,6 +192,16 @@ int llmtrain_b200_gemm_dropout_resid(int M, int N, int K, const void* A, int lda
                                      int ldb, void* C, int ldc, const float* bias, const void* R,
                                      int ldr, float p, uint64_t seed, uint64_t offset,
                                      uint32_t site, llm_stream_t stream);
+/* C = (row_keep[m] ? dropout(A B^T + bias) : 0) + R  (p = 0: no dropout): out_proj of the attention
+ * branch with the reference's padding-mask multiply fused (gpt.py:71-74). */
+int llmtrain_b200_gemm_resid_rowmask(int M, int N, int K, const void* A, int lda, const void* B,
+                                     int ldb, void* C, int ldc, const float* bias, const void* R,
+                                     int ldr, const uint8_t* row_keep, float p, uint64_t seed,
+                                     uint64_t offset, uint32_t site, llm_stream_t stream);
+/* y = x o dropout_mask o row_keep[:, None] (p = 0: row mask only); backward of that branch. */
+int llmtrain_b200_dropout_rowmask(const void* x, void* y, long long rows, int cols, int ld,
+                                  const uint8_t* row_keep, float p, uint64_t seed, uint64_t offset,
+                                  uint32_t site, llm_stream_t stream);
 /* attention with dropout on the probabilities; mask rows = B*H*T (index (b*H+h)*T+q), cols = T */
 int llmtrain_b200_attention_fwd_dropout(const void* qkv, void* out, float* lse,
                                         const uint8_t* key_mask, int B, int T, int H, int head_dim,

@@ -287,3 +287,40 @@ def test_deterministic_kernels_make_resume_reproduce_the_uninterrupted_run(tmp_p
         assert torch.equal(third._engine._gpt.p32, weights)
     finally:
         native.lib().llmtrain_b200_set_deterministic(0)
+
+
+def test_padding_mask_semantics_match_the_reference_at_every_position() -> None:
+    """With an ``attention_mask`` the attention branch of padded QUERY rows is dropped before the
+    residual add (reference `src/llmtrain/models/gpt.py:73-74`): logits agree with the torch-op
+    oracle at padded positions too, and so do the parameter gradients of a masked loss."""
+    from llmtrain.models.gpt import GPTAdapter
+
+    oracle = _model().cuda()
+    oracle.prefer_native = False
+    native = copy.deepcopy(oracle)
+    native.prefer_native = True
+    ids = torch.randint(0, 1000, (2, 96), device="cuda")
+    mask = torch.ones(2, 96, dtype=torch.long, device="cuda")
+    mask[0, 60:] = 0
+    mask[1, 90:] = 0
+    oracle.eval()
+    native.eval()
+    with torch.no_grad():
+        want = oracle(ids, attention_mask=mask)
+        got = native(ids, attention_mask=mask)
+    assert (got - want).abs().max().item() < 5e-2 * want.abs().max().item()
+
+    oracle.train()
+    native.train()
+    labels = torch.randint(0, 1000, (2, 96), device="cuda")
+    batch = {"input_ids": ids, "labels": labels, "attention_mask": mask}
+    adapter = GPTAdapter()
+    want_loss, _ = adapter.compute_loss(oracle, batch)
+    want_loss.backward()
+    got_loss, _ = adapter.compute_loss(native, batch)
+    got_loss.backward()
+    assert abs(got_loss.item() - want_loss.item()) < 2e-2 * abs(want_loss.item())
+    for (name, p), (_, q) in zip(native.named_parameters(), oracle.named_parameters(), strict=True):
+        denom = q.grad.abs().max().item() + 1e-8
+        err = (p.grad - q.grad).abs().max().item() / denom
+        assert err < 6e-2, f"{name}: rel err {err:.3e}"
