@@ -90,23 +90,32 @@ class NcclFallback:
         works = self._works
         works.clear()
 
+        failure: list[BaseException] = []
+
         def on_bucket(_ctx: Any, lo: int, length: int) -> int:
-            if length == 0:
+            # called from C++ between kernel launches: an exception must not cross that frame
+            try:
+                if length == 0:
+                    return 0
+                ready = torch.cuda.Event()
+                ready.record(compute)
+                side.wait_event(ready)
+                with torch.cuda.stream(side):
+                    works.append(dist.all_reduce(arena[lo:lo + length], op=dist.ReduceOp.SUM,
+                                                 async_op=True))
                 return 0
-            ready = torch.cuda.Event()
-            ready.record(compute)
-            side.wait_event(ready)
-            with torch.cuda.stream(side):
-                works.append(dist.all_reduce(arena[lo:lo + length], op=dist.ReduceOp.SUM,
-                                             async_op=True))
-            return 0
+            except BaseException as exc:  # noqa: BLE001  (re-raised below, on the Python side)
+                failure.append(exc)
+                return 1
 
         hook = _BUCKET_HOOK(on_bucket)
         lib = native.lib()
         lib.llmtrain_b200_gpt_backward_hooked.argtypes = [ctypes.c_void_p, _BUCKET_HOOK,
                                                           ctypes.c_void_p, ctypes.c_void_p]
-        check(lib.llmtrain_b200_gpt_backward_hooked(g._handle, hook, None, stream_handle()),
-              "gpt_backward_hooked")
+        status = lib.llmtrain_b200_gpt_backward_hooked(g._handle, hook, None, stream_handle())
+        if failure:
+            raise failure[0]
+        check(status, "gpt_backward_hooked")
         self._reduced = True
 
     def reduce_and_step(self, m: torch.Tensor, v: torch.Tensor, sumsq: torch.Tensor,
