@@ -126,10 +126,11 @@ __device__ __forceinline__ void softmax_tile(uint32_t t_s, uint32_t t_p, uint32_
                                              uint64_t mask_base, const Params& prm, int tj,
                                              bool tracer) {
   uint32_t v[BKV / 32][32];
-  // chunks wholly above the diagonal (kDiag, c > wq) are never loaded
+  // All four chunks are loaded unconditionally, also on the diagonal tile: a tcgen05.ld under a
+  // (warp-uniform) branch made ptxas keep the row in local memory, and the diagonal tiles — 22% of
+  // all tiles — then cost 2.2x a full tile.
 #pragma unroll
   for (int c = 0; c < BKV / 32; ++c) {
-    if (MODE == kDiag && c > wq) continue;
     tmem_ld_32x32b_x32(t_s + c * 32, v[c]);
     tmem_ld_wait();  // one load in flight: four back to back were measured 3x slower in total
   }
@@ -140,13 +141,14 @@ __device__ __forceinline__ void softmax_tile(uint32_t t_s, uint32_t t_p, uint32_
 
   // masked scores become -inf: they drop out of the max and exp2 turns them into exact zeros
   if (MODE == kDiag) {
+    // diagonal tile (kv0 == q0): column 32c + i is kept iff 32c + i <= 32 wq + lane.  Chunk c is
+    // kept whole for c < wq and dropped whole for c > wq (warp-uniform), per element for c == wq.
 #pragma unroll
     for (int c = 0; c < BKV / 32; ++c) {
-      if (c == wq) {
+      const bool dead = c > wq, edge = c == wq;
 #pragma unroll
-        for (int i = 0; i < 32; ++i)
-          if (i > lane) v[c][i] = 0xff800000u;
-      }
+      for (int i = 0; i < 32; ++i)
+        if (dead || (edge && i > lane)) v[c][i] = 0xff800000u;
     }
   } else if (MODE == kGeneral) {
 #pragma unroll
@@ -164,7 +166,6 @@ __device__ __forceinline__ void softmax_tile(uint32_t t_s, uint32_t t_p, uint32_
   float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
   for (int c = 0; c < BKV / 32; ++c) {
-    if (MODE == kDiag && c > wq) continue;
 #pragma unroll
     for (int i = 0; i < 32; i += 4) {
 #pragma unroll
@@ -207,10 +208,7 @@ __device__ __forceinline__ void softmax_tile(uint32_t t_s, uint32_t t_p, uint32_
 #pragma unroll
   for (int c = 0; c < BKV / 32; ++c) {
     uint32_t pk[16];
-    if (MODE == kDiag && c > wq) {
-#pragma unroll
-      for (int i = 0; i < 16; ++i) pk[i] = 0u;
-    } else {
+    {
       Rand8 rnd{};
 #pragma unroll
       for (int i = 0; i < 32; i += 2) {
@@ -248,6 +246,32 @@ __device__ __forceinline__ void softmax_tile(uint32_t t_s, uint32_t t_p, uint32_
   if (tracer) stamp(prm, 3, tj, 3);
 }
 
+// One unit of work: a 256-row query block of one (batch, head).
+struct Item {
+  int b, h, qb, q0, n0, n1, n_max;
+};
+__device__ __forceinline__ Item make_item(const Params& p, int idx) {
+  Item it;
+  const int bh_count = p.B * p.H;
+  it.qb = p.nqb - 1 - idx / bh_count;  // heaviest query blocks first
+  const int bh = idx % bh_count;
+  it.b = bh / p.H;
+  it.h = bh % p.H;
+  it.q0 = it.qb * 2 * BQ;
+  // key tiles of query tile t: 0 .. (2 qb + t); a tile that starts past T is inactive
+  it.n0 = 2 * it.qb + 1;
+  it.n1 = (it.q0 + BQ < p.T) ? 2 * it.qb + 2 : 0;
+  it.n_max = it.n1 > it.n0 ? it.n1 : it.n0;
+  return it;
+}
+
+// Persistent: one CTA per SM walks items blockIdx.x, + gridDim.x, ... of the heaviest-first list.
+// Every role keeps RUNNING counters for its barriers (a barrier completes once per use, whatever
+// item the use belongs to), so nothing is re-initialised between items and the roles drift apart
+// freely: while the softmax groups normalise and store item i, the TMA warp is already loading
+// Q/K/V of item i+1 and the tensor core computes its first score tiles.  (With one CTA per item
+// the prologue, the epilogue and the launch gap were ~40% of the kernel: 2430 cycles per tile
+// averaged over the kernel against 1500 in steady state.)
 template <bool DROP>
 __global__ void __launch_bounds__(THREADS, 1)
 fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmO,
@@ -257,7 +281,8 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
                                              ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
   uint64_t* q_full = bars + 0;                 // [2]
-  uint64_t* k_full = bars + 2;                 // [NST]
+  uint64_t* q_free = bars + 2;                 // [2]  O_t has left the Q_t tile it was staged in
+  uint64_t* k_full = bars + 4;                 // [NST]
   uint64_t* k_empty = k_full + NST;            // [NST]
   uint64_t* v_full = k_empty + NST;            // [NST]
   uint64_t* v_empty = v_full + NST;            // [NST]
@@ -268,22 +293,15 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(s_read + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int bh_count = p.B * p.H;
-  const int qb = p.nqb - 1 - int(blockIdx.x) / bh_count;  // heaviest query blocks first
-  const int bh = int(blockIdx.x) % bh_count;
-  const int b = bh / p.H, h = bh % p.H;
   const int d = p.H * HD;
-  const int q0 = qb * 2 * BQ;
-  // key tiles of query tile t: 0 .. (2 qb + t); a tile that starts past T is inactive
-  const int n0 = 2 * qb + 1;
-  const int n1 = (q0 + BQ < p.T) ? 2 * qb + 2 : 0;
-  const int n_max = n1 > n0 ? n1 : n0;
+  const int n_items = p.nqb * p.B * p.H;
 
   if (warp == 8 && lane == 0) {
     tma_prefetch_desc(&tmQKV);
     tma_prefetch_desc(&tmO);
     for (int t = 0; t < 2; ++t) {
       mbar_init(&q_full[t], 1);
+      mbar_init(&q_free[t], 1);
       mbar_init(&s_full[t], 1);
       mbar_init(&p_full[t], 4);
       mbar_init(&pv_done[t], 1);
@@ -296,17 +314,6 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
       mbar_init(&v_empty[s], 1);
     }
     fence_barrier_init();
-    pdl_wait();  // qkv comes from the previous kernel of the stream
-    mbar_expect_tx(&q_full[0], TILE_BYTES);
-    tma_load_3d(smem + OFF_Q, &tmQKV, &q_full[0], h * HD, q0, b);
-    mbar_expect_tx(&k_full[0], TILE_BYTES);
-    tma_load_3d(smem + OFF_K, &tmQKV, &k_full[0], d + h * HD, 0, b, kEvictLast);
-    if (n1 > 0) {
-      mbar_expect_tx(&q_full[1], TILE_BYTES);
-      tma_load_3d(smem + OFF_Q + TILE_BYTES, &tmQKV, &q_full[1], h * HD, q0 + BQ, b);
-    }
-    mbar_expect_tx(&v_full[0], TILE_BYTES);
-    tma_load_3d(smem + OFF_V, &tmQKV, &v_full[0], 2 * d + h * HD, 0, b, kEvictLast);
   }
   if (warp == 9) {
     tmem_alloc(tmem_slot, TMEM_COLS);
@@ -315,36 +322,57 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
-  pdl_enter();
+  pdl_enter();  // qkv comes from the previous kernel of the stream
   const uint32_t tmem = *tmem_slot;
 
   if (warp >= 8) {
     reg_dealloc<64>();
     if (warp == 8 && lane == 0) {
       // ------------------------------- TMA producer -------------------------------------------
-      for (int j = 1; j < n_max; ++j) {  // tile 0 was requested in the prologue
-        const int s = j % NST;
-        const uint32_t ph = uint32_t(j / NST) & 1u;
-        mbar_wait(&k_empty[s], ph ^ 1u);
-        mbar_expect_tx(&k_full[s], TILE_BYTES);
-        tma_load_3d(smem + OFF_K + s * TILE_BYTES, &tmQKV, &k_full[s], d + h * HD, j * BKV, b,
-                    kEvictLast);
-        mbar_wait(&v_empty[s], ph ^ 1u);
-        mbar_expect_tx(&v_full[s], TILE_BYTES);
-        tma_load_3d(smem + OFF_V + s * TILE_BYTES, &tmQKV, &v_full[s], 2 * d + h * HD, j * BKV, b,
-                    kEvictLast);
+      uint32_t kv = 0;            // K/V tiles requested so far (ring position)
+      uint32_t q_uses[2] = {0, 0};  // items in which tile t was active so far
+      for (int idx = blockIdx.x; idx < n_items; idx += gridDim.x) {
+        const Item it = make_item(p, idx);
+        for (int t = 0; t < 2; ++t) {
+          if ((t == 0 ? it.n0 : it.n1) == 0) continue;
+          // the previous item's O_t was staged in this tile: wait until its TMA store has read it
+          if (q_uses[t] > 0) mbar_wait(&q_free[t], (q_uses[t] - 1) & 1u);
+          ++q_uses[t];
+          mbar_expect_tx(&q_full[t], TILE_BYTES);
+          tma_load_3d(smem + OFF_Q + t * TILE_BYTES, &tmQKV, &q_full[t], it.h * HD,
+                      it.q0 + t * BQ, it.b);
+        }
+        for (int j = 0; j < it.n_max; ++j, ++kv) {
+          const int s = int(kv % NST);
+          const uint32_t ph = (kv / NST) & 1u;
+          mbar_wait(&k_empty[s], ph ^ 1u);
+          mbar_expect_tx(&k_full[s], TILE_BYTES);
+          tma_load_3d(smem + OFF_K + s * TILE_BYTES, &tmQKV, &k_full[s], d + it.h * HD, j * BKV,
+                      it.b, kEvictLast);
+          mbar_wait(&v_empty[s], ph ^ 1u);
+          mbar_expect_tx(&v_full[s], TILE_BYTES);
+          tma_load_3d(smem + OFF_V + s * TILE_BYTES, &tmQKV, &v_full[s], 2 * d + it.h * HD,
+                      j * BKV, it.b, kEvictLast);
+        }
       }
     } else if (warp == 9) {
       // ------------------------------- MMA issuer ---------------------------------------------
       constexpr uint32_t idesc_s = umma_idesc_bf16(BQ, BKV, false, false);
       constexpr uint32_t idesc_pv = umma_idesc_bf16(BQ, HD, false, true);
-      const int nt[2] = {n0, n1};
       const bool leader = elect_one();
       const uint32_t sQ0 = smem_u32(smem + OFF_Q), sK0 = smem_u32(smem + OFF_K),
                      sV0 = smem_u32(smem + OFF_V);
-      auto issue_s = [&](int t, int j) {  // S_t = Q_t K_j^T
+      uint32_t kv = 0;              // ring position of the current item's key tile 0
+      uint32_t n_s[2] = {0, 0};     // S_t products issued so far
+      uint32_t n_pv[2] = {0, 0};    // PV_t products issued so far
+      uint32_t q_uses[2] = {0, 0};
+      auto issue_s = [&](int t, uint32_t ring) {  // S_t = Q_t K^T, K in ring slot `ring`
+        // S_t may only be overwritten once the softmax group has pulled the previous one out
+        if (n_s[t] > 0) mbar_wait(&s_read[t], (n_s[t] - 1) & 1u);
+        ++n_s[t];
+        tc_fence_after_sync();
         const uint64_t dq = umma_smem_desc(sQ0 + t * TILE_BYTES, 0, 1024);
-        const uint64_t dk = umma_smem_desc(sK0 + (j % NST) * TILE_BYTES, 0, 1024);
+        const uint64_t dk = umma_smem_desc(sK0 + int(ring % NST) * TILE_BYTES, 0, 1024);
         if (leader) {
 #pragma unroll
           for (int k = 0; k < HD / 16; ++k)  // +32 B per K step = +2 in the address field
@@ -352,59 +380,57 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
           umma_commit(&s_full[t]);
         }
       };
-      auto issue_pv = [&](int t, int j) {  // O_t (+)= P_t V_j, P_t read from TMEM
-        const uint64_t dv = umma_smem_desc(sV0 + (j % NST) * TILE_BYTES, TILE_BYTES, 1024);
+      auto issue_pv = [&](int t, uint32_t ring, bool accumulate) {  // O_t (+)= P_t V
+        mbar_wait(&p_full[t], n_pv[t] & 1u);  // P_t has been written
+        ++n_pv[t];
+        tc_fence_after_sync();
+        const uint64_t dv = umma_smem_desc(sV0 + int(ring % NST) * TILE_BYTES, TILE_BYTES, 1024);
         if (leader) {
 #pragma unroll
           for (int k = 0; k < BKV / 16; ++k)  // +2048 B per K step = +128 in the address field
             umma_ts(tmem + COL_O + t * HD, tmem + COL_P + t * HD + k * 8, dv + 128 * k, idesc_pv,
-                    (j > 0) || (k > 0));
+                    accumulate || (k > 0));
           umma_commit(&pv_done[t]);
         }
       };
-      mbar_wait(&q_full[0], 0);
-      if (n1 > 0) mbar_wait(&q_full[1], 0);
-      mbar_wait(&k_full[0], 0);
-      tc_fence_after_sync();
-      issue_s(0, 0);
-      if (n1 > 0) issue_s(1, 0);
-      if (leader) umma_commit(&k_empty[0]);
-      // Round j, per query tile t: once S_t(j) has been pulled into registers (s_read), issue
-      // PV_t(j-1) and S_t(j+1).  PV is deliberately NOT issued the moment P_t(j-1) is complete: a
-      // tcgen05.ld is not served while the tensor core streams accumulators through TMEM, so a PV
-      // issued right at p_full would sit on the load of the next score tile (measured: 130 -> 930
-      // cycles).  Nothing needs O_t before the next rescale, and that waits on pv_done itself.
-      for (int j = 0; j < n_max; ++j) {
-        const int sv = j % NST, sn = (j + 1) % NST;
-        const uint32_t phv = uint32_t(j / NST) & 1u, phn = uint32_t((j + 1) / NST) & 1u;
-        bool k_ready = false, v_ready = false;
-        // scores of the next key tile, as soon as the current ones have left TMEM
+      for (int idx = blockIdx.x; idx < n_items; idx += gridDim.x) {
+        const Item it = make_item(p, idx);
+        const int nt[2] = {it.n0, it.n1};
+        for (int t = 0; t < 2; ++t)
+          if (nt[t] > 0) mbar_wait(&q_full[t], q_uses[t]++ & 1u);
+        // S_t(j+1) is issued as soon as S_t(j) has left TMEM (inside issue_s), PV_t(j) once P_t(j)
+        // is written: the next tile's scores are computed under the current tile's exponentials.
+        mbar_wait(&k_full[kv % NST], (kv / NST) & 1u);
+        for (int t = 0; t < 2; ++t)
+          if (nt[t] > 0) issue_s(t, kv);
+        if (leader) umma_commit(&k_empty[kv % NST]);
+        for (int j = 0; j < it.n_max; ++j) {
+          const uint32_t rv = kv + j, rn = kv + j + 1;
+          bool k_ready = false, v_ready = false;
 #pragma unroll
-        for (int t = 0; t < 2; ++t) {
-          if (j + 1 >= nt[t]) continue;
-          mbar_wait(&s_read[t], uint32_t(j) & 1u);
-          if (!k_ready) {
-            mbar_wait(&k_full[sn], phn);
-            k_ready = true;
+          for (int t = 0; t < 2; ++t) {
+            if (j + 1 >= nt[t]) continue;
+            if (!k_ready) {
+              mbar_wait(&k_full[rn % NST], (rn / NST) & 1u);
+              k_ready = true;
+            }
+            issue_s(t, rn);
+            if ((t == 1 || j + 1 >= nt[1]) && leader) umma_commit(&k_empty[rn % NST]);
           }
-          tc_fence_after_sync();
-          issue_s(t, j + 1);
-          if ((t == 1 || j + 1 >= nt[1]) && leader) umma_commit(&k_empty[sn]);  // last reader of K
-        }
 #pragma unroll
-        for (int t = 0; t < 2; ++t) {
-          if (j >= nt[t]) continue;
-          stamp(p, 2, j, 2 * t);
-          mbar_wait(&p_full[t], uint32_t(j) & 1u);  // P_t(j) has been written
-          stamp(p, 2, j, 2 * t + 1);
-          if (!v_ready) {
-            mbar_wait(&v_full[sv], phv);
-            v_ready = true;
+          for (int t = 0; t < 2; ++t) {
+            if (j >= nt[t]) continue;
+            if (!v_ready) {
+              mbar_wait(&v_full[rv % NST], (rv / NST) & 1u);
+              v_ready = true;
+            }
+            if (idx == int(blockIdx.x)) stamp(p, 2, j, 2 * t);
+            issue_pv(t, rv, j > 0);
+            if (idx == int(blockIdx.x)) stamp(p, 2, j, 2 * t + 1);
+            if ((t == 1 || j >= nt[1]) && leader) umma_commit(&v_empty[rv % NST]);
           }
-          tc_fence_after_sync();
-          issue_pv(t, j);
-          if ((t == 1 || j >= nt[1]) && leader) umma_commit(&v_empty[sv]);  // last reader of V_j
         }
+        kv += uint32_t(it.n_max);
       }
     }
   } else {
@@ -413,47 +439,56 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
     const int t = warp >> 2;         // query tile of this group
     const int wq = warp & 3;         // warp inside the group = 32-row quarter of the tile
     const int r = wq * 32 + lane;    // row inside the tile == TMEM lane
-    const int n_t = t == 0 ? n0 : n1;
-    const int qi = 2 * qb + t;       // query tile index == index of its diagonal key tile
-    const int qrow = q0 + t * BQ + r;
     const uint32_t lane_base = uint32_t(wq * 32) << 16;
     const uint32_t t_s = tmem + lane_base + COL_S + t * BKV;
     const uint32_t t_o = tmem + lane_base + COL_O + t * HD;
     const uint32_t t_p = tmem + lane_base + COL_P + t * HD;
-    const uint8_t* kmask = p.key_mask ? p.key_mask + size_t(b) * p.T : nullptr;
-    float m_ref = -INFINITY, l_run = 0.f;
+    uint32_t tiles = 0;  // score tiles of this group so far (all items)
 
-    for (int j = 0; j < n_t; ++j) {
-      const int kv0 = j * BKV;
-      if (r == 0) stamp(p, t, j, 0);
-      mbar_wait(&s_full[t], uint32_t(j) & 1u);
-      tc_fence_after_sync();
-      if (r == 0) stamp(p, t, j, 1);
-      const int mode = kmask != nullptr ? kGeneral : (j == qi ? kDiag : kNoMask);
-      const uint64_t mask_base =
-          DROP ? (uint64_t((size_t(b) * p.H + h) * p.T + qrow) * uint64_t(p.t_pad) + uint64_t(kv0))
-               : 0;
-      if (mode == kNoMask)
-        softmax_tile<kNoMask, DROP>(t_s, t_p, t_o, &s_read[t], &pv_done[t], j == 0,
-                                    uint32_t(j - 1) & 1u, kv0, qrow, p.T, kmask, p.scale_log2, m_ref,
-                                    l_run, wq, lane, p.drop, mask_base, p, j, threadIdx.x == 0);
-      else if (mode == kDiag)
-        softmax_tile<kDiag, DROP>(t_s, t_p, t_o, &s_read[t], &pv_done[t], j == 0,
-                                    uint32_t(j - 1) & 1u, kv0, qrow, p.T, kmask, p.scale_log2, m_ref,
-                                  l_run, wq, lane, p.drop, mask_base, p, j, threadIdx.x == 0);
-      else
-        softmax_tile<kGeneral, DROP>(t_s, t_p, t_o, &s_read[t], &pv_done[t], j == 0,
-                                    uint32_t(j - 1) & 1u, kv0, qrow, p.T, kmask, p.scale_log2, m_ref,
-                                     l_run, wq, lane, p.drop, mask_base, p, j, threadIdx.x == 0);
-      tc_fence_before_sync();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&p_full[t]);
-      if (r == 0) stamp(p, t, j, 2);
-    }
+    for (int idx = blockIdx.x; idx < n_items; idx += gridDim.x) {
+      const Item it = make_item(p, idx);
+      const int n_t = t == 0 ? it.n0 : it.n1;
+      if (n_t == 0) continue;
+      const int b = it.b, h = it.h;
+      const int qi = 2 * it.qb + t;  // query tile index == index of its diagonal key tile
+      const int qrow = it.q0 + t * BQ + r;
+      const uint8_t* kmask = p.key_mask ? p.key_mask + size_t(b) * p.T : nullptr;
+      const bool traced = idx == int(blockIdx.x);
+      float m_ref = -INFINITY, l_run = 0.f;
 
-    if (n_t > 0) {
-      // O_t / l -> bf16 -> the (now idle) Q_t tile as staging -> one TMA store per query tile
-      mbar_wait(&pv_done[t], uint32_t(n_t - 1) & 1u);
+      for (int j = 0; j < n_t; ++j, ++tiles) {
+        const int kv0 = j * BKV;
+        if (r == 0 && traced) stamp(p, t, j, 0);
+        mbar_wait(&s_full[t], tiles & 1u);
+        tc_fence_after_sync();
+        if (r == 0 && traced) stamp(p, t, j, 1);
+        const int mode = kmask != nullptr ? kGeneral : (j == qi ? kDiag : kNoMask);
+        const uint64_t mask_base =
+            DROP ? (uint64_t((size_t(b) * p.H + h) * p.T + qrow) * uint64_t(p.t_pad) + uint64_t(kv0))
+                 : 0;
+        const uint32_t pv_parity = (tiles - 1) & 1u;  // PV of the previous tile of this group
+        const bool tr = threadIdx.x == 0 && traced;
+        if (mode == kNoMask)
+          softmax_tile<kNoMask, DROP>(t_s, t_p, t_o, &s_read[t], &pv_done[t], j == 0, pv_parity, kv0,
+                                      qrow, p.T, kmask, p.scale_log2, m_ref, l_run, wq, lane,
+                                      p.drop, mask_base, p, j, tr);
+        else if (mode == kDiag)
+          softmax_tile<kDiag, DROP>(t_s, t_p, t_o, &s_read[t], &pv_done[t], j == 0, pv_parity, kv0,
+                                    qrow, p.T, kmask, p.scale_log2, m_ref, l_run, wq, lane, p.drop,
+                                    mask_base, p, j, tr);
+        else
+          softmax_tile<kGeneral, DROP>(t_s, t_p, t_o, &s_read[t], &pv_done[t], j == 0, pv_parity,
+                                       kv0, qrow, p.T, kmask, p.scale_log2, m_ref, l_run, wq, lane,
+                                       p.drop, mask_base, p, j, tr);
+        tc_fence_before_sync();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&p_full[t]);
+        if (r == 0 && traced) stamp(p, t, j, 2);
+      }
+
+      // O_t / l -> bf16 -> the (now idle) Q_t tile as staging -> one TMA store per query tile.
+      // (The wait also guarantees that P_t is free for the next item's first tile.)
+      mbar_wait(&pv_done[t], (tiles - 1) & 1u);
       tc_fence_after_sync();
       const float inv_l = l_run > 0.f ? 1.0f / l_run : 0.f;
       uint8_t* stage = smem + OFF_Q + t * TILE_BYTES;
@@ -481,9 +516,10 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
       fence_proxy_async_smem();
       named_bar_sync(1 + t, 128);
       if (r == 0) {
-        tma_store_3d(&tmO, stage, h * HD, q0 + t * BQ, b);
+        tma_store_3d(&tmO, stage, h * HD, it.q0 + t * BQ, b);
         tma_store_commit();
         tma_store_wait_read<0>();
+        mbar_arrive(&q_free[t]);  // the producer may load the next item's Q_t
       }
     }
   }
@@ -528,7 +564,8 @@ static int attention_fwd_launch(const void* qkv, void* out, float* lse, const ui
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, a2::SMEM + 1024));
     configured = true;
   }
-  const int grid = p.nqb * B * H;
+  const int items = p.nqb * B * H;
+  const int grid = items < sm_count() ? items : sm_count();  // persistent: one CTA per SM
   if (drop.threshold != 0)
     B200_LAUNCH((a2::fwd_kernel<true>), grid, a2::THREADS, a2::SMEM + 1024, stream, tQKV, tO, p);
   else
