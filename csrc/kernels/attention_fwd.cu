@@ -56,7 +56,8 @@ constexpr int COL_P = 384;  // + 64 * t
 constexpr int OFF_Q = 0;                          // [2]
 constexpr int OFF_K = OFF_Q + 2 * TILE_BYTES;     // [NST]
 constexpr int OFF_V = OFF_K + NST * TILE_BYTES;   // [NST]
-constexpr int OFF_BAR = OFF_V + NST * TILE_BYTES;
+constexpr int OFF_O = OFF_V + NST * TILE_BYTES;   // [2] bf16 output tiles on their way out
+constexpr int OFF_BAR = OFF_O + 2 * TILE_BYTES;
 constexpr int SMEM = OFF_BAR + 512;
 constexpr float kRescaleThreshold = 8.0f;  // log2 units
 // Of every 4 consecutive column pairs, this many take their exponential on the FMA pipe (the rest
@@ -116,8 +117,11 @@ __device__ __forceinline__ void stamp(const Params& p, int role, int j, int k) {
 }
 
 // One softmax step of one query row: S row (TMEM) -> P row (bf16, TMEM), running (m_ref, l).
-template <int MODE, bool DROP>
-__device__ __forceinline__ void softmax_tile(uint32_t t_s, uint32_t t_p, uint32_t t_o,
+// ONE copy of this code serves every tile: the mask mode only selects a short fix-up of the score
+// registers.  (Three specialised copies were 110 KB of SASS; the diagonal copy, entered once per
+// item, ran ~4x slower than the common one — instruction-cache misses on a cold 16 KB body.)
+template <bool DROP>
+__device__ __forceinline__ void softmax_tile(int mode, uint32_t t_s, uint32_t t_p, uint32_t t_o,
                                              uint64_t* s_read, uint64_t* pv_done, bool first,
                                              uint32_t pv_parity, int kv0,
                                              int qrow, int T, const uint8_t* kmask,
@@ -140,7 +144,7 @@ __device__ __forceinline__ void softmax_tile(uint32_t t_s, uint32_t t_p, uint32_
   if (tracer) stamp(prm, 3, tj, 0);
 
   // masked scores become -inf: they drop out of the max and exp2 turns them into exact zeros
-  if (MODE == kDiag) {
+  if (mode == kDiag) {
     // diagonal tile (kv0 == q0): column 32c + i is kept iff 32c + i <= 32 wq + lane.  Chunk c is
     // kept whole for c < wq and dropped whole for c > wq (warp-uniform), per element for c == wq.
 #pragma unroll
@@ -150,16 +154,27 @@ __device__ __forceinline__ void softmax_tile(uint32_t t_s, uint32_t t_p, uint32_
       for (int i = 0; i < 32; ++i)
         if (dead || (edge && i > lane)) v[c][i] = 0xff800000u;
     }
-  } else if (MODE == kGeneral) {
+  } else if (mode == kGeneral) {
+    // key padding: one keep-bit per column, gathered with a rolled loop (no indexing of v, which
+    // must stay in registers), then applied with static indices
+    uint32_t keep[BKV / 32];
 #pragma unroll
     for (int c = 0; c < BKV / 32; ++c) {
-#pragma unroll
+      uint32_t bits = 0;
+#pragma unroll 1
       for (int i = 0; i < 32; ++i) {
         const int col = kv0 + c * 32 + i;
         bool ok = col <= qrow;
         if (kmask != nullptr && col < T) ok = ok && (kmask[col] != 0);
-        if (!ok) v[c][i] = 0xff800000u;
+        bits |= uint32_t(ok) << i;
       }
+      keep[c] = bits;
+    }
+#pragma unroll
+    for (int c = 0; c < BKV / 32; ++c) {
+#pragma unroll
+      for (int i = 0; i < 32; ++i)
+        if (((keep[c] >> i) & 1u) == 0) v[c][i] = 0xff800000u;
     }
   }
 
@@ -215,7 +230,7 @@ __device__ __forceinline__ void softmax_tile(uint32_t t_s, uint32_t t_p, uint32_
         const f32x2 x2 =
             fma2(pack2(__uint_as_float(v[c][i]), __uint_as_float(v[c][i + 1])), sc2, nm2);
         float e0, e1;
-        if (MODE != kGeneral && ((i >> 1) & 3) < kPolyOf4) {
+        if (((i >> 1) & 3) < kPolyOf4) {
           exp2_poly_pair(x2, e0, e1);
         } else {
           float x0, x1;
@@ -281,7 +296,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
                                              ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
   uint64_t* q_full = bars + 0;                 // [2]
-  uint64_t* q_free = bars + 2;                 // [2]  O_t has left the Q_t tile it was staged in
+  uint64_t* q_free = bars + 2;                 // [2]  the item's last S_t product has read Q_t
   uint64_t* k_full = bars + 4;                 // [NST]
   uint64_t* k_empty = k_full + NST;            // [NST]
   uint64_t* v_full = k_empty + NST;            // [NST]
@@ -335,7 +350,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
         const Item it = make_item(p, idx);
         for (int t = 0; t < 2; ++t) {
           if ((t == 0 ? it.n0 : it.n1) == 0) continue;
-          // the previous item's O_t was staged in this tile: wait until its TMA store has read it
+          // the previous item's last score product must have read this tile
           if (q_uses[t] > 0) mbar_wait(&q_free[t], (q_uses[t] - 1) & 1u);
           ++q_uses[t];
           mbar_expect_tx(&q_full[t], TILE_BYTES);
@@ -401,8 +416,11 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
         // S_t(j+1) is issued as soon as S_t(j) has left TMEM (inside issue_s), PV_t(j) once P_t(j)
         // is written: the next tile's scores are computed under the current tile's exponentials.
         mbar_wait(&k_full[kv % NST], (kv / NST) & 1u);
-        for (int t = 0; t < 2; ++t)
-          if (nt[t] > 0) issue_s(t, kv);
+        for (int t = 0; t < 2; ++t) {
+          if (nt[t] == 0) continue;
+          issue_s(t, kv);
+          if (nt[t] == 1 && leader) umma_commit(&q_free[t]);  // Q_t is not needed again
+        }
         if (leader) umma_commit(&k_empty[kv % NST]);
         for (int j = 0; j < it.n_max; ++j) {
           const uint32_t rv = kv + j, rn = kv + j + 1;
@@ -415,6 +433,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
               k_ready = true;
             }
             issue_s(t, rn);
+            if (j + 2 == nt[t] && leader) umma_commit(&q_free[t]);  // that was the last S_t
             if ((t == 1 || j + 1 >= nt[1]) && leader) umma_commit(&k_empty[rn % NST]);
           }
 #pragma unroll
@@ -455,6 +474,9 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
       const uint8_t* kmask = p.key_mask ? p.key_mask + size_t(b) * p.T : nullptr;
       const bool traced = idx == int(blockIdx.x);
       float m_ref = -INFINITY, l_run = 0.f;
+      const int item_no = (idx - int(blockIdx.x)) / int(gridDim.x);
+      if (p.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0 && item_no < 32)
+        p.trace[4 * 32 * 4 + 2 * item_no] = clock64();
 
       for (int j = 0; j < n_t; ++j, ++tiles) {
         const int kv0 = j * BKV;
@@ -468,30 +490,29 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
                  : 0;
         const uint32_t pv_parity = (tiles - 1) & 1u;  // PV of the previous tile of this group
         const bool tr = threadIdx.x == 0 && traced;
-        if (mode == kNoMask)
-          softmax_tile<kNoMask, DROP>(t_s, t_p, t_o, &s_read[t], &pv_done[t], j == 0, pv_parity, kv0,
-                                      qrow, p.T, kmask, p.scale_log2, m_ref, l_run, wq, lane,
-                                      p.drop, mask_base, p, j, tr);
-        else if (mode == kDiag)
-          softmax_tile<kDiag, DROP>(t_s, t_p, t_o, &s_read[t], &pv_done[t], j == 0, pv_parity, kv0,
-                                    qrow, p.T, kmask, p.scale_log2, m_ref, l_run, wq, lane, p.drop,
-                                    mask_base, p, j, tr);
-        else
-          softmax_tile<kGeneral, DROP>(t_s, t_p, t_o, &s_read[t], &pv_done[t], j == 0, pv_parity,
-                                       kv0, qrow, p.T, kmask, p.scale_log2, m_ref, l_run, wq, lane,
-                                       p.drop, mask_base, p, j, tr);
+        softmax_tile<DROP>(mode, t_s, t_p, t_o, &s_read[t], &pv_done[t], j == 0, pv_parity, kv0, qrow,
+                           p.T, kmask, p.scale_log2, m_ref, l_run, wq, lane, p.drop, mask_base, p, j,
+                           tr);
         tc_fence_before_sync();
         __syncwarp();
         if (lane == 0) mbar_arrive(&p_full[t]);
         if (r == 0 && traced) stamp(p, t, j, 2);
       }
 
-      // O_t / l -> bf16 -> the (now idle) Q_t tile as staging -> one TMA store per query tile.
-      // (The wait also guarantees that P_t is free for the next item's first tile.)
+      // O_t / l -> bf16 -> this group's staging tile -> one TMA store per query tile.  (The wait
+      // also guarantees that P_t is free for the next item's first tile.)  The staging tile is
+      // separate from Q_t so that the next item's Q can be loaded — and its first score tile
+      // computed — while this one is still being normalised and stored: with O staged in the Q
+      // tile every item paid ~5600 cycles of exposed load + MMA latency after its epilogue.
       mbar_wait(&pv_done[t], (tiles - 1) & 1u);
       tc_fence_after_sync();
-      const float inv_l = l_run > 0.f ? 1.0f / l_run : 0.f;
-      uint8_t* stage = smem + OFF_Q + t * TILE_BYTES;
+      if (r == 0) tma_store_wait_read<0>();  // the previous item's store has read the staging tile
+      named_bar_sync(1 + t, 128);
+      // a row whose keys were all excluded never raised m_ref: zeros and LSE = -inf (its l holds
+      // only the clamped 2^-126 terms of the polynomial exponential)
+      const bool dead_row = m_ref == -INFINITY;
+      const float inv_l = (!dead_row && l_run > 0.f) ? 1.0f / l_run : 0.f;
+      uint8_t* stage = smem + OFF_O + t * TILE_BYTES;
 #pragma unroll
       for (int c = 0; c < HD / 32; ++c) {
         uint32_t o[32];
@@ -510,7 +531,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
       }
       if (qrow < p.T) {
         p.lse[(size_t(b) * p.H + h) * p.T + qrow] =
-            l_run > 0.f ? (m_ref + log2f(l_run)) * 0.6931471805599453f : -INFINITY;
+            (!dead_row && l_run > 0.f) ? (m_ref + log2f(l_run)) * 0.6931471805599453f : -INFINITY;
       }
       tc_fence_before_sync();
       fence_proxy_async_smem();
@@ -518,12 +539,13 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
       if (r == 0) {
         tma_store_3d(&tmO, stage, h * HD, it.q0 + t * BQ, b);
         tma_store_commit();
-        tma_store_wait_read<0>();
-        mbar_arrive(&q_free[t]);  // the producer may load the next item's Q_t
       }
+      if (p.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0 && item_no < 32)
+        p.trace[4 * 32 * 4 + 2 * item_no + 1] = clock64();
     }
   }
 
+  if (warp < 8 && (threadIdx.x & 127) == 0) tma_store_wait_read<0>();  // staging outlives its reader
   tc_fence_before_sync();
   __syncthreads();
   if (warp == 9) tmem_dealloc(tmem, TMEM_COLS);
@@ -553,8 +575,8 @@ static int attention_fwd_launch(const void* qkv, void* out, float* lse, const ui
   p.trace = nullptr;
   static const bool want_trace = std::getenv("LLMTRAIN_ATTN_TRACE") != nullptr;
   if (want_trace) {
-    B200_CHECK_CUDA(cudaMalloc(&p.trace, 4 * 32 * 4 * sizeof(long long)));
-    B200_CHECK_CUDA(cudaMemsetAsync(p.trace, 0, 4 * 32 * 4 * sizeof(long long), stream));
+    B200_CHECK_CUDA(cudaMalloc(&p.trace, (4 * 32 * 4 + 64) * sizeof(long long)));
+    B200_CHECK_CUDA(cudaMemsetAsync(p.trace, 0, (4 * 32 * 4 + 64) * sizeof(long long), stream));
   }
   static bool configured = false;
   if (!configured) {
@@ -573,7 +595,7 @@ static int attention_fwd_launch(const void* qkv, void* out, float* lse, const ui
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
   if (p.trace != nullptr) {  // debug: per-tile timeline of the heaviest CTA, cycles since its first stamp
-    static long long host[4 * 32 * 4];
+    static long long host[4 * 32 * 4 + 64];
     B200_CHECK_CUDA(cudaMemcpyAsync(host, p.trace, sizeof(host), cudaMemcpyDeviceToHost, stream));
     B200_CHECK_CUDA(cudaStreamSynchronize(stream));
     const long long t0 = host[1];
@@ -585,6 +607,11 @@ static int attention_fwd_launch(const void* qkv, void* out, float* lse, const ui
                        host[(role * 32 + j) * 4 + k] == 0 ? -1LL : host[(role * 32 + j) * 4 + k] - t0);
       std::fprintf(stderr, "\n");
     }
+    std::fprintf(stderr, "attn trace items (tiles, start, end) of CTA 0:");
+    for (int k = 0; k < 32 && host[4 * 32 * 4 + 2 * k] != 0; ++k)
+      std::fprintf(stderr, " [%lld %lld]", host[4 * 32 * 4 + 2 * k] - t0,
+                   host[4 * 32 * 4 + 2 * k + 1] - t0);
+    std::fprintf(stderr, "\n");
     cudaFree(p.trace);
   }
   return 0;
