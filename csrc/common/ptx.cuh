@@ -127,6 +127,32 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   }
 }
 
+// Polling wait for the one or two hand-overs per iteration that set a kernel's pace: no hardware
+// suspend (waking a suspended warp costs ~100 cycles more than noticing the flip in a poll), the
+// wall-clock bound is checked every 4096 polls.  The waiting warp burns issue slots; use it only
+// where its SM sub-partition has nothing better to run.
+__device__ __forceinline__ void mbar_wait_spin(uint64_t* bar, uint32_t parity) {
+  const uint32_t addr = smem_u32(bar);
+  unsigned long long t0 = 0;
+  for (uint32_t n = 1;; ++n) {
+    uint32_t done;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred P;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 P, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, P;\n\t"
+        "}\n"
+        : "=r"(done)
+        : "r"(addr), "r"(parity)
+        : "memory");
+    if (done) return;
+    if ((n & 4095u) == 0) {
+      if (t0 == 0) t0 = global_timer_ns();
+      if (global_timer_ns() - t0 > B200_MBAR_TIMEOUT_NS) mbar_timeout_trap();
+    }
+  }
+}
+
 // ----------------------------------------------------------------------------------------------
 // TMA
 // ----------------------------------------------------------------------------------------------
@@ -310,6 +336,45 @@ __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
                    smem_u32(bar))
                : "memory");
+}
+
+// Warp-collective forms: EVERY lane of a converged warp executes the call and one elected lane
+// issues the instruction.  Use these in loops that run warp-uniformly.  Under `if (lane == 0)` the
+// compiler cannot keep descriptors in uniform registers (the region is divergent), so each
+// UTCHMMA is fed through an ELECT / R2UR.BROADCAST loop: 85-170 cycles per instruction measured
+// (bench/mma_probe.cu), against a tensor-core floor of 32 cycles for a 128x64x16 product.
+__device__ __forceinline__ void umma_ss_w(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b,
+                                          uint32_t idesc, bool accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p, e;\n\t"
+      "elect.sync _|e, 0xffffffff;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "@e tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}\n" ::"r"(tmem_d),
+      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(static_cast<uint32_t>(accumulate))
+      : "memory");
+}
+__device__ __forceinline__ void umma_ts_w(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b,
+                                          uint32_t idesc, bool accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p, e;\n\t"
+      "elect.sync _|e, 0xffffffff;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "@e tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t"
+      "}\n" ::"r"(tmem_d),
+      "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(static_cast<uint32_t>(accumulate))
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit_w(uint64_t* bar) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred e;\n\t"
+      "elect.sync _|e, 0xffffffff;\n\t"
+      "@e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t"
+      "}\n" ::"r"(smem_u32(bar))
+      : "memory");
 }
 
 // ----------------------------------------------------------------------------------------------
@@ -504,6 +569,27 @@ __device__ __forceinline__ uint32_t swizzle64(uint32_t byte_off) {
 
 __device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+// 2^x for a pair, no MUFU: round-to-nearest split x = n + f (magic-number add), cubic minimax of
+// 2^f on [-0.5, 0.5] (relative error 7.7e-5, far inside bf16), exponent patched in by integer add.
+// Inputs below -126 (masked scores are -inf) are clamped: the result is ~1e-38, i.e. zero against
+// a row whose largest term is >= 2^-8.
+__device__ __forceinline__ void exp2_poly_pair(f32x2 x, float& e0, float& e1) {
+  float x0, x1;
+  unpack2(x, x0, x1);
+  x = pack2(fmaxf(x0, -126.f), fmaxf(x1, -126.f));
+  const f32x2 t = add2(x, splat2(12582912.f));           // low mantissa bits = round(x)
+  const f32x2 n = add2(t, splat2(-12582912.f));
+  const f32x2 f = fma2(n, splat2(-1.f), x);
+  f32x2 q = fma2(f, splat2(0.05508868396282196f), splat2(0.24260404706001282f));
+  q = fma2(q, f, splat2(0.6932762265205383f));
+  q = fma2(q, f, splat2(0.9999289512634277f));
+  float t0, t1, q0, q1;
+  unpack2(t, t0, t1);
+  unpack2(q, q0, q1);
+  e0 = __int_as_float(__float_as_int(q0) + (__float_as_int(t0) << 23));
+  e1 = __int_as_float(__float_as_int(q1) + (__float_as_int(t1) << 23));
 }
 
 }  // namespace b200

@@ -38,6 +38,7 @@
 #include "../common/philox.cuh"
 #include "../common/ptx.cuh"
 #include "../../include/llmtrain_b200.h"
+#include "attention_bwd_t.cuh"
 
 namespace b200 {
 namespace attn_bwd {
@@ -163,10 +164,34 @@ __device__ __forceinline__ void softmax_grad(uint32_t t_row, uint8_t* rp, uint8_
   }
 }
 
+// One work item = one (key tile jt, batch b, head h): the CTA keeps K_j / V_j in shared memory,
+// sweeps the query tiles jt..nq-1 and leaves dK_j / dV_j.  Items are numbered heaviest first
+// (jt = 0 has the most query tiles) and CTA c takes items c, c + grid, c + 2 grid, ...
+struct Item {
+  int jt, b, h, n_iter;
+};
+__device__ __forceinline__ Item make_item(const Params& p, int idx, int nq) {
+  const int bh = p.B * p.H;
+  Item w;
+  w.jt = idx / bh;
+  const int r = idx - w.jt * bh;
+  w.b = r / p.H;
+  w.h = r - w.b * p.H;
+  w.n_iter = nq - w.jt;
+  return w;
+}
+
+// Persistent: grid = min(items, SMs), one CTA per SM.  Every barrier runs on a counter that keeps
+// counting across items (g = query-tile iterations, k = items), so an item boundary costs no
+// barrier re-initialisation, no TMEM allocation and no CTA launch: the next item's first Q / dO
+// tile is requested while the current item's last MMAs run, K / V follow as soon as those MMAs
+// have retired (dkv_full), and the first score tile is issued while the softmax-grad warps still
+// convert dK / dV.  The one-CTA-per-item version spent 8 300 of 41 000 cycles per heaviest item
+// (and of 12 000 per lightest) outside its main loop.
 template <bool DROP>
 __global__ void __launch_bounds__(THREADS, 1)
 bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
-           const __grid_constant__ CUtensorMap tmDQKV, const __grid_constant__ CUtensorMap tmDQ,
+           const __grid_constant__ CUtensorMap tmDKV, const __grid_constant__ CUtensorMap tmDQ,
            const Params p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
@@ -177,27 +202,26 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
   uint64_t* q_empty = q_full + NQ;     // [NQ]
   uint64_t* s_full = q_empty + NQ;
   uint64_t* pds_full = s_full + 1;
-  uint64_t* dq_full = pds_full + 1;    // [2]: dQ_i accumulates in TMEM buffer i&1 and is drained
+  uint64_t* dq_full = pds_full + 1;    // [2]: dQ_g accumulates in TMEM buffer g&1 and is drained
                                        // one iteration later, behind the next tile's softmax-grad
-  uint64_t* dkv_full = dq_full + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(dkv_full + 1);
+  uint64_t* dkv_full = dq_full + 2;    // the item's last MMA has retired: dK / dV are complete and
+                                       // K / V / P / dS in shared memory are no longer read
+  uint64_t* dkv_drained = dkv_full + 1;  // 8 warps: dK / dV have left TMEM
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(dkv_drained + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nq = (p.T + BQ - 1) / BQ;
-  const int jt = blockIdx.x;  // kv tile; tile 0 has the most query tiles and is scheduled first
-  const int h = blockIdx.y, b = blockIdx.z;
-  const int kv0 = jt * BKV;
   const int d = p.H * HD;
-  const int n_iter = nq - jt;
+  const int total = nq * p.B * p.H;
+  const int first = blockIdx.x, stride = gridDim.x;
 
-  // The TMA thread initialises the barriers itself and issues the first loads (K_j, V_j, Q/dO of
-  // the first query tile) BEFORE the CTA-wide sync: TMEM allocation and the barrier round trip
-  // then overlap the ~1 us load latency instead of preceding it (one CTA per SM, so nothing else
-  // would hide it).
+  // The TMA thread initialises the barriers itself and issues the first item's loads (K_j, V_j,
+  // Q / dO of the first query tile) BEFORE the CTA-wide sync: TMEM allocation and the barrier
+  // round trip then overlap the ~1 us load latency instead of preceding it.
   if (warp == 8 && lane == 0) {
     tma_prefetch_desc(&tmQKV);
     tma_prefetch_desc(&tmDO);
-    tma_prefetch_desc(&tmDQKV);
+    tma_prefetch_desc(&tmDKV);
     tma_prefetch_desc(&tmDQ);
     mbar_init(kv_full, 1);
     for (int s = 0; s < NQ; ++s) {
@@ -209,14 +233,16 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
     mbar_init(&dq_full[0], 1);
     mbar_init(&dq_full[1], 1);
     mbar_init(dkv_full, 1);
+    mbar_init(dkv_drained, 8);
     fence_barrier_init();
     pdl_wait();  // qkv / dO come from the previous kernels of the stream
+    const Item w = make_item(p, first, nq);
     mbar_expect_tx(kv_full, 2 * TILE);
-    tma_load_3d(smem + OFF_K, &tmQKV, kv_full, d + h * HD, kv0, b);
-    tma_load_3d(smem + OFF_V, &tmQKV, kv_full, 2 * d + h * HD, kv0, b);
+    tma_load_3d(smem + OFF_K, &tmQKV, kv_full, d + w.h * HD, w.jt * BKV, w.b);
+    tma_load_3d(smem + OFF_V, &tmQKV, kv_full, 2 * d + w.h * HD, w.jt * BKV, w.b);
     mbar_expect_tx(&q_full[0], 2 * TILE);
-    tma_load_3d(smem + OFF_Q, &tmQKV, &q_full[0], h * HD, jt * BQ, b);
-    tma_load_3d(smem + OFF_DO, &tmDO, &q_full[0], h * HD, jt * BQ, b);
+    tma_load_3d(smem + OFF_Q, &tmQKV, &q_full[0], w.h * HD, w.jt * BQ, w.b);
+    tma_load_3d(smem + OFF_DO, &tmDO, &q_full[0], w.h * HD, w.jt * BQ, w.b);
   }
   if (warp == 9) {
     tmem_alloc(tmem_slot, TMEM_COLS);
@@ -231,16 +257,29 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
   if (warp == 8) {
     // ------------------------------- TMA producer -------------------------------------------
     if (lane == 0) {
-      for (int it = 1; it < n_iter; ++it) {  // tile 0 was requested in the prologue
-        const int st = it % NQ;
-        const uint32_t ph = uint32_t(it / NQ) & 1u;
-        const int q0 = (jt + it) * BQ;
-        stamp(p, 2, it, 0);
-        mbar_wait(&q_empty[st], ph ^ 1u);
-        stamp(p, 2, it, 1);
-        mbar_expect_tx(&q_full[st], 2 * TILE);
-        tma_load_3d(smem + OFF_Q + st * TILE, &tmQKV, &q_full[st], h * HD, q0, b);
-        tma_load_3d(smem + OFF_DO + st * TILE, &tmDO, &q_full[st], h * HD, q0, b);
+      int g = 0;
+      for (int idx = first, k = 0; idx < total; idx += stride, ++k) {
+        const Item w = make_item(p, idx, nq);
+        for (int it = 0; it < w.n_iter; ++it, ++g) {
+          if (k == 0 && it == 0) continue;  // requested in the prologue
+          const int st = g % NQ;
+          const uint32_t ph = uint32_t(g / NQ) & 1u;
+          const int q0 = (w.jt + it) * BQ;
+          stamp(p, 2, g, 0);
+          mbar_wait(&q_empty[st], ph ^ 1u);
+          stamp(p, 2, g, 1);
+          mbar_expect_tx(&q_full[st], 2 * TILE);
+          tma_load_3d(smem + OFF_Q + st * TILE, &tmQKV, &q_full[st], w.h * HD, q0, w.b);
+          tma_load_3d(smem + OFF_DO + st * TILE, &tmDO, &q_full[st], w.h * HD, q0, w.b);
+          if (it == 0) {
+            // The item's first Q / dO tile is on its way; K / V have a single buffer and wait for
+            // the previous item's last MMA.
+            mbar_wait(dkv_full, uint32_t(k - 1) & 1u);
+            mbar_expect_tx(kv_full, 2 * TILE);
+            tma_load_3d(smem + OFF_K, &tmQKV, kv_full, d + w.h * HD, w.jt * BKV, w.b);
+            tma_load_3d(smem + OFF_V, &tmQKV, kv_full, 2 * d + w.h * HD, w.jt * BKV, w.b);
+          }
+        }
       }
     }
   } else if (warp == 9) {
@@ -250,12 +289,12 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
       constexpr uint32_t id_t = umma_idesc_bf16(128, 64, true, true);     // P^T dO, dS^T Q
       constexpr uint32_t id_dq = umma_idesc_bf16(128, 64, false, true);   // dS K
       const uint32_t sK = smem_u32(smem + OFF_K), sV = smem_u32(smem + OFF_V);
-      auto issue_scores = [&](int it) {  // S = Q K^T and dP = dO V^T of query tile `it`
-        const int st = it % NQ;
+      auto issue_scores = [&](int g) {  // S = Q K^T and dP = dO V^T of iteration g
+        const int st = g % NQ;
         const uint32_t sQ = smem_u32(smem + OFF_Q + st * TILE);
         const uint32_t sDO = smem_u32(smem + OFF_DO + st * TILE);
-        mbar_wait(&q_full[st], uint32_t(it / NQ) & 1u);
-        stamp(p, 1, it, 0);
+        mbar_wait(&q_full[st], uint32_t(g / NQ) & 1u);
+        stamp(p, 1, g, 0);
         tc_fence_after_sync();
 #pragma unroll
         for (int k = 0; k < HD / 16; ++k)
@@ -267,41 +306,48 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
                   umma_smem_desc(sV + k * 32, 0, 1024), id_s, k > 0);
         umma_commit(s_full);
       };
-      mbar_wait(kv_full, 0);
-      issue_scores(0);
-      for (int it = 0; it < n_iter; ++it) {
-        const int st = it % NQ;
-        const uint32_t sQ = smem_u32(smem + OFF_Q + st * TILE);
-        const uint32_t sDO = smem_u32(smem + OFF_DO + st * TILE);
-        const uint32_t sP = smem_u32(smem + OFF_P);
-        const uint32_t sDS = smem_u32(smem + OFF_DS + (it & 1) * PDS_BYTES);
-        stamp(p, 1, it, 1);
-        mbar_wait(pds_full, it & 1);  // P_it / dS_it are in smem, S_it / dP_it have left TMEM
-        stamp(p, 1, it, 2);
-        tc_fence_after_sync();
-        // dV += P^T dO   (A, B both MN-major: 16 q-rows = 2048 B per K step).  First in the queue:
-        // it is the only reader of the single P buffer.
+      int g = 0;
+      for (int idx = first, item = 0; idx < total; idx += stride, ++item) {
+        const int n_iter = nq - idx / (p.B * p.H);
+        mbar_wait(kv_full, uint32_t(item) & 1u);
+        // S / dP of the previous item were read before its last pds_full, so the first score tile
+        // of this item may be issued while the other warps are still in the previous epilogue.
+        issue_scores(g);
+        for (int it = 0; it < n_iter; ++it, ++g) {
+          const int st = g % NQ;
+          const uint32_t sQ = smem_u32(smem + OFF_Q + st * TILE);
+          const uint32_t sDO = smem_u32(smem + OFF_DO + st * TILE);
+          const uint32_t sP = smem_u32(smem + OFF_P);
+          const uint32_t sDS = smem_u32(smem + OFF_DS + (g & 1) * PDS_BYTES);
+          stamp(p, 1, g, 1);
+          mbar_wait(pds_full, uint32_t(g) & 1u);  // P_g / dS_g are in smem, S_g / dP_g have left TMEM
+          if (it == 0 && item > 0) mbar_wait(dkv_drained, uint32_t(item - 1) & 1u);
+          stamp(p, 1, g, 2);
+          tc_fence_after_sync();
+          // dV += P^T dO   (A, B both MN-major: 16 q-rows = 2048 B per K step).  First in the
+          // queue: it is the only reader of the single P buffer.
 #pragma unroll
-        for (int k = 0; k < BQ / 16; ++k)
-          umma_ss(tmem + COL_DV, umma_smem_desc(sP + k * 2048, TILE, 1024),
-                  umma_smem_desc(sDO + k * 2048, TILE, 1024), id_t, (it > 0) || (k > 0));
-        if (it + 1 < n_iter) issue_scores(it + 1);  // the softmax-grad warps wait on these
-        // dK += dS^T Q
+          for (int k = 0; k < BQ / 16; ++k)
+            umma_ss(tmem + COL_DV, umma_smem_desc(sP + k * 2048, TILE, 1024),
+                    umma_smem_desc(sDO + k * 2048, TILE, 1024), id_t, (it > 0) || (k > 0));
+          if (it + 1 < n_iter) issue_scores(g + 1);  // the softmax-grad warps wait on these
+          // dK += dS^T Q
 #pragma unroll
-        for (int k = 0; k < BQ / 16; ++k)
-          umma_ss(tmem + COL_DK, umma_smem_desc(sDS + k * 2048, TILE, 1024),
-                  umma_smem_desc(sQ + k * 2048, TILE, 1024), id_t, (it > 0) || (k > 0));
-        umma_commit(&q_empty[st]);
-        // dQ_i = dS K  (A K-major over 128 kv = two 64-wide regions; B = K_j MN-major)
+          for (int k = 0; k < BQ / 16; ++k)
+            umma_ss(tmem + COL_DK, umma_smem_desc(sDS + k * 2048, TILE, 1024),
+                    umma_smem_desc(sQ + k * 2048, TILE, 1024), id_t, (it > 0) || (k > 0));
+          umma_commit(&q_empty[st]);
+          // dQ_g = dS K  (A K-major over 128 kv = two 64-wide regions; B = K_j MN-major)
 #pragma unroll
-        for (int k = 0; k < BKV / 16; ++k)
-          umma_ss(tmem + COL_DQ + (it & 1) * HD,
-                  umma_smem_desc(sDS + (k >> 2) * TILE + (k & 3) * 32, 0, 1024),
-                  umma_smem_desc(sK + k * 2048, TILE, 1024), id_dq, k > 0);
-        umma_commit(&dq_full[it & 1]);
-        stamp(p, 1, it, 3);
+          for (int k = 0; k < BKV / 16; ++k)
+            umma_ss(tmem + COL_DQ + (g & 1) * HD,
+                    umma_smem_desc(sDS + (k >> 2) * TILE + (k & 3) * 32, 0, 1024),
+                    umma_smem_desc(sK + k * 2048, TILE, 1024), id_dq, k > 0);
+          umma_commit(&dq_full[g & 1]);
+          stamp(p, 1, g, 3);
+        }
+        umma_commit(dkv_full);
       }
-      umma_commit(dkv_full);
     }
   } else {
     // ------------------------------- softmax-grad / epilogue warps --------------------------
@@ -310,179 +356,181 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
     const int quarter = warp & 3, half = warp >> 2;
     const int r = quarter * 32 + lane;  // 0..127
     const uint32_t lane_base = uint32_t(quarter * 32) << 16;
-    const uint8_t* kmask = p.key_mask ? p.key_mask + size_t(b) * p.T : nullptr;
-    const size_t stat_base = (size_t(b) * p.H + h) * p.T;
+    // This warp's 4 KB staging slice: 32 rows of 128 bytes, swizzled.  It carries the warp's
+    // 32 x 32 fp32 slice of every dQ tile and, at the end of an item, its 32 x 64 bf16 slice of
+    // dV (half 0) or dK (half 1).  Each warp issues and tracks its own bulk copies, so the slice
+    // needs no CTA-wide synchronisation.
+    uint8_t* stage = smem + OFF_DQS + half * TILE + quarter * 4096;
 
-    // dQ_i: TMEM -> registers -> this warp's 32-row x 32-column fp32 slice of a swizzled staging
-    // tile -> ONE TMA reduce-add per warp into dq32.  (Per-thread red.global.add.v4 of the same
-    // data was the single largest cost of this kernel: 453 MB of 16-byte L2 reductions per layer,
-    // 76 us of 425 at B = 32; the TMA unit hands L2 whole 128-byte lines.)  Called one iteration
-    // late, so the MMAs that precede dq_full(i) are never waited for; each warp owns its slice and
-    // its own bulk group, so no CTA-wide barrier is involved.  Rows past T are clipped by the map.
-    uint8_t* dq_stage = smem + OFF_DQS + half * TILE + quarter * 4096;
-    auto drain_dq = [&](int i) {
-      mbar_wait(&dq_full[i & 1], (i >> 1) & 1);
-      tc_fence_after_sync();
-      uint32_t v[32];
-      tmem_ld_32x32b_x32(tmem + COL_DQ + (i & 1) * HD + lane_base + half * 32, v);
-      tmem_ld_wait();
-      tc_fence_before_sync();
-      if (lane == 0) tma_store_wait_read<0>();  // the previous slice has left shared memory
-      __syncwarp();
+    int g = 0;
+    for (int idx = first, item = 0; idx < total; idx += stride, ++item) {
+      const Item w = make_item(p, idx, nq);
+      const int jt = w.jt, b = w.b, h = w.h, n_iter = w.n_iter;
+      const int kv0 = jt * BKV;
+      const uint8_t* kmask = p.key_mask ? p.key_mask + size_t(b) * p.T : nullptr;
+      const size_t stat_base = (size_t(b) * p.H + h) * p.T;
+
+      // dQ of iteration gi (query tile qt): TMEM -> registers -> the staging slice -> ONE TMA
+      // reduce-add per warp into dq32.  (Per-thread red.global.add.v4 of the same data was the
+      // single largest cost of this kernel: 453 MB of 16-byte L2 reductions per layer, 76 us of
+      // 425 at B = 32; the TMA unit hands L2 whole 128-byte lines.)  Called one iteration late, so
+      // the MMAs that precede dq_full(gi) are never waited for.  Rows past T are clipped by the map.
+      auto drain_dq = [&](int gi, int qt) {
+        mbar_wait(&dq_full[gi & 1], uint32_t(gi >> 1) & 1u);
+        tc_fence_after_sync();
+        uint32_t v[32];
+        tmem_ld_32x32b_x32(tmem + COL_DQ + (gi & 1) * HD + lane_base + half * 32, v);
+        tmem_ld_wait();
+        tc_fence_before_sync();
+        if (lane == 0) tma_store_wait_read<0>();  // the previous slice has left shared memory
+        __syncwarp();
 #pragma unroll
-      for (int q = 0; q < 8; ++q)
-        *reinterpret_cast<uint4*>(dq_stage + swizzle128(lane * 128 + q * 16)) =
-            make_uint4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
-      fence_proxy_async_smem();
-      __syncwarp();
-      if (lane == 0) {
-        // Deterministic mode: the key tiles add into a query tile in ascending order.  This CTA
-        // (key tile jt) waits until jt earlier contributions to this 32x32 slice have landed and
-        // publishes its own once the reduction has completed.  CTAs with a smaller key tile have
-        // a smaller block index, so they are resident or done: the wait cannot deadlock.
-        int* turn = nullptr;
-        if (p.turn != nullptr) {
-          turn = p.turn + ((size_t(b) * p.H + h) * nq + (jt + i)) * 8 + (warp & 7);
-          const unsigned long long t0 = global_timer_ns();
-          int seen;
-          do {
-            asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(seen) : "l"(turn) : "memory");
-            if (seen != jt && global_timer_ns() - t0 > B200_MBAR_TIMEOUT_NS) mbar_timeout_trap();
-          } while (seen != jt);
+        for (int q = 0; q < 8; ++q)
+          *reinterpret_cast<uint4*>(stage + swizzle128(lane * 128 + q * 16)) =
+              make_uint4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+          // Deterministic mode: the key tiles add into a query tile in ascending order.  This item
+          // (key tile jt) waits until jt earlier contributions to this 32x32 slice have landed and
+          // publishes its own once the reduction has completed.  An item with a smaller key tile
+          // has a smaller index; every CTA is resident and walks its items in ascending index
+          // order, so the unfinished item with the smallest index is always running and never
+          // waits: the chain cannot deadlock.
+          int* turn = nullptr;
+          if (p.turn != nullptr) {
+            turn = p.turn + ((size_t(b) * p.H + h) * nq + qt) * 8 + (warp & 7);
+            const unsigned long long t0 = global_timer_ns();
+            int seen;
+            do {
+              asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(seen) : "l"(turn) : "memory");
+              if (seen != jt && global_timer_ns() - t0 > B200_MBAR_TIMEOUT_NS) mbar_timeout_trap();
+            } while (seen != jt);
+          }
+          tma_reduce_add_3d(&tmDQ, stage, h * HD + half * 32, qt * BQ + quarter * 32, b);
+          tma_store_commit();
+          if (turn != nullptr) {
+            tma_store_wait<0>();  // the reduction has been performed, not merely read from smem
+            __threadfence();
+            asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(turn), "r"(jt + 1) : "memory");
+          }
         }
-        tma_reduce_add_3d(&tmDQ, dq_stage, h * HD + half * 32, (jt + i) * BQ + quarter * 32, b);
-        tma_store_commit();
-        if (turn != nullptr) {
-          tma_store_wait<0>();  // the reduction has been performed, not merely read from smem
-          __threadfence();
-          asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(turn), "r"(jt + 1) : "memory");
+      };
+
+      // Row statistics of the NEXT query tile are requested before this tile's math so their
+      // global-memory latency is never exposed.
+      float lse_next = 0.f, dsum_next = 0.f;
+      {
+        const int qrow0 = jt * BQ + r;
+        if (qrow0 < p.T) {
+          lse_next = p.lse[stat_base + qrow0];
+          dsum_next = p.dsum[stat_base + qrow0];
         }
       }
-    };
+      for (int it = 0; it < n_iter; ++it, ++g) {
+        const int qt = jt + it;
+        const int q0 = qt * BQ;
+        const int qrow = q0 + r;
+        const bool row_ok = qrow < p.T;
+        const float lse2 = row_ok ? lse_next * 1.4426950408889634f : 0.f;
+        const float dsum = row_ok ? dsum_next : 0.f;
+        if (it + 1 < n_iter && qrow + BQ < p.T) {
+          lse_next = p.lse[stat_base + qrow + BQ];
+          dsum_next = p.dsum[stat_base + qrow + BQ];
+        }
+        const bool dead_row = !row_ok || (lse2 == -INFINITY);
+        // warp-uniform on purpose: the variants contain .sync.aligned TMEM loads
+        const int mode = (kmask != nullptr || __any_sync(0xffffffffu, dead_row) != 0)
+                             ? kGeneral
+                             : (it == 0 ? kDiag : kNoMask);
 
-    // Row statistics of the NEXT query tile are requested before this tile's math so their
-    // global-memory latency is never exposed.
-    float lse_next = 0.f, dsum_next = 0.f;
-    {
-      const int qrow0 = jt * BQ + r;
-      if (qrow0 < p.T) {
-        lse_next = p.lse[stat_base + qrow0];
-        dsum_next = p.dsum[stat_base + qrow0];
-      }
-    }
-    for (int it = 0; it < n_iter; ++it) {
-      const int qt = jt + it;
-      const int q0 = qt * BQ;
-      const int qrow = q0 + r;
-      const bool row_ok = qrow < p.T;
-      const float lse2 = row_ok ? lse_next * 1.4426950408889634f : 0.f;
-      const float dsum = row_ok ? dsum_next : 0.f;
-      if (it + 1 < n_iter && qrow + BQ < p.T) {
-        lse_next = p.lse[stat_base + qrow + BQ];
-        dsum_next = p.dsum[stat_base + qrow + BQ];
-      }
-      const bool dead_row = !row_ok || (lse2 == -INFINITY);
-      // warp-uniform on purpose: the variants contain .sync.aligned TMEM loads
-      const int mode = (kmask != nullptr || __any_sync(0xffffffffu, dead_row) != 0)
-                           ? kGeneral
-                           : (it == 0 ? kDiag : kNoMask);
-
-      if (threadIdx.x == 0) stamp(p, 0, it, 0);
-      mbar_wait(s_full, it & 1);
-      tc_fence_after_sync();
-      if (threadIdx.x == 0) stamp(p, 0, it, 1);
-      uint8_t* rp = smem + OFF_P + half * TILE;
-      uint8_t* rd = smem + OFF_DS + (it & 1) * PDS_BYTES + half * TILE;
-      const uint32_t t_row = tmem + lane_base + half * 64;
-      const uint64_t mask_base =
-          DROP ? (uint64_t((size_t(b) * p.H + h) * p.T + qrow) * uint64_t(p.t_pad) +
-                  uint64_t(kv0 + half * 64))
-               : 0;
-      if (mode == kNoMask)
-        softmax_grad<kNoMask, DROP>(t_row, rp, rd, r, kv0 + half * 64, qrow, p.T, kmask, dead_row,
+        if (threadIdx.x == 0) stamp(p, 0, g, 0);
+        mbar_wait(s_full, uint32_t(g) & 1u);
+        tc_fence_after_sync();
+        if (threadIdx.x == 0) stamp(p, 0, g, 1);
+        uint8_t* rp = smem + OFF_P + half * TILE;
+        uint8_t* rd = smem + OFF_DS + (g & 1) * PDS_BYTES + half * TILE;
+        const uint32_t t_row = tmem + lane_base + half * 64;
+        const uint64_t mask_base =
+            DROP ? (uint64_t((size_t(b) * p.H + h) * p.T + qrow) * uint64_t(p.t_pad) +
+                    uint64_t(kv0 + half * 64))
+                 : 0;
+        if (mode == kNoMask)
+          softmax_grad<kNoMask, DROP>(t_row, rp, rd, r, kv0 + half * 64, qrow, p.T, kmask, dead_row,
+                                      p.scale_log2, p.scale, lse2, dsum, quarter, half, lane,
+                                      p.drop, mask_base);
+        else if (mode == kDiag)
+          softmax_grad<kDiag, DROP>(t_row, rp, rd, r, kv0 + half * 64, qrow, p.T, kmask, dead_row,
                                     p.scale_log2, p.scale, lse2, dsum, quarter, half, lane, p.drop,
                                     mask_base);
-      else if (mode == kDiag)
-        softmax_grad<kDiag, DROP>(t_row, rp, rd, r, kv0 + half * 64, qrow, p.T, kmask, dead_row,
-                                  p.scale_log2, p.scale, lse2, dsum, quarter, half, lane, p.drop,
-                                  mask_base);
-      else
-        softmax_grad<kGeneral, DROP>(t_row, rp, rd, r, kv0 + half * 64, qrow, p.T, kmask, dead_row,
-                                     p.scale_log2, p.scale, lse2, dsum, quarter, half, lane,
-                                     p.drop, mask_base);
-      fence_proxy_async_smem();
+        else
+          softmax_grad<kGeneral, DROP>(t_row, rp, rd, r, kv0 + half * 64, qrow, p.T, kmask,
+                                       dead_row, p.scale_log2, p.scale, lse2, dsum, quarter, half,
+                                       lane, p.drop, mask_base);
+        fence_proxy_async_smem();
+        tc_fence_before_sync();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(pds_full);
+        if (threadIdx.x == 0) stamp(p, 0, g, 2);
+
+        if (it > 0) drain_dq(g - 1, qt - 1);
+        if (threadIdx.x == 0) stamp(p, 0, g, 3);
+      }
+      drain_dq(g - 1, jt + n_iter - 1);
+
+      // dV (warps 0-3) / dK (warps 4-7): 32 kv rows x 64 columns per warp, TMEM -> bf16 -> the
+      // staging slice -> one TMA store per warp.
+      mbar_wait(dkv_full, uint32_t(item) & 1u);
+      tc_fence_after_sync();
+      uint32_t packed[32];
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32b_x32(tmem + (half == 0 ? COL_DV : COL_DK) + lane_base + c * 32, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int u = 0; u < 16; ++u)
+          packed[c * 16 + u] =
+              pack_bf16x2(__uint_as_float(v[2 * u]), __uint_as_float(v[2 * u + 1]));
+      }
       tc_fence_before_sync();
+      if (lane == 0) tma_store_wait_read<0>();  // the last dQ slice has left the staging slice
       __syncwarp();
-      if (lane == 0) mbar_arrive(pds_full);
-      if (threadIdx.x == 0) stamp(p, 0, it, 2);
-
-      if (it > 0) drain_dq(it - 1);
-      if (threadIdx.x == 0) stamp(p, 0, it, 3);
-    }
-    drain_dq(n_iter - 1);
-    if (lane == 0) tma_store_wait_read<0>();  // staging must outlive the last reduction's read
-
-    // dV, dK: TMEM -> bf16 -> swizzled staging (P / dS buffers are free now) -> TMA store.
-    // Each warp converts its 32-column half of both accumulators.
-    mbar_wait(dkv_full, 0);
-    tc_fence_after_sync();
+      if (lane == 0) mbar_arrive(dkv_drained);  // the next item may overwrite dK / dV in TMEM
 #pragma unroll
-    for (int which = 0; which < 2; ++which) {
-      uint8_t* stage = smem + (which == 0 ? OFF_P : OFF_DS);
-      const uint32_t col_base = which == 0 ? COL_DV : COL_DK;
-      uint32_t v[32];
-      tmem_ld_32x32b_x32(tmem + col_base + lane_base + half * 32, v);
-      tmem_ld_wait();
-#pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        uint32_t w[4];
-#pragma unroll
-        for (int u = 0; u < 4; ++u)
-          w[u] = pack_bf16x2(__uint_as_float(v[q * 8 + 2 * u]), __uint_as_float(v[q * 8 + 2 * u + 1]));
-        *reinterpret_cast<uint4*>(stage + swizzle128(r * 128 + (half * 4 + q) * 16)) =
-            make_uint4(w[0], w[1], w[2], w[3]);
+      for (int q = 0; q < 8; ++q)
+        *reinterpret_cast<uint4*>(stage + swizzle128(lane * 128 + q * 16)) =
+            make_uint4(packed[4 * q], packed[4 * q + 1], packed[4 * q + 2], packed[4 * q + 3]);
+      fence_proxy_async_smem();
+      __syncwarp();
+      const int col0 = (half == 0 ? 2 * d : d) + h * HD;
+      if (lane == 0) {
+        tma_store_3d(&tmDKV, stage, col0, kv0 + quarter * 32, b);
+        tma_store_commit();
       }
-    }
-    tc_fence_before_sync();
-    fence_proxy_async_smem();
-    named_bar_sync(1, 256);
-    if (p.dbias != nullptr) {
-      // qkv_proj's bias gradient is the column sum of dqkv: take the k and v thirds from the two
-      // bf16 tiles just staged (warp w: rows 16w..16w+15, lane l: columns 2l, 2l+1; conflict-free
-      // in the swizzled layout), combine the eight warps through the idle second dS buffer, and
-      // add 128 values per CTA to global memory.  Rows past T hold exact zeros.  The q third comes
-      // from dq_convert_kernel.
-      float* red = reinterpret_cast<float*>(smem + OFF_DS + PDS_BYTES);  // [8][2][64]
-#pragma unroll
-      for (int which = 0; which < 2; ++which) {
-        const uint8_t* stage = smem + (which == 0 ? OFF_P : OFF_DS);
+      if (p.dbias != nullptr) {
+        // qkv_proj's bias gradient is the column sum of dqkv: the k and v thirds come from the
+        // bf16 tile just staged (lane l: columns 2l, 2l+1 over the warp's 32 rows; conflict-free
+        // in the swizzled layout).  Rows past T hold exact zeros.  The q third comes from
+        // dq_convert_kernel.
         float s0 = 0.f, s1 = 0.f;
+#pragma unroll 1
+        for (int r8 = 0; r8 < 32; r8 += 8) {
 #pragma unroll
-        for (int rr = 0; rr < 16; ++rr) {
-          const uint32_t row = uint32_t(warp * 16 + rr);
-          const uint32_t off = row * 128u + ((uint32_t(lane >> 2) ^ (row & 7u)) << 4) +
-                               (uint32_t(lane & 3) << 2);
-          const float2 f = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(stage + off));
-          s0 += f.x;
-          s1 += f.y;
+          for (int j = 0; j < 8; ++j) {
+            const uint32_t off = uint32_t(r8 + j) * 128u +
+                                 ((uint32_t(lane >> 2) ^ uint32_t(j)) << 4) +
+                                 (uint32_t(lane & 3) << 2);
+            const float2 f = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(stage + off));
+            s0 += f.x;
+            s1 += f.y;
+          }
         }
-        *reinterpret_cast<float2*>(red + (warp * 2 + which) * 64 + 2 * lane) = make_float2(s0, s1);
-      }
-      named_bar_sync(1, 256);
-      if (threadIdx.x < 128) {
-        const int which = threadIdx.x >> 6, col = threadIdx.x & 63;
-        float t = 0.f;
-#pragma unroll
-        for (int w = 0; w < 8; ++w) t += red[(w * 2 + which) * 64 + col];
-        atomicAdd(p.dbias + (which == 0 ? 2 * d : d) + h * HD + col, t);
+        atomicAdd(p.dbias + col0 + 2 * lane, s0);
+        atomicAdd(p.dbias + col0 + 2 * lane + 1, s1);
       }
     }
-    if (threadIdx.x == 0) {
-      tma_store_3d(&tmDQKV, smem + OFF_P, 2 * d + h * HD, kv0, b);   // dV
-      tma_store_3d(&tmDQKV, smem + OFF_DS, d + h * HD, kv0, b);      // dK
-      tma_store_commit();
-      tma_store_wait_read<0>();  // smem may go once it has been read; the writes land on their own
-    }
+    if (lane == 0) tma_store_wait_read<0>();  // shared memory must outlive the last store's read
   }
 
   tc_fence_before_sync();
@@ -575,11 +623,27 @@ __global__ void dq_convert_kernel(const float* __restrict__ dq32, __nv_bfloat16*
 
 using namespace b200;
 
-extern "C" size_t llmtrain_b200_attention_bwd_scratch_bytes(int B, int T, int H, int head_dim) {
-  // fp32 dQ accumulator [B,T,d], D [B,H,T], and the deterministic mode's turn counters [B,H,nq,8]
+namespace {
+// Scratch layout (every region 256-byte aligned): fp32 dQ accumulator [B,T,d] | D [B,H,T] (dropout
+// path) | the deterministic mode's turn counters [B,H,nq,8] | statistics [B,H,nq*128] float2.
+struct BwdScratch {
+  size_t dq, dsum, turn, stats, total;
+};
+inline size_t up256(size_t x) { return (x + 255) & ~size_t(255); }
+inline BwdScratch bwd_scratch(int B, int T, int H, int head_dim) {
   const size_t nq = size_t((T + 127) / 128);
-  return size_t(B) * T * H * head_dim * sizeof(float) + size_t(B) * H * T * sizeof(float) +
-         size_t(B) * H * nq * 8 * sizeof(int);
+  BwdScratch s;
+  s.dq = 0;
+  s.dsum = up256(size_t(B) * T * H * head_dim * sizeof(float));
+  s.turn = s.dsum + up256(size_t(B) * H * T * sizeof(float));
+  s.stats = s.turn + up256(size_t(B) * H * nq * 8 * sizeof(int));
+  s.total = s.stats + up256(size_t(B) * H * nq * 128 * sizeof(float2));
+  return s;
+}
+}  // namespace
+
+extern "C" size_t llmtrain_b200_attention_bwd_scratch_bytes(int B, int T, int H, int head_dim) {
+  return bwd_scratch(B, T, H, head_dim).total;
 }
 
 // qkv [B,T,3d], out/dout [B,T,d] bf16, lse [B,H,T]  ->  dqkv [B,T,3d] bf16.
@@ -589,77 +653,106 @@ static int attention_bwd_impl(const void* qkv, const void* out, const void* dout
                               const DropoutParams& drop, float* dbias, float softmax_scale,
                               cudaStream_t stream) {
   namespace ab = attn_bwd;
+  namespace at = attn_bwd_t;
   B200_REQUIRE(head_dim == ab::HD, "attention_bwd: specialised for head_dim 64");
   B200_REQUIRE(B > 0 && T > 0 && H > 0, "attention_bwd: empty problem");
   const int d = H * ab::HD;
-  const size_t dq_bytes = size_t(B) * T * d * sizeof(float);
-  B200_REQUIRE(scratch_bytes >= llmtrain_b200_attention_bwd_scratch_bytes(B, T, H, head_dim),
-               "attention_bwd: scratch too small");
+  const BwdScratch lay = bwd_scratch(B, T, H, head_dim);
+  B200_REQUIRE(scratch_bytes >= lay.total, "attention_bwd: scratch too small");
   B200_REQUIRE((reinterpret_cast<uintptr_t>(scratch) & 255) == 0, "attention_bwd: scratch alignment");
-  float* dq32 = static_cast<float*>(scratch);
-  float* dsum = reinterpret_cast<float*>(static_cast<uint8_t*>(scratch) + dq_bytes);
+  uint8_t* base = static_cast<uint8_t*>(scratch);
+  float* dq32 = reinterpret_cast<float*>(base + lay.dq);
+  float* dsum = reinterpret_cast<float*>(base + lay.dsum);
+  float2* stats = reinterpret_cast<float2*>(base + lay.stats);
+  const size_t dq_bytes = size_t(B) * T * d * sizeof(float);
   B200_CHECK_CUDA(cudaMemsetAsync(dq32, 0, dq_bytes, stream));
 
+  // Probability dropout regenerates its keep mask along key positions, which only the
+  // row-oriented kernel walks; everything else takes the key-row-oriented kernel.
+  const bool with_dropout = drop.threshold != 0;
   const int rows = B * T;
-  B200_LAUNCH((ab::dsum_kernel), ceil_div(rows * H * 8, 256), 256, 0, stream,
-              static_cast<const __nv_bfloat16*>(dout), static_cast<const __nv_bfloat16*>(out), dsum,
-              B, T, H);
+  const int nq = ceil_div(T, ab::BQ);
+  const int t_stat = nq * ab::BQ;
+  if (with_dropout) {
+    B200_LAUNCH((ab::dsum_kernel), ceil_div(rows * H * 8, 256), 256, 0, stream,
+                static_cast<const __nv_bfloat16*>(dout), static_cast<const __nv_bfloat16*>(out),
+                dsum, B, T, H);
+  } else {
+    const long long lanes = (long long)B * t_stat * H * 8;
+    B200_LAUNCH((at::stats_kernel), unsigned(ceil_div(lanes, 256LL)), 256, 0, stream,
+                static_cast<const __nv_bfloat16*>(dout), static_cast<const __nv_bfloat16*>(out), lse,
+                stats, B, T, H, t_stat);
+  }
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
 
-  CUtensorMap tQKV, tDO, tDQKV;
+  CUtensorMap tQKV, tDO, tDKV, tDQ;
   if (make_tmap_3d(&tQKV, static_cast<const __nv_bfloat16*>(qkv), B, T, 3 * d, 3 * d,
                    uint64_t(T) * 3 * d, 128, ab::HD, Swz::B128)) return 1;
   if (make_tmap_3d(&tDO, static_cast<const __nv_bfloat16*>(dout), B, T, d, d, uint64_t(T) * d, 128,
                    ab::HD, Swz::B128)) return 1;
-  if (make_tmap_3d(&tDQKV, static_cast<__nv_bfloat16*>(dqkv), B, T, 3 * d, 3 * d,
-                   uint64_t(T) * 3 * d, 128, ab::HD, Swz::B128)) return 1;
-
-  CUtensorMap tDQ;  // fp32 accumulator [B, T, d], boxes of 32 rows x 32 columns (128-byte rows)
+  // dK / dV leave in per-warp boxes of 32 kv rows x 64 columns
+  if (make_tmap_3d(&tDKV, static_cast<__nv_bfloat16*>(dqkv), B, T, 3 * d, 3 * d,
+                   uint64_t(T) * 3 * d, 32, ab::HD, Swz::B128)) return 1;
+  // fp32 accumulator [B, T, d], boxes of 32 rows x 32 columns (128-byte rows)
   if (make_tmap_3d(&tDQ, dq32, B, T, d, d, uint64_t(T) * d, 32, 32, Swz::B128)) return 1;
 
-  ab::Params p;
-  p.B = B; p.T = T; p.H = H;
-  p.scale = softmax_scale > 0.f ? softmax_scale : 1.0f / std::sqrt(float(head_dim));
-  p.scale_log2 = p.scale * 1.4426950408889634f;
-  p.lse = lse;
-  p.dsum = dsum;
-  p.key_mask = key_mask;
-  p.dq32 = dq32;
-  p.dbias = dbias;
-  p.drop = drop;
-  p.t_pad = (T + 7) & ~7;
-  p.turn = nullptr;
+  const float scale = softmax_scale > 0.f ? softmax_scale : 1.0f / std::sqrt(float(head_dim));
+  int* turn = nullptr;
   if (deterministic()) {
-    const size_t turn_bytes = size_t(B) * H * ceil_div(T, ab::BQ) * 8 * sizeof(int);
-    p.turn = reinterpret_cast<int*>(static_cast<uint8_t*>(scratch) + dq_bytes +
-                                    size_t(B) * H * T * sizeof(float));
-    B200_CHECK_CUDA(cudaMemsetAsync(p.turn, 0, turn_bytes, stream));
+    turn = reinterpret_cast<int*>(base + lay.turn);
+    B200_CHECK_CUDA(cudaMemsetAsync(turn, 0, size_t(B) * H * nq * 8 * sizeof(int), stream));
   }
-  p.trace = nullptr;
+  constexpr size_t kTraceWords = 3 * 16 * 4;
+  long long* trace = nullptr;
   static const bool want_trace = std::getenv("LLMTRAIN_ATTN_TRACE") != nullptr;
   if (want_trace) {
-    B200_CHECK_CUDA(cudaMalloc(&p.trace, 3 * 16 * 4 * sizeof(long long)));
-    B200_CHECK_CUDA(cudaMemsetAsync(p.trace, 0, 3 * 16 * 4 * sizeof(long long), stream));
+    B200_CHECK_CUDA(cudaMalloc(&trace, kTraceWords * sizeof(long long)));
+    B200_CHECK_CUDA(cudaMemsetAsync(trace, 0, kTraceWords * sizeof(long long), stream));
   }
   static bool configured = false;
   if (!configured) {
-    B200_CHECK_CUDA(cudaFuncSetAttribute(ab::bwd_kernel<false>,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, ab::SMEM));
     B200_CHECK_CUDA(cudaFuncSetAttribute(ab::bwd_kernel<true>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, ab::SMEM));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(at::bwd_kernel,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, at::SMEM));
     configured = true;
   }
-  dim3 grid(ceil_div(T, ab::BKV), H, B);
-  if (drop.threshold != 0)
-    B200_LAUNCH((ab::bwd_kernel<true>), grid, ab::THREADS, ab::SMEM, stream, tQKV, tDO, tDQKV, tDQ, p);
-  else
-    B200_LAUNCH((ab::bwd_kernel<false>), grid, ab::THREADS, ab::SMEM, stream, tQKV, tDO, tDQKV, tDQ, p);
+  const int items = nq * H * B;
+  const int grid = items < sm_count() ? items : sm_count();  // persistent: one CTA per SM
+  if (with_dropout) {
+    ab::Params p;
+    p.B = B; p.T = T; p.H = H;
+    p.scale = scale;
+    p.scale_log2 = scale * 1.4426950408889634f;
+    p.lse = lse;
+    p.dsum = dsum;
+    p.key_mask = key_mask;
+    p.dq32 = dq32;
+    p.dbias = dbias;
+    p.drop = drop;
+    p.t_pad = (T + 7) & ~7;
+    p.turn = turn;
+    p.trace = trace;
+    B200_LAUNCH((ab::bwd_kernel<true>), grid, ab::THREADS, ab::SMEM, stream, tQKV, tDO, tDKV, tDQ, p);
+  } else {
+    at::Params p;
+    p.B = B; p.T = T; p.H = H;
+    p.t_stat = t_stat;
+    p.scale = scale;
+    p.scale_log2 = scale * 1.4426950408889634f;
+    p.stats = stats;
+    p.key_mask = key_mask;
+    p.dbias = dbias;
+    p.trace = trace;
+    p.turn = turn;
+    B200_LAUNCH((at::bwd_kernel), grid, at::THREADS, at::SMEM, stream, tQKV, tDO, tDKV, tDQ, p);
+  }
   B200_CHECK_CUDA(cudaGetLastError());
   B200_COUNT_LAUNCH(1);
-  if (p.trace != nullptr) {  // debug: timeline of the CTA with the most query tiles
-    static long long host[3 * 16 * 4];
-    B200_CHECK_CUDA(cudaMemcpyAsync(host, p.trace, sizeof(host), cudaMemcpyDeviceToHost, stream));
+  if (trace != nullptr) {  // debug: timeline of CTA 0's first 16 (query tile, key tile) pairs
+    static long long host[kTraceWords];
+    B200_CHECK_CUDA(cudaMemcpyAsync(host, trace, sizeof(host), cudaMemcpyDeviceToHost, stream));
     B200_CHECK_CUDA(cudaStreamSynchronize(stream));
     const long long t0 = host[1];
     for (int it = 0; it < 16 && host[it * 4] != 0; ++it) {
@@ -670,7 +763,7 @@ static int attention_bwd_impl(const void* qkv, const void* out, const void* dout
                        host[(role * 16 + it) * 4 + k] == 0 ? -1LL : host[(role * 16 + it) * 4 + k] - t0);
       std::fprintf(stderr, "\n");
     }
-    cudaFree(p.trace);
+    cudaFree(trace);
   }
 
   {

@@ -68,27 +68,6 @@ constexpr float kRescaleThreshold = 8.0f;  // log2 units
 #endif
 constexpr int kPolyOf4 = B200_ATTN_POLY_OF4;
 
-// 2^x for a pair, no MUFU: round-to-nearest split x = n + f (magic-number add), cubic minimax of
-// 2^f on [-0.5, 0.5] (relative error 7.7e-5, far inside bf16), exponent patched in by integer add.
-// Inputs below -126 (masked scores are -inf) are clamped: the result is ~1e-38, i.e. zero against
-// a row whose largest term is >= 2^-8.
-__device__ __forceinline__ void exp2_poly_pair(f32x2 x, float& e0, float& e1) {
-  float x0, x1;
-  unpack2(x, x0, x1);
-  x = pack2(fmaxf(x0, -126.f), fmaxf(x1, -126.f));
-  const f32x2 t = add2(x, splat2(12582912.f));           // low mantissa bits = round(x)
-  const f32x2 n = add2(t, splat2(-12582912.f));
-  const f32x2 f = fma2(n, splat2(-1.f), x);
-  f32x2 q = fma2(f, splat2(0.05508868396282196f), splat2(0.24260404706001282f));
-  q = fma2(q, f, splat2(0.6932762265205383f));
-  q = fma2(q, f, splat2(0.9999289512634277f));
-  float t0, t1, q0, q1;
-  unpack2(t, t0, t1);
-  unpack2(q, q0, q1);
-  e0 = __int_as_float(__float_as_int(q0) + (__float_as_int(t0) << 23));
-  e1 = __int_as_float(__float_as_int(q1) + (__float_as_int(t1) << 23));
-}
-
 enum MaskMode : int { kNoMask = 0, kDiag = 1, kGeneral = 2 };
 
 template <int N>
@@ -265,6 +244,9 @@ __device__ __forceinline__ void softmax_tile(int mode, uint32_t t_s, uint32_t t_
 struct Item {
   int b, h, qb, q0, n0, n1, n_max;
 };
+// (Cutting the list into groups of (b, h) pairs whose K / V stay in L2 between query blocks, as
+// the backward kernel does for Q / dO / dQ, was measured: the kernel alone 126 against 119 us
+// (the rounds lose their balance) and no change in the training step.)
 __device__ __forceinline__ Item make_item(const Params& p, int idx) {
   Item it;
   const int bh_count = p.B * p.H;

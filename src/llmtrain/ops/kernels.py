@@ -252,8 +252,13 @@ def attention_fwd(qkv, n_heads, *, key_mask=None, out=None, lse=None, dropout=No
     return out, lse
 
 
-def attention_bwd(qkv, out, dout, lse, n_heads, *, key_mask=None, dqkv=None, dropout=None):
-    """Gradient of :func:`attention_fwd` w.r.t. the fused ``qkv`` buffer."""
+def attention_bwd(qkv, out, dout, lse, n_heads, *, key_mask=None, dqkv=None, dropout=None,
+                  dbias=None):
+    """Gradient of :func:`attention_fwd` w.r.t. the fused ``qkv`` buffer.
+
+    ``dbias`` (fp32 ``[3 * d_model]``, optional): the column sums of ``dqkv`` — ``qkv_proj``'s bias
+    gradient — are ADDED to it by the same kernels (what the training engine does).
+    """
     b, t, three_d = qkv.shape
     hd = three_d // 3 // n_heads
     dqkv = torch.empty_like(qkv) if dqkv is None else dqkv
@@ -261,6 +266,19 @@ def attention_bwd(qkv, out, dout, lse, n_heads, *, key_mask=None, dqkv=None, dro
     need = lib.llmtrain_b200_attention_bwd_scratch_bytes(_c_int(b), _c_int(t), _c_int(n_heads),
                                                          _c_int(hd))
     buf = scratch(need, qkv.device)
+    if dbias is not None:
+        assert dbias.dtype == torch.float32 and dbias.numel() == three_d and dbias.is_contiguous()
+        p, seed, offset, site = dropout if dropout is not None else (0.0, 0, 0, 0)
+        check(
+            lib.llmtrain_b200_attention_bwd_fused(
+                ptr(qkv), ptr(out), ptr(dout), ptr(lse), ptr(key_mask), ptr(dqkv), ptr(dbias),
+                ptr(buf), _c_size(buf.numel()), _c_int(b), _c_int(t), _c_int(n_heads), _c_int(hd),
+                _c_float(0.0), _c_float(p), _c_u64(seed), _c_u64(offset), ctypes.c_uint32(site),
+                stream_handle(),
+            ),
+            "attention_bwd_fused",
+        )
+        return dqkv
     if dropout is not None:
         p, seed, offset, site = dropout
         check(

@@ -254,6 +254,23 @@ def test_attention_bwd_key_padding() -> None:
     assert _rel(dqkv, ref_in.grad) < 3e-2
 
 
+@pytest.mark.parametrize("b,t,h", [(2, 384, 3), (1, 200, 2)])
+def test_attention_bwd_accumulates_the_qkv_bias_gradient(b: int, t: int, h: int) -> None:
+    """``dbias`` (what the engine passes) receives the column sums of the dqkv the same call
+    writes, added to what it held (reference: ``qkv_proj``'s bias, `gpt.py:27`)."""
+    from llmtrain.ops import kernels as K
+
+    qkv = _bf((b, t, 3 * h * 64))
+    out, lse = K.attention_fwd(qkv, h)
+    dout = _bf((b, t, h * 64))
+    plain = K.attention_bwd(qkv, out, dout, lse, h)
+    dbias = torch.full((3 * h * 64,), 0.5, device="cuda")
+    dqkv = K.attention_bwd(qkv, out, dout, lse, h, dbias=dbias)
+    assert _rel(dqkv, plain) < 1e-3  # dq is summed by atomics: not bit-identical across calls
+    want = dqkv.float().sum(dim=(0, 1)) + 0.5
+    assert torch.allclose(dbias, want, rtol=1e-4, atol=1e-3), (dbias - want).abs().max()
+
+
 def test_synthetic_tokens_are_shifted_in_range_and_reproducible() -> None:
     from llmtrain.ops import kernels as K
 
