@@ -739,6 +739,16 @@ static int attention_bwd_impl(const void* qkv, const void* out, const void* dout
     at::Params p;
     p.B = B; p.T = T; p.H = H;
     p.t_stat = t_stat;
+    {
+      // Q / dO / fp32 dQ of one (b, h) pair: nq x 64 KB.  When all pairs together fit in L2 the
+      // list is one group (best balance); otherwise a group is as many pairs as there are CTAs.
+      static const int forced = [] {
+        const char* e = std::getenv("LLMTRAIN_ATTN_BWD_GROUP");
+        return e != nullptr ? std::atoi(e) : 0;
+      }();
+      const size_t pair_bytes = size_t(nq) * 64 * 1024;
+      p.group = forced > 0 ? forced : (size_t(B) * H * pair_bytes <= (size_t(64) << 20) ? B * H : grid);
+    }
     p.scale = scale;
     p.scale_log2 = scale * 1.4426950408889634f;
     p.stats = stats;

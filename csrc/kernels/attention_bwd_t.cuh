@@ -64,6 +64,7 @@ static_assert(SMEM <= 227 * 1024, "shared memory budget");
 struct Params {
   int B, T, H;
   int t_stat;          // T rounded up to a multiple of 128: row pitch of `stats`
+  int group;           // (b, h) pairs per scheduling group (see Schedule)
   float scale;         // head_dim^-0.5
   float scale_log2;    // scale * log2(e)
   const float2* stats; // [B, H, t_stat] (LSE * log2 e or +inf for an empty / padded row, D)
@@ -92,7 +93,7 @@ struct Schedule {
   int nq, bh, group, total, grid, cta;
   __device__ __forceinline__ Schedule(const Params& p, int nq_)
       : nq(nq_), bh(p.B * p.H), total(nq_ * p.B * p.H), grid(int(gridDim.x)), cta(int(blockIdx.x)) {
-    group = max(1, min(bh, 512 / nq));
+    group = max(1, min(bh, p.group));
   }
   // position of this CTA's k-th item, or -1 when it has no more
   __device__ __forceinline__ int position(int k) const {
@@ -122,7 +123,7 @@ __device__ __forceinline__ Item make_item(const Params& p, const Schedule& s, in
 // on the split exponent, see exp2_poly_pair); the rest use MUFU.EX2, 16 per clock per SM — one
 // 128x128 tile needs 1024 MUFU cycles.
 #ifndef B200_ATTN_BWD_POLY_OF4
-#define B200_ATTN_BWD_POLY_OF4 1
+#define B200_ATTN_BWD_POLY_OF4 0
 #endif
 constexpr int kPolyOf4 = B200_ATTN_BWD_POLY_OF4;
 
