@@ -94,6 +94,41 @@ def _sub(module: nn.Module, dotted: str) -> nn.Module:
     return module
 
 
+
+class StepScalars:
+    """Loss and gradient norm of one optimiser step on their way to the host.
+
+    ``train_step`` enqueues a device-to-pinned-host copy of both and an event behind it; reading
+    (``float(x)``, ``x.grad_norm``) waits for THAT event only, so a caller may enqueue the next
+    step first and read this one while the GPU is busy (``Trainer.fit`` does).
+    """
+
+    __slots__ = ("_row", "_event", "_value")
+
+    def __init__(self, row: torch.Tensor, event: torch.cuda.Event) -> None:
+        self._row = row
+        self._event: torch.cuda.Event | None = event
+        self._value: tuple[float, float] | None = None
+
+    def _read(self) -> tuple[float, float]:
+        if self._value is None:
+            assert self._event is not None
+            self._event.synchronize()
+            self._value = (float(self._row[0]), float(self._row[1]))
+            self._event = None  # the ring slot may be reused from here on
+        return self._value
+
+    def __float__(self) -> float:
+        return self._read()[0]
+
+    def item(self) -> float:
+        return self._read()[0]
+
+    @property
+    def grad_norm(self) -> float:
+        return self._read()[1]
+
+
 class GPTEngine:
     """Memory plan + kernel sequencing for one GPT module on one B200."""
 
@@ -546,10 +581,34 @@ class B200TrainEngine(TrainEngine):
         else:
             self._comm.reduce_and_step(self._m, self._v, self._sumsq, self._norm, hyper)
         self._mark(marks, final=True)
-        loss = self._loss_acc.clone().reshape(())
+        loss = self._publish_scalars()
         if self._prefetch:
             self._prefetched = self._stage(next_batch())
         return loss, tokens
+
+    _SCALAR_RING = 512
+
+    def _publish_scalars(self) -> StepScalars:
+        """Device -> pinned-host copy of (loss, grad norm) of the step just enqueued."""
+        ring = getattr(self, "_scalar_ring", None)
+        if ring is None:
+            ring = torch.zeros(self._SCALAR_RING, 2, dtype=torch.float32).pin_memory()
+            self._scalar_ring = ring
+            self._scalar_events: list[torch.cuda.Event | None] = [None] * self._SCALAR_RING
+            self._scalar_pending: list[StepScalars | None] = [None] * self._SCALAR_RING
+        slot = self._step % self._SCALAR_RING
+        stale = self._scalar_pending[slot]
+        if stale is not None:
+            stale._read()  # 512 steps old: complete long ago; keeps its value before the overwrite
+        row = ring[slot]
+        row[0:1].copy_(self._loss_acc.reshape(1), non_blocking=True)
+        row[1:2].copy_(self._norm.reshape(1), non_blocking=True)
+        event = torch.cuda.Event()
+        event.record()
+        out = StepScalars(row, event)
+        self._scalar_pending[slot] = out
+        self._last_scalars = out
+        return out
 
     def _mark(self, marks: list[torch.cuda.Event] | None = None, *, final: bool = False):
         if not self._phase_timing:
@@ -635,8 +694,11 @@ class B200TrainEngine(TrainEngine):
                     break
         return 2250.0
 
-    def extra_metrics(self, tokens_per_sec: float | None = None) -> dict[str, float]:
-        out = {"train/grad_norm": float(self._norm.item())}
+    def extra_metrics(self, tokens_per_sec: float | None = None,
+                      step_result: Any = None) -> dict[str, float]:
+        # the norm of the step being logged (already on the host), not of the newest enqueued one
+        norm = getattr(step_result, "grad_norm", None)
+        out = {"train/grad_norm": float(self._norm.item()) if norm is None else float(norm)}
         if tokens_per_sec and self._last_seq_len:
             tflops = tokens_per_sec * self.model_flops_per_token(self._last_seq_len) / 1e12
             out["train/model_tflops_per_gpu"] = tflops

@@ -57,11 +57,13 @@ class TrainEngine(abc.ABC):
     def peak_memory_bytes(self) -> float:
         return 0.0
 
-    def extra_metrics(self, tokens_per_sec: float | None = None) -> dict[str, float]:
+    def extra_metrics(self, tokens_per_sec: float | None = None,
+                      step_result: Any = None) -> dict[str, float]:
         """Engine-specific metrics appended (never renaming the reference's keys).
 
         ``tokens_per_sec`` is this rank's rate over the interval being logged, for engines that
-        report utilisation.
+        report utilisation; ``step_result`` is what ``train_step`` returned for the interval's
+        last step (log lines are written one step late, see ``Trainer.fit``).
         """
-        del tokens_per_sec
+        del tokens_per_sec, step_result
         return {}

@@ -281,7 +281,8 @@ class Trainer:
 
     # ------------------------------------------------------------------ logging blocks
     def _log_train_interval(self, step: int, max_steps: int, window: _Interval,
-                            tokens_local_total: int, tokens_global_total: int) -> int:
+                            tokens_local_total: int, tokens_global_total: int,
+                            lr_now: float) -> int:
         # Read the losses back FIRST: on CUDA that is the synchronisation point, and the interval
         # must not end while the interval's kernels are still in flight.
         loss_sum = window.loss_sum()
@@ -289,7 +290,7 @@ class Trainer:
         mean_loss = loss_sum / window.steps
         step_time = elapsed / window.steps
         rate = window.tokens / elapsed if elapsed > 0 else 0.0
-        lr_now = float(self._scheduler.get_last_lr()[0])
+        extra = self._engine.extra_metrics(rate, window.losses[-1])
 
         if self._is_ddp_active:
             rows = self._gather_scalars(
@@ -322,7 +323,7 @@ class Trainer:
                         "train/tokens_per_sec": pooled["tokens"] / elapsed if elapsed > 0 else 0.0,
                         "train/tokens_total": float(tokens_global_total),
                         "train/step_time_sec": step_time,
-                        **self._engine.extra_metrics(rate),
+                        **extra,
                     },
                     step=step,
                 )
@@ -334,7 +335,7 @@ class Trainer:
                     "train/tokens_per_sec": rate,
                     "train/step_time_sec": step_time,
                     "train/tokens_total": float(tokens_local_total),
-                    **self._engine.extra_metrics(rate),
+                    **extra,
                 },
                 step=step,
             )
@@ -412,9 +413,26 @@ class Trainer:
         tokens_local_total = 0
         tokens_global_total = 0
         window = _Interval()
+        # A log line is written one step late: the interval's scalars are read back (and, under
+        # DDP, exchanged between the ranks) after the NEXT step has been enqueued, so the device
+        # never waits for the host's logging.  Values, step numbers and the order relative to
+        # checkpoints and evaluations are those of immediate logging.
+        pending: tuple[int, _Interval, int, float] | None = None
+
+        def flush_log() -> None:
+            nonlocal pending, tokens_global_total
+            if pending is None:
+                return
+            at_step, interval, tokens_then, lr_then = pending
+            pending = None
+            tokens_global_total = self._log_train_interval(
+                at_step, max_steps, interval, tokens_then, tokens_global_total, lr_then
+            )
+            window.started = time.perf_counter()  # the next interval starts where this one ended
 
         for step in range(first_step, max_steps + 1):
             last_loss, step_tokens = self._engine.train_step(next_batch, accum)
+            flush_log()  # the previous interval: the device is busy with this step meanwhile
             self._scheduler.step()
             tokens_local_total += step_tokens
             if step == 1:
@@ -433,11 +451,14 @@ class Trainer:
 
             window.add(last_loss, step_tokens)
             if step % cfg.log_every_steps == 0 or is_final:
-                tokens_global_total = self._log_train_interval(
-                    step, max_steps, window, tokens_local_total, tokens_global_total
-                )
+                pending = (step, window, tokens_local_total,
+                           float(self._scheduler.get_last_lr()[0]))
+                window = _Interval()
+                if is_final:
+                    flush_log()
 
             if step % cfg.eval_every_steps == 0 or is_final:
+                flush_log()
                 outcome = self._evaluate()
                 if outcome is None:
                     continue  # no validation data configured

@@ -212,7 +212,7 @@ def _check_ddp_equivalence(rank: int, world: int, nvls: bool, backend: str = "nv
         loss_one, _ = one.train_step(lambda whole=whole: whole, 1)
         torch.cuda.synchronize()
         say(f"step {step}: both steps done")
-        mean = loss_many.detach().clone()
+        mean = torch.tensor(float(loss_many), device="cuda")
         dist.all_reduce(mean)
         mean /= world
         assert abs(mean.item() - loss_one.item()) < 2e-3 * abs(loss_one.item()), (

@@ -72,6 +72,31 @@ def test_log_eval_and_save_cadences(tmp_path: Path, caplog: pytest.LogCaptureFix
     assert not list((tmp_path / "run" / "checkpoints").glob("*.tmp"))
 
 
+def test_deferred_log_lines_keep_their_order_values_and_steps(tmp_path: Path) -> None:
+    """A train log line is written one step late (after the next step has been enqueued) but is
+    still the line of ITS step: before that step's validation line, with that step's learning
+    rate and running token total, and every step is logged exactly once."""
+    cfg = config(tmp_path, trainer={"max_steps": 6, "log_every_steps": 1, "eval_every_steps": 3,
+                                    "save_every_steps": 100, "warmup_steps": 2, "lr": 1e-2})
+    tracker = Mock()
+    trainer = Trainer(cfg, run_dir=tmp_path / "run", tracker=tracker)
+    trainer.fit()
+    order = [("val" if "val/loss" in c.args[0] else "train", c.kwargs["step"])
+             for c in tracker.log_metrics.call_args_list
+             if "val/loss" in c.args[0] or "train/loss" in c.args[0]]
+    assert order == [("train", 1), ("train", 2), ("train", 3), ("val", 3), ("train", 4),
+                     ("train", 5), ("train", 6), ("val", 6)]
+    train = {c.kwargs["step"]: c.args[0] for c in tracker.log_metrics.call_args_list
+             if "train/loss" in c.args[0]}
+    per_step = train[1]["train/tokens_total"]
+    assert per_step > 0 and [train[k]["train/tokens_total"] for k in range(1, 7)] == [
+        k * per_step for k in range(1, 7)]
+    # warm-up over 2 steps: the line of step 1 carries the rate in force after step 1, and so on
+    f = warmup_cosine_multiplier(2, 6)
+    assert [train[k]["train/lr"] for k in range(1, 7)] == pytest.approx(
+        [1e-2 * f(k) for k in range(1, 7)])
+
+
 def test_checkpoint_payload_and_manager(tmp_path: Path) -> None:
     cfg = config(tmp_path, model=TINY_GPT, trainer={"max_steps": 2, "save_every_steps": 1})
     trainer = Trainer(cfg, run_dir=tmp_path / "r")
