@@ -284,70 +284,79 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CU
     }
   } else if (warp == 9) {
     // ------------------------------- MMA issuer ---------------------------------------------
-    if (lane == 0) {
-      constexpr uint32_t id_s = umma_idesc_bf16(128, 128, false, false);   // Q K^T, dO V^T
-      constexpr uint32_t id_t = umma_idesc_bf16(128, 64, true, true);     // P^T dO, dS^T Q
-      constexpr uint32_t id_dq = umma_idesc_bf16(128, 64, false, true);   // dS K
-      const uint32_t sK = smem_u32(smem + OFF_K), sV = smem_u32(smem + OFF_V);
-      auto issue_scores = [&](int g) {  // S = Q K^T and dP = dO V^T of iteration g
-        const int st = g % NQ;
-        const uint32_t sQ = smem_u32(smem + OFF_Q + st * TILE);
-        const uint32_t sDO = smem_u32(smem + OFF_DO + st * TILE);
-        mbar_wait(&q_full[st], uint32_t(g / NQ) & 1u);
+    // The whole warp walks the loop, one elected lane issues, descriptors are built outside the
+    // elected region and advanced by one add per instruction (see attention_bwd_t.cuh: inside
+    // `if (lane == 0)` every tcgen05.mma cost ~85 cycles of issue).
+    constexpr uint32_t id_s = umma_idesc_bf16(128, 128, false, false);   // Q K^T, dO V^T
+    constexpr uint32_t id_t = umma_idesc_bf16(128, 64, true, true);     // P^T dO, dS^T Q
+    constexpr uint32_t id_dq = umma_idesc_bf16(128, 64, false, true);   // dS K
+    const bool leader = elect_one();
+    const uint32_t sQ0 = smem_u32(smem + OFF_Q), sDO0 = smem_u32(smem + OFF_DO);
+    // K-major tiles: +32 B per K step = +2 in the address field; MN-major: +2048 B = +128
+    const uint64_t kK = umma_smem_desc(smem_u32(smem + OFF_K), 0, 1024);
+    const uint64_t kV = umma_smem_desc(smem_u32(smem + OFF_V), 0, 1024);
+    const uint64_t mK = umma_smem_desc(smem_u32(smem + OFF_K), TILE, 1024);
+    const uint64_t mP = umma_smem_desc(smem_u32(smem + OFF_P), TILE, 1024);
+    auto issue_scores = [&](int g) {  // S = Q K^T and dP = dO V^T of iteration g
+      const int st = g % NQ;
+      mbar_wait(&q_full[st], uint32_t(g / NQ) & 1u);
+      tc_fence_after_sync();
+      const uint64_t kQ = umma_smem_desc(sQ0 + st * TILE, 0, 1024);
+      const uint64_t kDO = umma_smem_desc(sDO0 + st * TILE, 0, 1024);
+      if (leader) {
         stamp(p, 1, g, 0);
-        tc_fence_after_sync();
+#pragma unroll
+        for (int k = 0; k < HD / 16; ++k) umma_ss(tmem + COL_S, kQ + 2 * k, kK + 2 * k, id_s, k > 0);
 #pragma unroll
         for (int k = 0; k < HD / 16; ++k)
-          umma_ss(tmem + COL_S, umma_smem_desc(sQ + k * 32, 0, 1024),
-                  umma_smem_desc(sK + k * 32, 0, 1024), id_s, k > 0);
-#pragma unroll
-        for (int k = 0; k < HD / 16; ++k)
-          umma_ss(tmem + COL_DP, umma_smem_desc(sDO + k * 32, 0, 1024),
-                  umma_smem_desc(sV + k * 32, 0, 1024), id_s, k > 0);
+          umma_ss(tmem + COL_DP, kDO + 2 * k, kV + 2 * k, id_s, k > 0);
         umma_commit(s_full);
-      };
-      int g = 0;
-      for (int idx = first, item = 0; idx < total; idx += stride, ++item) {
-        const int n_iter = nq - idx / (p.B * p.H);
-        mbar_wait(kv_full, uint32_t(item) & 1u);
-        // S / dP of the previous item were read before its last pds_full, so the first score tile
-        // of this item may be issued while the other warps are still in the previous epilogue.
-        issue_scores(g);
-        for (int it = 0; it < n_iter; ++it, ++g) {
-          const int st = g % NQ;
-          const uint32_t sQ = smem_u32(smem + OFF_Q + st * TILE);
-          const uint32_t sDO = smem_u32(smem + OFF_DO + st * TILE);
-          const uint32_t sP = smem_u32(smem + OFF_P);
-          const uint32_t sDS = smem_u32(smem + OFF_DS + (g & 1) * PDS_BYTES);
-          stamp(p, 1, g, 1);
-          mbar_wait(pds_full, uint32_t(g) & 1u);  // P_g / dS_g are in smem, S_g / dP_g have left TMEM
-          if (it == 0 && item > 0) mbar_wait(dkv_drained, uint32_t(item - 1) & 1u);
+      }
+    };
+    int g = 0;
+    for (int idx = first, item = 0; idx < total; idx += stride, ++item) {
+      const int n_iter = nq - idx / (p.B * p.H);
+      mbar_wait(kv_full, uint32_t(item) & 1u);
+      // S / dP of the previous item were read before its last pds_full, so the first score tile
+      // of this item may be issued while the other warps are still in the previous epilogue.
+      issue_scores(g);
+      for (int it = 0; it < n_iter; ++it, ++g) {
+        const int st = g % NQ;
+        const uint64_t mQ = umma_smem_desc(sQ0 + st * TILE, TILE, 1024);
+        const uint64_t mDO = umma_smem_desc(sDO0 + st * TILE, TILE, 1024);
+        const uint32_t sDS = smem_u32(smem + OFF_DS + (g & 1) * PDS_BYTES);
+        const uint64_t mDS = umma_smem_desc(sDS, TILE, 1024);
+        // dS as the K-major left operand of dQ: two 64-wide regions TILE apart, 32 B per K step
+        const uint64_t kDS0 = umma_smem_desc(sDS, 0, 1024), kDS1 = umma_smem_desc(sDS + TILE, 0, 1024);
+        if (leader) stamp(p, 1, g, 1);
+        mbar_wait(pds_full, uint32_t(g) & 1u);  // P_g / dS_g are in smem, S_g / dP_g have left TMEM
+        if (it == 0 && item > 0) mbar_wait(dkv_drained, uint32_t(item - 1) & 1u);
+        tc_fence_after_sync();
+        if (leader) {
           stamp(p, 1, g, 2);
-          tc_fence_after_sync();
           // dV += P^T dO   (A, B both MN-major: 16 q-rows = 2048 B per K step).  First in the
           // queue: it is the only reader of the single P buffer.
 #pragma unroll
           for (int k = 0; k < BQ / 16; ++k)
-            umma_ss(tmem + COL_DV, umma_smem_desc(sP + k * 2048, TILE, 1024),
-                    umma_smem_desc(sDO + k * 2048, TILE, 1024), id_t, (it > 0) || (k > 0));
-          if (it + 1 < n_iter) issue_scores(g + 1);  // the softmax-grad warps wait on these
+            umma_ss(tmem + COL_DV, mP + 128 * k, mDO + 128 * k, id_t, (it > 0) || (k > 0));
+        }
+        if (it + 1 < n_iter) issue_scores(g + 1);  // the softmax-grad warps wait on these
+        if (leader) {
           // dK += dS^T Q
 #pragma unroll
           for (int k = 0; k < BQ / 16; ++k)
-            umma_ss(tmem + COL_DK, umma_smem_desc(sDS + k * 2048, TILE, 1024),
-                    umma_smem_desc(sQ + k * 2048, TILE, 1024), id_t, (it > 0) || (k > 0));
+            umma_ss(tmem + COL_DK, mDS + 128 * k, mQ + 128 * k, id_t, (it > 0) || (k > 0));
           umma_commit(&q_empty[st]);
           // dQ_g = dS K  (A K-major over 128 kv = two 64-wide regions; B = K_j MN-major)
 #pragma unroll
           for (int k = 0; k < BKV / 16; ++k)
-            umma_ss(tmem + COL_DQ + (g & 1) * HD,
-                    umma_smem_desc(sDS + (k >> 2) * TILE + (k & 3) * 32, 0, 1024),
-                    umma_smem_desc(sK + k * 2048, TILE, 1024), id_dq, k > 0);
+            umma_ss(tmem + COL_DQ + (g & 1) * HD, ((k >> 2) ? kDS1 : kDS0) + 2 * (k & 3),
+                    mK + 128 * k, id_dq, k > 0);
           umma_commit(&dq_full[g & 1]);
           stamp(p, 1, g, 3);
         }
-        umma_commit(dkv_full);
       }
+      if (leader) umma_commit(dkv_full);
     }
   } else {
     // ------------------------------- softmax-grad / epilogue warps --------------------------
