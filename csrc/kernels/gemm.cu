@@ -248,8 +248,20 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
   } else if (warp == 1) {
     // ===================================== MMA issuer =======================================
-    if (lane == 0 && leader) {
+    // The whole warp of the leader CTA walks the loop and waits on the barriers; one elected
+    // lane issues.  A stage's descriptors are built once, outside the elected region, and
+    // advanced by one 64-bit add per instruction: inside `if (lane == 0)` (a divergent region,
+    // so no uniform registers) every tcgen05.mma was preceded by ~20 dependent instructions,
+    // ~100 cycles of issue against the 128 cycles the instruction takes to execute — no slack
+    // for the barrier wait and the commit of a 4-instruction stage.
+    if (leader) {
       constexpr uint32_t idesc = umma_idesc_bf16(BM * CTAS, BN, A_MN, B_MN);
+      // K-major: 32 B per UMMA_K inside the swizzled 128 B row (+2 in the address field);
+      // SBO = 8 rows * 128 B.  MN-major: 16 K-rows * 128 B per UMMA_K (+128); LBO = one 64-wide
+      // box (BK rows * 128 B).
+      constexpr uint32_t a_step = A_MN ? (UK * 128) >> 4 : (UK * 2) >> 4;
+      constexpr uint32_t b_step = B_MN ? (UK * 128) >> 4 : (UK * 2) >> 4;
+      const bool issuer = elect_one();
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
@@ -266,25 +278,27 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           tc_fence_after_sync();
           const uint32_t sa = smem_u32(smem + stage * STAGE_BYTES);
           const uint32_t sb = sa + A_BYTES;
+          const uint64_t da = A_MN ? umma_smem_desc(sa, BK * 128, 1024) : umma_smem_desc(sa, 0, 1024);
+          const uint64_t db = B_MN ? umma_smem_desc(sb, BK * 128, 1024) : umma_smem_desc(sb, 0, 1024);
+          if (issuer) {
 #pragma unroll
-          for (int k = 0; k < BK / UK; ++k) {
-            // K-major: 32 B per UMMA_K inside the swizzled 128 B row; SBO = 8 rows * 128 B.
-            // MN-major: 16 K-rows * 128 B per UMMA_K; LBO = one 64-wide box (BK rows * 128 B).
-            const uint64_t da = A_MN ? umma_smem_desc(sa + k * (UK * 128), BK * 128, 1024)
-                                     : umma_smem_desc(sa + k * (UK * 2), 0, 1024);
-            const uint64_t db = B_MN ? umma_smem_desc(sb + k * (UK * 128), BK * 128, 1024)
-                                     : umma_smem_desc(sb + k * (UK * 2), 0, 1024);
-            if (CTAS == 2) umma_ss_pair(d_tmem, da, db, idesc, (kb > kb_begin) || (k > 0));
-            else umma_ss(d_tmem, da, db, idesc, (kb > kb_begin) || (k > 0));
+            for (int k = 0; k < BK / UK; ++k) {
+              if (CTAS == 2)
+                umma_ss_pair(d_tmem, da + a_step * k, db + b_step * k, idesc, (kb > kb_begin) || (k > 0));
+              else
+                umma_ss(d_tmem, da + a_step * k, db + b_step * k, idesc, (kb > kb_begin) || (k > 0));
+            }
+            // frees this smem stage (in both CTAs of a pair) once the MMAs have read it
+            if (CTAS == 2) umma_commit_pair(&empty_bar[stage], 0b11);
+            else umma_commit(&empty_bar[stage]);
           }
-          // frees this smem stage (in both CTAs of a pair) once the MMAs have read it
-          if (CTAS == 2) umma_commit_pair(&empty_bar[stage], 0b11);
-          else umma_commit(&empty_bar[stage]);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
         // accumulator complete -> epilogue (of both CTAs)
-        if (CTAS == 2) umma_commit_pair(&tfull_bar[acc], 0b11);
-        else umma_commit(&tfull_bar[acc]);
+        if (issuer) {
+          if (CTAS == 2) umma_commit_pair(&tfull_bar[acc], 0b11);
+          else umma_commit(&tfull_bar[acc]);
+        }
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }
