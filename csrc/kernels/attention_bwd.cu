@@ -687,8 +687,8 @@ static int attention_bwd_impl(const void* qkv, const void* out, const void* dout
                 static_cast<const __nv_bfloat16*>(dout), static_cast<const __nv_bfloat16*>(out),
                 dsum, B, T, H);
   } else {
-    const long long lanes = (long long)B * t_stat * H * 8;
-    B200_LAUNCH((at::stats_kernel), unsigned(ceil_div(lanes, 256LL)), 256, 0, stream,
+    B200_LAUNCH((at::stats_kernel), dim3(unsigned(ceil_div(t_stat * H * 8, 256)), unsigned(B)), 256, 0,
+                stream,
                 static_cast<const __nv_bfloat16*>(dout), static_cast<const __nv_bfloat16*>(out), lse,
                 stats, B, T, H, t_stat);
   }

@@ -666,13 +666,14 @@ __global__ void stats_kernel(const __nv_bfloat16* __restrict__ dO, const __nv_bf
                              const float* __restrict__ lse, float2* __restrict__ stats, int B, int T,
                              int H, int t_stat) {
   pdl_enter();  // previous kernel finished, its writes are visible
-  const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  const long long pair = gid >> 3;  // (b, t < t_stat, head) index
-  const int sub = int(gid & 7);
-  const long long total = (long long)B * t_stat * H;
-  const long long row = pair / H;
-  const int h = int(pair - row * H);
-  const int b = int(row / t_stat), t = int(row - (long long)b * t_stat);
+  // grid = (ceil(t_stat * H * 8 / 256), B): 32-bit index arithmetic, one batch row per blockIdx.y
+  const int gid = int(blockIdx.x * blockDim.x + threadIdx.x);
+  const int pair = gid >> 3;  // (t < t_stat, head) index
+  const int sub = gid & 7;
+  const int total = t_stat * H;
+  const int b = int(blockIdx.y);
+  const int t = pair / H;
+  const int h = pair - t * H;
   const bool real = pair < total && t < T;
   float v = 0.f;
   if (real) {

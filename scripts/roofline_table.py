@@ -49,6 +49,7 @@ def main() -> int:
         "gemm::gemm_kernel<1, 1, 4>": ("flop", L * (g(3 * d, d, M) + g(d, d, M) + 2 * g(F, d, M)) + g(V, d, M)),
         "attn::fwd_kernel": ("flop", L * attn),
         "attn_bwd::bwd_kernel": ("flop", L * attn * 2.5),
+        "attn_bwd_t::bwd_kernel": ("flop", L * attn * 2.5),
         "ew::ce_kernel<1>": ("byte", 2.0 * M * Vp * 2),
         "ew::ce_row_kernel<1>": ("byte", 2.0 * M * Vp * 2),
         "ln::fwd_kernel": ("byte", (2 * L + 1) * 2.0 * M * d * 2),
@@ -56,6 +57,7 @@ def main() -> int:
         "ew::colsum_partial_kernel": ("byte", L * (3 * d + F) * M * 2.0),
         "optim::adamw_kernel": ("byte", n_params * (16.0 + 14.0 + 4.0)),
         "attn_bwd::dsum_kernel": ("byte", L * 2.0 * M * d * 2),
+        "attn_bwd_t::stats_kernel": ("byte", L * 2.0 * M * d * 2),
         "attn_bwd::dq_convert_kernel": ("byte", L * (M * d * 4.0 + M * d * 2.0)),
     }
     total = sum(v[1] for v in agg.values())
