@@ -40,8 +40,10 @@ class TrainEngine(abc.ABC):
         """Run ``accum_steps`` micro-batches + one optimiser update.
 
         Returns ``(mean micro-batch loss, tokens consumed on this rank)``.  The loss may be a
-        float or a 0-dim device tensor; the trainer calls ``float()`` on it only when a value
-        is needed on the host (first step, log steps, last step).
+        float, a 0-dim device tensor, or any object with ``__float__`` whose value arrives later
+        (the B200 engine returns ``StepScalars``: a pinned-host copy guarded by an event); the
+        trainer calls ``float()`` on it only when a value is needed on the host (first step, log
+        lines — written one step late —, last step).
         """
 
     @abc.abstractmethod
