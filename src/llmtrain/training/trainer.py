@@ -406,7 +406,7 @@ class Trainer:
             for _ in range(resumed_from_step * accum):
                 next_batch()
 
-        first_step_loss: float | None = None
+        first_step_obj: Any = None
         final_val_loss: float | None = None
         final_val_metrics: dict[str, float] | None = None
         last_loss: Any = 0.0
@@ -436,7 +436,7 @@ class Trainer:
             self._scheduler.step()
             tokens_local_total += step_tokens
             if step == 1:
-                first_step_loss = float(last_loss)
+                first_step_obj = last_loss  # read at the end: no host sync in the first step
             is_final = step == max_steps
 
             if (
@@ -484,7 +484,7 @@ class Trainer:
             total_time=time.perf_counter() - t_start,
             peak_memory=self._engine.peak_memory_bytes(),
             val_metrics=final_val_metrics,
-            first_step_loss=first_step_loss,
+            first_step_loss=None if first_step_obj is None else float(first_step_obj),
             resumed_from_step=resumed_from_step,
             parameter_count=parameter_count,
             trainable_parameter_count=trainable_parameter_count,
