@@ -443,12 +443,28 @@ int backward(Gpt& g, cudaStream_t s, BucketHook hook = nullptr, void* hook_ctx =
       B200_CHECK_CUDA(cudaMemsetAsync(dbq, 0, size_t(3) * dq * 4, s));
     }
     B200_TRY(linear_wgrad(M, d, dq, dout, d, v.bf(a.atty), dwo, s));
-    B200_TRY(linear_dgrad(0, M, d, dq, dout, wo, datty, nullptr, s));
-    // dqkv and, fused, qkv_proj's bias gradient (column sums of dqkv)
-    B200_TRY(llmtrain_b200_attention_bwd_fused(
-        v.bf(a.qkv), v.bf(a.atty), datty, v.f32(a.lse), g.key_mask, dqkv, det ? nullptr : dbq,
-        g.act + g.a_attn_scratch, g.attn_scratch_bytes, B, T, g.H, 64, sm_scale, drop ? dp : 0.f,
-        seed, off, drop_site(l, 0), st));
+    // dqkv and, fused, qkv_proj's bias gradient (column sums of dqkv).  Without probability
+    // dropout the attention kernel's per-row statistics (LSE, rowsum(dO o O)) come out of
+    // out_proj's dgrad epilogue, which has dO in registers, instead of a pass over dO and O.
+    static const bool fuse_stats = std::getenv("LLMTRAIN_ATTN_STATS_PASS") == nullptr;
+    if (!drop && fuse_stats) {
+      void* stats = nullptr;
+      int t_stat = 0;
+      B200_TRY(llmtrain_b200_attention_bwd_stats_buffer(g.act + g.a_attn_scratch,
+                                                        g.attn_scratch_bytes, B, T, g.H, 64, &stats,
+                                                        &t_stat));
+      B200_TRY(llmtrain_b200_gemm_rowdot(M, dq, d, dout, d, wo, dq, datty, dq, v.bf(a.atty), dq,
+                                         v.f32(a.lse), stats, T, g.H, t_stat, st));
+      B200_TRY(llmtrain_b200_attention_bwd_prestats(
+          v.bf(a.qkv), v.bf(a.atty), datty, v.f32(a.lse), g.key_mask, dqkv, det ? nullptr : dbq,
+          g.act + g.a_attn_scratch, g.attn_scratch_bytes, B, T, g.H, 64, sm_scale, st));
+    } else {
+      B200_TRY(linear_dgrad(0, M, d, dq, dout, wo, datty, nullptr, s));
+      B200_TRY(llmtrain_b200_attention_bwd_fused(
+          v.bf(a.qkv), v.bf(a.atty), datty, v.f32(a.lse), g.key_mask, dqkv, det ? nullptr : dbq,
+          g.act + g.a_attn_scratch, g.attn_scratch_bytes, B, T, g.H, 64, sm_scale,
+          drop ? dp : 0.f, seed, off, drop_site(l, 0), st));
+    }
     if (det) B200_TRY(llmtrain_b200_bias_grad(dqkv, 3 * dq, M, 3 * dq, dbq, red, red_bytes, st));
     B200_TRY(linear_wgrad(M, 3 * dq, d, dqkv, 3 * dq, v.bf(a.ln1), dwq, s));
     B200_TRY(linear_dgrad(0, M, 3 * dq, d, dqkv, wq, dtmp, nullptr, s));

@@ -660,11 +660,13 @@ static int attention_bwd_impl(const void* qkv, const void* out, const void* dout
                               const uint8_t* key_mask, void* dqkv, void* scratch,
                               size_t scratch_bytes, int B, int T, int H, int head_dim,
                               const DropoutParams& drop, float* dbias, float softmax_scale,
-                              cudaStream_t stream) {
+                              cudaStream_t stream, bool stats_ready = false) {
   namespace ab = attn_bwd;
   namespace at = attn_bwd_t;
   B200_REQUIRE(head_dim == ab::HD, "attention_bwd: specialised for head_dim 64");
   B200_REQUIRE(B > 0 && T > 0 && H > 0, "attention_bwd: empty problem");
+  B200_REQUIRE(!stats_ready || drop.threshold == 0,
+               "attention_bwd: precomputed statistics are not used with probability dropout");
   const int d = H * ab::HD;
   const BwdScratch lay = bwd_scratch(B, T, H, head_dim);
   B200_REQUIRE(scratch_bytes >= lay.total, "attention_bwd: scratch too small");
@@ -686,14 +688,17 @@ static int attention_bwd_impl(const void* qkv, const void* out, const void* dout
     B200_LAUNCH((ab::dsum_kernel), ceil_div(rows * H * 8, 256), 256, 0, stream,
                 static_cast<const __nv_bfloat16*>(dout), static_cast<const __nv_bfloat16*>(out),
                 dsum, B, T, H);
-  } else {
+  } else if (!stats_ready) {
     B200_LAUNCH((at::stats_kernel), dim3(unsigned(ceil_div(t_stat * H * 8, 256)), unsigned(B)), 256, 0,
                 stream,
                 static_cast<const __nv_bfloat16*>(dout), static_cast<const __nv_bfloat16*>(out), lse,
                 stats, B, T, H, t_stat);
+  } else if (t_stat != T) {
+    B200_LAUNCH((at::stats_pad_kernel), ceil_div(B * H * (t_stat - T), 256), 256, 0, stream, stats,
+                B * H, T, t_stat);
   }
   B200_CHECK_CUDA(cudaGetLastError());
-  B200_COUNT_LAUNCH(1);
+  if (with_dropout || !stats_ready || t_stat != T) B200_COUNT_LAUNCH(1);
 
   CUtensorMap tQKV, tDO, tDKV, tDQ;
   if (make_tmap_3d(&tQKV, static_cast<const __nv_bfloat16*>(qkv), B, T, 3 * d, 3 * d,
@@ -833,4 +838,32 @@ extern "C" int llmtrain_b200_attention_bwd_fused(const void* qkv, const void* ou
   return attention_bwd_impl(qkv, out, dout, lse, key_mask, dqkv, scratch, scratch_bytes, B, T, H,
                             head_dim, make_dropout(p, seed, offset, site), dbias_qkv,
                             softmax_scale, stream);
+}
+
+// Where llmtrain_b200_gemm_rowdot has to write the statistics for a following
+// llmtrain_b200_attention_bwd_prestats with the same scratch and shape: pointer and row pitch.
+extern "C" int llmtrain_b200_attention_bwd_stats_buffer(void* scratch, size_t scratch_bytes, int B,
+                                                        int T, int H, int head_dim, void** stats,
+                                                        int* t_stat) {
+  B200_REQUIRE(scratch != nullptr && stats != nullptr && t_stat != nullptr, "attention_bwd_stats_buffer: null");
+  const BwdScratch lay = bwd_scratch(B, T, H, head_dim);
+  B200_REQUIRE(scratch_bytes >= lay.total, "attention_bwd_stats_buffer: scratch too small");
+  *stats = static_cast<uint8_t*>(scratch) + lay.stats;
+  *t_stat = ceil_div(T, 128) * 128;
+  return 0;
+}
+
+// As llmtrain_b200_attention_bwd_fused without probability dropout, for callers whose out_proj
+// dgrad already left the per-row statistics in the scratch (llmtrain_b200_gemm_rowdot): the
+// pre-pass over dout / out is skipped.
+extern "C" int llmtrain_b200_attention_bwd_prestats(const void* qkv, const void* out,
+                                                    const void* dout, const float* lse,
+                                                    const uint8_t* key_mask, void* dqkv,
+                                                    float* dbias_qkv, void* scratch,
+                                                    size_t scratch_bytes, int B, int T, int H,
+                                                    int head_dim, float softmax_scale,
+                                                    cudaStream_t stream) {
+  return attention_bwd_impl(qkv, out, dout, lse, key_mask, dqkv, scratch, scratch_bytes, B, T, H,
+                            head_dim, make_dropout(0.f, 0, 0, 0), dbias_qkv, softmax_scale, stream,
+                            true);
 }

@@ -700,5 +700,18 @@ __global__ void stats_kernel(const __nv_bfloat16* __restrict__ dO, const __nv_bf
   }
 }
 
+// The padding entries t in [T, t_stat) of every (b, h) row of `stats`: (+inf, 0).  Needed when the
+// statistics come from out_proj's dgrad epilogue (llmtrain_b200_gemm_rowdot), which only writes
+// real rows; launched only if T is not a multiple of 128.
+__global__ void stats_pad_kernel(float2* __restrict__ stats, int BH, int T, int t_stat) {
+  pdl_enter();
+  const int pad = t_stat - T;
+  const int i = int(blockIdx.x * blockDim.x + threadIdx.x);
+  if (i < BH * pad) {
+    const int bh = i / pad, t = T + (i - bh * pad);
+    stats[size_t(bh) * t_stat + t] = make_float2(INFINITY, 0.f);
+  }
+}
+
 }  // namespace attn_bwd_t
 }  // namespace b200

@@ -78,6 +78,8 @@ enum Epi : int {
   kDGelu = 3,     // C = acc * R                 (R holds gelu'(pre-activation) saved by forward)
   kAccumF32 = 4,  // C(fp32) += acc              (TMA reduce-add)
   kBiasDropResid = 5,  // C = dropout(acc + bias) + R   (mask regenerated in backward, philox.cuh)
+  kRowDot = 6,    // C = acc; stats[b, h, t] = (lse * log2 e, sum over head h's 64 columns of C o R):
+                  // the attention backward's per-row statistics out of out_proj's dgrad
 };
 
 struct Params {
@@ -94,6 +96,12 @@ struct Params {
                            // of the layer that produced this GEMM's output gradient)
   const uint8_t* row_keep; // optional, kBiasResid / kBiasDropResid: rows with row_keep[m] == 0 get
                            // C = R (the branch is dropped, `gpt.py:73-74`: padded query rows)
+  // kRowDot: rows are (b, t) with t < rd_T, columns are (head, 64); R is the attention output O,
+  // C the gradient dO.  stats[(b * rd_H + h) * rd_tstat + t] = (lse2, D) with
+  // D = sum_c bf16(dO)[b,t,h,c] * O[b,t,h,c] and lse2 = lse[b,h,t] * log2(e) (+inf for an empty row).
+  const float* lse;
+  float2* stats;
+  int rd_T, rd_H, rd_tstat;
 };
 
 // Tile order.  Consecutive tiles walk `group_m` row-tiles for one column-tile, then the next
@@ -325,7 +333,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       // Residual / saved gelu' for this thread's row (64 bf16): issued BEFORE waiting for the
       // accumulator so the HBM latency hides behind this tile's mainloop.
       uint4 rv[8];
-      if (EPI == kBiasResid || EPI == kDGelu || EPI == kBiasDropResid) {
+      if (EPI == kBiasResid || EPI == kDGelu || EPI == kBiasDropResid || EPI == kRowDot) {
 #pragma unroll
         for (int q = 0; q < 8; ++q) rv[q] = make_uint4(0u, 0u, 0u, 0u);
         if (row_ok && n0 < p.N) {
@@ -390,6 +398,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       } else {
         // 2 pieces of 32 bf16 columns (64 B rows).
         const uint32_t* rw = reinterpret_cast<const uint32_t*>(rv);
+        float row_dot = 0.f;  // kRowDot
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
           const int col0 = n0 + h * 32;
@@ -435,6 +444,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               unpack2(y2, x0, x1);
             }
             out[j / 2] = pack_bf16x2(x0, x1);
+            if (EPI == kRowDot) {  // on the ROUNDED gradient: the same values the attention reads
+              const float2 c = unpack_bf16x2(out[j / 2]);
+              const float2 f = unpack_bf16x2(rw[h * 16 + (j >> 1)]);
+              row_dot = fmaf(c.x, f.x, fmaf(c.y, f.y, row_dot));
+            }
           }
 
           tma_store_wait_read<0>();  // previous piece's TMA stores have finished reading the buffers
@@ -488,6 +502,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               if (cc + 1 < p.N) atomicAdd(p.colsum + cc + 1, s1);
             }
           }
+        }
+        if (EPI == kRowDot && row_ok && n0 < p.N) {
+          // this warp's 64 columns are exactly one head: the thread owns D of (row, head)
+          const int b = row / p.rd_T, t = row - b * p.rd_T, head = n0 >> 6;
+          const size_t bh = size_t(b) * p.rd_H + head;
+          const float l = __ldg(p.lse + bh * p.rd_T + t);
+          p.stats[bh * p.rd_tstat + t] =
+              make_float2(l == -INFINITY ? INFINITY : l * 1.4426950408889634f, row_dot);
         }
       }
       // TMEM reads for this accumulator are complete (wait::ld above): hand it back.
@@ -569,9 +591,18 @@ using namespace b200::gemm;
 static int gemm_dispatch(int layout, int epilogue, int M, int N, int K, const void* A, int lda,
                          const void* B, int ldb, void* C, int ldc, void* C2, int ldc2,
                          const float* bias, const void* R, int ldr, const DropoutParams& drop,
-                         float* colsum, cudaStream_t stream, const uint8_t* row_keep = nullptr) {
+                         float* colsum, cudaStream_t stream, const uint8_t* row_keep = nullptr,
+                         const Params* row_dot = nullptr) {
   B200_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem");
   Params p{};
+  if (row_dot != nullptr) {
+    p.lse = row_dot->lse;
+    p.stats = row_dot->stats;
+    p.rd_T = row_dot->rd_T;
+    p.rd_H = row_dot->rd_H;
+    p.rd_tstat = row_dot->rd_tstat;
+  }
+  B200_REQUIRE((epilogue == kRowDot) == (row_dot != nullptr), "gemm: row statistics go with kRowDot");
   p.drop = drop;
   p.colsum = colsum;
   p.row_keep = row_keep;
@@ -630,7 +661,8 @@ static int gemm_dispatch(int layout, int epilogue, int M, int N, int K, const vo
       if (make_tmap_2d(&tC2, static_cast<__nv_bfloat16*>(C2), M, N, ldc2, 32, 32, Swz::B64))
         return 1;
     }
-    if (epilogue == kBiasResid || epilogue == kDGelu || epilogue == kBiasDropResid)
+    if (epilogue == kBiasResid || epilogue == kDGelu || epilogue == kBiasDropResid ||
+        epilogue == kRowDot)
       B200_REQUIRE(R != nullptr, "gemm: this epilogue needs R");
     if (epilogue == kBiasDropResid)
       B200_REQUIRE(N % 8 == 0, "gemm: the dropout epilogue needs N to be a multiple of 8");
@@ -646,6 +678,7 @@ static int gemm_dispatch(int layout, int epilogue, int M, int N, int K, const vo
   B200_GEMM_CASE(0, false, false, kBiasDropResid)
   B200_GEMM_CASE(1, false, true, kBias)
   B200_GEMM_CASE(1, false, true, kDGelu)
+  B200_GEMM_CASE(1, false, true, kRowDot)
   B200_GEMM_CASE(2, true, true, kAccumF32)
 #undef B200_GEMM_CASE
   return fail("gemm: unsupported layout/epilogue combination");
@@ -670,6 +703,27 @@ extern "C" int llmtrain_b200_gemm_colsum(int layout, int epilogue, int M, int N,
   B200_REQUIRE(colsum != nullptr, "gemm_colsum: colsum must not be null");
   return gemm_dispatch(layout, epilogue, M, N, K, A, lda, B, ldb, C, ldc, nullptr, 0, bias, R, ldr,
                        make_dropout(0.f, 0, 0, 0), colsum, stream);
+}
+
+// dO[M, H*64] = A[M,K] * B[K, H*64]  (NN layout: out_proj's dgrad) and, from the same epilogue, the
+// attention backward's per-row statistics: stats[(b*H + h) * t_stat + t] = (lse[b,h,t] * log2 e,
+// sum_c bf16(dO)[b,t,h,c] * O[b,t,h,c]) — rows are (b, t), M = B*T.  Replaces the statistics
+// pre-pass of llmtrain_b200_attention_bwd (which re-read dO and O): call
+// llmtrain_b200_attention_bwd_prestats afterwards with the same scratch.
+extern "C" int llmtrain_b200_gemm_rowdot(int M, int N, int K, const void* A, int lda, const void* B,
+                                         int ldb, void* dO, int ldc, const void* O, int ldo,
+                                         const float* lse, void* stats, int T, int H, int t_stat,
+                                         cudaStream_t stream) {
+  B200_REQUIRE(T > 0 && H > 0 && N == H * 64 && M % T == 0, "gemm_rowdot: rows are (b, t), columns (head, 64)");
+  B200_REQUIRE(lse != nullptr && stats != nullptr && t_stat >= T, "gemm_rowdot: statistics buffers");
+  Params rd{};
+  rd.lse = lse;
+  rd.stats = static_cast<float2*>(stats);
+  rd.rd_T = T;
+  rd.rd_H = H;
+  rd.rd_tstat = t_stat;
+  return gemm_dispatch(1, kRowDot, M, N, K, A, lda, B, ldb, dO, ldc, nullptr, 0, nullptr, O, ldo,
+                       make_dropout(0.f, 0, 0, 0), nullptr, stream, nullptr, &rd);
 }
 
 // C[M,N] = dropout(A[M,K] * B[N,K]^T + bias) + R   (NT layout; mask element index row * N + col,

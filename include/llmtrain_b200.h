@@ -174,6 +174,22 @@ int llmtrain_b200_gemm_colsum(int layout, int epilogue, int M, int N, int K, con
                               const void* B, int ldb, void* C, int ldc, const float* bias,
                               const void* R, int ldr, float* colsum, llm_stream_t stream);
 
+/* dO[M, H*64] = A[M,K] * B[K, H*64] (NN: out_proj's dgrad, src/llmtrain/models/gpt.py:29) and, from
+ * the same epilogue, the attention backward's per-row statistics (rows are (b, t), M = B*T):
+ * stats[(b*H + h) * t_stat + t] = (lse[b,h,t] * log2 e, sum_c bf16(dO)[b,t,h,c] * O[b,t,h,c]) as
+ * float pairs.  `stats` / `t_stat` come from llmtrain_b200_attention_bwd_stats_buffer; follow with
+ * llmtrain_b200_attention_bwd_prestats (same scratch), which then skips its pass over dO and O. */
+int llmtrain_b200_gemm_rowdot(int M, int N, int K, const void* A, int lda, const void* B, int ldb,
+                              void* dO, int ldc, const void* O, int ldo, const float* lse,
+                              void* stats, int T, int H, int t_stat, llm_stream_t stream);
+int llmtrain_b200_attention_bwd_stats_buffer(void* scratch, size_t scratch_bytes, int B, int T,
+                                             int H, int head_dim, void** stats, int* t_stat);
+int llmtrain_b200_attention_bwd_prestats(const void* qkv, const void* out, const void* dout,
+                                         const float* lse, const uint8_t* key_mask, void* dqkv,
+                                         float* dbias_qkv, void* scratch, size_t scratch_bytes,
+                                         int B, int T, int H, int head_dim, float softmax_scale,
+                                         llm_stream_t stream);
+
 /* ---------------------------------------------------------------------------------------------
  * Dropout (csrc/common/philox.cuh, csrc/kernels/dropout.cu).  Replaces the four nn.Dropout modules
  * of src/llmtrain/models/gpt.py:28,30,97,129.  A mask is a pure function of (seed, offset, site,

@@ -67,6 +67,28 @@ def gemm_colsum(
     return c
 
 
+def gemm_rowdot(dy: torch.Tensor, w: torch.Tensor, d_out: torch.Tensor, o: torch.Tensor,
+                lse: torch.Tensor, stats: torch.Tensor, seq_len: int, n_heads: int) -> torch.Tensor:
+    """``d_out[M, H*64] = dy[M, K] @ w[K, H*64]`` (out_proj's dgrad) and, from the same epilogue,
+    ``stats[b, h, t] = (lse[b, h, t] * log2 e, sum_c d_out[b, t, h, c] * o[b, t, h, c])``.
+
+    ``stats``: fp32 ``[B, H, t_stat, 2]`` with ``t_stat >= seq_len`` (entries ``t >= seq_len`` are
+    left alone); rows of ``dy`` / ``o`` are ``(b, t)``.
+    """
+    m, n = d_out.shape
+    k = dy.shape[1]
+    assert stats.dtype == torch.float32 and stats.shape[-1] == 2 and stats.is_contiguous()
+    status = native.lib().llmtrain_b200_gemm_rowdot(
+        ctypes.c_int(m), ctypes.c_int(n), ctypes.c_int(k), native.ptr(dy), ctypes.c_int(_ld(dy)),
+        native.ptr(w), ctypes.c_int(_ld(w)), native.ptr(d_out), ctypes.c_int(_ld(d_out)),
+        native.ptr(o), ctypes.c_int(_ld(o)), native.ptr(lse), native.ptr(stats),
+        ctypes.c_int(seq_len), ctypes.c_int(n_heads), ctypes.c_int(int(stats.shape[-2])),
+        native.stream_handle(),
+    )
+    native.check(status, "gemm_rowdot")
+    return d_out
+
+
 def linear_forward(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None = None) -> torch.Tensor:
     """``x @ w.T + bias`` with bf16 operands, fp32 accumulate, bf16 result."""
     out = torch.empty(x.shape[0], w.shape[0], dtype=torch.bfloat16, device=x.device)

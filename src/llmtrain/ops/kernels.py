@@ -301,6 +301,42 @@ def attention_bwd(qkv, out, dout, lse, n_heads, *, key_mask=None, dqkv=None, dro
     return dqkv
 
 
+def attention_bwd_out_proj(dy, w_out, qkv, out, lse, n_heads, *, key_mask=None, dbias=None):
+    """out_proj's dgrad fused with the attention backward's statistics pre-pass, then the attention
+    backward itself (what the training engine runs without probability dropout).
+
+    ``dy`` ``[B*T, d_model]`` is the gradient w.r.t. out_proj's output, ``w_out`` ``[d_model, H*64]``
+    its weight.  Returns ``(d_out [B, T, H*64], dqkv, stats [B, H, t_stat, 2])``.
+    """
+    from llmtrain.ops import gemm as G
+
+    b, t, three_d = qkv.shape
+    hd = three_d // 3 // n_heads
+    lib = _lib()
+    need = lib.llmtrain_b200_attention_bwd_scratch_bytes(_c_int(b), _c_int(t), _c_int(n_heads),
+                                                         _c_int(hd))
+    buf = scratch(need, qkv.device)
+    stats_ptr, t_stat = ctypes.c_void_p(), ctypes.c_int()
+    check(lib.llmtrain_b200_attention_bwd_stats_buffer(
+        ptr(buf), _c_size(buf.numel()), _c_int(b), _c_int(t), _c_int(n_heads), _c_int(hd),
+        ctypes.byref(stats_ptr), ctypes.byref(t_stat)), "attention_bwd_stats_buffer")
+    offset = stats_ptr.value - buf.data_ptr()
+    stats = buf[offset:offset + b * n_heads * t_stat.value * 8].view(torch.float32).view(
+        b, n_heads, t_stat.value, 2)
+    d_out = torch.empty(b * t, n_heads * hd, dtype=torch.bfloat16, device=qkv.device)
+    G.gemm_rowdot(dy, w_out, d_out, out.view(b * t, -1), lse, stats, t, n_heads)
+    dqkv = torch.empty_like(qkv)
+    check(
+        lib.llmtrain_b200_attention_bwd_prestats(
+            ptr(qkv), ptr(out), ptr(d_out), ptr(lse), ptr(key_mask), ptr(dqkv), ptr(dbias),
+            ptr(buf), _c_size(buf.numel()), _c_int(b), _c_int(t), _c_int(n_heads), _c_int(hd),
+            _c_float(0.0), stream_handle(),
+        ),
+        "attention_bwd_prestats",
+    )
+    return d_out.view(b, t, -1), dqkv, stats
+
+
 def synthetic_tokens(batch: int, seq: int, vocab: int, *, seed: int, first_row: int = 0,
                      device: torch.device | str = "cuda", with_labels: bool = True):
     """Device-resident ``(input_ids, labels)`` (next-token targets) from a counter-based hash."""

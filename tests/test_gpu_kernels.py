@@ -271,6 +271,32 @@ def test_attention_bwd_accumulates_the_qkv_bias_gradient(b: int, t: int, h: int)
     assert torch.allclose(dbias, want, rtol=1e-4, atol=1e-3), (dbias - want).abs().max()
 
 
+@pytest.mark.parametrize("b,t,h", [(2, 384, 3), (2, 200, 2)])
+def test_out_proj_dgrad_hands_the_row_statistics_to_attention_backward(b: int, t: int, h: int) -> None:
+    """The engine's default path: out_proj's dgrad epilogue writes (LSE * log2 e, rowsum(dO o O));
+    the attention backward then skips its own pass over dO and O and must give the same dqkv."""
+    from llmtrain.ops import gemm as G
+    from llmtrain.ops import kernels as K
+
+    d = h * 64
+    qkv = _bf((b, t, 3 * d))
+    out, lse = K.attention_fwd(qkv, h)
+    dy = _bf((b * t, d))
+    w_out = (_bf((d, d)).float() / d ** 0.5).to(torch.bfloat16)
+    d_out, dqkv, stats = K.attention_bwd_out_proj(dy, w_out, qkv, out, lse, h)
+
+    want_dout = torch.empty(b * t, d, dtype=torch.bfloat16, device="cuda")
+    G.gemm(G.NN, G.EPI_BIAS, dy, w_out, want_dout)
+    assert torch.equal(d_out.view(b * t, d), want_dout)
+    want_d = (d_out.float() * out.float()).view(b, t, h, 64).sum(-1).permute(0, 2, 1)  # [b, h, t]
+    assert torch.allclose(stats[:, :, :t, 1], want_d, rtol=1e-4, atol=1e-3)
+    assert torch.allclose(stats[:, :, :t, 0], lse * 1.4426950408889634, rtol=1e-6, atol=1e-6)
+    if stats.shape[2] > t:  # padding rows: exact zeros for the probabilities
+        assert torch.isinf(stats[:, :, t:, 0]).all() and (stats[:, :, t:, 1] == 0).all()
+    want = K.attention_bwd(qkv, out, d_out, lse, h)
+    assert _rel(dqkv, want) < 2e-3
+
+
 def test_synthetic_tokens_are_shifted_in_range_and_reproducible() -> None:
     from llmtrain.ops import kernels as K
 
