@@ -40,11 +40,16 @@ def main() -> int:
         agg[name][1] += ms
     g = lambda m, n, k: 2.0 * m * n * k  # noqa: E731
     attn = 4.0 * mb * H * T * T * 64 / 2
+    # out_proj's dgrad runs with the row-statistics epilogue (<0, 1, 6>) in launch lists taken after
+    # that fusion; older lists have it in the plain dgrad class
+    rowdot = any(k.replace("true", "1").replace("false", "0").startswith("gemm::gemm_kernel<0, 1, 6")
+                 for k in agg)
     work = {  # class -> ("flop" | "byte", amount per step)
         "gemm::gemm_kernel<0, 0, 0>": ("flop", L * g(M, 3 * d, d) + g(M, Vp, d)),
         "gemm::gemm_kernel<0, 0, 1>": ("flop", L * g(M, F, d)),
         "gemm::gemm_kernel<0, 0, 2>": ("flop", L * (g(M, d, d) + g(M, d, F))),
-        "gemm::gemm_kernel<0, 1, 0>": ("flop", L * (g(M, d, 3 * d) + g(M, d, d) + g(M, d, F)) + g(M, d, Vp)),
+        "gemm::gemm_kernel<0, 1, 0>": ("flop", L * (g(M, d, 3 * d) + (0 if rowdot else g(M, d, d)) + g(M, d, F)) + g(M, d, Vp)),
+        "gemm::gemm_kernel<0, 1, 6>": ("flop", L * g(M, d, d)),
         "gemm::gemm_kernel<0, 1, 3>": ("flop", L * g(M, F, d)),
         "gemm::gemm_kernel<1, 1, 4>": ("flop", L * (g(3 * d, d, M) + g(d, d, M) + 2 * g(F, d, M)) + g(V, d, M)),
         "attn::fwd_kernel": ("flop", L * attn),
