@@ -21,6 +21,7 @@ from __future__ import annotations
 
 import ctypes
 import logging
+import os
 from collections.abc import Callable
 from typing import Any
 
@@ -95,6 +96,9 @@ def _sub(module: nn.Module, dotted: str) -> nn.Module:
 
 
 
+_TRACE_FIT = os.environ.get("LLMTRAIN_FIT_TRACE") is not None  # Trainer.fit host/device timeline
+
+
 class StepScalars:
     """Loss and gradient norm of one optimiser step on their way to the host.
 
@@ -103,7 +107,7 @@ class StepScalars:
     step first and read this one while the GPU is busy (``Trainer.fit`` does).
     """
 
-    __slots__ = ("_row", "_event", "_value")
+    __slots__ = ("_row", "_event", "_value", "timing_event")
 
     def __init__(self, row: torch.Tensor, event: torch.cuda.Event) -> None:
         self._row = row
@@ -603,9 +607,11 @@ class B200TrainEngine(TrainEngine):
         row = ring[slot]
         row[0:1].copy_(self._loss_acc.reshape(1), non_blocking=True)
         row[1:2].copy_(self._norm.reshape(1), non_blocking=True)
-        event = torch.cuda.Event()
+        event = torch.cuda.Event(enable_timing=_TRACE_FIT)
         event.record()
         out = StepScalars(row, event)
+        if _TRACE_FIT:
+            out.timing_event = event  # type: ignore[attr-defined]
         self._scalar_pending[slot] = out
         self._last_scalars = out
         return out

@@ -16,6 +16,8 @@ the real high-water mark instead of the reference's hard-coded ``0.0``.
 from __future__ import annotations
 
 import logging
+import os
+import sys
 import time
 from pathlib import Path
 from typing import Any
@@ -360,6 +362,8 @@ class Trainer:
     ) -> TrainResult:
         """Train until ``max_steps`` optimiser updates have been applied."""
         cfg = self._cfg.trainer
+        t_fit = time.perf_counter()
+        trace_fit = os.environ.get("LLMTRAIN_FIT_TRACE") is not None  # host-side phase times
         self._model.train()
         max_steps = cfg.max_steps if max_steps_override is None else max_steps_override
         accum = cfg.grad_accum_steps
@@ -430,9 +434,19 @@ class Trainer:
             )
             window.started = time.perf_counter()  # the next interval starts where this one ended
 
+        t_loop = time.perf_counter()
+        t_first = t_loop
+        trace_rows: list[tuple[float, float, float, Any]] = []
         for step in range(first_step, max_steps + 1):
+            t_call = time.perf_counter()
             last_loss, step_tokens = self._engine.train_step(next_batch, accum)
+            t_enq = time.perf_counter()
+            if step == first_step:
+                t_first = t_enq
             flush_log()  # the previous interval: the device is busy with this step meanwhile
+            if trace_fit:
+                trace_rows.append((t_call - t_loop, t_enq - t_loop, time.perf_counter() - t_loop,
+                                   getattr(last_loss, "timing_event", None)))
             self._scheduler.step()
             tokens_local_total += step_tokens
             if step == 1:
@@ -477,6 +491,17 @@ class Trainer:
                     rendered = "  ".join(f"{k}={v:.4f}" for k, v in sorted(seen.items()))
                     logger.info("val_step=%d/%d  %s", step, max_steps, rendered)
 
+        if trace_fit:
+            now = time.perf_counter()
+            print(f"fit trace: prologue {1e3 * (t_loop - t_fit):.2f} ms, first train_step call "
+                  f"{1e3 * (t_first - t_loop):.2f} ms, loop {1e3 * (now - t_loop):.2f} ms",
+                  file=sys.stderr, flush=True)
+            prev = None
+            for i, (a, b, c, ev) in enumerate(trace_rows):
+                gap = "" if prev is None or ev is None else f"  device step {prev.elapsed_time(ev):.2f} ms"
+                print(f"fit trace: step {i + 1}: train_step called at {1e3 * a:.2f} ms, enqueued by "
+                      f"{1e3 * b:.2f}, previous log flushed by {1e3 * c:.2f}{gap}", file=sys.stderr)
+                prev = ev if ev is not None else prev
         return TrainResult(
             final_step=max_steps,
             final_loss=float(last_loss),
