@@ -127,32 +127,6 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   }
 }
 
-// Polling wait for the one or two hand-overs per iteration that set a kernel's pace: no hardware
-// suspend (waking a suspended warp costs ~100 cycles more than noticing the flip in a poll), the
-// wall-clock bound is checked every 4096 polls.  The waiting warp burns issue slots; use it only
-// where its SM sub-partition has nothing better to run.
-__device__ __forceinline__ void mbar_wait_spin(uint64_t* bar, uint32_t parity) {
-  const uint32_t addr = smem_u32(bar);
-  unsigned long long t0 = 0;
-  for (uint32_t n = 1;; ++n) {
-    uint32_t done;
-    asm volatile(
-        "{\n\t"
-        ".reg .pred P;\n\t"
-        "mbarrier.test_wait.parity.shared::cta.b64 P, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, P;\n\t"
-        "}\n"
-        : "=r"(done)
-        : "r"(addr), "r"(parity)
-        : "memory");
-    if (done) return;
-    if ((n & 4095u) == 0) {
-      if (t0 == 0) t0 = global_timer_ns();
-      if (global_timer_ns() - t0 > B200_MBAR_TIMEOUT_NS) mbar_timeout_trap();
-    }
-  }
-}
-
 // ----------------------------------------------------------------------------------------------
 // TMA
 // ----------------------------------------------------------------------------------------------
@@ -305,6 +279,12 @@ __host__ __device__ constexpr uint32_t umma_idesc_bf16(uint32_t m, uint32_t n, b
 // tcgen05: MMA issue / commit
 // ----------------------------------------------------------------------------------------------
 // D[tmem] (+)= A[smem] * B[smem]; issued by ONE thread for the whole CTA.
+// How to call it: let the WHOLE issuing warp walk the loop and wait on the barriers, build the
+// descriptors outside the elected region (`if (elect_one()) { ... }`) and advance them by one
+// 64-bit add per instruction.  With the loop inside `if (lane == 0)` the region is divergent, the
+// descriptors cannot live in uniform registers and every UTCHMMA is fed through an
+// ELECT / R2UR.BROADCAST sequence: 85 - 170 cycles of issue per instruction measured
+// (bench/mma_probe.cu) against a tensor-core floor of 32 cycles for a 128x64x16 product.
 __device__ __forceinline__ void umma_ss(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b,
                                         uint32_t idesc, bool accumulate) {
   asm volatile(
@@ -336,45 +316,6 @@ __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
                    smem_u32(bar))
                : "memory");
-}
-
-// Warp-collective forms: EVERY lane of a converged warp executes the call and one elected lane
-// issues the instruction.  Use these in loops that run warp-uniformly.  Under `if (lane == 0)` the
-// compiler cannot keep descriptors in uniform registers (the region is divergent), so each
-// UTCHMMA is fed through an ELECT / R2UR.BROADCAST loop: 85-170 cycles per instruction measured
-// (bench/mma_probe.cu), against a tensor-core floor of 32 cycles for a 128x64x16 product.
-__device__ __forceinline__ void umma_ss_w(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b,
-                                          uint32_t idesc, bool accumulate) {
-  asm volatile(
-      "{\n\t"
-      ".reg .pred p, e;\n\t"
-      "elect.sync _|e, 0xffffffff;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "@e tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
-      "}\n" ::"r"(tmem_d),
-      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(static_cast<uint32_t>(accumulate))
-      : "memory");
-}
-__device__ __forceinline__ void umma_ts_w(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b,
-                                          uint32_t idesc, bool accumulate) {
-  asm volatile(
-      "{\n\t"
-      ".reg .pred p, e;\n\t"
-      "elect.sync _|e, 0xffffffff;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "@e tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t"
-      "}\n" ::"r"(tmem_d),
-      "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(static_cast<uint32_t>(accumulate))
-      : "memory");
-}
-__device__ __forceinline__ void umma_commit_w(uint64_t* bar) {
-  asm volatile(
-      "{\n\t"
-      ".reg .pred e;\n\t"
-      "elect.sync _|e, 0xffffffff;\n\t"
-      "@e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t"
-      "}\n" ::"r"(smem_u32(bar))
-      : "memory");
 }
 
 // ----------------------------------------------------------------------------------------------
