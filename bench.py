@@ -484,6 +484,10 @@ def run_reference(args: argparse.Namespace) -> dict[str, Any]:
     rank, local_rank, world = _dist_env()
     if world != args.gpus:
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torchrun for N>1")
+    import torch
+
+    if not torch.cuda.is_available():
+        return {"impl": "reference", "unavailable": "no CUDA device visible to this process"}
     try:
         return ref_harness.run(args, rank=rank, local_rank=local_rank, world=world,
                                model=MODELS[args.model], metric=metric_name(args.model),
