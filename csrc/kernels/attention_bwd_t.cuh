@@ -9,22 +9,28 @@
 //   dQ_i = dS   K_j    (A = dS^T tile in shared memory read MN-major, B = K_j)
 //
 // TMEM lane == key row, so the softmax-grad warps hold one key row each and walk the query
-// columns; the per-query statistics (LSE, D) are staged in shared memory next to Q_i / dO_i and
-// read as broadcasts.  P^T and dS^T are written back as bf16 over the fp32 S^T / dP^T columns they
-// came from; only dS^T also goes to shared memory.  Why: the row-oriented kernel reads 224 KB of
-// MMA operands from shared memory per (i, j) pair (P and dS twice each as 128-row left operands of
-// N = 64 products) and writes 64 KB of P / dS, against a shared-memory port of 128 B/clk: ~3 300
-// cycles of operand traffic per pair, which is the whole iteration.  Here a pair reads 144 KB and
-// writes 32 KB, and the 32 KB that held P hold a second K / V stage instead: the next item's
-// K / V arrive while the current item still runs, and its first score tile is issued in the slot
-// where the next query tile's would be, so an item boundary costs the epilogue only.
+// columns; the per-query statistics (LSE, D) are staged in shared memory by their own small ring
+// and read as broadcasts.  P^T is written back as bf16 into its own 64 TMEM columns, dS^T over the
+// fp32 dP^T columns it came from; only dS^T also goes to shared memory (single buffer).
+//
+// Why.  (1) Operand traffic: the row-oriented kernel reads 224 KB of MMA operands from shared
+// memory per (i, j) pair (P and dS twice each as 128-row left operands of N = 64 products) and
+// writes 64 KB of P / dS; here a pair reads 144 KB and writes 32 KB, and a TS product of N = 64
+// runs at the tensor-core floor (32 cycles) where the SS form is shared-memory bound (48;
+// bench/mma_probe.cu).  (2) The shared memory that held P and the second dS buffer holds a second
+// K / V stage and a third Q / dO stage: the next item's K / V arrive while the current item still
+// runs and its first score tile is issued in the slot where the next query tile's would be, so an
+// item boundary costs the epilogue only (it was 6 000 - 8 000 cycles of a 33 000-cycle item).
 //
 // Tensor-core queue per pair (issue order == execution order):
-//     [P^T_g, dS^T_g handed over]  S^T_{g+1}, dK += dS^T_g Q_g, dP^T_{g+1}  -> the warps wait on these
-//                                  dV += P^T_g dO_g                         -> releases P^T and Q/dO
-//                                  dQ_g = dS_g K    (after dQ_{g-1} has been read out of TMEM)
+//     [P^T_g, dS^T_g handed over]  S^T_{g+1}                    -> s_full: the exponentials start
+//                                  dK += dS^T_g Q_g, dP^T_{g+1} -> dp_full
+//                                  dQ_g = dS_g K    (after dQ_{g-1} has been read out of TMEM;
+//                                                    first in the queue for an item's last pair)
+//                                  dV += P^T_g dO_g             -> releases P^T and the Q / dO stage
 // dP^T_{g+1} overwrites the columns dS^T_g lives in; it is queued behind the product that reads
-// them.  The chain that sets the pace is  hand-over -> S^T, dK, dP^T (3 x 256 cycles) -> softmax-grad.
+// them.  What sets the pace is the softmax-grad warps (~2 400 of ~3 900 cycles per pair) plus the
+// hand-over -> S^T hop; the dQ drain of the previous pair runs underneath that hop.
 
 #pragma once
 
