@@ -1,4 +1,7 @@
-// Causal flash attention backward on tcgen05 (head_dim 64).
+// Causal flash attention backward on tcgen05 (head_dim 64): launcher, pre / post passes and the
+// ROW-ORIENTED main kernel, which serves probability dropout (its keep mask is regenerated along
+// key positions, the direction this orientation walks).  Everything else runs the key-row-oriented
+// kernel of attention_bwd_t.cuh, which is faster; both are persistent and share the launcher.
 //
 // Autograd of `src/llmtrain/models/gpt.py:56-70` without ever storing P (work
 // item W3).  One CTA owns a 128-row key/value tile j of one (batch, head) and walks the query
@@ -29,7 +32,8 @@
 // accumulators and is drained one iteration late.  The 32 KB saved on P hold the fp32 dQ tile on
 // its way out: each warp stages its 32x32 slice and hands it to the TMA unit as one reduce-add
 // into the fp32 dQ buffer (a post-kernel converts that buffer into the q third of dqkv).
-// What limits the kernel (B = 32, T = 1024, H = 12, 425 us per layer before this change; each
+// What limited this kernel when it had one CTA per item and issued from `if (lane == 0)`
+// (B = 32, T = 1024, H = 12, 425 us per layer before this change; each
 // variant measured with that work removed): per-thread dQ atomics 76 us, the softmax-grad math
 // 55 us, all five MMAs together ~45 us; the remaining skeleton (barrier hops MMA <-> warps, TMA
 // latency) is ~230 us, and the dsum / memset / convert passes around the kernel ~60 us.
