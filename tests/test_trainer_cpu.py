@@ -179,3 +179,25 @@ def test_engine_selection_rules() -> None:
     if not torch.cuda.is_available():
         with pytest.raises(RuntimeError, match="no CUDA device"):
             Trainer(config(run={"device": "cuda"}))
+
+
+def test_step_scalars_wait_once_for_their_event_and_keep_their_value() -> None:
+    """What the B200 engine's ``train_step`` returns: reading waits for the step's own event (not
+    for the stream), once, and the value survives the ring slot being rewritten."""
+    from llmtrain.engine.b200 import StepScalars
+
+    class Event:
+        waits = 0
+
+        def synchronize(self) -> None:
+            Event.waits += 1
+
+    row = torch.tensor([1.5, 2.5])
+    scalars = StepScalars(row, Event())  # type: ignore[arg-type]
+    assert Event.waits == 0  # nothing is read until somebody asks
+    assert float(scalars) == 1.5 and scalars.grad_norm == 2.5 and scalars.item() == 1.5
+    assert Event.waits == 1
+    row[0] = 9.0  # the slot is reused by a later step
+    assert float(scalars) == 1.5
+    assert not torch.is_tensor(scalars)  # the trainer's interval sums it as a host number
+
